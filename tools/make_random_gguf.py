@@ -1,0 +1,263 @@
+#!/usr/bin/env python3
+"""Random-init GGUF writer for the Qwen3-TTS-12Hz-0.6B architecture in the reference's
+on-disk layout (reference converters
+scripts/convert_tts_to_gguf.py:244-319,440-471 and scripts/convert_tokenizer_to_gguf.py:45-166,270-300).
+
+The real checkpoint is not available offline, so parity and benchmarks run on seeded random
+weights of the real shapes.  numpy's PCG64 stream is platform independent, so the same seed
+gives byte-identical files in the build container and on the GPU box.
+
+Presets
+  full : the real 0.6B shapes (28 talker layers, 5 code-predictor layers, text vocab 151936)
+  tiny : same per-layer shapes (the kernels are specialised on them) but 2 talker layers,
+         2 code-predictor layers and a 512-entry text vocabulary -> ~0.2 GB, fast CPU tests.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+
+import numpy as np
+import gguf
+
+PRESETS = {
+    "full": dict(n_layers=28, cp_layers=5, text_vocab=151936,
+                 tts_bos=151672, tts_eos=151673, tts_pad=151671),
+    "tiny": dict(n_layers=2, cp_layers=2, text_vocab=512,
+                 tts_bos=510, tts_eos=511, tts_pad=509),
+}
+
+H, NH, NKV, HD, FFN = 1024, 16, 8, 128, 3072
+TEXT_DIM = 2048
+CODEC_VOCAB, CP_VOCAB, N_CB = 3072, 2048, 16
+
+
+class _Rng:
+    """float32 normal stream; one Generator so tensor order defines the values."""
+
+    def __init__(self, seed: int):
+        self.g = np.random.Generator(np.random.PCG64(seed))
+
+    def normal(self, shape, std):
+        a = self.g.standard_normal(size=shape, dtype=np.float32)
+        a *= np.float32(std)
+        return a
+
+
+def _add(writer, name, data, qtype):
+    """1-D -> F32; >=2-D -> F16 or Q8_0 (quantised along the last numpy axis = ggml ne[0])."""
+    if data.ndim <= 1:
+        writer.add_tensor(name, data.astype(np.float32), raw_dtype=gguf.GGMLQuantizationType.F32)
+    elif qtype == "q8_0":
+        q = gguf.quants.quantize(data.astype(np.float32), gguf.GGMLQuantizationType.Q8_0)
+        writer.add_tensor(name, q, raw_dtype=gguf.GGMLQuantizationType.Q8_0)
+    else:
+        writer.add_tensor(name, data.astype(np.float16), raw_dtype=gguf.GGMLQuantizationType.F16)
+
+
+def write_tts_gguf(path: str, preset: str = "full", seed: int = 1234, wtype: str = "f16",
+                   w_std: float = 0.02) -> dict:
+    """Talker + code predictor file (reference name: qwen3-tts-0.6b-f16.gguf).
+
+    wtype "q8_0" quantises exactly the tensors the reference converter quantises
+    (attn q/k/v/o, ffn gate/up/down, text_proj fc1/fc2); embeddings and heads stay F16
+    (scripts/convert_tts_to_gguf.py:244-270).
+    """
+    p = PRESETS[preset]
+    rng = _Rng(seed)
+    arch = "qwen3-tts"
+    w = gguf.GGUFWriter(path=None, arch=arch)
+    w.add_name(f"qwen3-tts-random-{preset}")
+    w.add_uint32(f"{arch}.block_count", p["n_layers"])
+    w.add_uint32(f"{arch}.embedding_length", H)
+    w.add_uint32(f"{arch}.feed_forward_length", FFN)
+    w.add_uint32(f"{arch}.attention.head_count", NH)
+    w.add_uint32(f"{arch}.attention.head_count_kv", NKV)
+    w.add_uint32(f"{arch}.attention.key_length", HD)
+    w.add_float32(f"{arch}.attention.layer_norm_rms_epsilon", 1e-6)
+    w.add_float32(f"{arch}.rope.freq_base", 1000000.0)
+    w.add_uint32(f"{arch}.vocab_size", CODEC_VOCAB)
+    w.add_uint32(f"{arch}.text_vocab_size", p["text_vocab"])
+    w.add_uint32(f"{arch}.text_hidden_size", TEXT_DIM)
+    w.add_uint32(f"{arch}.num_code_groups", N_CB)
+    w.add_uint32(f"{arch}.code_predictor.layer_count", p["cp_layers"])
+    w.add_uint32(f"{arch}.code_predictor.vocab_size", CP_VOCAB)
+    w.add_uint32(f"{arch}.codec.pad_id", 2148)
+    w.add_uint32(f"{arch}.codec.bos_id", 2149)
+    w.add_uint32(f"{arch}.codec.eos_id", 2150)
+    w.add_uint32(f"{arch}.tts_bos_token_id", p["tts_bos"])
+    w.add_uint32(f"{arch}.tts_eos_token_id", p["tts_eos"])
+    w.add_uint32(f"{arch}.tts_pad_token_id", p["tts_pad"])
+
+    q = wtype  # quantisable class
+    f = "f16"  # always-F16 class
+
+    _add(w, "talker.text_embd.weight", rng.normal((p["text_vocab"], TEXT_DIM), w_std), f)
+    _add(w, "talker.text_proj.fc1.weight", rng.normal((TEXT_DIM, TEXT_DIM), w_std), q)
+    _add(w, "talker.text_proj.fc1.bias", rng.normal((TEXT_DIM,), 0.01), f)
+    _add(w, "talker.text_proj.fc2.weight", rng.normal((H, TEXT_DIM), w_std), q)
+    _add(w, "talker.text_proj.fc2.bias", rng.normal((H,), 0.01), f)
+    _add(w, "talker.codec_embd.weight", rng.normal((CODEC_VOCAB, H), w_std), f)
+    _add(w, "talker.codec_head.weight", rng.normal((CODEC_VOCAB, H), w_std), f)
+    _add(w, "talker.output_norm.weight", 1.0 + rng.normal((H,), 0.02), f)
+
+    def layer(prefix):
+        _add(w, f"{prefix}.attn_norm.weight", 1.0 + rng.normal((H,), 0.02), f)
+        _add(w, f"{prefix}.attn_q.weight", rng.normal((NH * HD, H), w_std), q)
+        _add(w, f"{prefix}.attn_k.weight", rng.normal((NKV * HD, H), w_std), q)
+        _add(w, f"{prefix}.attn_v.weight", rng.normal((NKV * HD, H), w_std), q)
+        _add(w, f"{prefix}.attn_output.weight", rng.normal((H, NH * HD), w_std), q)
+        _add(w, f"{prefix}.attn_q_norm.weight", 1.0 + rng.normal((HD,), 0.02), f)
+        _add(w, f"{prefix}.attn_k_norm.weight", 1.0 + rng.normal((HD,), 0.02), f)
+        _add(w, f"{prefix}.ffn_norm.weight", 1.0 + rng.normal((H,), 0.02), f)
+        _add(w, f"{prefix}.ffn_gate.weight", rng.normal((FFN, H), w_std), q)
+        _add(w, f"{prefix}.ffn_up.weight", rng.normal((FFN, H), w_std), q)
+        _add(w, f"{prefix}.ffn_down.weight", rng.normal((H, FFN), w_std), q)
+
+    for il in range(p["n_layers"]):
+        layer(f"talker.blk.{il}")
+    for il in range(p["cp_layers"]):
+        layer(f"code_pred.blk.{il}")
+    for cb in range(N_CB - 1):
+        _add(w, f"code_pred.codec_embd.{cb}.weight", rng.normal((CP_VOCAB, H), w_std), f)
+    for cb in range(N_CB - 1):
+        _add(w, f"code_pred.lm_head.{cb}.weight", rng.normal((CP_VOCAB, H), w_std), f)
+    _add(w, "code_pred.output_norm.weight", 1.0 + rng.normal((H,), 0.02), f)
+
+    w.write_header_to_file(path=path)
+    w.write_kv_data_to_file()
+    w.write_tensors_to_file()
+    w.close()
+    return dict(preset=preset, seed=seed, wtype=wtype, **p)
+
+
+def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain: float = 0.06) -> dict:
+    """Vocoder file (reference name: qwen3-tts-tokenizer-f16.gguf), `tok_dec.*` tensors only.
+
+    Conv / linear weights ~ N(0, gain^2 / fan_in); snake alpha/beta ~ N(0, 0.1^2) (log-scale
+    parameters, reference src/audio_tokenizer_decoder.cpp:383-397); layer scales 0.01-ish;
+    codebooks N(0,1).  `out_gain` scales the final 96->1 conv so the pre-tanh RMS stays well
+    inside the linear range of tanh (otherwise an SNR test is meaningless).
+    """
+    rng = _Rng(seed)
+    arch = "qwen3-tts-tokenizer"
+    w = gguf.GGUFWriter(path=None, arch=arch)
+    w.add_name("qwen3-tts-tokenizer-random")
+    w.add_uint32(f"{arch}.num_codebooks", 16)
+    w.add_uint32(f"{arch}.codebook_size", 2048)
+    w.add_uint32(f"{arch}.sample_rate", 24000)
+    f = "f16"
+
+    def fan(shape, fan_in, g=gain):
+        return rng.normal(shape, g / np.sqrt(fan_in))
+
+    _add(w, "tok_dec.vq_first.input_proj.weight", fan((256, 512, 1), 512), f)
+    _add(w, "tok_dec.vq_first.output_proj.weight", fan((512, 256, 1), 256 * 16), f)
+    _add(w, "tok_dec.vq_first.0.codebook", rng.normal((2048, 256), 1.0), f)
+    _add(w, "tok_dec.vq_rest.input_proj.weight", fan((256, 512, 1), 512), f)
+    _add(w, "tok_dec.vq_rest.output_proj.weight", fan((512, 256, 1), 256 * 16), f)
+    for i in range(15):
+        _add(w, f"tok_dec.vq_rest.{i}.codebook", rng.normal((2048, 256), 1.0), f)
+    _add(w, "tok_dec.pre_conv.weight", fan((1024, 512, 3), 512 * 3), f)
+    _add(w, "tok_dec.pre_conv.bias", rng.normal((1024,), 0.01), f)
+    _add(w, "tok_dec.pre_tfm.input_proj.weight", fan((512, 1024), 1024), f)
+    _add(w, "tok_dec.pre_tfm.input_proj.bias", rng.normal((512,), 0.01), f)
+    for i in range(8):
+        b = f"tok_dec.pre_tfm.blk.{i}"
+        _add(w, f"{b}.attn_norm.weight", 1.0 + rng.normal((512,), 0.02), f)
+        _add(w, f"{b}.attn_q.weight", fan((1024, 512), 512), f)
+        _add(w, f"{b}.attn_k.weight", fan((1024, 512), 512), f)
+        _add(w, f"{b}.attn_v.weight", fan((1024, 512), 512), f)
+        _add(w, f"{b}.attn_output.weight", fan((512, 1024), 1024), f)
+        _add(w, f"{b}.attn_scale", 0.01 + rng.normal((512,), 0.002), f)
+        _add(w, f"{b}.ffn_norm.weight", 1.0 + rng.normal((512,), 0.02), f)
+        _add(w, f"{b}.ffn_gate.weight", fan((1024, 512), 512), f)
+        _add(w, f"{b}.ffn_up.weight", fan((1024, 512), 512), f)
+        _add(w, f"{b}.ffn_down.weight", fan((512, 1024), 1024), f)
+        _add(w, f"{b}.ffn_scale", 0.01 + rng.normal((512,), 0.002), f)
+    _add(w, "tok_dec.pre_tfm.norm.weight", 1.0 + rng.normal((512,), 0.02), f)
+    _add(w, "tok_dec.pre_tfm.output_proj.weight", fan((1024, 512), 512), f)
+    _add(w, "tok_dec.pre_tfm.output_proj.bias", rng.normal((1024,), 0.01), f)
+    for i in range(2):
+        b = f"tok_dec.upsample.{i}"
+        _add(w, f"{b}.conv.weight", fan((1024, 1024, 2), 1024), f)      # ConvT [Cin,Cout,K]
+        _add(w, f"{b}.conv.bias", rng.normal((1024,), 0.01), f)
+        _add(w, f"{b}.dwconv.weight", fan((1024, 1, 7), 7), f)
+        _add(w, f"{b}.dwconv.bias", rng.normal((1024,), 0.01), f)
+        _add(w, f"{b}.norm.weight", 1.0 + rng.normal((1024,), 0.02), f)
+        _add(w, f"{b}.norm.bias", rng.normal((1024,), 0.01), f)
+        _add(w, f"{b}.pwconv1.weight", fan((4096, 1024), 1024), f)
+        _add(w, f"{b}.pwconv1.bias", rng.normal((4096,), 0.01), f)
+        _add(w, f"{b}.pwconv2.weight", fan((1024, 4096), 4096), f)
+        _add(w, f"{b}.pwconv2.bias", rng.normal((1024,), 0.01), f)
+        _add(w, f"{b}.gamma", 0.1 + rng.normal((1024,), 0.01), f)
+    _add(w, "tok_dec.dec.0.conv.weight", fan((1536, 1024, 7), 1024 * 7), f)
+    _add(w, "tok_dec.dec.0.conv.bias", rng.normal((1536,), 0.01), f)
+    cin = 1536
+    for bi, s in enumerate((8, 5, 4, 3), start=1):
+        cout = cin // 2
+        b = f"tok_dec.dec.{bi}"
+        _add(w, f"{b}.snake.alpha", rng.normal((cin,), 0.1), f)
+        _add(w, f"{b}.snake.beta", rng.normal((cin,), 0.1), f)
+        # each output sample sees K/s = 2 taps x Cin inputs
+        _add(w, f"{b}.conv_t.weight", fan((cin, cout, 2 * s), cin * 2), f)
+        _add(w, f"{b}.conv_t.bias", rng.normal((cout,), 0.01), f)
+        for r in (2, 3, 4):
+            rb = f"{b}.res.{r}"
+            _add(w, f"{rb}.act1.alpha", rng.normal((cout,), 0.1), f)
+            _add(w, f"{rb}.act1.beta", rng.normal((cout,), 0.1), f)
+            _add(w, f"{rb}.conv1.weight", fan((cout, cout, 7), cout * 7), f)
+            _add(w, f"{rb}.conv1.bias", rng.normal((cout,), 0.01), f)
+            _add(w, f"{rb}.act2.alpha", rng.normal((cout,), 0.1), f)
+            _add(w, f"{rb}.act2.beta", rng.normal((cout,), 0.1), f)
+            _add(w, f"{rb}.conv2.weight", fan((cout, cout, 1), cout, g=0.5 * gain), f)
+            _add(w, f"{rb}.conv2.bias", rng.normal((cout,), 0.01), f)
+        cin = cout
+    _add(w, "tok_dec.dec.5.snake.alpha", rng.normal((96,), 0.1), f)
+    _add(w, "tok_dec.dec.5.snake.beta", rng.normal((96,), 0.1), f)
+    _add(w, "tok_dec.dec.6.conv.weight", fan((1, 96, 7), 96 * 7, g=out_gain), f)
+    _add(w, "tok_dec.dec.6.conv.bias", rng.normal((1,), 0.01), f)
+
+    w.write_header_to_file(path=path)
+    w.write_kv_data_to_file()
+    w.write_tensors_to_file()
+    w.close()
+    return dict(seed=seed, gain=gain, out_gain=out_gain)
+
+
+def ensure_models(model_dir: str, preset: str = "tiny", wtype: str = "f16", seed: int = 1234,
+                  voc_seed: int = 4321, verbose: bool = False) -> tuple[str, str]:
+    """Create (if missing) the two GGUFs under model_dir; returns (tts_path, vocoder_path).
+
+    File names follow the reference pipeline (src/qwen3_tts.cpp:118-119) with a preset /
+    weight-type infix so several variants can sit side by side in one cache directory.
+    """
+    os.makedirs(model_dir, exist_ok=True)
+    tts = os.path.join(model_dir, f"qwen3-tts-0.6b-{preset}-{wtype}-s{seed}.gguf")
+    voc = os.path.join(model_dir, f"qwen3-tts-tokenizer-f16-s{voc_seed}.gguf")
+    if not os.path.exists(tts):
+        if verbose:
+            print(f"[make_random_gguf] writing {tts}", file=sys.stderr)
+        write_tts_gguf(tts + ".tmp", preset=preset, seed=seed, wtype=wtype)
+        os.replace(tts + ".tmp", tts)
+    if not os.path.exists(voc):
+        if verbose:
+            print(f"[make_random_gguf] writing {voc}", file=sys.stderr)
+        write_vocoder_gguf(voc + ".tmp", seed=voc_seed)
+        os.replace(voc + ".tmp", voc)
+    return tts, voc
+
+
+def main():
+    ap = argparse.ArgumentParser(description=__doc__)
+    ap.add_argument("--dir", required=True)
+    ap.add_argument("--preset", default="tiny", choices=list(PRESETS))
+    ap.add_argument("--wtype", default="f16", choices=["f16", "q8_0"])
+    ap.add_argument("--seed", type=int, default=1234)
+    a = ap.parse_args()
+    print(*ensure_models(a.dir, a.preset, a.wtype, a.seed, verbose=True))
+
+
+if __name__ == "__main__":
+    main()
