@@ -1,0 +1,223 @@
+/*
+ * q3t.h — C ABI of the B200-native codes-to-audio engine (libq3t_b200.so).
+ *
+ * This is the drop-in boundary for the hot path of clawd20130/qwen3-tts.cpp:
+ * plain pointers and sizes, no C++/torch types.  Two layers are exported from
+ * the same shared library:
+ *
+ *   (1) q3t_*   — the device engine (CUDA translation units).  This is what the
+ *       reference's ggml graph build/alloc/compute sequence is replaced by.
+ *       Each entry point cites the reference interface it stands in for
+ *       (paths relative to the reference repository root).
+ *
+ *   (2) q3t_tts_* / q3t_dec_* / q3t_gguf_* — a C view of the C++ host classes
+ *       qwen3_tts::TTSTransformer / AudioTokenizerDecoder / GGUFLoader that
+ *       this repo re-implements with the reference's method names, argument
+ *       meaning and error behaviour (src/tts_transformer.h:190-280,
+ *       src/audio_tokenizer_decoder.h:159-179, src/gguf_loader.h:16-81).  It
+ *       exists so non-C++ callers (ctypes, cgo, JNI ...) can bind the same API.
+ *
+ * All functions return 0 on success and a negative q3t_status otherwise unless
+ * stated; q3t_last_error()/q3t_*_get_error() give the message.  Pointers are
+ * HOST pointers unless the parameter name ends in _dev.  Outputs are caller
+ * allocated.  One context / object is bound to one CUDA device and must be
+ * used from one thread at a time (same rule as the reference, AGENTS.md:44-47).
+ * There is no CPU fallback: without a CUDA device every compute call fails.
+ */
+#ifndef Q3T_H
+#define Q3T_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define Q3T_API __declspec(dllexport)
+#else
+#define Q3T_API __attribute__((visibility("default")))
+#endif
+
+typedef enum q3t_status {
+    Q3T_OK            =  0,
+    Q3T_ERR_ARG       = -1,  /* bad argument                          */
+    Q3T_ERR_CUDA      = -2,  /* CUDA runtime error / no device        */
+    Q3T_ERR_STATE     = -3,  /* call order (weights not finalized...) */
+    Q3T_ERR_CTX_FULL  = -4,  /* "Context length exceeded"             */
+    Q3T_ERR_IO        = -5,
+    Q3T_ERR_FORMAT    = -6,  /* malformed GGUF / unsupported dtype    */
+    Q3T_ERR_DEVICE    = -7   /* device-side watchdog tripped          */
+} q3t_status;
+
+/* ggml type ids as stored in GGUF (ggml/include/ggml.h:390-398) */
+enum { Q3T_TYPE_F32 = 0, Q3T_TYPE_F16 = 1, Q3T_TYPE_Q8_0 = 8 };
+
+typedef struct q3t_ctx q3t_ctx;
+
+/* Mirror of tts_transformer_config (src/tts_transformer.h:58-99), POD. */
+typedef struct q3t_tts_config {
+    int32_t text_vocab_size, text_embd_dim;
+    int32_t hidden_size, n_layers, n_attention_heads, n_key_value_heads;
+    int32_t intermediate_size, head_dim;
+    float   rms_norm_eps, rope_theta;
+    int32_t codec_vocab_size, n_codebooks;
+    int32_t code_pred_layers, code_pred_vocab_size;
+    int32_t codec_pad_id, codec_bos_id, codec_eos_id;
+    int32_t tts_bos_token_id, tts_eos_token_id, tts_pad_token_id;
+    int32_t codec_think_id, codec_nothink_id, codec_think_bos_id, codec_think_eos_id;
+    int32_t english_language_id;
+} q3t_tts_config;
+
+/* Per-phase device timings of the last generate (CUDA events), the counterpart of
+ * struct tts_timing (src/tts_transformer.h:19-53). */
+typedef struct q3t_timing {
+    double prefill_ms, frames_ms, vocoder_ms;
+    int32_t n_frames;
+    int64_t kernel_launches;
+} q3t_timing;
+
+/* ------------------------------------------------------------------ engine */
+
+/* replaces init_preferred_backend()/ggml_backend_sched_new (src/gguf_loader.cpp:27-58,
+ * src/tts_transformer.cpp:123-150): binds a CUDA device, creates the stream. */
+Q3T_API int  q3t_ctx_create(int device, q3t_ctx ** out);
+Q3T_API void q3t_ctx_destroy(q3t_ctx * ctx);
+Q3T_API const char * q3t_last_error(q3t_ctx * ctx);   /* ctx may be NULL for create errors */
+Q3T_API int  q3t_device_info(q3t_ctx * ctx, int32_t * sm_count, int32_t * cc_major, int32_t * cc_minor);
+
+/* replaces parse_config (src/tts_transformer.cpp:212-344): must precede uploads. */
+Q3T_API int  q3t_set_tts_config(q3t_ctx * ctx, const q3t_tts_config * cfg);
+
+/* replaces ggml_backend_tensor_set per tensor in load_tensor_data
+ * (src/tts_transformer.cpp:648-677) and load_tensor_data_from_file
+ * (src/gguf_loader.cpp:154-227).  `name` is the GGUF tensor name, `type` a Q3T_TYPE_*,
+ * `ne` the ggml shape (ne[0] fastest).  Unknown names are ignored (returns 1). */
+Q3T_API int  q3t_upload_tensor(q3t_ctx * ctx, const char * name, int32_t type,
+                               const int64_t ne[4], const void * data, size_t nbytes);
+/* private device repack after the last upload (fused QKV / gate-up planes, Q8_0 split into
+ * quant + scale planes, RoPE tables).  `which`: 1 = talker+code predictor, 2 = vocoder. */
+Q3T_API int  q3t_finalize_weights(q3t_ctx * ctx, int32_t which);
+Q3T_API int  q3t_unload(q3t_ctx * ctx, int32_t which);
+
+/* init_kv_cache / clear_kv_cache (src/tts_transformer.cpp:685-737) */
+Q3T_API int  q3t_kv_init(q3t_ctx * ctx, int32_t n_ctx);
+Q3T_API int  q3t_kv_n_ctx(q3t_ctx * ctx);
+
+/* forward_prefill (src/tts_transformer.cpp:1831-1961): embd f32[n_tokens*H] ->
+ * hidden_out f32[n_tokens*H] (may be NULL), logits_out f32[codec_vocab] of the last row. */
+Q3T_API int  q3t_talker_prefill(q3t_ctx * ctx, const float * embd, int32_t n_tokens, int32_t n_past,
+                                float * hidden_out, float * logits_out);
+/* forward_step (src/tts_transformer.cpp:1993-2108) */
+Q3T_API int  q3t_talker_step(q3t_ctx * ctx, const float * embd, int32_t n_past,
+                             float * logits_out, float * hidden_out);
+/* predict_codes_autoregressive (src/tts_transformer.cpp:2310-2575): hidden f32[H], cb0 ->
+ * codes15_out int32[15].  temperature<=0 = greedy.  `seed` drives the device sampler
+ * (the reference's rng_ is unseedable, src/tts_transformer.h:336). */
+Q3T_API int  q3t_codepred_frame(q3t_ctx * ctx, const float * hidden, int32_t cb0,
+                                float temperature, int32_t top_k, uint64_t seed, int32_t * codes15_out);
+/* predict_codes, the legacy parallel-heads formulation (src/tts_transformer.cpp:2130-2180,
+ * graph :1413-1532): logits_out f32[15*code_pred_vocab]. prev_codes may be NULL. */
+Q3T_API int  q3t_codepred_parallel(q3t_ctx * ctx, const float * hidden, const int32_t * prev_codes,
+                                   float * logits_out);
+/* build_prefill_graph (src/tts_transformer.cpp:984-1122): prompt assembly on device.
+ * Outputs may be NULL; prefill_len/trailing_len are always written. */
+Q3T_API int  q3t_build_prompt(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_tokens,
+                              const float * speaker_embd, int32_t language_id,
+                              float * prefill_out, int32_t * prefill_len,
+                              float * trailing_out, int32_t * trailing_len, float * pad_out);
+/* project_text_tokens (src/tts_transformer.cpp:917-982): out f32[n_tokens*H] */
+Q3T_API int  q3t_project_text(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_tokens, float * out);
+/* lookup_embedding_rows on talker.codec_embd (src/tts_transformer.cpp:793-915) */
+Q3T_API int  q3t_codec_embed(q3t_ctx * ctx, const int32_t * ids, int32_t n, float * out);
+
+/* TTSTransformer::generate (src/tts_transformer.cpp:2577-2851), whole loop on device.
+ * codes_out int32[max_len*n_codebooks] frame-major; *n_frames_out = frames produced
+ * (EOS stops before emitting a frame; max_len<=0 -> 0 frames, success). */
+Q3T_API int  q3t_generate(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_tokens,
+                          const float * speaker_embd, int32_t max_len, int32_t language_id,
+                          float repetition_penalty, float temperature, int32_t top_k, uint64_t seed,
+                          int32_t * codes_out, int32_t * n_frames_out);
+
+/* AudioTokenizerDecoder::decode (src/audio_tokenizer_decoder.cpp:804-879):
+ * codes int32[n_frames*16] frame-major -> samples f32; returns sample count
+ * (1920*n_frames-555) or a negative status.  cap = capacity of samples_out in floats. */
+Q3T_API int64_t q3t_vocoder_decode(q3t_ctx * ctx, const int32_t * codes, int32_t n_frames,
+                                   float * samples_out, int64_t cap);
+Q3T_API int64_t q3t_vocoder_n_samples(int32_t n_frames);
+
+/* Device-resident variants used by bench.py `value` (inputs already in HBM):
+ * run generate+decode for a prompt that was staged with q3t_stage_prompt, leave the
+ * result on the device, report frames and samples. */
+Q3T_API int  q3t_stage_prompt(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_tokens,
+                              const float * speaker_embd, int32_t language_id);
+Q3T_API int  q3t_run_staged(q3t_ctx * ctx, int32_t max_len, float repetition_penalty,
+                            float temperature, int32_t top_k, uint64_t seed, int32_t with_vocoder,
+                            int32_t * n_frames_out, int64_t * n_samples_out);
+Q3T_API int  q3t_fetch_codes(q3t_ctx * ctx, int32_t * codes_out, int32_t n_frames);
+Q3T_API int64_t q3t_fetch_samples(q3t_ctx * ctx, float * samples_out, int64_t cap);
+
+/* Repeats the talker decode step `iters` times at position n_past (KV must hold >= n_past
+ * rows) and returns the mean device time per step in microseconds (CUDA events on the
+ * engine stream).  Used for the roofline figure; does not advance any state. */
+Q3T_API int  q3t_bench_talker_step(q3t_ctx * ctx, int32_t n_past, int32_t iters, float * us_per_step);
+Q3T_API int  q3t_get_timing(q3t_ctx * ctx, q3t_timing * out);
+Q3T_API int64_t q3t_weight_bytes(q3t_ctx * ctx, int32_t which); /* 1 talker stack, 2 code-pred stack (one pass), 3 vocoder */
+
+/* --------------------------------------------------- host classes, C view */
+
+typedef struct q3t_gguf q3t_gguf;              /* qwen3_tts::GGUFLoader (src/gguf_loader.h:16-62) */
+Q3T_API q3t_gguf * q3t_gguf_open(const char * path);
+Q3T_API void       q3t_gguf_close(q3t_gguf * g);
+Q3T_API const char * q3t_gguf_get_error(q3t_gguf * g);
+Q3T_API int64_t    q3t_gguf_get_n_tensors(q3t_gguf * g);
+Q3T_API const char * q3t_gguf_get_tensor_name(q3t_gguf * g, int64_t idx);
+Q3T_API int32_t    q3t_gguf_get_tensor_type(q3t_gguf * g, int64_t idx);
+Q3T_API size_t     q3t_gguf_get_tensor_offset(q3t_gguf * g, int64_t idx);
+Q3T_API size_t     q3t_gguf_get_tensor_size(q3t_gguf * g, int64_t idx);
+Q3T_API int32_t    q3t_gguf_get_tensor_ne(q3t_gguf * g, int64_t idx, int64_t ne_out[4]);
+Q3T_API int32_t    q3t_gguf_get_u32(q3t_gguf * g, const char * key, int32_t default_val);
+Q3T_API float      q3t_gguf_get_f32(q3t_gguf * g, const char * key, float default_val);
+Q3T_API size_t     q3t_gguf_get_data_offset(q3t_gguf * g);
+
+typedef struct q3t_tts q3t_tts;                /* qwen3_tts::TTSTransformer */
+Q3T_API q3t_tts * q3t_tts_new(void);
+Q3T_API void      q3t_tts_delete(q3t_tts * t);
+Q3T_API int  q3t_tts_load_model(q3t_tts * t, const char * model_path);      /* 1 = true, 0 = false */
+Q3T_API void q3t_tts_unload_model(q3t_tts * t);
+Q3T_API int  q3t_tts_init_kv_cache(q3t_tts * t, int32_t n_ctx);
+Q3T_API void q3t_tts_clear_kv_cache(q3t_tts * t);
+Q3T_API int  q3t_tts_forward_prefill(q3t_tts * t, const float * prefill_embd, int32_t n_tokens, int32_t n_past,
+                                     float * hidden_out, float * logits_out);
+Q3T_API int  q3t_tts_forward_step(q3t_tts * t, const float * step_embd, int32_t n_past,
+                                  float * logits_out, float * hidden_out);
+Q3T_API int  q3t_tts_forward_text(q3t_tts * t, const int32_t * text_tokens, int32_t n_tokens,
+                                  const float * speaker_embd, int32_t n_past, float * hidden_out);
+Q3T_API int  q3t_tts_forward_codec(q3t_tts * t, int32_t codec_token, int32_t n_past, float * logits_out);
+Q3T_API int  q3t_tts_get_hidden_states(q3t_tts * t, float * hidden_out);
+Q3T_API int  q3t_tts_predict_codes(q3t_tts * t, const float * hidden, const int32_t * prev_codes, float * logits_out);
+Q3T_API int  q3t_tts_predict_codes_autoregressive(q3t_tts * t, const float * hidden, int32_t codebook_0_token,
+                                                  int32_t * codes15_out, float temperature, int32_t top_k);
+Q3T_API int  q3t_tts_generate(q3t_tts * t, const int32_t * text_tokens, int32_t n_tokens,
+                              const float * speaker_embd, int32_t max_len,
+                              int32_t * codes_out, int32_t * n_frames_out,
+                              int32_t language_id, float repetition_penalty, float temperature, int32_t top_k);
+Q3T_API void q3t_tts_set_seed(q3t_tts * t, uint64_t seed);   /* extension: the reference has no seed API */
+Q3T_API int  q3t_tts_get_config(q3t_tts * t, q3t_tts_config * out);
+Q3T_API const char * q3t_tts_get_error(q3t_tts * t);
+Q3T_API q3t_ctx * q3t_tts_engine(q3t_tts * t);                /* the engine context behind the object */
+
+typedef struct q3t_dec q3t_dec;                /* qwen3_tts::AudioTokenizerDecoder */
+Q3T_API q3t_dec * q3t_dec_new(void);
+Q3T_API void      q3t_dec_delete(q3t_dec * d);
+Q3T_API int  q3t_dec_load_model(q3t_dec * d, const char * model_path);
+Q3T_API void q3t_dec_unload_model(q3t_dec * d);
+Q3T_API int64_t q3t_dec_decode(q3t_dec * d, const int32_t * codes, int32_t n_frames, float * samples_out, int64_t cap);
+Q3T_API const char * q3t_dec_get_error(q3t_dec * d);
+Q3T_API q3t_ctx * q3t_dec_engine(q3t_dec * d);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* Q3T_H */

@@ -1,0 +1,93 @@
+// Device-side helpers shared by the sm_100a kernels of the engine.
+#pragma once
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace q3t {
+
+// ---- fixed 0.6B shapes the decode kernels are specialised on (src/tts_transformer.h:58-99)
+constexpr int H      = 1024;   // hidden_size
+constexpr int NH     = 16;     // attention heads
+constexpr int NKV    = 8;      // key/value heads
+constexpr int HD     = 128;    // head_dim
+constexpr int FFN    = 3072;   // intermediate_size
+constexpr int QKV_N  = (NH + 2 * NKV) * HD;   // 4096 fused rows: q | k | v
+constexpr int NCB    = 16;     // codebooks
+
+// ---- cache-policy loads ------------------------------------------------------------------
+// weights: read-only, streamed once per pass -> no L1 allocation
+__device__ __forceinline__ uint4 ld_weight(const void * p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+// activations written by other CTAs inside the same launch: must not be served by a stale L1 line
+__device__ __forceinline__ float ld_act(const float * p) { return __ldcg(p); }
+__device__ __forceinline__ float4 ld_act4(const float * p) { return __ldcg(reinterpret_cast<const float4 *>(p)); }
+__device__ __forceinline__ int ld_act_i(const int * p) { return __ldcg(p); }
+
+// TMA-unit driven L2 prefetch of a contiguous byte range (fire and forget); size multiple of 16
+__device__ __forceinline__ void l2_prefetch_bulk(const void * p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p), "r"(bytes) : "memory");
+}
+
+// ---- acquire / release on global counters ---------------------------------------------------
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long * p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_add_u64(unsigned long long * p, unsigned long long v) {
+    asm volatile("red.release.gpu.global.add.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+
+// ---- warp reductions ----------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// round-to-nearest-even to F16 and back: the oracle's `from_float` before every F16 mat-mul
+// (ggml/src/ggml-cpu/ggml-cpu.c:1291-1331)
+__device__ __forceinline__ float r16(float v) { return __half2float(__float2half_rn(v)); }
+
+// 8 halves (one 16-byte vector) dotted with 8 halves, F32 accumulate, products exact in F32
+__device__ __forceinline__ float dot8_hh(const uint4 & w, const uint4 & x, float acc) {
+    const __half2 * wh = reinterpret_cast<const __half2 *>(&w);
+    const __half2 * xh = reinterpret_cast<const __half2 *>(&x);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float2 a = __half22float2(wh[i]);
+        float2 b = __half22float2(xh[i]);
+        acc = fmaf(a.x, b.x, acc);
+        acc = fmaf(a.y, b.y, acc);
+    }
+    return acc;
+}
+// 8 halves (weights, exact in F32) dotted with 8 floats
+__device__ __forceinline__ float dot8_hf(const uint4 & w, const float4 & x0, const float4 & x1, float acc) {
+    const __half2 * wh = reinterpret_cast<const __half2 *>(&w);
+    float2 a0 = __half22float2(wh[0]), a1 = __half22float2(wh[1]);
+    float2 a2 = __half22float2(wh[2]), a3 = __half22float2(wh[3]);
+    acc = fmaf(a0.x, x0.x, acc); acc = fmaf(a0.y, x0.y, acc);
+    acc = fmaf(a1.x, x0.z, acc); acc = fmaf(a1.y, x0.w, acc);
+    acc = fmaf(a2.x, x1.x, acc); acc = fmaf(a2.y, x1.y, acc);
+    acc = fmaf(a3.x, x1.z, acc); acc = fmaf(a3.y, x1.w, acc);
+    return acc;
+}
+
+} // namespace q3t

@@ -1,0 +1,792 @@
+// Engine context, weight upload / private HBM repack, KV cache and the q3t_* C-ABI entry points
+// for the talker + code predictor.  Replaces (reference, file:line):
+//   init_preferred_backend / ggml_backend_sched_new      src/gguf_loader.cpp:27-58, src/tts_transformer.cpp:123-150
+//   create_tensors / load_tensor_data                    src/tts_transformer.cpp:346-683
+//   init_kv_cache / init_code_pred_kv_cache              src/tts_transformer.cpp:685-791
+//   forward_prefill / forward_step / predict_codes_autoregressive / generate   :1831-2108, :2310-2851
+#include "common.cuh"
+#include "engine.h"
+
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+
+using namespace q3t;
+
+static std::string g_create_err;
+
+namespace q3t {
+
+int set_err(q3t_ctx * ctx, int code, const std::string & msg) {
+    if (ctx) ctx->err = msg; else g_create_err = msg;
+    return code;
+}
+
+int cuda_check(q3t_ctx * ctx, cudaError_t e, const char * what) {
+    if (e == cudaSuccess) return Q3T_OK;
+    return set_err(ctx, Q3T_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+} // namespace q3t
+
+#define CK(call) do { int _rc = cuda_check(ctx, (call), #call); if (_rc != Q3T_OK) return _rc; } while (0)
+
+template <typename T>
+static int dev_alloc(q3t_ctx * ctx, T ** out, size_t count, bool zero = false, bool owned = true) {
+    void * p = nullptr;
+    int rc = cuda_check(ctx, cudaMalloc(&p, std::max<size_t>(count * sizeof(T), 16)), "cudaMalloc");
+    if (rc != Q3T_OK) return rc;
+    if (zero) cudaMemsetAsync(p, 0, std::max<size_t>(count * sizeof(T), 16), ctx->stream);
+    if (owned) ctx->owned.push_back(p);
+    *out = reinterpret_cast<T *>(p);
+    return Q3T_OK;
+}
+
+// ------------------------------------------------------------------------------ context
+extern "C" int q3t_ctx_create(int device, q3t_ctx ** out) {
+    if (!out) return Q3T_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0)
+        return set_err(nullptr, Q3T_ERR_CUDA, std::string("no CUDA device available (this engine has no CPU fallback): ") +
+                                               (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"));
+    if (device < 0 || device >= n) return set_err(nullptr, Q3T_ERR_ARG, "device index out of range");
+    q3t_ctx * ctx = new q3t_ctx();
+    ctx->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) { delete ctx; return set_err(nullptr, Q3T_ERR_CUDA, "cudaSetDevice failed"); }
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device);
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->cc_major = prop.major; ctx->cc_minor = prop.minor;
+    if (prop.major != 10) {
+        delete ctx;
+        return set_err(nullptr, Q3T_ERR_CUDA, "this engine is compiled for sm_100a (B200) only; device reports cc " +
+                                               std::to_string(prop.major) + "." + std::to_string(prop.minor));
+    }
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete ctx; return set_err(nullptr, Q3T_ERR_CUDA, "cudaStreamCreate failed");
+    }
+    for (auto & ev : ctx->ev) cudaEventCreate(&ev);
+    *out = ctx;
+    return Q3T_OK;
+}
+
+static void free_raw(q3t_ctx * ctx, const char * prefix) {
+    for (auto it = ctx->raw.begin(); it != ctx->raw.end();) {
+        if (it->first.compare(0, strlen(prefix), prefix) == 0) { cudaFree(it->second.dev); it = ctx->raw.erase(it); }
+        else ++it;
+    }
+}
+
+extern "C" int q3t_unload(q3t_ctx * ctx, int32_t which) {
+    if (!ctx) return Q3T_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (which & 1) {
+        for (void * p : ctx->owned) cudaFree(p);
+        ctx->owned.clear();
+        if (ctx->kv_alloc) { cudaFree(ctx->kv_alloc); ctx->kv_alloc = nullptr; }
+        ctx->n_ctx = 0;
+        free_raw(ctx, "talker."); free_raw(ctx, "code_pred.");
+        ctx->tts_ready = false;
+        ctx->hm = DevModel{};
+        ctx->d_passes = nullptr; ctx->passes_cap = 0;
+        ctx->d_prefill = nullptr; ctx->d_hidden_all = nullptr; ctx->d_trailing = nullptr; ctx->trailing_cap = 0;
+        ctx->d_pad = nullptr; ctx->d_codes = nullptr; ctx->codes_cap = 0; ctx->d_tokens = nullptr; ctx->tokens_cap = 0;
+        ctx->d_spk = nullptr; ctx->d_tmp = nullptr; ctx->tmp_cap = 0;
+    }
+    if (which & 2) {
+        vocoder_free(ctx);
+        free_raw(ctx, "tok_dec.");
+        ctx->voc_ready = false;
+    }
+    return Q3T_OK;
+}
+
+extern "C" void q3t_ctx_destroy(q3t_ctx * ctx) {
+    if (!ctx) return;
+    q3t_unload(ctx, 3);
+    for (auto & kv : ctx->raw) cudaFree(kv.second.dev);
+    ctx->raw.clear();
+    for (auto & ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" const char * q3t_last_error(q3t_ctx * ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+extern "C" int q3t_device_info(q3t_ctx * ctx, int32_t * sm_count, int32_t * cc_major, int32_t * cc_minor) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (sm_count) *sm_count = ctx->sm_count;
+    if (cc_major) *cc_major = ctx->cc_major;
+    if (cc_minor) *cc_minor = ctx->cc_minor;
+    return Q3T_OK;
+}
+
+extern "C" int q3t_set_tts_config(q3t_ctx * ctx, const q3t_tts_config * cfg) {
+    if (!ctx || !cfg) return Q3T_ERR_ARG;
+    // the decode kernels are specialised on the 0.6B per-layer shapes (SURVEY.md §8 constants)
+    if (cfg->hidden_size != H || cfg->n_attention_heads != NH || cfg->n_key_value_heads != NKV ||
+        cfg->head_dim != HD || cfg->intermediate_size != FFN || cfg->n_codebooks != NCB)
+        return set_err(ctx, Q3T_ERR_FORMAT, "unsupported model shape: kernels are built for hidden 1024, 16/8 heads x 128, ffn 3072, 16 codebooks");
+    if (cfg->codec_vocab_size > 3072 || cfg->code_pred_vocab_size > 3072 || cfg->codec_vocab_size < 1024)
+        return set_err(ctx, Q3T_ERR_FORMAT, "unsupported vocabulary size (max 3072)");
+    if (cfg->n_layers < 1 || cfg->code_pred_layers < 1) return set_err(ctx, Q3T_ERR_FORMAT, "layer counts must be >= 1");
+    ctx->cfg = *cfg;
+    ctx->have_cfg = true;
+    return Q3T_OK;
+}
+
+static size_t type_row_bytes(int32_t type, int64_t ne0) {
+    switch (type) {
+        case Q3T_TYPE_F32:  return (size_t) ne0 * 4;
+        case Q3T_TYPE_F16:  return (size_t) ne0 * 2;
+        case Q3T_TYPE_Q8_0: return (size_t) (ne0 / 32) * 34;
+        default: return 0;
+    }
+}
+
+extern "C" int q3t_upload_tensor(q3t_ctx * ctx, const char * name, int32_t type, const int64_t ne[4],
+                                 const void * data, size_t nbytes) {
+    if (!ctx || !name || !ne || !data) return Q3T_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    const bool mine = !strncmp(name, "talker.", 7) || !strncmp(name, "code_pred.", 10) || !strncmp(name, "tok_dec.", 8);
+    if (!mine) return 1;       // spk_enc.*, tok_enc.* ...: not on this path (src/tts_transformer.cpp:375-377)
+    const size_t rb = type_row_bytes(type, ne[0]);
+    if (rb == 0) return set_err(ctx, Q3T_ERR_FORMAT, std::string("unsupported tensor type for ") + name);
+    if (type == Q3T_TYPE_Q8_0 && (ne[0] % 32) != 0) return set_err(ctx, Q3T_ERR_FORMAT, std::string("Q8_0 row not a multiple of 32: ") + name);
+    const size_t expect = rb * (size_t) (ne[1] * ne[2] * ne[3]);
+    if (expect != nbytes) return set_err(ctx, Q3T_ERR_FORMAT, std::string("size mismatch for ") + name);
+    auto it = ctx->raw.find(name);
+    if (it != ctx->raw.end()) { cudaFree(it->second.dev); ctx->raw.erase(it); }
+    q3t_host_tensor t{};
+    t.type = type; t.nbytes = nbytes;
+    for (int i = 0; i < 4; ++i) t.ne[i] = ne[i];
+    CK(cudaMalloc(&t.dev, std::max<size_t>(nbytes, 16)));
+    cudaError_t e = cudaMemcpyAsync(t.dev, data, nbytes, cudaMemcpyHostToDevice, ctx->stream);
+    if (e != cudaSuccess) { cudaFree(t.dev); return cuda_check(ctx, e, "tensor upload"); }
+    ctx->raw[name] = t;
+    return Q3T_OK;
+}
+
+// ------------------------------------------------------------------------------ finalize (repack)
+static const q3t_host_tensor * find_raw(q3t_ctx * ctx, const std::string & name) {
+    auto it = ctx->raw.find(name);
+    return it == ctx->raw.end() ? nullptr : &it->second;
+}
+
+static int need(q3t_ctx * ctx, const std::string & name, int32_t type, int64_t ne0, int64_t ne1, const q3t_host_tensor ** out) {
+    const q3t_host_tensor * t = find_raw(ctx, name);
+    if (!t) return set_err(ctx, Q3T_ERR_FORMAT, "missing tensor: " + name);
+    if (type >= 0 && t->type != type) return set_err(ctx, Q3T_ERR_FORMAT, "unexpected dtype for tensor: " + name);
+    if (t->ne[0] != ne0 || t->ne[1] != ne1) return set_err(ctx, Q3T_ERR_FORMAT, "unexpected shape for tensor: " + name);
+    *out = t;
+    return Q3T_OK;
+}
+
+// copies `rows` rows of `row_bytes` into dst with a destination pitch (row interleave for gate/up)
+static int copy_rows(q3t_ctx * ctx, void * dst, size_t dst_pitch, const void * src, size_t row_bytes, size_t rows) {
+    return cuda_check(ctx, cudaMemcpy2DAsync(dst, dst_pitch, src, row_bytes, row_bytes, rows, cudaMemcpyDeviceToDevice, ctx->stream),
+                      "repack copy");
+}
+
+static int build_stack(q3t_ctx * ctx, const char * prefix, int n_layers, StackW & W, int64_t & bytes) {
+    // dtype of the big matrices follows the file (F16 or Q8_0); all seven must agree
+    const q3t_host_tensor * probe = find_raw(ctx, std::string(prefix) + ".blk.0.attn_q.weight");
+    if (!probe) return set_err(ctx, Q3T_ERR_FORMAT, std::string("missing tensor: ") + prefix + ".blk.0.attn_q.weight");
+    const int32_t wt = probe->type;
+    if (wt != Q3T_TYPE_F16) return set_err(ctx, Q3T_ERR_FORMAT, "only F16 layer weights are wired up in this build");
+    W.n_layers = n_layers; W.wtype = wt;
+    __half * wqkv, * wo, * wgu, * wdown;
+    float * an, * fn, * qn, * kn;
+    int rc;
+    if ((rc = dev_alloc(ctx, &wqkv,  (size_t) n_layers * QKV_N * H))) return rc;
+    if ((rc = dev_alloc(ctx, &wo,    (size_t) n_layers * H * NH * HD))) return rc;
+    if ((rc = dev_alloc(ctx, &wgu,   (size_t) n_layers * 2 * FFN * H))) return rc;
+    if ((rc = dev_alloc(ctx, &wdown, (size_t) n_layers * H * FFN))) return rc;
+    if ((rc = dev_alloc(ctx, &an, (size_t) n_layers * H))) return rc;
+    if ((rc = dev_alloc(ctx, &fn, (size_t) n_layers * H))) return rc;
+    if ((rc = dev_alloc(ctx, &qn, (size_t) n_layers * HD))) return rc;
+    if ((rc = dev_alloc(ctx, &kn, (size_t) n_layers * HD))) return rc;
+    for (int l = 0; l < n_layers; ++l) {
+        const std::string b = std::string(prefix) + ".blk." + std::to_string(l) + ".";
+        const q3t_host_tensor * q, * k, * v, * o, * g, * u, * d, * t;
+        if ((rc = need(ctx, b + "attn_q.weight", wt, H, NH * HD, &q))) return rc;
+        if ((rc = need(ctx, b + "attn_k.weight", wt, H, NKV * HD, &k))) return rc;
+        if ((rc = need(ctx, b + "attn_v.weight", wt, H, NKV * HD, &v))) return rc;
+        if ((rc = need(ctx, b + "attn_output.weight", wt, NH * HD, H, &o))) return rc;
+        if ((rc = need(ctx, b + "ffn_gate.weight", wt, H, FFN, &g))) return rc;
+        if ((rc = need(ctx, b + "ffn_up.weight", wt, H, FFN, &u))) return rc;
+        if ((rc = need(ctx, b + "ffn_down.weight", wt, FFN, H, &d))) return rc;
+        __half * dq = wqkv + (size_t) l * QKV_N * H;
+        if ((rc = copy_rows(ctx, dq, H * 2, q->dev, H * 2, NH * HD))) return rc;
+        if ((rc = copy_rows(ctx, dq + (size_t) NH * HD * H, H * 2, k->dev, H * 2, NKV * HD))) return rc;
+        if ((rc = copy_rows(ctx, dq + (size_t) (NH + NKV) * HD * H, H * 2, v->dev, H * 2, NKV * HD))) return rc;
+        if ((rc = copy_rows(ctx, wo + (size_t) l * H * NH * HD, NH * HD * 2, o->dev, NH * HD * 2, H))) return rc;
+        __half * dg = wgu + (size_t) l * 2 * FFN * H;
+        if ((rc = copy_rows(ctx, dg, 2 * H * 2, g->dev, H * 2, FFN))) return rc;          // even rows: gate
+        if ((rc = copy_rows(ctx, dg + H, 2 * H * 2, u->dev, H * 2, FFN))) return rc;      // odd rows: up
+        if ((rc = copy_rows(ctx, wdown + (size_t) l * H * FFN, FFN * 2, d->dev, FFN * 2, H))) return rc;
+        if ((rc = need(ctx, b + "attn_norm.weight", Q3T_TYPE_F32, H, 1, &t))) return rc;
+        if ((rc = copy_rows(ctx, an + (size_t) l * H, H * 4, t->dev, H * 4, 1))) return rc;
+        if ((rc = need(ctx, b + "ffn_norm.weight", Q3T_TYPE_F32, H, 1, &t))) return rc;
+        if ((rc = copy_rows(ctx, fn + (size_t) l * H, H * 4, t->dev, H * 4, 1))) return rc;
+        if ((rc = need(ctx, b + "attn_q_norm.weight", Q3T_TYPE_F32, HD, 1, &t))) return rc;
+        if ((rc = copy_rows(ctx, qn + (size_t) l * HD, HD * 4, t->dev, HD * 4, 1))) return rc;
+        if ((rc = need(ctx, b + "attn_k_norm.weight", Q3T_TYPE_F32, HD, 1, &t))) return rc;
+        if ((rc = copy_rows(ctx, kn + (size_t) l * HD, HD * 4, t->dev, HD * 4, 1))) return rc;
+    }
+    W.wqkv = wqkv; W.wo = wo; W.wgu = wgu; W.wdown = wdown;
+    W.sqkv = W.so = W.sgu = W.sdown = nullptr;
+    W.attn_norm = an; W.ffn_norm = fn; W.q_norm = qn; W.k_norm = kn;
+    bytes = (int64_t) n_layers * ((int64_t) QKV_N * H + (int64_t) H * NH * HD + 2LL * FFN * H + (int64_t) H * FFN) * 2
+          + (int64_t) n_layers * (2 * H + 2 * HD) * 4;
+    return Q3T_OK;
+}
+
+static void drop_stack_raw(q3t_ctx * ctx, const char * prefix) {
+    const std::string p = std::string(prefix) + ".blk.";
+    cudaStreamSynchronize(ctx->stream);
+    free_raw(ctx, p.c_str());
+}
+
+static int finalize_tts(q3t_ctx * ctx) {
+    if (!ctx->have_cfg) return set_err(ctx, Q3T_ERR_STATE, "q3t_set_tts_config must precede q3t_finalize_weights");
+    const q3t_tts_config & c = ctx->cfg;
+    DevModel & m = ctx->hm;
+    m = DevModel{};
+    int rc;
+    if ((rc = build_stack(ctx, "talker", c.n_layers, m.talker, ctx->talker_bytes))) return rc;
+    drop_stack_raw(ctx, "talker");
+    if ((rc = build_stack(ctx, "code_pred", c.code_pred_layers, m.cp, ctx->cp_bytes))) return rc;
+    drop_stack_raw(ctx, "code_pred");
+    const q3t_host_tensor * t;
+    if ((rc = need(ctx, "talker.output_norm.weight", Q3T_TYPE_F32, H, 1, &t))) return rc;
+    m.talker.out_norm = (const float *) t->dev;
+    if ((rc = need(ctx, "code_pred.output_norm.weight", Q3T_TYPE_F32, H, 1, &t))) return rc;
+    m.cp.out_norm = (const float *) t->dev;
+    if ((rc = need(ctx, "talker.codec_head.weight", Q3T_TYPE_F16, H, c.codec_vocab_size, &t))) return rc;
+    m.codec_head.w = (const __half *) t->dev; m.codec_head.vocab = c.codec_vocab_size;
+    if ((rc = need(ctx, "talker.codec_embd.weight", Q3T_TYPE_F16, H, c.codec_vocab_size, &t))) return rc;
+    m.codec_embd = (const __half *) t->dev;
+    for (int i = 0; i < NCB - 1; ++i) {
+        if ((rc = need(ctx, "code_pred.lm_head." + std::to_string(i) + ".weight", Q3T_TYPE_F16, H, c.code_pred_vocab_size, &t))) return rc;
+        m.cp_head[i].w = (const __half *) t->dev; m.cp_head[i].vocab = c.code_pred_vocab_size;
+        if ((rc = need(ctx, "code_pred.codec_embd." + std::to_string(i) + ".weight", Q3T_TYPE_F16, H, c.code_pred_vocab_size, &t))) return rc;
+        m.cp_embd[i] = (const __half *) t->dev;
+    }
+    ctx->talker_bytes += (int64_t) c.codec_vocab_size * H * 2 + H * 4;
+    ctx->cp_bytes     += (int64_t) c.code_pred_vocab_size * H * 2 + H * 4 + H * 2;   // one head + norm + one embedding row per pass
+    m.eps = c.rms_norm_eps;
+
+    // code-predictor KV: 16 positions (src/tts_transformer.cpp:2336-2341) + F32 shadow of positions 0,1
+    const int L2 = c.code_pred_layers;
+    __half * ck, * cv; float * kf, * vf;
+    if ((rc = dev_alloc(ctx, &ck, (size_t) L2 * NKV * 16 * HD, true))) return rc;
+    if ((rc = dev_alloc(ctx, &cv, (size_t) L2 * NKV * 16 * HD, true))) return rc;
+    if ((rc = dev_alloc(ctx, &kf, (size_t) L2 * 2 * NKV * HD, true))) return rc;
+    if ((rc = dev_alloc(ctx, &vf, (size_t) L2 * 2 * NKV * HD, true))) return rc;
+    m.cp.kcache = ck; m.cp.vcache = cv; m.cp.kf32 = kf; m.cp.vf32 = vf; m.cp.n_ctx = 16;
+
+    // activations / scratch
+    if ((rc = dev_alloc(ctx, &m.xa, H, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.xb, H, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.qkv, QKV_N, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.mbuf, FFN, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.hidden, H, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.logits, 3072, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.part_ms, NKV * LM_MAXC * 4, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.part_o, (size_t) NKV * LM_MAXC * 2 * HD, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.cand_val, 512, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.cand_idx, 512, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.seen, 4096, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.bar, 1, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.gbar, NKV, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.st, 1, true))) return rc;
+    ctx->passes_cap = 64;
+    if ((rc = dev_alloc(ctx, &ctx->d_passes, ctx->passes_cap))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->d_prefill, 16 * H, true))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->d_hidden_all, 64 * H, true))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->d_pad, H, true))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->d_spk, H, true))) return rc;
+    ctx->tmp_cap = 8 * 3072;
+    if ((rc = dev_alloc(ctx, &ctx->d_tmp, ctx->tmp_cap, true))) return rc;
+    m.pad_embed = ctx->d_pad;
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->tts_ready = true;
+    ctx->grid = 0;
+    return Q3T_OK;
+}
+
+extern "C" int q3t_finalize_weights(q3t_ctx * ctx, int32_t which) {
+    if (!ctx) return Q3T_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    if (which == 1) return finalize_tts(ctx);
+    if (which == 2) return vocoder_finalize(ctx);
+    return set_err(ctx, Q3T_ERR_ARG, "q3t_finalize_weights: which must be 1 (tts) or 2 (vocoder)");
+}
+
+extern "C" int64_t q3t_weight_bytes(q3t_ctx * ctx, int32_t which) {
+    if (!ctx) return 0;
+    return which == 1 ? ctx->talker_bytes : which == 2 ? ctx->cp_bytes : ctx->voc_bytes;
+}
+
+// ------------------------------------------------------------------------------ KV cache + RoPE table
+// K/V are F16, private layout [layer][kv_head][n_ctx][128] (the reference keeps [128][8][n_ctx],
+// src/tts_transformer.cpp:714-724; a head-major layout makes a chunk of one head contiguous).
+// The RoPE table reproduces ggml_rope_cache_init (ggml/src/ggml-cpu/ops.cpp:5548-5562) with the
+// host libm so cos/sin are bit-identical to the oracle's: theta_i = pos * s^i by repeated multiply.
+extern "C" int q3t_kv_init(q3t_ctx * ctx, int32_t n_ctx) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (n_ctx <= 0) return set_err(ctx, Q3T_ERR_ARG, "n_ctx must be > 0");
+    if (n_ctx > LM_MAXC * 1024) return set_err(ctx, Q3T_ERR_ARG, "n_ctx exceeds the attention kernel's limit (18432)");
+    cudaSetDevice(ctx->device);
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->kv_alloc) { cudaFree(ctx->kv_alloc); ctx->kv_alloc = nullptr; ctx->n_ctx = 0; }
+    const int L = ctx->cfg.n_layers;
+    const size_t per = (size_t) L * NKV * n_ctx * HD;                    // halves per K (or V)
+    const int n_rope = std::max(n_ctx, 16);
+    const size_t rope_bytes = (size_t) n_rope * HD * sizeof(float);
+    const size_t total = per * 2 * sizeof(__half) + rope_bytes;
+    CK(cudaMalloc(&ctx->kv_alloc, total));
+    CK(cudaMemsetAsync(ctx->kv_alloc, 0, per * 2 * sizeof(__half), ctx->stream));
+    DevModel & m = ctx->hm;
+    m.talker.kcache = (__half *) ctx->kv_alloc;
+    m.talker.vcache = m.talker.kcache + per;
+    m.talker.kf32 = nullptr; m.talker.vf32 = nullptr;
+    m.talker.n_ctx = n_ctx;
+    float * rope_dev = (float *) (m.talker.vcache + per);
+    std::vector<float> tab((size_t) n_rope * HD);
+    const float theta_scale = powf(ctx->cfg.rope_theta, -2.0f / (float) HD);
+    for (int p = 0; p < n_rope; ++p) {
+        float theta = (float) p;
+        for (int i = 0; i < HD / 2; ++i) {
+            tab[(size_t) p * HD + i]          = cosf(theta);
+            tab[(size_t) p * HD + HD / 2 + i] = sinf(theta);
+            theta *= theta_scale;
+        }
+    }
+    CK(cudaMemcpyAsync(rope_dev, tab.data(), rope_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    m.rope = rope_dev; m.n_rope_pos = n_rope;
+    ctx->n_ctx = n_ctx;
+    return Q3T_OK;
+}
+
+extern "C" int q3t_kv_n_ctx(q3t_ctx * ctx) { return ctx ? ctx->n_ctx : 0; }
+
+// ------------------------------------------------------------------------------ program helpers
+static int reset_state(q3t_ctx * ctx, const GenState & init, bool clear_seen) {
+    DevModel & m = ctx->hm;
+    GenState st = init;
+    st.bar_base = 0;
+    for (int i = 0; i < 8; ++i) st.gbar_base[i] = 0;
+    st.error = 0;
+    CK(cudaMemsetAsync(m.bar, 0, sizeof(unsigned long long), ctx->stream));
+    CK(cudaMemsetAsync(m.gbar, 0, NKV * sizeof(unsigned long long), ctx->stream));
+    if (clear_seen) CK(cudaMemsetAsync(m.seen, 0, 4096, ctx->stream));
+    CK(cudaMemcpyAsync(m.st, &st, sizeof(GenState), cudaMemcpyHostToDevice, ctx->stream));
+    return Q3T_OK;
+}
+
+static GenState default_state(q3t_ctx * ctx) {
+    GenState st{};
+    st.frame = 0; st.n_past = 0; st.max_len = 1 << 30; st.done = 0; st.trailing_len = 0;
+    st.eos_id = ctx->cfg.codec_eos_id;
+    st.suppress_start = ctx->cfg.codec_vocab_size - 1024;      // src/tts_transformer.cpp:2658
+    st.codec_vocab = ctx->cfg.codec_vocab_size;
+    st.rep_penalty = 1.0f; st.temperature = 0.0f; st.top_k = 0;
+    st.seed = 0; st.draw = 0; st.pending = -1;
+    return st;
+}
+
+static int upload_passes(q3t_ctx * ctx, const std::vector<PassDesc> & v, int offset = 0) {
+    if ((int) v.size() + offset > ctx->passes_cap) return set_err(ctx, Q3T_ERR_ARG, "program too long");
+    return cuda_check(ctx, cudaMemcpyAsync(ctx->d_passes + offset, v.data(), v.size() * sizeof(PassDesc),
+                                           cudaMemcpyHostToDevice, ctx->stream), "program upload");
+}
+
+static PassDesc make_pass(int stack, int xmode, int arg, int pos, int f32attn, int head, int n_layers, int process) {
+    PassDesc p{};
+    p.stack = stack; p.xmode = xmode; p.arg = arg; p.pos = pos; p.f32attn = f32attn; p.head = head;
+    p.n_layers = n_layers; p.process = process;
+    p.xsrc = nullptr; p.hidden_dst = nullptr; p.logits_dst = nullptr;
+    return p;
+}
+
+// the 16 code-predictor passes of one frame (src/tts_transformer.cpp:2398-2569): prefill of
+// [hidden, codec_embd[cb0]] at positions 0,1 (run as two causal single-token passes, F32
+// attention numerics), then 14 steps at positions 2..15 with per-step input table and head.
+static void append_codepred(q3t_ctx * ctx, std::vector<PassDesc> & v, int first_xmode, const float * hidden_src) {
+    const int L = ctx->cfg.code_pred_layers;
+    PassDesc p0 = make_pass(1, first_xmode, 0, 0, 1, -1, L, 0);
+    p0.xsrc = hidden_src;
+    v.push_back(p0);
+    v.push_back(make_pass(1, XM_CB0_EMBD, 0, 1, 1, 1, L, 0));
+    for (int s = 1; s < NCB - 1; ++s) v.push_back(make_pass(1, XM_CP_EMBD, s, s + 1, 0, s + 1, L, 0));
+}
+
+static int check_device_error(q3t_ctx * ctx) {
+    GenState st;
+    CK(cudaMemcpyAsync(&st, ctx->hm.st, sizeof(GenState), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (st.error) return set_err(ctx, Q3T_ERR_DEVICE, "device watchdog: a grid barrier timed out inside lm_kernel");
+    return Q3T_OK;
+}
+
+static int ensure_ctx(q3t_ctx * ctx, int need_rows, int min_default) {
+    // forward_prefill/forward_step lazily create a cache (src/tts_transformer.cpp:1847-1857, 2005-2015)
+    if (ctx->n_ctx == 0) {
+        int rc = q3t_kv_init(ctx, std::max(256, min_default));
+        if (rc) return rc;
+    }
+    if (need_rows > ctx->n_ctx) return set_err(ctx, Q3T_ERR_CTX_FULL, "Context length exceeded");
+    return Q3T_OK;
+}
+
+// ------------------------------------------------------------------------------ talker prefill / step
+static int run_talker_rows(q3t_ctx * ctx, const float * embd_dev, int n_tokens, int n_past, bool all_heads, int process,
+                           float * hidden_all_dev /* [n_tokens][H] or null */) {
+    const int L = ctx->cfg.n_layers;
+    int done = 0;
+    while (done < n_tokens) {
+        const int n = std::min(n_tokens - done, ctx->passes_cap);
+        std::vector<PassDesc> v;
+        for (int i = 0; i < n; ++i) {
+            const int r = done + i;
+            const bool last = r == n_tokens - 1;
+            PassDesc p = make_pass(0, XM_BUF, 0, n_past + r, 0, (all_heads || last) ? 0 : -1, L, last ? process : 0);
+            p.xsrc = embd_dev + (size_t) r * H;
+            if (hidden_all_dev && (all_heads || last)) p.hidden_dst = hidden_all_dev + (size_t) r * H;
+            v.push_back(p);
+        }
+        int rc = upload_passes(ctx, v);
+        if (rc) return rc;
+        if ((rc = lm_launch(ctx, ctx->d_passes, n, 0))) return rc;
+        done += n;
+    }
+    return Q3T_OK;
+}
+
+extern "C" int q3t_talker_prefill(q3t_ctx * ctx, const float * embd, int32_t n_tokens, int32_t n_past,
+                                  float * hidden_out, float * logits_out) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (!embd) return set_err(ctx, Q3T_ERR_ARG, "prefill_embd is null");
+    if (n_tokens <= 0) return set_err(ctx, Q3T_ERR_ARG, "n_tokens must be > 0");
+    cudaSetDevice(ctx->device);
+    int rc = ensure_ctx(ctx, n_past + n_tokens, n_past + n_tokens + 16);
+    if (rc) return rc;
+    float * d_in = nullptr, * d_hid = nullptr;
+    CK(cudaMalloc(&d_in, (size_t) n_tokens * H * 4));
+    CK(cudaMalloc(&d_hid, (size_t) n_tokens * H * 4));
+    rc = cuda_check(ctx, cudaMemcpyAsync(d_in, embd, (size_t) n_tokens * H * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D");
+    if (!rc) rc = reset_state(ctx, default_state(ctx), false);
+    if (!rc) rc = run_talker_rows(ctx, d_in, n_tokens, n_past, true, 0, d_hid);
+    if (!rc && hidden_out) rc = cuda_check(ctx, cudaMemcpyAsync(hidden_out, d_hid, (size_t) n_tokens * H * 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H");
+    if (!rc && logits_out) rc = cuda_check(ctx, cudaMemcpyAsync(logits_out, ctx->hm.logits, (size_t) ctx->cfg.codec_vocab_size * 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H");
+    if (!rc) rc = check_device_error(ctx);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_in); cudaFree(d_hid);
+    return rc;
+}
+
+extern "C" int q3t_talker_step(q3t_ctx * ctx, const float * embd, int32_t n_past, float * logits_out, float * hidden_out) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (!embd) return set_err(ctx, Q3T_ERR_ARG, "step_embd is null");
+    cudaSetDevice(ctx->device);
+    int rc = ensure_ctx(ctx, n_past + 1, n_past + 1 + 16);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(ctx->d_tmp, embd, H * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if ((rc = reset_state(ctx, default_state(ctx), false))) return rc;
+    if ((rc = run_talker_rows(ctx, ctx->d_tmp, 1, n_past, true, 0, nullptr))) return rc;
+    if (logits_out) CK(cudaMemcpyAsync(logits_out, ctx->hm.logits, (size_t) ctx->cfg.codec_vocab_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (hidden_out) CK(cudaMemcpyAsync(hidden_out, ctx->hm.hidden, H * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    return check_device_error(ctx);
+}
+
+// ------------------------------------------------------------------------------ code predictor, one frame
+extern "C" int q3t_codepred_frame(q3t_ctx * ctx, const float * hidden, int32_t cb0, float temperature, int32_t top_k,
+                                  uint64_t seed, int32_t * codes15_out) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (!hidden || !codes15_out) return set_err(ctx, Q3T_ERR_ARG, "null argument");
+    if (cb0 < 0 || cb0 >= ctx->cfg.codec_vocab_size) return set_err(ctx, Q3T_ERR_ARG, "Embedding token ID out of range");
+    cudaSetDevice(ctx->device);
+    int rc;
+    if (ctx->n_ctx == 0 && (rc = q3t_kv_init(ctx, 256))) return rc;     // the RoPE table lives with the KV allocation
+    CK(cudaMemcpyAsync(ctx->d_tmp, hidden, H * 4, cudaMemcpyHostToDevice, ctx->stream));
+    GenState st = default_state(ctx);
+    st.temperature = temperature; st.top_k = top_k; st.seed = seed;
+    st.cur[0] = cb0;
+    if ((rc = reset_state(ctx, st, false))) return rc;
+    std::vector<PassDesc> v;
+    append_codepred(ctx, v, XM_BUF, ctx->d_tmp);
+    v.push_back(make_pass(1, XM_SELECT_ONLY, 0, 0, 0, -1, 0, 0));
+    if ((rc = upload_passes(ctx, v))) return rc;
+    if ((rc = lm_launch(ctx, ctx->d_passes, (int) v.size(), 0))) return rc;
+    GenState out;
+    CK(cudaMemcpyAsync(&out, ctx->hm.st, sizeof(GenState), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (out.error) return set_err(ctx, Q3T_ERR_DEVICE, "device watchdog: a grid barrier timed out inside lm_kernel");
+    for (int i = 0; i < NCB - 1; ++i) codes15_out[i] = out.cur[i + 1];
+    return Q3T_OK;
+}
+
+// ------------------------------------------------------------------------------ prompt staging
+static int ensure_buf_i(q3t_ctx * ctx, int ** buf, int * cap, int need_n) {
+    if (*cap >= need_n) return Q3T_OK;
+    int * p = nullptr;
+    int rc = dev_alloc(ctx, &p, (size_t) need_n, true);
+    if (rc) return rc;
+    *buf = p; *cap = need_n;          // the old buffer stays in `owned` until unload (tiny)
+    return Q3T_OK;
+}
+static int ensure_buf_f(q3t_ctx * ctx, float ** buf, int * cap, int need_n) {
+    if (*cap >= need_n) return Q3T_OK;
+    float * p = nullptr;
+    int rc = dev_alloc(ctx, &p, (size_t) need_n, true);
+    if (rc) return rc;
+    *buf = p; *cap = need_n;
+    return Q3T_OK;
+}
+
+extern "C" int q3t_stage_prompt(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_tokens,
+                                const float * speaker_embd, int32_t language_id) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (!text_tokens) return set_err(ctx, Q3T_ERR_ARG, "text_tokens is null");
+    if (n_tokens < 4) return set_err(ctx, Q3T_ERR_ARG, "Need at least 4 text tokens for generation");
+    for (int i = 0; i < n_tokens; ++i)
+        if (text_tokens[i] < 0 || text_tokens[i] >= ctx->cfg.text_vocab_size) return set_err(ctx, Q3T_ERR_ARG, "Embedding token ID out of range");
+    if (language_id >= ctx->cfg.codec_vocab_size) return set_err(ctx, Q3T_ERR_ARG, "Embedding token ID out of range");
+    cudaSetDevice(ctx->device);
+    int rc;
+    if ((rc = ensure_buf_i(ctx, &ctx->d_tokens, &ctx->tokens_cap, n_tokens + 8))) return rc;
+    int trailing_rows = std::max(0, n_tokens - 9) + 1;
+    int tcap = ctx->trailing_cap / H;
+    if (tcap < trailing_rows) {
+        int capf = ctx->trailing_cap;
+        if ((rc = ensure_buf_f(ctx, &ctx->d_trailing, &capf, (trailing_rows + 16) * H))) return rc;
+        ctx->trailing_cap = capf;
+    }
+    CK(cudaMemcpyAsync(ctx->d_tokens, text_tokens, (size_t) n_tokens * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (speaker_embd) CK(cudaMemcpyAsync(ctx->d_spk, speaker_embd, H * 4, cudaMemcpyHostToDevice, ctx->stream));
+    int pl = 0, tl = 0;
+    if ((rc = prompt_build(ctx, ctx->d_tokens, n_tokens, speaker_embd ? ctx->d_spk : nullptr, language_id,
+                           ctx->d_prefill, &pl, ctx->d_trailing, &tl, ctx->d_pad))) return rc;
+    ctx->staged_prefill_len = pl; ctx->staged_trailing_len = tl;
+    ctx->hm.trailing = ctx->d_trailing; ctx->hm.pad_embed = ctx->d_pad;
+    return Q3T_OK;
+}
+
+extern "C" int q3t_build_prompt(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd,
+                                int32_t language_id, float * prefill_out, int32_t * prefill_len,
+                                float * trailing_out, int32_t * trailing_len, float * pad_out) {
+    int rc = q3t_stage_prompt(ctx, text_tokens, n_tokens, speaker_embd, language_id);
+    if (rc) return rc;
+    if (prefill_len) *prefill_len = ctx->staged_prefill_len;
+    if (trailing_len) *trailing_len = ctx->staged_trailing_len;
+    if (prefill_out) CK(cudaMemcpyAsync(prefill_out, ctx->d_prefill, (size_t) ctx->staged_prefill_len * H * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (trailing_out) CK(cudaMemcpyAsync(trailing_out, ctx->d_trailing, (size_t) ctx->staged_trailing_len * H * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (pad_out) CK(cudaMemcpyAsync(pad_out, ctx->d_pad, H * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return Q3T_OK;
+}
+
+extern "C" int q3t_project_text(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_tokens, float * out) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (n_tokens <= 0) return Q3T_OK;
+    if (!text_tokens || !out) return set_err(ctx, Q3T_ERR_ARG, "text_tokens is null");
+    for (int i = 0; i < n_tokens; ++i)
+        if (text_tokens[i] < 0 || text_tokens[i] >= ctx->cfg.text_vocab_size) return set_err(ctx, Q3T_ERR_ARG, "Embedding token ID out of range");
+    cudaSetDevice(ctx->device);
+    int rc;
+    if ((rc = ensure_buf_i(ctx, &ctx->d_tokens, &ctx->tokens_cap, n_tokens + 8))) return rc;
+    float * d_out = nullptr;
+    CK(cudaMalloc(&d_out, (size_t) n_tokens * H * 4));
+    rc = cuda_check(ctx, cudaMemcpyAsync(ctx->d_tokens, text_tokens, (size_t) n_tokens * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D");
+    if (!rc) rc = prompt_project(ctx, ctx->d_tokens, n_tokens, d_out);
+    if (!rc) rc = cuda_check(ctx, cudaMemcpyAsync(out, d_out, (size_t) n_tokens * H * 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H");
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_out);
+    return rc;
+}
+
+extern "C" int q3t_codec_embed(q3t_ctx * ctx, const int32_t * ids, int32_t n, float * out) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (n <= 0) return Q3T_OK;
+    if (!ids || !out) return set_err(ctx, Q3T_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->device);
+    std::vector<__half> row(H);
+    for (int i = 0; i < n; ++i) {
+        if (ids[i] < 0 || ids[i] >= ctx->cfg.codec_vocab_size) return set_err(ctx, Q3T_ERR_ARG, "Embedding token ID out of range");
+        CK(cudaMemcpyAsync(row.data(), ctx->hm.codec_embd + (size_t) ids[i] * H, H * 2, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        for (int k = 0; k < H; ++k) out[(size_t) i * H + k] = __half2float(row[k]);
+    }
+    return Q3T_OK;
+}
+
+// ------------------------------------------------------------------------------ generate
+static int run_generate(q3t_ctx * ctx, int max_len, float rep_penalty, float temperature, int top_k, uint64_t seed,
+                        int * n_frames_out) {
+    const q3t_tts_config & c = ctx->cfg;
+    const int M = ctx->staged_prefill_len;
+    if (M <= 0) return set_err(ctx, Q3T_ERR_STATE, "no prompt staged");
+    int rc;
+    // KV sizing rule of the reference (src/tts_transformer.cpp:2630-2636)
+    const int required_ctx = M + max_len + 8;
+    if (ctx->n_ctx < required_ctx || ctx->n_ctx > std::max(required_ctx * 2, 512))
+        if ((rc = q3t_kv_init(ctx, required_ctx))) return rc;
+    if ((rc = ensure_buf_i(ctx, &ctx->d_codes, &ctx->codes_cap, max_len * NCB))) return rc;
+    ctx->hm.codes_out = ctx->d_codes;
+
+    GenState st = default_state(ctx);
+    st.max_len = max_len; st.n_past = M; st.trailing_len = ctx->staged_trailing_len;
+    st.rep_penalty = rep_penalty; st.temperature = temperature; st.top_k = top_k; st.seed = seed;
+    if ((rc = reset_state(ctx, st, true))) return rc;
+
+    cudaEventRecord(ctx->ev[0], ctx->stream);
+    // prefill: M causal single-token talker passes in one launch; only the last needs the head
+    if ((rc = run_talker_rows(ctx, ctx->d_prefill, M, 0, false, 1, nullptr))) return rc;
+    cudaEventRecord(ctx->ev[1], ctx->stream);
+
+    // frame program: 16 code-predictor passes + the talker step (src/tts_transformer.cpp:2664-2804)
+    std::vector<PassDesc> v;
+    append_codepred(ctx, v, XM_HIDDEN, nullptr);
+    v.push_back(make_pass(0, XM_TALKER_NEXT, 0, -1, 0, 0, c.n_layers, 1));
+    if ((rc = upload_passes(ctx, v))) return rc;
+
+    // enqueue frames in batches; poll `done` one batch behind so the GPU never idles on the host
+    const int BATCH = 32;
+    int * h_done = nullptr;
+    CK(cudaMallocHost(&h_done, 2 * sizeof(int)));
+    h_done[0] = h_done[1] = 0;
+    cudaEvent_t evs[2];
+    cudaEventCreateWithFlags(&evs[0], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&evs[1], cudaEventDisableTiming);
+    int launched = 0, batch = 0;
+    bool stop = false;
+    rc = Q3T_OK;
+    while (launched < max_len && !stop && !rc) {
+        const int n = std::min(BATCH, max_len - launched);
+        for (int i = 0; i < n && !rc; ++i) rc = lm_launch(ctx, ctx->d_passes, (int) v.size(), 1);
+        launched += n;
+        const int slot = batch & 1;
+        if (batch >= 1) {                          // wait for the previous batch's flag
+            cudaEventSynchronize(evs[slot ^ 1]);
+            if (h_done[slot ^ 1]) stop = true;
+        }
+        cudaMemcpyAsync(&h_done[slot], &ctx->hm.st->done, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+        cudaEventRecord(evs[slot], ctx->stream);
+        ++batch;
+    }
+    cudaEventRecord(ctx->ev[2], ctx->stream);
+    cudaEventDestroy(evs[0]); cudaEventDestroy(evs[1]);
+    GenState out;
+    if (!rc) rc = cuda_check(ctx, cudaMemcpyAsync(&out, ctx->hm.st, sizeof(GenState), cudaMemcpyDeviceToHost, ctx->stream), "D2H state");
+    if (!rc) rc = cuda_check(ctx, cudaStreamSynchronize(ctx->stream), "generate sync");
+    cudaFreeHost(h_done);
+    if (rc) return rc;
+    if (out.error) return set_err(ctx, Q3T_ERR_DEVICE, "device watchdog: a grid barrier timed out inside lm_kernel");
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->timing.prefill_ms = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); ctx->timing.frames_ms = ms;
+    ctx->timing.n_frames = out.frame;
+    ctx->last_n_frames = out.frame;
+    *n_frames_out = out.frame;
+    return Q3T_OK;
+}
+
+extern "C" int q3t_generate(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd,
+                            int32_t max_len, int32_t language_id, float repetition_penalty, float temperature,
+                            int32_t top_k, uint64_t seed, int32_t * codes_out, int32_t * n_frames_out) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (!text_tokens) return set_err(ctx, Q3T_ERR_ARG, "text_tokens is null");
+    if (n_tokens < 4) return set_err(ctx, Q3T_ERR_ARG, "Need at least 4 text tokens for generation");
+    if (n_frames_out) *n_frames_out = 0;
+    if (max_len <= 0) return Q3T_OK;                        // src/tts_transformer.cpp:2604-2607
+    int rc = q3t_stage_prompt(ctx, text_tokens, n_tokens, speaker_embd, language_id);
+    if (rc) return rc;
+    int nf = 0;
+    if ((rc = run_generate(ctx, max_len, repetition_penalty, temperature, top_k, seed, &nf))) return rc;
+    if (codes_out && nf > 0) {
+        CK(cudaMemcpyAsync(codes_out, ctx->d_codes, (size_t) nf * NCB * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    if (n_frames_out) *n_frames_out = nf;
+    return Q3T_OK;
+}
+
+extern "C" int q3t_run_staged(q3t_ctx * ctx, int32_t max_len, float repetition_penalty, float temperature, int32_t top_k,
+                              uint64_t seed, int32_t with_vocoder, int32_t * n_frames_out, int64_t * n_samples_out) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    cudaSetDevice(ctx->device);
+    int nf = 0;
+    int rc = run_generate(ctx, max_len, repetition_penalty, temperature, top_k, seed, &nf);
+    if (rc) return rc;
+    if (n_frames_out) *n_frames_out = nf;
+    if (n_samples_out) *n_samples_out = 0;
+    if (with_vocoder && nf > 0) {
+        if (!ctx->voc_ready) return set_err(ctx, Q3T_ERR_STATE, "vocoder not loaded");
+        cudaEventRecord(ctx->ev[2], ctx->stream);
+        float * smp = nullptr;
+        const int64_t ns = vocoder_run(ctx, ctx->d_codes, nf, &smp);
+        if (ns < 0) return (int) ns;
+        cudaEventRecord(ctx->ev[3], ctx->stream);
+        CK(cudaStreamSynchronize(ctx->stream));
+        float ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]); ctx->timing.vocoder_ms = ms;
+        ctx->last_n_samples = ns;
+        if (n_samples_out) *n_samples_out = ns;
+    }
+    return Q3T_OK;
+}
+
+extern "C" int q3t_fetch_codes(q3t_ctx * ctx, int32_t * codes_out, int32_t n_frames) {
+    if (!ctx || !codes_out) return Q3T_ERR_ARG;
+    if (n_frames > ctx->last_n_frames) return set_err(ctx, Q3T_ERR_ARG, "more frames requested than generated");
+    CK(cudaMemcpyAsync(codes_out, ctx->d_codes, (size_t) n_frames * NCB * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return Q3T_OK;
+}
+
+extern "C" int q3t_get_timing(q3t_ctx * ctx, q3t_timing * out) {
+    if (!ctx || !out) return Q3T_ERR_ARG;
+    *out = ctx->timing;
+    return Q3T_OK;
+}
+
+// mean device time of the talker decode step at a fixed position (roofline figure)
+extern "C" int q3t_bench_talker_step(q3t_ctx * ctx, int32_t n_past, int32_t iters, float * us_per_step) {
+    if (!ctx || !us_per_step || iters <= 0) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    cudaSetDevice(ctx->device);
+    int rc = ensure_ctx(ctx, n_past + 1, n_past + 1 + 16);
+    if (rc) return rc;
+    if ((rc = reset_state(ctx, default_state(ctx), false))) return rc;
+    std::vector<PassDesc> v;
+    PassDesc p = make_pass(0, XM_BUF, 0, n_past, 0, 0, ctx->cfg.n_layers, 0);
+    p.xsrc = ctx->d_tmp;
+    const int per_launch = std::min(iters, 16);
+    for (int i = 0; i < per_launch; ++i) v.push_back(p);
+    if ((rc = upload_passes(ctx, v))) return rc;
+    if ((rc = lm_launch(ctx, ctx->d_passes, per_launch, 0))) return rc;          // warm-up
+    const int launches = (iters + per_launch - 1) / per_launch;
+    cudaEventRecord(ctx->ev[0], ctx->stream);
+    for (int i = 0; i < launches; ++i) if ((rc = lm_launch(ctx, ctx->d_passes, per_launch, 0))) return rc;
+    cudaEventRecord(ctx->ev[1], ctx->stream);
+    CK(cudaStreamSynchronize(ctx->stream));
+    float ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+    *us_per_step = ms * 1000.0f / (float) (launches * per_launch);
+    return check_device_error(ctx);
+}

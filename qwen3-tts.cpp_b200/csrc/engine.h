@@ -1,0 +1,191 @@
+// Internal layout of the engine context shared by the CUDA translation units.
+// Nothing here is part of the public ABI (include/q3t.h).
+#pragma once
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/q3t.h"
+
+namespace q3t {
+
+// ------------------------------------------------------------------ device-visible structs
+
+// One decoder-layer stack (talker: 28 layers, code predictor: 5) in the private HBM layout:
+// all layers of one matrix kind are contiguous so a CTA's row slice of layer l is
+// base + l*layer_stride + row0*K.
+struct StackW {
+    int n_layers;
+    int wtype;                 // Q3T_TYPE_F16 or Q3T_TYPE_Q8_0 for the 7 big matrices
+    // F16 planes (or int8 quant planes when wtype == Q8_0); row-major [rows][K]
+    const void * wqkv;         // [L][4096][1024]   rows: q(2048) | k(1024) | v(1024)
+    const void * wo;           // [L][1024][2048]
+    const void * wgu;          // [L][6144][1024]   row 2i = gate_i, row 2i+1 = up_i
+    const void * wdown;        // [L][1024][3072]
+    // Q8_0 scale planes (half), [rows][K/32]
+    const __half * sqkv, * so, * sgu, * sdown;
+    const float * attn_norm;   // [L][1024]
+    const float * ffn_norm;    // [L][1024]
+    const float * q_norm;      // [L][128]
+    const float * k_norm;      // [L][128]
+    const float * out_norm;    // [1024]
+    __half * kcache;           // [L][8][n_ctx][128]
+    __half * vcache;
+    float  * kf32;             // [L][2][8][128]  F32 shadow of positions 0,1 (code-pred prefill numerics)
+    float  * vf32;
+    int n_ctx;
+};
+
+struct HeadW {                 // F16 [vocab][1024]
+    const __half * w;
+    int vocab;
+};
+
+enum XMode : int {
+    XM_BUF = 0,        // x = xsrc[0..1024) (float, device)
+    XM_HIDDEN,         // x = last talker hidden (normed); also selects cb0 from the talker head
+    XM_CB0_EMBD,       // x = f32(talker.codec_embd[cb0])
+    XM_CP_EMBD,        // x = f32(code_pred.codec_embd[arg-1][code[arg-1]]); code[arg-1] selected from previous head
+    XM_TALKER_NEXT,    // x = sum of the 16 code embeddings + trailing/pad row; selects code[14] first
+    XM_SELECT_ONLY     // no stack: only select the pending token (used to close a code-predictor run)
+};
+
+struct PassDesc {
+    int stack;         // 0 talker, 1 code predictor
+    int xmode;
+    int arg;           // code-predictor step for XM_CP_EMBD
+    int pos;           // position; <0 -> GenState::n_past
+    int f32attn;       // code-predictor prefill numerics (F32 K/V/Q/P)
+    int head;          // -1 none, 0 talker codec_head, 1..15 -> code_pred.lm_head[head-1]
+    int n_layers;      // layers to run (<= stack layers)
+    int process;       // 1: apply suppress / repetition penalty to the talker logits before select
+    const float * xsrc;
+    float * hidden_dst;   // optional extra copy of the normed hidden (device)
+    float * logits_dst;   // optional extra copy of the raw logits (device)
+};
+
+// Generation state living in HBM, updated by CTA 0, read by all CTAs at kernel entry.
+struct GenState {
+    int frame;             // frames emitted so far
+    int n_past;            // talker KV rows in use
+    int max_len;
+    int done;              // EOS seen or max_len reached
+    int trailing_len;
+    int eos_id, suppress_start, codec_vocab;
+    float rep_penalty, temperature;
+    int top_k;
+    int error;             // device watchdog
+    unsigned long long seed;
+    unsigned long long draw;       // sampler draw counter
+    unsigned long long bar_base;   // grid-barrier epoch base (see grid_barrier)
+    unsigned long long gbar_base[NKV > 0 ? 8 : 8];
+    int cur[16];           // codes of the frame being built
+    int pending;           // 1: a head result is waiting to be selected
+};
+
+struct DevModel {
+    StackW talker, cp;
+    HeadW  codec_head;
+    HeadW  cp_head[15];
+    const __half * codec_embd;       // [3072][1024]
+    const __half * cp_embd[15];      // [2048][1024]
+    const float * rope;              // [n_rope_pos][128]: cos[64] | sin[64]
+    int n_rope_pos;
+    float eps;
+    // activations / scratch (device)
+    float * xa, * xb;                // [1024] each
+    float * qkv;                     // [4096]
+    float * mbuf;                    // [3072]
+    float * hidden;                  // [1024]
+    float * logits;                  // [3072]
+    float * part_ms;                 // [8][MAXC][2][2]
+    float * part_o;                  // [8][MAXC][2][128]
+    float * cand_val; int * cand_idx;// [grid]
+    unsigned char * seen;            // [3072] repetition-penalty set
+    const float * trailing;          // [trailing_len][1024]
+    const float * pad_embed;         // [1024]
+    int * codes_out;                 // [max_len][16]
+    unsigned long long * bar;        // grid barrier counter
+    unsigned long long * gbar;       // [8] group barrier counters
+    GenState * st;
+};
+
+constexpr int LM_THREADS = 512;
+constexpr int LM_MAXC    = 18;       // max KV chunks per kv-head in the attention phase
+constexpr int LM_MIN_GRID = 128;
+
+} // namespace q3t
+
+// ------------------------------------------------------------------ host-side context
+
+struct q3t_host_tensor {
+    int32_t type;
+    int64_t ne[4];
+    void * dev;          // raw upload in GGUF layout
+    size_t nbytes;
+};
+
+struct q3t_vocoder;      // defined in vocoder.cu
+
+struct q3t_ctx {
+    int device = 0;
+    int sm_count = 0;
+    int cc_major = 0, cc_minor = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+
+    bool have_cfg = false;
+    q3t_tts_config cfg{};
+
+    std::map<std::string, q3t_host_tensor> raw;     // uploaded tensors by GGUF name
+    bool tts_ready = false;
+    bool voc_ready = false;
+
+    // talker / code predictor
+    q3t::DevModel hm{};               // host mirror of the device model struct
+    q3t::DevModel * dm = nullptr;     // device copy
+    std::vector<void *> owned;        // device allocations freed on unload(1)
+    int n_ctx = 0;
+    void * kv_alloc = nullptr;        // talker KV (k then v)
+    int grid = 0;
+    q3t::PassDesc * d_passes = nullptr;   // device program buffer
+    int passes_cap = 0;
+    float * d_prefill = nullptr;      // staged prompt rows [<=16][1024]
+    float * d_hidden_all = nullptr;   // [<=16+..][1024]
+    int staged_prefill_len = 0, staged_trailing_len = 0;
+    float * d_trailing = nullptr; int trailing_cap = 0;
+    float * d_pad = nullptr;
+    int * d_codes = nullptr; int codes_cap = 0;
+    int * d_tokens = nullptr; int tokens_cap = 0;
+    float * d_spk = nullptr;
+    float * d_tmp = nullptr; size_t tmp_cap = 0;   // misc staging
+    int64_t talker_bytes = 0, cp_bytes = 0, voc_bytes = 0;
+
+    // vocoder
+    q3t_vocoder * voc = nullptr;
+    float * d_samples = nullptr; int64_t samples_cap = 0; int64_t last_n_samples = 0;
+    int last_n_frames = 0;
+
+    q3t_timing timing{};
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+};
+
+// internal entry points implemented across the .cu files
+namespace q3t {
+int  set_err(q3t_ctx * ctx, int code, const std::string & msg);
+int  cuda_check(q3t_ctx * ctx, cudaError_t e, const char * what);
+int  lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int frame_mode);
+int  lm_max_grid(q3t_ctx * ctx);
+int  prompt_build(q3t_ctx * ctx, const int32_t * tokens_dev, int n_tokens, const float * spk_dev,
+                  int language_id, float * prefill_dev, int * prefill_len, float * trailing_dev,
+                  int * trailing_len, float * pad_dev);
+int  prompt_project(q3t_ctx * ctx, const int32_t * tokens_dev, int n_tokens, float * out_dev);
+int  vocoder_finalize(q3t_ctx * ctx);
+void vocoder_free(q3t_ctx * ctx);
+int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int n_frames, float ** samples_dev);
+}

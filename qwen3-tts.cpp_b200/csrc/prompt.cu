@@ -1,0 +1,181 @@
+// On-device prompt assembly: text-embedding gather, text-projection MLP and the prefill /
+// trailing row layout.  Replaces project_text_tokens, lookup_embedding_rows and the host
+// assembly in build_prefill_graph (src/tts_transformer.cpp:793-982, 984-1122), which the
+// reference runs as four tiny ggml graphs plus host memcpys per utterance.
+#include "common.cuh"
+#include "engine.h"
+
+#include <algorithm>
+
+namespace q3t {
+
+// rows of the F16 text embedding table -> contiguous F16 matrix [T][K]
+__global__ void gather_rows_h(const __half * __restrict__ table, const int * __restrict__ ids, int K, __half * __restrict__ out) {
+    const int r = blockIdx.x;
+    const uint4 * src = reinterpret_cast<const uint4 *>(table + (size_t) ids[r] * K);
+    uint4 * dst = reinterpret_cast<uint4 *>(out + (size_t) r * K);
+    for (int i = threadIdx.x; i < K / 8; i += blockDim.x) dst[i] = src[i];
+}
+
+// out[t][n] = act( W[n][:] . X[t][:] + bias[n] );  W, X F16 (X already F16-rounded = the oracle's
+// from_float before an F16 mat-mul), F32 accumulate.  One warp per output row, 8 tokens per sweep
+// so the weight row is streamed once per 8 tokens.  SILU=1 applies x/(1+exp(-x)) and stores the
+// result rounded to F16 (it is the next mat-mul's input); SILU=0 stores F32.
+template <int SILU>
+__global__ void __launch_bounds__(256)
+proj_rows(const __half * __restrict__ W, const __half * __restrict__ X, const float * __restrict__ bias,
+          int N, int K, int T, float * __restrict__ out_f, __half * __restrict__ out_h) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n = blockIdx.x * 8 + warp;
+    if (n >= N) return;
+    const uint4 * wrow = reinterpret_cast<const uint4 *>(W + (size_t) n * K);
+    for (int t0 = 0; t0 < T; t0 += 8) {
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        for (int i = lane; i < K / 8; i += 32) {
+            const uint4 wv = ld_weight(wrow + i);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (t0 + j < T) {
+                    const uint4 xv = *(reinterpret_cast<const uint4 *>(X + (size_t) (t0 + j) * K) + i);
+                    acc[j] = dot8_hh(wv, xv, acc[j]);
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float v = warp_sum(acc[j]);
+            if (lane == 0 && t0 + j < T) {
+                v += bias[n];
+                if (SILU) { v = v / (1.0f + expf(-v)); out_h[(size_t) (t0 + j) * N + n] = __float2half_rn(v); }
+                else out_f[(size_t) (t0 + j) * N + n] = v;
+            }
+        }
+    }
+}
+
+struct AsmArgs {
+    const float * proj;       // [7 + tc][H]: bos, eos, pad, role0..2, first_text, trailing...
+    const __half * codec_embd;
+    const float * spk;        // may be null
+    int codec_ids[6];         // prefill codec tokens then pad, bos
+    int n_codec_prefill;      // 3 or 4
+    int has_spk;
+    int prefill_len, trailing_len;
+    float * prefill, * trailing, * pad;
+};
+
+// one block per output row: prefill rows, then trailing rows, then the pad row
+__global__ void assemble_prompt(const AsmArgs a) {
+    const int row = blockIdx.x;
+    const int L = a.n_codec_prefill + a.has_spk + 2;            // codec_input_len
+    for (int h = threadIdx.x; h < H; h += blockDim.x) {
+        auto codec_in = [&](int t) -> float {                   // codec_input_embedding[t][h]
+            if (t < a.n_codec_prefill) return __half2float(a.codec_embd[(size_t) a.codec_ids[t] * H + h]);
+            if (a.has_spk && t == a.n_codec_prefill) return a.spk[h];
+            const int k = t - a.n_codec_prefill - a.has_spk;    // 0: codec_pad, 1: codec_bos
+            return __half2float(a.codec_embd[(size_t) a.codec_ids[a.n_codec_prefill + k] * H + h]);
+        };
+        if (row < a.prefill_len) {
+            float v;
+            if (row < 3) v = a.proj[(size_t) (3 + row) * H + h];                       // role tokens
+            else if (row < a.prefill_len - 1) {
+                const int t = row - 3;                                                 // overlay rows
+                const float ov = (t == L - 2) ? a.proj[0 * H + h] : a.proj[2 * H + h]; // tts_bos : tts_pad
+                v = ov + codec_in(t);
+            } else v = a.proj[(size_t) 6 * H + h] + codec_in(L - 1);                   // first text + codec_bos
+            a.prefill[(size_t) row * H + h] = v;
+        } else if (row < a.prefill_len + a.trailing_len) {
+            const int t = row - a.prefill_len;
+            a.trailing[(size_t) t * H + h] = (t == a.trailing_len - 1) ? a.proj[1 * H + h]      // tts_eos
+                                                                       : a.proj[(size_t) (7 + t) * H + h];
+        } else {
+            a.pad[h] = a.proj[2 * H + h];
+        }
+    }
+}
+
+__global__ void fill_ids(int * dst, const int * __restrict__ tokens, int n_tokens, int bos, int eos, int pad, int tc) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) dst[0] = bos;
+    if (i == 1) dst[1] = eos;
+    if (i == 2) dst[2] = pad;
+    if (i >= 3 && i < 7) dst[i] = tokens[i - 3];
+    if (i >= 7 && i < 7 + tc) dst[i] = tokens[4 + (i - 7)];
+}
+
+static int project_ids(q3t_ctx * ctx, const int * ids_dev, int T, float * out_dev) {
+    const q3t_tts_config & c = ctx->cfg;
+    const int K = c.text_embd_dim;
+    auto get = [&](const char * n) -> const q3t_host_tensor * {
+        auto it = ctx->raw.find(n);
+        return it == ctx->raw.end() ? nullptr : &it->second;
+    };
+    const q3t_host_tensor * emb = get("talker.text_embd.weight");
+    const q3t_host_tensor * w1 = get("talker.text_proj.fc1.weight"), * b1 = get("talker.text_proj.fc1.bias");
+    const q3t_host_tensor * w2 = get("talker.text_proj.fc2.weight"), * b2 = get("talker.text_proj.fc2.bias");
+    if (!emb || !w1 || !b1 || !w2 || !b2) return set_err(ctx, Q3T_ERR_FORMAT, "missing text embedding / projection tensors");
+    if (emb->type != Q3T_TYPE_F16 || w1->type != Q3T_TYPE_F16 || w2->type != Q3T_TYPE_F16)
+        return set_err(ctx, Q3T_ERR_FORMAT, "text projection: only F16 weights are wired up in this build");
+    if (K % 8 != 0 || emb->ne[0] != K || w1->ne[0] != K || w1->ne[1] != K || w2->ne[0] != K || w2->ne[1] != H)
+        return set_err(ctx, Q3T_ERR_FORMAT, "unexpected text projection shapes");
+    __half * xh = nullptr, * hh = nullptr;
+    int rc = cuda_check(ctx, cudaMalloc(&xh, (size_t) T * K * 2), "cudaMalloc");
+    if (rc) return rc;
+    rc = cuda_check(ctx, cudaMalloc(&hh, (size_t) T * K * 2), "cudaMalloc");
+    if (rc) { cudaFree(xh); return rc; }
+    gather_rows_h<<<T, 128, 0, ctx->stream>>>((const __half *) emb->dev, ids_dev, K, xh);
+    proj_rows<1><<<(K + 7) / 8, 256, 0, ctx->stream>>>((const __half *) w1->dev, xh, (const float *) b1->dev, K, K, T, nullptr, hh);
+    proj_rows<0><<<(H + 7) / 8, 256, 0, ctx->stream>>>((const __half *) w2->dev, hh, (const float *) b2->dev, H, K, T, out_dev, nullptr);
+    ctx->timing.kernel_launches += 3;
+    rc = cuda_check(ctx, cudaGetLastError(), "text projection launch");
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(xh); cudaFree(hh);
+    return rc;
+}
+
+int prompt_project(q3t_ctx * ctx, const int32_t * tokens_dev, int n_tokens, float * out_dev) {
+    return project_ids(ctx, tokens_dev, n_tokens, out_dev);
+}
+
+int prompt_build(q3t_ctx * ctx, const int32_t * tokens_dev, int n_tokens, const float * spk_dev, int language_id,
+                 float * prefill_dev, int * prefill_len, float * trailing_dev, int * trailing_len, float * pad_dev) {
+    const q3t_tts_config & c = ctx->cfg;
+    const int tc = std::max(0, n_tokens - 9);                   // trailing_token_count (:1105)
+    const int T = 7 + tc;
+    int * ids = nullptr; float * proj = nullptr;
+    int rc = cuda_check(ctx, cudaMalloc(&ids, (size_t) T * 4), "cudaMalloc");
+    if (rc) return rc;
+    rc = cuda_check(ctx, cudaMalloc(&proj, (size_t) T * H * 4), "cudaMalloc");
+    if (rc) { cudaFree(ids); return rc; }
+    fill_ids<<<(T + 127) / 128, 128, 0, ctx->stream>>>(ids, tokens_dev, n_tokens, c.tts_bos_token_id, c.tts_eos_token_id,
+                                                       c.tts_pad_token_id, tc);
+    rc = project_ids(ctx, ids, T, proj);
+    if (!rc) {
+        AsmArgs a{};
+        a.proj = proj; a.codec_embd = ctx->hm.codec_embd; a.spk = spk_dev; a.has_spk = spk_dev ? 1 : 0;
+        if (language_id < 0) {
+            a.n_codec_prefill = 3;
+            a.codec_ids[0] = c.codec_nothink_id; a.codec_ids[1] = c.codec_think_bos_id; a.codec_ids[2] = c.codec_think_eos_id;
+        } else {
+            a.n_codec_prefill = 4;
+            a.codec_ids[0] = c.codec_think_id; a.codec_ids[1] = c.codec_think_bos_id;
+            a.codec_ids[2] = language_id;      a.codec_ids[3] = c.codec_think_eos_id;
+        }
+        a.codec_ids[a.n_codec_prefill] = c.codec_pad_id; a.codec_ids[a.n_codec_prefill + 1] = c.codec_bos_id;
+        const int L = a.n_codec_prefill + a.has_spk + 2;
+        a.prefill_len = 3 + (L - 1) + 1;
+        a.trailing_len = tc + 1;
+        a.prefill = prefill_dev; a.trailing = trailing_dev; a.pad = pad_dev;
+        assemble_prompt<<<a.prefill_len + a.trailing_len + 1, 256, 0, ctx->stream>>>(a);
+        ctx->timing.kernel_launches += 2;
+        rc = cuda_check(ctx, cudaGetLastError(), "assemble_prompt launch");
+        *prefill_len = a.prefill_len; *trailing_len = a.trailing_len;
+    }
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(ids); cudaFree(proj);
+    return rc;
+}
+
+} // namespace q3t

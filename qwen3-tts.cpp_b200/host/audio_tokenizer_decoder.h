@@ -1,0 +1,52 @@
+// qwen3_tts::AudioTokenizerDecoder with the reference's public interface
+// (src/audio_tokenizer_decoder.h:15-29,159-179) on the B200 engine.
+#pragma once
+
+#include "../../include/q3t.h"
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace qwen3_tts {
+
+struct audio_decoder_config {                 // src/audio_tokenizer_decoder.h:15-29
+    int32_t sample_rate = 24000;
+    int32_t n_codebooks = 16;
+    int32_t codebook_size = 2048;
+    int32_t codebook_dim = 256;
+    int32_t latent_dim = 1024;
+    int32_t hidden_dim = 512;
+    int32_t n_pre_tfm_layers = 8;
+    int32_t n_heads = 16;
+    int32_t ffn_dim = 1024;
+    int32_t decoder_dim = 1536;
+    int32_t upsample_rates[4] = {8, 5, 4, 3};
+    float rms_norm_eps = 1e-5f;
+    float rope_theta = 10000.0f;
+};
+
+class AudioTokenizerDecoder {
+public:
+    AudioTokenizerDecoder();
+    ~AudioTokenizerDecoder();
+
+    bool load_model(const std::string & model_path);
+    void unload_model();
+
+    // codes: [n_frames, n_codebooks] row-major -> samples in [-1,1] at 24 kHz (1920*n_frames-555 of them)
+    bool decode(const int32_t * codes, int32_t n_frames, std::vector<float> & samples);
+
+    const audio_decoder_config & get_config() const { return config_; }
+    const std::string & get_error() const { return error_msg_; }
+
+    q3t_ctx * engine() const { return engine_; }      // extension
+
+private:
+    audio_decoder_config config_;
+    q3t_ctx * engine_ = nullptr;
+    bool loaded_ = false;
+    std::string error_msg_;
+};
+
+} // namespace qwen3_tts
