@@ -170,3 +170,50 @@ int ref_enc_embed(const char * model_path, const float * samples, int32_t n_samp
 }
 
 } // extern "C"
+
+// ---------------- debug: per-node trace of one talker step (bisecting numerics) ----------------
+#include "ggml-backend.h"
+struct trace_rec { std::string name; std::string op; int64_t ne[4]; int type; std::vector<float> data; };
+static std::vector<trace_rec> g_trace;
+
+static bool trace_cb(struct ggml_tensor * t, bool ask, void *) {
+    if (ask) return true;
+    trace_rec r;
+    r.name = t->name; r.op = ggml_op_name(t->op); r.type = (int) t->type;
+    for (int i = 0; i < 4; ++i) r.ne[i] = t->ne[i];
+    const int64_t n = ggml_nelements(t);
+    if (ggml_is_contiguous(t) && n <= (1 << 22)) {
+        r.data.resize((size_t) n);
+        if (t->type == GGML_TYPE_F32) memcpy(r.data.data(), t->data, (size_t) n * 4);
+        else if (t->type == GGML_TYPE_F16) { const ggml_fp16_t * h = (const ggml_fp16_t *) t->data; for (int64_t i = 0; i < n; ++i) r.data[(size_t) i] = ggml_fp16_to_fp32(h[i]); }
+        else r.data.clear();
+    }
+    g_trace.push_back(std::move(r));
+    return true;
+}
+
+extern "C" {
+int ref_tts_trace_step(void * h, const float * embd, int32_t n_past) {
+    auto * t = (TTSTransformer *) h;
+    g_trace.clear();
+    ggml_backend_sched_set_eval_callback(t->state_.sched, trace_cb, nullptr);
+    std::vector<float> logits, hid;
+    bool ok = t->forward_step(embd, n_past, logits, &hid);
+    ggml_backend_sched_set_eval_callback(t->state_.sched, nullptr, nullptr);
+    if (!ok) { g_err = t->get_error(); return -1; }
+    return (int) g_trace.size();
+}
+int ref_trace_info(int i, char * name, char * op, int64_t * ne, int * type, long * n) {
+    if (i < 0 || i >= (int) g_trace.size()) return -1;
+    strncpy(name, g_trace[i].name.c_str(), 63); name[63] = 0;
+    strncpy(op, g_trace[i].op.c_str(), 31); op[31] = 0;
+    for (int k = 0; k < 4; ++k) ne[k] = g_trace[i].ne[k];
+    *type = g_trace[i].type; *n = (long) g_trace[i].data.size();
+    return 0;
+}
+int ref_trace_data(int i, float * out) {
+    if (i < 0 || i >= (int) g_trace.size()) return -1;
+    memcpy(out, g_trace[i].data.data(), g_trace[i].data.size() * 4);
+    return 0;
+}
+}
