@@ -90,4 +90,40 @@ __device__ __forceinline__ float dot8_hf(const uint4 & w, const float4 & x0, con
     return acc;
 }
 
+// ------------------------------------------------------------------------------- exact math
+// ggml_v_expf, AVX2+FMA variant, one lane (ggml/src/ggml-cpu/vec.h:1230-1267)
+__device__ __forceinline__ float v_expf(float x) {
+    const float r = 0x1.8p23f;
+    const float z = __fmaf_rn(x, 0x1.715476p+0f, r);
+    const float n = __fsub_rn(z, r);
+    const float b = __fmaf_rn(-n, 0x1.7f7d1cp-20f, __fmaf_rn(-n, 0x1.62e4p-1f, x));
+    const unsigned e = __float_as_uint(z) << 23;
+    const float k = __uint_as_float(e + 0x3f800000u);
+    const float u = __fmul_rn(b, b);
+    const float j = __fmaf_rn(__fmaf_rn(__fmaf_rn(0x1.0e4020p-7f, b, 0x1.573e2ep-5f), u,
+                                        __fmaf_rn(0x1.555e66p-3f, b, 0x1.fffdb6p-2f)),
+                              u, __fmul_rn(0x1.ffffecp-1f, b));
+    if (!(fabsf(n) > 126.0f)) return __fmaf_rn(j, k, k);
+    const unsigned g = (n <= 0.0f) ? 0x82000000u : 0u;
+    const float s1 = __uint_as_float(g + 0x7f000000u);
+    const float s2 = __uint_as_float(e - g);
+    if (fabsf(n) > 192.0f) return __fmul_rn(s1, s1);
+    return __fmul_rn(__fmaf_rn(s2, j, s2), s1);
+}
+// scalar tail of the SIMD loops calls libm expf (vec.cpp:611-615); glibc's expf is correctly
+// rounded in all but ~1e-3 of cases, so round-to-float of a double exp matches it
+__device__ __forceinline__ float tail_expf(float x) { return (float) exp((double) x); }
+
+// the oracle's horizontal reduction of the 32 accumulator lanes, lane = k%32
+// ((s0+s2)+(s1+s3) per AVX lane -> lane l + lane l+4 -> hadd, hadd)
+__device__ __forceinline__ float reduce32_lanes(float v) {
+    v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, 16));
+    v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, 8));
+    v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, 4));
+    v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, 1));
+    v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, 2));
+    return v;
+}
+
+
 } // namespace q3t

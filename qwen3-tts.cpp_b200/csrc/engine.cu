@@ -299,7 +299,8 @@ static int finalize_tts(q3t_ctx * ctx) {
     if ((rc = dev_alloc(ctx, &m.hidden, H, true))) return rc;
     if ((rc = dev_alloc(ctx, &m.logits, 3072, true))) return rc;
     if ((rc = dev_alloc(ctx, &m.part_ms, NKV * LM_MAXC * 4, true))) return rc;
-    if ((rc = dev_alloc(ctx, &m.part_o, (size_t) NKV * LM_MAXC * 2 * HD, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.part_o, (size_t) NH * HD, true))) return rc;
+    if ((rc = dev_alloc(ctx, &m.sbuf, (size_t) NH * LM_ATT_MAX_KV, true))) return rc;
     if ((rc = dev_alloc(ctx, &m.cand_val, 512, true))) return rc;
     if ((rc = dev_alloc(ctx, &m.cand_idx, 512, true))) return rc;
     if ((rc = dev_alloc(ctx, &m.seen, 4096, true))) return rc;
@@ -343,7 +344,7 @@ extern "C" int q3t_kv_init(q3t_ctx * ctx, int32_t n_ctx) {
     if (!ctx) return Q3T_ERR_ARG;
     if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
     if (n_ctx <= 0) return set_err(ctx, Q3T_ERR_ARG, "n_ctx must be > 0");
-    if (n_ctx > LM_MAXC * 1024) return set_err(ctx, Q3T_ERR_ARG, "n_ctx exceeds the attention kernel's limit (18432)");
+    if (n_ctx > LM_ATT_MAX_KV) return set_err(ctx, Q3T_ERR_ARG, "n_ctx exceeds the attention kernel's limit (4608)");
     cudaSetDevice(ctx->device);
     CK(cudaStreamSynchronize(ctx->stream));
     if (ctx->kv_alloc) { cudaFree(ctx->kv_alloc); ctx->kv_alloc = nullptr; ctx->n_ctx = 0; }

@@ -103,8 +103,9 @@ struct DevModel {
     float * mbuf;                    // [3072]
     float * hidden;                  // [1024]
     float * logits;                  // [3072]
-    float * part_ms;                 // [8][MAXC][2][2]
-    float * part_o;                  // [8][MAXC][2][128]
+    float * part_ms;                 // [8][16][2]  per-split score maxima
+    float * part_o;                  // [16][128]   attention output of the layer
+    float * sbuf;                    // [16][LM_ATT_MAX_KV] attention scores
     float * cand_val; int * cand_idx;// [grid]
     unsigned char * seen;            // [3072] repetition-penalty set
     const float * trailing;          // [trailing_len][1024]
@@ -117,7 +118,8 @@ struct DevModel {
 
 constexpr int LM_THREADS = 512;
 constexpr int LM_MAXC    = 18;       // max KV chunks per kv-head in the attention phase
-constexpr int LM_MIN_GRID = 128;
+constexpr int LM_MIN_GRID = 140;
+constexpr int LM_ATT_MAX_KV = 4608;  // KV positions the attention phase supports (P kept in shared memory)
 
 } // namespace q3t
 

@@ -9,51 +9,60 @@
 //     passes (a pass = one token through one layer stack + optional head): a frame is
 //     16 code-predictor passes + 1 talker pass, a prefill is M talker passes.
 //   * Batch-1 decode is HBM/latency bound, so the weight stream is decoupled from the
-//     dependency chain: one thread per CTA issues TMA-unit bulk L2 prefetches
-//     (cp.async.bulk.prefetch.L2) one layer ahead, and every thread pulls its 16-byte slices
-//     of the NEXT phase's weight rows into registers *before* waiting on the grid barrier, so
-//     the barrier latency is covered by loads in flight.
+//     dependency chain in two stages: one thread per CTA issues TMA-unit bulk L2 prefetches
+//     (cp.async.bulk.prefetch.L2) one layer ahead, and a producer warp issues TMA bulk copies
+//     (cp.async.bulk global->shared, mbarrier complete_tx) of the CTA's weight-row slice of the
+//     phase after next into one of two shared-memory buffers *before* the grid barrier, so
+//     barrier latency is covered by copies in flight and the compute reads only shared memory.
 //   * Every phase boundary is an all-to-all dependency (GEMV output -> next GEMV input); it is
-//     implemented as a release/acquire counter barrier in global memory (one red.release +
-//     one polling thread per CTA), not a kernel boundary.
-//   * All rounding points of the oracle are reproduced: activations
-//     are rounded to F16 before F16 mat-vecs, ffn_down runs on F32 activations, K/V are stored
-//     F16, P is rounded to F16 after a *global* softmax normalisation, RMSNorm sums in double,
-//     RoPE uses a host table built with the oracle's recurrence.
+//     a release/acquire counter barrier in global memory, not a kernel boundary.
+//   * BIT-EXACT with the oracle: F16 rounding points amplify any F32 re-association noise into
+//     ~1e-3 logit differences, enough to flip greedy tokens of a random-init model within a few
+//     hundred steps.  So every dot product is accumulated in the order of ggml-cpu's AVX2+FMA
+//     build (32 accumulator lanes k%32, FMA chain over k/32, fixed reduction tree;
+//     ggml/src/ggml-cpu/vec.cpp:265-390, simd-mappings.h:549-567), exp() is the same
+//     polynomial (vec.h:1230-1267), soft-max sums follow the 8-lane pattern (vec.cpp:558-568).
+//     oracle/q3t_oracle.c is the executable statement of these rules.
 #include "common.cuh"
 #include "engine.h"
 
-#include <cooperative_groups.h>
 #include <math_constants.h>
 
 namespace q3t {
 
-constexpr int MAXV   = 12;     // 16-byte weight vectors a thread may hold for one phase
-constexpr int MAXU   = MAXV * 4;
-constexpr int SC_MAX = 1024;   // max KV positions per attention chunk
+// ------------------------------------------------------------------------------- shared memory
+constexpr int PAD_B      = 64;                         // row pitch = K*2 + 64 B: conflict-free 64-bit/32-bit row-parallel reads
+constexpr int PITCH_1K   = 1024 * 2 + PAD_B;           // 2112
+constexpr int PITCH_2K   = 2048 * 2 + PAD_B;           // 4160
+constexpr int PITCH_3K   = 3072 * 2 + PAD_B;           // 6208
+constexpr int MAXR_GU    = 44;                         // gate/up rows per CTA   (grid >= 140)
+constexpr int MAXR_H     = 8;                          // rows of a 1024-row matrix per CTA
+constexpr int BUF0_BYTES = MAXR_GU * PITCH_1K;         // qkv / gate-up / head slices     92,928 B
+constexpr int BUF1_BYTES = MAXR_H * PITCH_3K;          // attn_output / ffn_down slices   49,664 B
+constexpr int ATT_MAX_KV = LM_ATT_MAX_KV;              // positions the attention phase can hold (P in F16)
+constexpr int VT_HALVES  = 8192;                       // V^T tile: nd dims x TB positions
 
-struct __align__(16) Smem {
-    float  xres[H];            // residual stream of the current token (x, then x1)
-    float  xin_f[FFN];         // F32 GEMV input (ffn_down) / scratch
-    __half xin_h[FFN];         // F16-rounded GEMV input
-    float  red[MAXU * 4];      // per-unit warp partials
-    float  outv[MAXU];         // finalised row values of the phase
+struct __align__(128) Smem {
+    unsigned char buf0[BUF0_BYTES];
+    unsigned char buf1[BUF1_BYTES];
+    float  xres[H];                // residual stream of the current token (x, then x1)
+    float  xf[FFN];                // GEMV input as F32 (already F16-rounded where the oracle rounds)
+    float  outv[64];               // finalised row values of the phase
     // attention
-    __half qh[2][HD];          // normed+roped q of the two heads of this kv group (F16-rounded)
-    float  qf[2][HD];          // same, unrounded (F32-attention mode)
-    __half knew_h[HD], vnew_h[HD];
+    float  qf[2][HD];              // normed+roped q of the two heads of this kv group (F32)
+    float  qr[2][HD];              // same, F16-rounded, as float
     float  knew_f[HD], vnew_f[HD];
-    float  sc[2][SC_MAX];      // scores of this CTA's chunk
-    float  red_o[16][2][HD];   // per-warp partial outputs
-    float  wred[2][16][2];     // per-warp (max,sum) for both heads
-    float  gms[2][2];          // global (max, inv_sum)
-    double dred[16];
+    __half knew_h[HD], vnew_h[HD];
+    __half ph[2][ATT_MAX_KV];      // soft-max probabilities rounded to F16 (oracle D.4)
+    __half vt[VT_HALVES];          // V^T tile [dim][position]
+    double dred[2][16];
     float  fred[32];
     int    ired[32];
     int    tok;
+    unsigned long long mbar[2];    // TMA completion barriers of buf0 / buf1
 };
 
-// --------------------------------------------------------------------------- barriers
+// ------------------------------------------------------------------------------- grid barriers
 struct BarState {
     unsigned long long target;       // grid barrier epoch target
     unsigned long long gtarget;      // group barrier target of this CTA's kv group
@@ -85,7 +94,7 @@ __device__ __forceinline__ void grid_barrier(const DevModel & m, BarState & bs) 
     __syncthreads();
 }
 
-// barrier among the `n` CTAs that share kv group g (attention softmax statistics exchange)
+// barrier among the `n` CTAs that share kv group g (attention soft-max statistics exchange)
 __device__ __forceinline__ void group_barrier(const DevModel & m, BarState & bs, int g, int n, bool participate) {
     bs.gtarget += (unsigned long long) n;
     if (!participate) return;
@@ -98,92 +107,147 @@ __device__ __forceinline__ void group_barrier(const DevModel & m, BarState & bs,
     __syncthreads();
 }
 
-// --------------------------------------------------------------------------- row slices
+// ------------------------------------------------------------------------------- TMA weight stream
+__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long * bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long * bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long * bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "W_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra D_%=;\n\t"
+        "bra W_%=;\n\t"
+        "D_%=:\n\t}"
+        :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// TMA bulk copy global -> shared::cta, completion signalled on an mbarrier (bytes multiple of 16)
+__device__ __forceinline__ void tma_load_1d(void * dst_smem, const void * src_gmem, uint32_t bytes, unsigned long long * bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+struct WStream {                 // per-thread view of the two weight buffers
+    uint32_t parity[2];          // phase parity the next wait on buffer b must observe
+    bool     pending[2];         // a fetch into buffer b has been issued and not yet waited for
+};
+
+// Warp 0 stages `n_rows` rows of `row_bytes` (contiguous in HBM) into buffer `b` with the padded
+// pitch.  Must be called by all threads AFTER a __syncthreads that ends all reads of that buffer.
+__device__ __forceinline__ void issue_fetch(Smem & s, WStream & ws, int b, const void * src, int n_rows, int row_bytes) {
+    ws.pending[b] = true;
+    if (threadIdx.x < 32) {
+        unsigned char * dst = b == 0 ? s.buf0 : s.buf1;
+        const int pitch = row_bytes + PAD_B;
+        if (threadIdx.x == 0) mbar_expect_tx(&s.mbar[b], (uint32_t) (n_rows * row_bytes));
+        __syncwarp();
+        for (int r = threadIdx.x; r < n_rows; r += 32)
+            tma_load_1d(dst + (size_t) r * pitch, (const unsigned char *) src + (size_t) r * row_bytes, (uint32_t) row_bytes, &s.mbar[b]);
+    }
+}
+__device__ __forceinline__ void wait_fetch(Smem & s, WStream & ws, int b) {
+    mbar_wait(&s.mbar[b], ws.parity[b]);
+    ws.parity[b] ^= 1u;
+    ws.pending[b] = false;
+}
+
 __device__ __forceinline__ void cta_rows(int n_rows, int & r0, int & r1) {
     r0 = (int) (((long long) blockIdx.x * n_rows) / gridDim.x);
     r1 = (int) (((long long) (blockIdx.x + 1) * n_rows) / gridDim.x);
 }
 
-// A *unit* is 1024 consecutive weights of one row (128 threads x 8 halves). A row of
-// K = NSEG*1024 is NSEG consecutive units; a CTA's row slice is a contiguous unit range.
-__device__ __forceinline__ void prefetch_w(uint4 (&w)[MAXV], const __half * slice, int n_units) {
-    const int q = threadIdx.x >> 7, k = threadIdx.x & 127;
+// ------------------------------------------------------------------------------- ordered GEMV
+// rows of F16 weights in shared memory (pitch K*2+64) times the activation vector s.xf (F32 values;
+// already F16-rounded for the F16 mat-vecs, raw F32 for ffn_down).  A task = (row, group of ACC
+// accumulator lanes); each thread walks the k/32 chain with fused multiply-adds exactly like one
+// SIMD lane group of ggml_vec_dot_f16 / ggml_vec_dot_f32, then the lanes of a row are folded in
+// the oracle's order.  Result of row r lands in s.outv[r].
+template <int ACC, int K>
+__device__ __forceinline__ void gemv_chain(const unsigned char * __restrict__ wbuf, int n_rows, Smem & s) {
+    static_assert(ACC == 2 || ACC == 4, "ACC");
+    constexpr int LPR = 32 / ACC;                 // lanes per row
+    constexpr int PITCH = K * 2 + PAD_B;
+    const int task = threadIdx.x;
+    const int r = task / LPR, q = task % LPR;
+    float acc[ACC];
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-        const int u = i * 4 + q;
-        if (u < n_units) w[i] = ld_weight(slice + (size_t) u * 1024 + k * 8);
-    }
-}
-
-// F16 weights x F16-rounded activations (oracle D.1)
-template <int NSEG>
-__device__ __forceinline__ void gemv_units_h(const uint4 (&w)[MAXV], int n_units, Smem & s) {
-    const int q = threadIdx.x >> 7, k = threadIdx.x & 127, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-#pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-        const int u = i * 4 + q;
-        if (u < n_units) {
-            const int seg = u % NSEG;
-            const uint4 xv = *reinterpret_cast<const uint4 *>(s.xin_h + seg * 1024 + k * 8);
-            float p = dot8_hh(w[i], xv, 0.0f);
-            p = warp_sum(p);
-            if (lane == 0) s.red[u * 4 + (warp & 3)] = p;
+    for (int e = 0; e < ACC; ++e) acc[e] = 0.0f;
+    if (r < n_rows) {
+        const unsigned char * wrow = wbuf + (size_t) r * PITCH + q * ACC * 2;
+        const float * xp = s.xf + q * ACC;
+#pragma unroll 8
+        for (int c = 0; c < K / 32; ++c) {
+            if (ACC == 4) {
+                const uint2 wv = *reinterpret_cast<const uint2 *>(wrow + c * 64);
+                const float4 xv = *reinterpret_cast<const float4 *>(xp + c * 32);
+                const float2 w01 = __half22float2(*reinterpret_cast<const __half2 *>(&wv.x));
+                const float2 w23 = __half22float2(*reinterpret_cast<const __half2 *>(&wv.y));
+                acc[0] = __fmaf_rn(w01.x, xv.x, acc[0]);
+                acc[1] = __fmaf_rn(w01.y, xv.y, acc[1]);
+                acc[2] = __fmaf_rn(w23.x, xv.z, acc[2]);
+                acc[3] = __fmaf_rn(w23.y, xv.w, acc[3]);
+            } else {
+                const unsigned wv = *reinterpret_cast<const unsigned *>(wrow + c * 64);
+                const float2 xv = *reinterpret_cast<const float2 *>(xp + c * 32);
+                const float2 w01 = __half22float2(*reinterpret_cast<const __half2 *>(&wv));
+                acc[0] = __fmaf_rn(w01.x, xv.x, acc[0]);
+                acc[1] = __fmaf_rn(w01.y, xv.y, acc[1]);
+            }
         }
     }
-}
-
-// F16 weights (exact in F32) x F32 activations (oracle D.3: ffn_down)
-template <int NSEG>
-__device__ __forceinline__ void gemv_units_f(const uint4 (&w)[MAXV], int n_units, Smem & s) {
-    const int q = threadIdx.x >> 7, k = threadIdx.x & 127, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // fold: accumulator index a = q*ACC + e; oracle order flips a-bits 16, 8, 4, then 1, 2
+    float res;
+    if (ACC == 4) {
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-        const int u = i * 4 + q;
-        if (u < n_units) {
-            const int seg = u % NSEG;
-            const float4 * xp = reinterpret_cast<const float4 *>(s.xin_f + seg * 1024 + k * 8);
-            float p = dot8_hf(w[i], xp[0], xp[1], 0.0f);
-            p = warp_sum(p);
-            if (lane == 0) s.red[u * 4 + (warp & 3)] = p;
+        for (int e = 0; e < 4; ++e) {
+            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 4));
+            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 2));
+            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 1));
         }
-    }
-}
-
-// after __syncthreads: thread r < n_rows folds the NSEG*4 partials of row r in a fixed order
-template <int NSEG>
-__device__ __forceinline__ float fold_row(const Smem & s, int r) {
-    float v = 0.0f;
+        res = __fadd_rn(__fadd_rn(acc[0], acc[1]), __fadd_rn(acc[2], acc[3]));
+    } else {
 #pragma unroll
-    for (int j = 0; j < NSEG * 4; ++j) v += s.red[r * NSEG * 4 + j];
-    return v;
+        for (int e = 0; e < 2; ++e) {
+            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 8));
+            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 4));
+            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 2));
+        }
+        const float u = __fadd_rn(acc[0], acc[1]);
+        res = __fadd_rn(u, __shfl_xor_sync(0xffffffffu, u, 1));
+    }
+    if (r < n_rows && q == 0) s.outv[r] = res;
 }
 
-// --------------------------------------------------------------------------- RMSNorm
-// y = (x * rsqrt(mean(x^2)+eps)) * gamma, sum of squares in double (oracle D.5,
-// ggml/src/ggml-cpu/ops.cpp:3666-3691); result rounded to F16 into xin_h, optional F32 copy.
-__device__ __forceinline__ void rmsnorm_to_h(Smem & s, const float * __restrict__ gamma, float eps,
-                                             float * hidden_f32_out /* smem/global or null */) {
+// ------------------------------------------------------------------------------- RMSNorm
+// y = (x * rsqrt(mean(x^2)+eps)) * gamma; sum of squares in double (oracle D.5,
+// ggml/src/ggml-cpu/ops.cpp:3666-3691).  Writes float(r16(y)) to s.xf (the F16 mat-vec input)
+// and optionally the unrounded y (the `hidden_states` output).
+__device__ __forceinline__ void rmsnorm_to_xf(Smem & s, const float * __restrict__ gamma, float eps, float * y_out) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const float a = s.xres[t], b = s.xres[t + 512];
-    double sq = (double) (a * a) + (double) (b * b);
+    double sq = (double) __fmul_rn(a, a) + (double) __fmul_rn(b, b);
     sq = warp_sum_d(sq);
-    if (lane == 0) s.dred[warp] = sq;
+    if (lane == 0) s.dred[0][warp] = sq;
     __syncthreads();
     double tot = 0.0;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) tot += s.dred[i];
+    for (int i = 0; i < 16; ++i) tot += s.dred[0][i];
     const float mean  = (float) (tot / (double) H);
-    const float scale = 1.0f / sqrtf(mean + eps);
-    const float ya = (a * scale) * __ldg(gamma + t);
-    const float yb = (b * scale) * __ldg(gamma + t + 512);
-    s.xin_h[t]       = __float2half_rn(ya);
-    s.xin_h[t + 512] = __float2half_rn(yb);
-    if (hidden_f32_out) { hidden_f32_out[t] = ya; hidden_f32_out[t + 512] = yb; }
+    const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
+    const float ya = __fmul_rn(__fmul_rn(a, scale), __ldg(gamma + t));
+    const float yb = __fmul_rn(__fmul_rn(b, scale), __ldg(gamma + t + 512));
+    s.xf[t] = r16(ya); s.xf[t + 512] = r16(yb);
+    if (y_out) { y_out[t] = ya; y_out[t + 512] = yb; }
     __syncthreads();
 }
 
-// per-head RMSNorm(128) * gamma then NEOX RoPE, one warp; lane l owns dims {l, l+32, l+64, l+96}
-// (pairs (l,l+64) and (l+32,l+96)); rope row = cos[64] | sin[64] (oracle D.7).
+// per-head RMSNorm(128)*gamma then NEOX RoPE (unfused mul/sub like the oracle's build), one warp;
+// lane l owns dims {l, l+32, l+64, l+96}; rope row = cos[64] | sin[64] (oracle D.7)
 __device__ __forceinline__ void head_norm_rope(const float * __restrict__ raw, const float * __restrict__ gamma,
                                                const float * __restrict__ rope_row, float eps, bool do_norm,
                                                float (&out)[4]) {
@@ -194,36 +258,40 @@ __device__ __forceinline__ void head_norm_rope(const float * __restrict__ raw, c
     if (do_norm) {
         double sq = 0.0;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) sq += (double) (v[i] * v[i]);
+        for (int i = 0; i < 4; ++i) sq += (double) __fmul_rn(v[i], v[i]);
         sq = warp_sum_d(sq);
         const float mean  = (float) (sq / (double) HD);
-        const float scale = 1.0f / sqrtf(mean + eps);
+        const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
 #pragma unroll
-        for (int i = 0; i < 4; ++i) v[i] = (v[i] * scale) * __ldg(gamma + lane + 32 * i);
+        for (int i = 0; i < 4; ++i) v[i] = __fmul_rn(__fmul_rn(v[i], scale), __ldg(gamma + lane + 32 * i));
         const float c0 = __ldg(rope_row + lane),      s0 = __ldg(rope_row + 64 + lane);
         const float c1 = __ldg(rope_row + lane + 32), s1 = __ldg(rope_row + 64 + lane + 32);
-        out[0] = v[0] * c0 - v[2] * s0;
-        out[2] = v[0] * s0 + v[2] * c0;
-        out[1] = v[1] * c1 - v[3] * s1;
-        out[3] = v[1] * s1 + v[3] * c1;
+        out[0] = __fsub_rn(__fmul_rn(v[0], c0), __fmul_rn(v[2], s0));
+        out[2] = __fadd_rn(__fmul_rn(v[0], s0), __fmul_rn(v[2], c0));
+        out[1] = __fsub_rn(__fmul_rn(v[1], c1), __fmul_rn(v[3], s1));
+        out[3] = __fadd_rn(__fmul_rn(v[1], s1), __fmul_rn(v[3], c1));
     } else {
 #pragma unroll
         for (int i = 0; i < 4; ++i) out[i] = v[i];
     }
 }
 
-// --------------------------------------------------------------------------- attention (phase B)
+// ------------------------------------------------------------------------------- attention (phase B)
 // CTA role: kv group g = blockIdx % 8 (q heads 2g, 2g+1 share kv head g — GQA by broadcast,
-// ggml-cpu.c:1160-1199), KV chunk c = blockIdx / 8.  Softmax statistics are exchanged between
-// the C chunk-CTAs of a group so that P can be rounded to F16 *after* the global normalisation,
-// exactly where the oracle rounds it.
-__device__ __forceinline__ int attn_chunks(int n_kv, bool f32attn) {
-    if (f32attn) return 1;
-    int C = (n_kv + 31) >> 5;
-    const int maxc = min((int) gridDim.x / NKV, LM_MAXC);
-    if (C > maxc) C = maxc;
-    if (C < 1) C = 1;
-    return C;
+// ggml-cpu.c:1160-1199), split index c = blockIdx / 8 of C.  Stage 1 splits the positions for the
+// scores, stage 2 splits the head dimension for P.V, so every dot product keeps the oracle's
+// accumulation order (D.4): s_t = dot_f16(K_t, r16(q)) * scale ; P = softmax ; o_d =
+// dot_f16(V^T_d, r16(P)) over positions (32 accumulator lanes t%32 + double-precision leftovers).
+__device__ __forceinline__ int attn_splits(int n_kv, bool f32attn) {
+    if (f32attn || n_kv <= 48) return 1;
+    if (n_kv <= 192) return 4;
+    if (n_kv <= 1024) return 8;
+    return 16;
+}
+
+__device__ __forceinline__ float ld_half_cg(const __half * p) {
+    const unsigned short u = __ldcg(reinterpret_cast<const unsigned short *>(p));
+    return __half2float(__ushort_as_half(u));
 }
 
 __device__ void attention_phase(const DevModel & m, const StackW & W, int l, int pos, bool f32attn,
@@ -231,203 +299,233 @@ __device__ void attention_phase(const DevModel & m, const StackW & W, int l, int
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int g = blockIdx.x % NKV, c = blockIdx.x / NKV;
     const int n_kv = pos + 1;
-    const int C  = attn_chunks(n_kv, f32attn);
-    const int Lc = (n_kv + C - 1) / C;
+    const int C = attn_splits(n_kv, f32attn);
     const bool active = c < C;
-    const int t0 = min(c * Lc, n_kv), t1 = min(n_kv, t0 + Lc);
-    const bool owns_new = active && (pos >= t0) && (pos < t1);
     const float kq_scale = 1.0f / sqrtf((float) HD);
     const size_t kv_head_base = ((size_t) (l * NKV + g) * W.n_ctx) * HD;
+    float * ao = m.part_o;                                   // [16 heads][128] attention output
 
-    if (active) {
-        if (warp < 4) {
-            const float * rope_row = m.rope + (size_t) pos * HD;
-            float o[4];
-            if (warp < 2) {
-                head_norm_rope(m.qkv + (2 * g + warp) * HD, W.q_norm + l * HD, rope_row, m.eps, true, o);
+    if (!active) {
+        if (C > 1) group_barrier(m, bs, g, C, false);
+        return;
+    }
+    // ---- prologue: q (2 heads), k, v of the new token; the CTA with c == 0 appends K/V to the cache
+    if (warp < 4) {
+        const float * rope_row = m.rope + (size_t) pos * HD;
+        float o[4];
+        if (warp < 2) {
+            head_norm_rope(m.qkv + (2 * g + warp) * HD, W.q_norm + l * HD, rope_row, m.eps, true, o);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) { s.qf[warp][lane + 32 * i] = o[i]; s.qh[warp][lane + 32 * i] = __float2half_rn(o[i]); }
-            } else if (warp == 2) {
-                head_norm_rope(m.qkv + NH * HD + g * HD, W.k_norm + l * HD, rope_row, m.eps, true, o);
+            for (int i = 0; i < 4; ++i) { s.qf[warp][lane + 32 * i] = o[i]; s.qr[warp][lane + 32 * i] = r16(o[i]); }
+        } else if (warp == 2) {
+            head_norm_rope(m.qkv + NH * HD + g * HD, W.k_norm + l * HD, rope_row, m.eps, true, o);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int d = lane + 32 * i;
-                    const __half hv = __float2half_rn(o[i]);
-                    s.knew_f[d] = o[i]; s.knew_h[d] = hv;
-                    if (owns_new) {
-                        W.kcache[kv_head_base + (size_t) pos * HD + d] = hv;
-                        if (W.kf32 && pos < 2) W.kf32[((size_t) (l * 2 + pos) * NKV + g) * HD + d] = o[i];
-                    }
+            for (int i = 0; i < 4; ++i) {
+                const int d = lane + 32 * i;
+                const __half hv = __float2half_rn(o[i]);
+                s.knew_f[d] = o[i]; s.knew_h[d] = hv;
+                if (c == 0) {
+                    W.kcache[kv_head_base + (size_t) pos * HD + d] = hv;
+                    if (W.kf32 && pos < 2) W.kf32[((size_t) (l * 2 + pos) * NKV + g) * HD + d] = o[i];
                 }
-            } else {
-                head_norm_rope(m.qkv + (NH + NKV) * HD + g * HD, nullptr, rope_row, m.eps, false, o);
+            }
+        } else {
+            head_norm_rope(m.qkv + (NH + NKV) * HD + g * HD, nullptr, rope_row, m.eps, false, o);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int d = lane + 32 * i;
-                    const __half hv = __float2half_rn(o[i]);
-                    s.vnew_f[d] = o[i]; s.vnew_h[d] = hv;
-                    if (owns_new) {
-                        W.vcache[kv_head_base + (size_t) pos * HD + d] = hv;
-                        if (W.vf32 && pos < 2) W.vf32[((size_t) (l * 2 + pos) * NKV + g) * HD + d] = o[i];
-                    }
+            for (int i = 0; i < 4; ++i) {
+                const int d = lane + 32 * i;
+                const __half hv = __float2half_rn(o[i]);
+                s.vnew_f[d] = o[i]; s.vnew_h[d] = hv;
+                if (c == 0) {
+                    W.vcache[kv_head_base + (size_t) pos * HD + d] = hv;
+                    if (W.vf32 && pos < 2) W.vf32[((size_t) (l * 2 + pos) * NKV + g) * HD + d] = o[i];
                 }
             }
         }
-        __syncthreads();
     }
+    __syncthreads();
 
     if (f32attn) {
-        // code-predictor prefill numerics: K, V, Q and P all stay F32 because the reference graph
-        // multiplies the fresh F32 Kcur/Vcur, not the F16 cache (src/tts_transformer.cpp:1624-1635).
-        if (active && warp < 2) {
+        // code-predictor prefill numerics: the reference graph multiplies the fresh F32 Kcur/Vcur/Q
+        // and does not round P (src/tts_transformer.cpp:1624-1635): ggml_vec_dot_f32 order.
+        if (warp < 2) {
             float sc_t[2];
             float mx = -CUDART_INF_F;
-            for (int tt = 0; tt <= pos && tt < 2; ++tt) {
+            const int n = pos + 1 < 2 ? pos + 1 : 2;
+            for (int tt = 0; tt < n; ++tt) {
                 const float * krow = (tt == pos) ? s.knew_f : (W.kf32 + ((size_t) (l * 2 + tt) * NKV + g) * HD);
-                float d = 0.0f;
+                float acc = 0.0f;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) d = fmaf(krow[lane + 32 * i], s.qf[warp][lane + 32 * i], d);
-                d = warp_sum(d) * kq_scale;
-                sc_t[tt] = d;
-                mx = fmaxf(mx, d);
+                for (int i = 0; i < 4; ++i) {
+                    const float kv = (tt == pos) ? krow[lane + 32 * i] : ld_act(krow + lane + 32 * i);
+                    acc = __fmaf_rn(kv, s.qf[warp][lane + 32 * i], acc);
+                }
+                sc_t[tt] = __fmul_rn(reduce32_lanes(acc), kq_scale);
+                mx = fmaxf(mx, sc_t[tt]);
             }
             double sum = 0.0;
-            for (int tt = 0; tt <= pos && tt < 2; ++tt) { sc_t[tt] = expf(sc_t[tt] - mx); sum += (double) sc_t[tt]; }
+            for (int tt = 0; tt < n; ++tt) { sc_t[tt] = tail_expf(__fsub_rn(sc_t[tt], mx)); sum += (double) sc_t[tt]; }
             const float inv = (float) (1.0 / sum);
             float o[4] = {0.f, 0.f, 0.f, 0.f};
-            for (int tt = 0; tt <= pos && tt < 2; ++tt) {
+            for (int tt = 0; tt < n; ++tt) {
                 const float * vrow = (tt == pos) ? s.vnew_f : (W.vf32 + ((size_t) (l * 2 + tt) * NKV + g) * HD);
-                const float p = sc_t[tt] * inv;
+                const float p = __fmul_rn(sc_t[tt], inv);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) o[i] = fmaf(vrow[lane + 32 * i], p, o[i]);
+                for (int i = 0; i < 4; ++i) {
+                    const float vv = (tt == pos) ? vrow[lane + 32 * i] : ld_act(vrow + lane + 32 * i);
+                    o[i] = __fmaf_rn(vv, p, o[i]);
+                }
             }
-            float * dst = m.part_o + ((size_t) (g * LM_MAXC + 0) * 2 + warp) * HD;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) dst[lane + 32 * i] = o[i];
+            for (int i = 0; i < 4; ++i) ao[(2 * g + warp) * HD + lane + 32 * i] = o[i];
         }
         return;
     }
 
-    const int hlf = lane >> 4, sub = lane & 15;
-    const int n_loc = t1 - t0;
-    float Mh[2] = {-CUDART_INF_F, -CUDART_INF_F};
-    float inv_h[2] = {0.f, 0.f};
-
-    if (active) {
-        // ---- stage 1: scores s_t = (K_t . r16(q)) * scale
-        float qa[8], qb[8];
+    float * sb0 = m.sbuf + (size_t) (2 * g) * ATT_MAX_KV;
+    float * sb1 = sb0 + ATT_MAX_KV;
+    // ---- stage 1: scores of this CTA's position chunk
+    {
+        const int Lc = (n_kv + C - 1) / C;
+        const int t0 = min(c * Lc, n_kv), t1 = min(n_kv, t0 + Lc);
+        float q0[4], q1[4];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { qa[j] = __half2float(s.qh[0][sub * 8 + j]); qb[j] = __half2float(s.qh[1][sub * 8 + j]); }
-        for (int base = t0 + warp * 2; base < t1; base += 32) {
-            const int tt = base + hlf;
-            const bool valid = tt < t1;
-            uint4 kv = make_uint4(0, 0, 0, 0);
-            if (valid) {
-                const __half * krow = (tt == pos) ? s.knew_h : (W.kcache + kv_head_base + (size_t) tt * HD);
-                kv = *reinterpret_cast<const uint4 *>(krow + sub * 8);
-            }
-            const __half2 * kh = reinterpret_cast<const __half2 *>(&kv);
-            float da = 0.f, db = 0.f;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float2 kf = __half22float2(kh[j]);
-                da = fmaf(kf.x, qa[2 * j], da); da = fmaf(kf.y, qa[2 * j + 1], da);
-                db = fmaf(kf.x, qb[2 * j], db); db = fmaf(kf.y, qb[2 * j + 1], db);
-            }
-#pragma unroll
-            for (int o = 8; o > 0; o >>= 1) { da += __shfl_xor_sync(0xffffffffu, da, o); db += __shfl_xor_sync(0xffffffffu, db, o); }
-            if (valid && sub == 0) { s.sc[0][tt - t0] = da * kq_scale; s.sc[1][tt - t0] = db * kq_scale; }
-        }
-        __syncthreads();
-        // ---- chunk-local max and sum(exp)
+        for (int i = 0; i < 4; ++i) { q0[i] = s.qr[0][lane + 32 * i]; q1[i] = s.qr[1][lane + 32 * i]; }
         float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F;
-        for (int i = t; i < n_loc; i += LM_THREADS) { mx0 = fmaxf(mx0, s.sc[0][i]); mx1 = fmaxf(mx1, s.sc[1][i]); }
-        mx0 = warp_max(mx0); mx1 = warp_max(mx1);
-        if (lane == 0) { s.wred[0][warp][0] = mx0; s.wred[1][warp][0] = mx1; }
-        __syncthreads();
-        mx0 = -CUDART_INF_F; mx1 = -CUDART_INF_F;
+        for (int tt = t0 + warp; tt < t1; tt += 16) {
+            float kv[4];
+            if (tt == pos) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) { mx0 = fmaxf(mx0, s.wred[0][i][0]); mx1 = fmaxf(mx1, s.wred[1][i][0]); }
-        double sm0 = 0.0, sm1 = 0.0;
-        for (int i = t; i < n_loc; i += LM_THREADS) { sm0 += (double) expf(s.sc[0][i] - mx0); sm1 += (double) expf(s.sc[1][i] - mx1); }
-        sm0 = warp_sum_d(sm0); sm1 = warp_sum_d(sm1);
-        __syncthreads();
-        if (lane == 0) { s.dred[warp] = sm0; }
-        __syncthreads();
-        double S0 = 0.0;
+                for (int i = 0; i < 4; ++i) kv[i] = __half2float(s.knew_h[lane + 32 * i]);
+            } else {
+                const __half * krow = W.kcache + kv_head_base + (size_t) tt * HD;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) S0 += s.dred[i];
-        __syncthreads();
-        if (lane == 0) { s.dred[warp] = sm1; }
-        __syncthreads();
-        double S1 = 0.0;
+                for (int i = 0; i < 4; ++i) kv[i] = ld_half_cg(krow + lane + 32 * i);
+            }
+            float a0 = 0.0f, a1 = 0.0f;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) S1 += s.dred[i];
-        if (C == 1) {
-            Mh[0] = mx0; Mh[1] = mx1;
-            inv_h[0] = (float) (1.0 / S0); inv_h[1] = (float) (1.0 / S1);
-        } else if (t == 0) {
-            float * pm = m.part_ms + (size_t) (g * LM_MAXC + c) * 4;
-            pm[0] = mx0; pm[1] = (float) S0; pm[2] = mx1; pm[3] = (float) S1;
+            for (int i = 0; i < 4; ++i) { a0 = __fmaf_rn(kv[i], q0[i], a0); a1 = __fmaf_rn(kv[i], q1[i], a1); }
+            const float s0 = __fmul_rn(reduce32_lanes(a0), kq_scale);
+            const float s1 = __fmul_rn(reduce32_lanes(a1), kq_scale);
+            mx0 = fmaxf(mx0, s0); mx1 = fmaxf(mx1, s1);
+            if (lane == 0) { sb0[tt] = s0; sb1[tt] = s1; }
+        }
+        if (lane == 0) { s.fred[warp] = mx0; s.fred[16 + warp] = mx1; }
+        __threadfence_block();
+        __syncthreads();
+        if (t == 0) {
+            float a = s.fred[0], b = s.fred[16];
+            for (int i = 1; i < 16; ++i) { a = fmaxf(a, s.fred[i]); b = fmaxf(b, s.fred[16 + i]); }
+            float * pm = m.part_ms + (size_t) (g * 16 + c) * 2;
+            pm[0] = a; pm[1] = b;
         }
     }
-    if (C > 1) {
-        group_barrier(m, bs, g, C, active);
-        if (active) {
-            float M0 = -CUDART_INF_F, M1 = -CUDART_INF_F;
-            for (int i = 0; i < C; ++i) {
-                const float * pm = m.part_ms + (size_t) (g * LM_MAXC + i) * 4;
-                M0 = fmaxf(M0, ld_act(pm + 0)); M1 = fmaxf(M1, ld_act(pm + 2));
-            }
-            double S0 = 0.0, S1 = 0.0;
-            for (int i = 0; i < C; ++i) {
-                const float * pm = m.part_ms + (size_t) (g * LM_MAXC + i) * 4;
-                const float s0 = ld_act(pm + 1), s1 = ld_act(pm + 3);
-                if (s0 > 0.f) S0 += (double) s0 * (double) expf(ld_act(pm + 0) - M0);
-                if (s1 > 0.f) S1 += (double) s1 * (double) expf(ld_act(pm + 2) - M1);
-            }
-            Mh[0] = M0; Mh[1] = M1;
-            inv_h[0] = (float) (1.0 / S0); inv_h[1] = (float) (1.0 / S1);
-        }
-    }
-    if (!active) return;
+    if (C > 1) group_barrier(m, bs, g, C, true);
+    else { __threadfence_block(); __syncthreads(); }
 
-    // ---- stage 2: o = sum_t r16(p_t) * V_t with p_t = expf(s_t - M) * (1/S)
-    float aa[8], ab[8];
+    // ---- soft-max over all n_kv positions (every CTA of the group, redundantly)
+    float M0 = -CUDART_INF_F, M1 = -CUDART_INF_F;
+    for (int i = 0; i < C; ++i) {
+        const float * pm = m.part_ms + (size_t) (g * 16 + i) * 2;
+        M0 = fmaxf(M0, ld_act(pm)); M1 = fmaxf(M1, ld_act(pm + 1));
+    }
+    const int n8 = n_kv >> 3;
+    double ds0 = 0.0, ds1 = 0.0;
+    for (int ch = t; ch < n8; ch += LM_THREADS) {          // ggml_vec_soft_max_f32, 8 lanes at a time (vec.cpp:558-568)
+        float e0[8], e1[8];
+        const float4 * p0 = reinterpret_cast<const float4 *>(sb0 + ch * 8);
+        const float4 * p1 = reinterpret_cast<const float4 *>(sb1 + ch * 8);
+        const float4 x0 = __ldcg(p0), x1 = __ldcg(p0 + 1), y0 = __ldcg(p1), y1 = __ldcg(p1 + 1);
+        const float xs[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+        const float ys[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { aa[j] = 0.f; ab[j] = 0.f; }
-    for (int base = t0 + warp * 2; base < t1; base += 32) {
-        const int tt = base + hlf;
-        if (tt < t1) {
-            const __half * vrow = (tt == pos) ? s.vnew_h : (W.vcache + kv_head_base + (size_t) tt * HD);
-            const uint4 vv = *reinterpret_cast<const uint4 *>(vrow + sub * 8);
-            const __half2 * vh = reinterpret_cast<const __half2 *>(&vv);
-            const float pa = r16(expf(s.sc[0][tt - t0] - Mh[0]) * inv_h[0]);
-            const float pb = r16(expf(s.sc[1][tt - t0] - Mh[1]) * inv_h[1]);
+        for (int j = 0; j < 8; ++j) { e0[j] = v_expf(__fsub_rn(xs[j], M0)); e1[j] = v_expf(__fsub_rn(ys[j], M1)); }
+        ds0 += (double) __fadd_rn(__fadd_rn(__fadd_rn(e0[4], e0[0]), __fadd_rn(e0[6], e0[2])),
+                                  __fadd_rn(__fadd_rn(e0[5], e0[1]), __fadd_rn(e0[7], e0[3])));
+        ds1 += (double) __fadd_rn(__fadd_rn(__fadd_rn(e1[4], e1[0]), __fadd_rn(e1[6], e1[2])),
+                                  __fadd_rn(__fadd_rn(e1[5], e1[1]), __fadd_rn(e1[7], e1[3])));
+    }
+    if (t < (n_kv & 7)) {                                   // scalar tail: libm expf
+        const int tt = n8 * 8 + t;
+        ds0 += (double) tail_expf(__fsub_rn(ld_act(sb0 + tt), M0));
+        ds1 += (double) tail_expf(__fsub_rn(ld_act(sb1 + tt), M1));
+    }
+    ds0 = warp_sum_d(ds0); ds1 = warp_sum_d(ds1);
+    if (lane == 0) { s.dred[0][warp] = ds0; s.dred[1][warp] = ds1; }
+    __syncthreads();
+    double S0 = 0.0, S1 = 0.0;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float2 vf = __half22float2(vh[j]);
-                aa[2 * j] = fmaf(pa, vf.x, aa[2 * j]); aa[2 * j + 1] = fmaf(pa, vf.y, aa[2 * j + 1]);
-                ab[2 * j] = fmaf(pb, vf.x, ab[2 * j]); ab[2 * j + 1] = fmaf(pb, vf.y, ab[2 * j + 1]);
+    for (int i = 0; i < 16; ++i) { S0 += s.dred[0][i]; S1 += s.dred[1][i]; }
+    const float inv0 = (float) (1.0 / S0), inv1 = (float) (1.0 / S1);
+    for (int tt = t; tt < n_kv; tt += LM_THREADS) {
+        const float x = __fsub_rn(ld_act(sb0 + tt), M0), y = __fsub_rn(ld_act(sb1 + tt), M1);
+        const bool simd = tt < n8 * 8;
+        s.ph[0][tt] = __float2half_rn(__fmul_rn(simd ? v_expf(x) : tail_expf(x), inv0));
+        s.ph[1][tt] = __float2half_rn(__fmul_rn(simd ? v_expf(y) : tail_expf(y), inv1));
+    }
+    __syncthreads();
+
+    // ---- stage 2: o[d] for this CTA's nd = 128/C dims, both heads
+    const int nd = HD / C, d0 = c * nd;
+    const int TB = VT_HALVES / nd;                          // positions per V^T tile (multiple of 32)
+    const int np = n_kv & ~31;
+    const int ndg = nd >> 3;                                // 16-byte groups per position
+    float acc0[8], acc1[8];                                 // up to 8 dims per warp (nd = 128)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { acc0[j] = 0.0f; acc1[j] = 0.0f; }
+    const __half * vbase = W.vcache + kv_head_base;
+    for (int tb0 = 0; tb0 < np; tb0 += TB) {
+        const int tbn = min(TB, np - tb0);
+        for (int idx = t; idx < tbn * ndg; idx += LM_THREADS) {
+            const int tt = idx / ndg, dg = idx % ndg;
+            const int tg = tb0 + tt;
+            uint4 v;
+            if (tg == pos) v = *reinterpret_cast<const uint4 *>(s.vnew_h + d0 + dg * 8);
+            else v = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tg * HD + d0 + dg * 8));
+            const __half * vh = reinterpret_cast<const __half *>(&v);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) s.vt[(dg * 8 + e) * TB + tt] = vh[e];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int dl = warp + 16 * j;
+            if (dl < nd) {
+                for (int tt = lane; tt < tbn; tt += 32) {
+                    const float vv = __half2float(s.vt[dl * TB + tt]);
+                    acc0[j] = __fmaf_rn(vv, __half2float(s.ph[0][tb0 + tt]), acc0[j]);
+                    acc1[j] = __fmaf_rn(vv, __half2float(s.ph[1][tb0 + tt]), acc1[j]);
+                }
             }
         }
+        __syncthreads();
+    }
+    // leftovers t in [np, n_kv): staged into the tile, then one thread per (head, dim) adds them
+    // sequentially in double like ggml_vec_dot_f16's scalar tail (vec.cpp:381-384)
+    const int nleft = n_kv - np;
+    for (int idx = t; idx < nleft * ndg; idx += LM_THREADS) {
+        const int tt = idx / ndg, dg = idx % ndg;
+        const int tg = np + tt;
+        uint4 v;
+        if (tg == pos) v = *reinterpret_cast<const uint4 *>(s.vnew_h + d0 + dg * 8);
+        else v = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tg * HD + d0 + dg * 8));
+        const __half * vh = reinterpret_cast<const __half *>(&v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s.vt[(dg * 8 + e) * TB + tt] = vh[e];
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        aa[j] += __shfl_xor_sync(0xffffffffu, aa[j], 16);
-        ab[j] += __shfl_xor_sync(0xffffffffu, ab[j], 16);
-    }
-    if (hlf == 0) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { s.red_o[warp][0][sub * 8 + j] = aa[j]; s.red_o[warp][1][sub * 8 + j] = ab[j]; }
+        const int dl = warp + 16 * j;
+        const float r0 = reduce32_lanes(acc0[j]), r1 = reduce32_lanes(acc1[j]);
+        if (dl < nd && lane == 0) { s.xf[dl] = r0; s.xf[HD + dl] = r1; }      // xf is free during phase B
     }
     __syncthreads();
-    if (t < 2 * HD) {
-        const int h = t >> 7, d = t & 127;
-        float o = 0.f;
-#pragma unroll
-        for (int w = 0; w < 16; ++w) o += s.red_o[w][h][d];
-        m.part_o[((size_t) (g * LM_MAXC + c) * 2 + h) * HD + d] = o;
+    if (t < 2 * nd) {
+        const int h = t / nd, dl = t % nd;
+        double sumf = (double) s.xf[h * HD + dl];
+        for (int i = 0; i < nleft; ++i)
+            sumf += (double) __fmul_rn(__half2float(s.vt[dl * TB + i]), __half2float(s.ph[h][np + i]));
+        ao[(2 * g + h) * HD + d0 + dl] = (float) sumf;
     }
 }
 
@@ -493,7 +591,7 @@ __device__ int select_sample(const DevModel & m, Smem & s, int vocab, bool proce
         l[i] = -CUDART_INF_F;
         if (idx < vocab) l[i] = proc_logit(m, ld_act(m.logits + idx), idx, process, suppress_start, eos_id, rep_penalty) / temperature;
     }
-    int * hist = reinterpret_cast<int *>(s.sc[0]);           // 256 bins + 2 control words
+    int * hist = reinterpret_cast<int *>(s.vt);              // 256 bins + 2 control words
     if (top_k > 0 && top_k < vocab) {
         unsigned int prefix = 0, mask = 0;
         int k_rem = top_k;
@@ -542,11 +640,11 @@ __device__ int select_sample(const DevModel & m, Smem & s, int vocab, bool proce
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const double v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
     __syncthreads();
-    if (lane == 31) s.dred[warp] = inc;
+    if (lane == 31) s.dred[0][warp] = inc;
     __syncthreads();
     double woff = 0.0, total = 0.0;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) { if (i < warp) woff += s.dred[i]; total += s.dred[i]; }
+    for (int i = 0; i < 16; ++i) { if (i < warp) woff += s.dred[0][i]; total += s.dred[0][i]; }
     inc += woff;
     const double target = u01(seed, draw) * total;
     if (t == 0) s.tok = -1;
@@ -572,7 +670,8 @@ __device__ int select_sample(const DevModel & m, Smem & s, int vocab, bool proce
     return tok;
 }
 
-// --------------------------------------------------------------------------- weight slices
+
+// ------------------------------------------------------------------------------- weight slices
 struct Slices {            // this CTA's row ranges (fixed for the whole launch)
     int a0, a1;            // qkv rows            (of 4096, K=1024)
     int o0, o1;            // attn_output rows    (of 1024, K=2048)
@@ -609,78 +708,77 @@ __device__ __forceinline__ void l2_prefetch_layer(const StackW & W, int l, const
     l2_prefetch_range(sl_d(W, l, z),  (size_t) (z.d1 - z.d0) * FFN * 2);
 }
 
-// --------------------------------------------------------------------------- one pass
+// ------------------------------------------------------------------------------- one pass
 // One token through `n_layers` layers of stack W (+ optional head).  s.xres holds x on entry;
-// `w` holds the phase-A weights of layer 0 on entry (prefetched by the caller).
+// the TMA fetches of A(0) -> buf0 and C(0) -> buf1 have been issued by the caller.  On exit the
+// fetches of the next pass' A(0)/C(0) (stack NW, if any) are in flight.
 __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc & p, int pos,
                           const HeadW * head, bool process, const GenState & gs,
-                          const Slices & z, const __half * next_a0, int next_a0_units,
-                          Smem & s, BarState & bs, uint4 (&w)[MAXV]) {
+                          const Slices & z, const StackW * NW,
+                          Smem & s, BarState & bs, WStream & ws) {
     const int t = threadIdx.x;
     const int nA = z.a1 - z.a0, nO = z.o1 - z.o0, nP = z.p1 - z.p0, nD = z.d1 - z.d0;
     int h0 = 0, h1 = 0;
     if (head) cta_rows(head->vocab, h0, h1);
+    const int nH = h1 - h0;
 
     for (int l = 0; l < p.n_layers; ++l) {
+        const bool last = l + 1 == p.n_layers;
         if (t == 0) {
-            if (l + 1 < p.n_layers) l2_prefetch_layer(W, l + 1, z);
-            else if (head) l2_prefetch_range(head->w + (size_t) h0 * H, (size_t) (h1 - h0) * H * 2);
+            if (!last) l2_prefetch_layer(W, l + 1, z);
+            else if (head) l2_prefetch_range(head->w + (size_t) h0 * H, (size_t) nH * H * 2);
         }
         // ---- phase A: RMSNorm + fused QKV mat-vec
-        rmsnorm_to_h(s, W.attn_norm + (size_t) l * H, m.eps, nullptr);
-        gemv_units_h<1>(w, nA, s);
+        rmsnorm_to_xf(s, W.attn_norm + (size_t) l * H, m.eps, nullptr);
+        wait_fetch(s, ws, 0);
+        gemv_chain<4, 1024>(s.buf0, nA, s);
         __syncthreads();
-        if (t < nA) m.qkv[z.a0 + t] = fold_row<1>(s, t);
+        if (t < nA) m.qkv[z.a0 + t] = s.outv[t];
+        issue_fetch(s, ws, 0, sl_gu(W, l, z), 2 * nP, H * 2);
         grid_barrier(m, bs);
 
         // ---- phase B: per-head norm + RoPE + KV append + attention
-        prefetch_w(w, sl_o(W, l, z), 2 * nO);
         attention_phase(m, W, l, pos, p.f32attn != 0, s, bs);
         grid_barrier(m, bs);
 
-        // ---- phase C: attn_output mat-vec + residual
-        {
-            const int C = attn_chunks(pos + 1, p.f32attn != 0);
+        // ---- phase C: attn_output mat-vec (input rounded to F16) + residual
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int idx = t + LM_THREADS * i;
-                const int j = idx >> 7, d = idx & 127;
-                const float * src = m.part_o + ((size_t) ((j >> 1) * LM_MAXC) * 2 + (j & 1)) * HD + d;
-                float o = 0.f;
-                for (int c = 0; c < C; ++c) o += ld_act(src + (size_t) c * 2 * HD);
-                s.xin_h[idx] = __float2half_rn(o);
-            }
-        }
+        for (int i = 0; i < 4; ++i) s.xf[t + LM_THREADS * i] = r16(ld_act(m.part_o + t + LM_THREADS * i));
         __syncthreads();
-        gemv_units_h<2>(w, 2 * nO, s);
+        wait_fetch(s, ws, 1);
+        gemv_chain<2, 2048>(s.buf1, nO, s);
         __syncthreads();
-        if (t < nO) m.xb[z.o0 + t] = fold_row<2>(s, t) + s.xres[z.o0 + t];
-        prefetch_w(w, sl_gu(W, l, z), 2 * nP);
+        if (t < nO) m.xb[z.o0 + t] = __fadd_rn(s.outv[t], s.xres[z.o0 + t]);
+        issue_fetch(s, ws, 1, sl_d(W, l, z), nD, FFN * 2);
         grid_barrier(m, bs);
 
         // ---- phase D: RMSNorm + gate/up mat-vec + SwiGLU
         s.xres[t] = ld_act(m.xb + t); s.xres[t + 512] = ld_act(m.xb + t + 512);
         __syncthreads();
-        rmsnorm_to_h(s, W.ffn_norm + (size_t) l * H, m.eps, nullptr);
-        gemv_units_h<1>(w, 2 * nP, s);
+        rmsnorm_to_xf(s, W.ffn_norm + (size_t) l * H, m.eps, nullptr);
+        wait_fetch(s, ws, 0);
+        gemv_chain<4, 1024>(s.buf0, 2 * nP, s);
         __syncthreads();
         if (t < nP) {
-            const float gt = fold_row<1>(s, 2 * t), up = fold_row<1>(s, 2 * t + 1);
-            m.mbuf[z.p0 + t] = (gt / (1.0f + expf(-gt))) * up;
+            const float gt = s.outv[2 * t], up = s.outv[2 * t + 1];
+            const float sl = __fdiv_rn(gt, __fadd_rn(1.0f, v_expf(__fsub_rn(0.0f, gt))));   // ggml_v_silu
+            m.mbuf[z.p0 + t] = __fmul_rn(sl, up);
         }
-        prefetch_w(w, sl_d(W, l, z), 3 * nD);
+        if (!last)      issue_fetch(s, ws, 0, sl_a(W, l + 1, z), nA, H * 2);
+        else if (head)  issue_fetch(s, ws, 0, head->w + (size_t) h0 * H, nH, H * 2);
+        else if (NW)    issue_fetch(s, ws, 0, sl_a(*NW, 0, z), nA, H * 2);
         grid_barrier(m, bs);
 
-        // ---- phase E: ffn_down on F32 activations + residual
+        // ---- phase E: ffn_down on F32 activations (weights exact in F32) + residual
 #pragma unroll
-        for (int i = 0; i < FFN / LM_THREADS; ++i) s.xin_f[t + LM_THREADS * i] = ld_act(m.mbuf + t + LM_THREADS * i);
+        for (int i = 0; i < FFN / LM_THREADS; ++i) s.xf[t + LM_THREADS * i] = ld_act(m.mbuf + t + LM_THREADS * i);
         __syncthreads();
-        gemv_units_f<3>(w, 3 * nD, s);
+        wait_fetch(s, ws, 1);
+        gemv_chain<2, 3072>(s.buf1, nD, s);
         __syncthreads();
-        if (t < nD) m.xa[z.d0 + t] = fold_row<3>(s, t) + s.xres[z.d0 + t];
-        if (l + 1 < p.n_layers) prefetch_w(w, sl_a(W, l + 1, z), nA);
-        else if (head)          prefetch_w(w, head->w + (size_t) h0 * H, h1 - h0);
-        else if (next_a0)       prefetch_w(w, next_a0, next_a0_units);
+        if (t < nD) m.xa[z.d0 + t] = __fadd_rn(s.outv[t], s.xres[z.d0 + t]);
+        if (!last)      issue_fetch(s, ws, 1, sl_o(W, l + 1, z), nO, NH * HD * 2);
+        else if (NW)    issue_fetch(s, ws, 1, sl_o(*NW, 0, z), nO, NH * HD * 2);
         grid_barrier(m, bs);
         s.xres[t] = ld_act(m.xa + t); s.xres[t + 512] = ld_act(m.xa + t + 512);
         __syncthreads();
@@ -688,20 +786,20 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
 
     if (!head) return;
     // ---- head: final RMSNorm (= hidden_states) + vocabulary mat-vec + per-CTA arg-max candidate
-    rmsnorm_to_h(s, W.out_norm, m.eps, blockIdx.x == 0 ? m.hidden : nullptr);
-    if (p.hidden_dst && blockIdx.x == 0) {
-        // xres * scale * gamma was just written to m.hidden by this CTA's threads
-        p.hidden_dst[t] = m.hidden[t]; p.hidden_dst[t + 512] = m.hidden[t + 512];
-    }
-    const int nH = h1 - h0;
-    gemv_units_h<1>(w, nH, s);
+    rmsnorm_to_xf(s, W.out_norm, m.eps, blockIdx.x == 0 ? m.hidden : nullptr);
+    if (p.hidden_dst && blockIdx.x == 0) { p.hidden_dst[t] = m.hidden[t]; p.hidden_dst[t + 512] = m.hidden[t + 512]; }
+    wait_fetch(s, ws, 0);
+    gemv_chain<4, 1024>(s.buf0, nH, s);
     __syncthreads();
+    float pv = -CUDART_INF_F;
     if (t < nH) {
-        const float raw = fold_row<1>(s, t);
+        const float raw = s.outv[t];
         m.logits[h0 + t] = raw;
         if (p.logits_dst) p.logits_dst[h0 + t] = raw;
-        s.outv[t] = proc_logit(m, raw, h0 + t, process, gs.suppress_start, gs.eos_id, gs.rep_penalty);
+        pv = proc_logit(m, raw, h0 + t, process, gs.suppress_start, gs.eos_id, gs.rep_penalty);
     }
+    __syncthreads();
+    if (t < nH) s.outv[t] = pv;
     __syncthreads();
     if (t == 0) {
         float bv = -CUDART_INF_F; int bi = 0x7fffffff;
@@ -709,7 +807,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         if (nH > 0 && bi == 0x7fffffff) bi = h0;       // all -inf: keep first-index semantics
         m.cand_val[blockIdx.x] = bv; m.cand_idx[blockIdx.x] = bi;
     }
-    if (next_a0) prefetch_w(w, next_a0, next_a0_units);
+    if (NW) issue_fetch(s, ws, 0, sl_a(*NW, 0, z), nA, H * 2);
     grid_barrier(m, bs);
 }
 
@@ -719,7 +817,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
 // n_past) in GenState so the identical launch can be replayed once per frame.
 __global__ void __launch_bounds__(LM_THREADS, 1)
 lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ passes, int n_passes, int frame_mode) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem & s = *reinterpret_cast<Smem *>(smem_raw);
     __shared__ GenState gs;
     __shared__ PassDesc pd;
@@ -740,12 +838,18 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
     cta_rows(FFN,   z.p0, z.p1);
     cta_rows(H,     z.d0, z.d1);
 
-    uint4 w[MAXV];
+    WStream ws;
+    ws.parity[0] = ws.parity[1] = 0u;
+    ws.pending[0] = ws.pending[1] = false;
+    if (t == 0) {
+        mbar_init(&s.mbar[0], 1);
+        mbar_init(&s.mbar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
     int frame = gs.frame, n_past = gs.n_past, done = gs.done, pending = gs.pending;
     int pending_vocab = gs.codec_vocab, pending_process = 1;
     unsigned long long draw = gs.draw;
-    bool have_w = false;
-    int  have_w_stack = -1;
 
     for (int ip = 0; ip < n_passes; ++ip) {
         if (t == 0) pd = passes[ip];
@@ -753,12 +857,12 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
         const PassDesc p = pd;
         const StackW & W = p.stack == 0 ? m.talker : m.cp;
 
-        // start pulling layer 0 of this stack towards L2 / registers before the (serial) selection
+        // start pulling layer 0 of this stack towards L2 / shared memory before the (serial) selection
         if (p.xmode != XM_SELECT_ONLY) {
             if (t == 0) l2_prefetch_layer(W, 0, z);
-            if (!(have_w && have_w_stack == p.stack)) prefetch_w(w, sl_a(W, 0, z), z.a1 - z.a0);
+            if (!ws.pending[0]) issue_fetch(s, ws, 0, sl_a(W, 0, z), z.a1 - z.a0, H * 2);
+            if (!ws.pending[1]) issue_fetch(s, ws, 1, sl_o(W, 0, z), z.o1 - z.o0, NH * HD * 2);
         }
-        have_w = false;
 
         // ---- select the token produced by the previous head, if one is waiting
         const bool needs_select = p.xmode == XM_HIDDEN || p.xmode == XM_CP_EMBD ||
@@ -806,11 +910,11 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
 #pragma unroll
                     for (int cb = 1; cb < NCB; ++cb) {
                         const __half * q = m.cp_embd[cb - 1] + (size_t) gs.cur[cb] * H;
-                        xa += __half2float(q[t]); xb += __half2float(q[t + 512]);
+                        xa = __fadd_rn(xa, __half2float(q[t])); xb = __fadd_rn(xb, __half2float(q[t + 512]));
                     }
                     const int fr = frame - 1;      // the frame just emitted
                     const float * tr = (fr < gs.trailing_len) ? (m.trailing + (size_t) fr * H) : m.pad_embed;
-                    xa += ld_act(tr + t); xb += ld_act(tr + t + 512);
+                    xa = __fadd_rn(xa, ld_act(tr + t)); xb = __fadd_rn(xb, ld_act(tr + t + 512));
                 } break;
                 default: break;
             }
@@ -820,21 +924,20 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
 
         const int pos = p.pos >= 0 ? p.pos : n_past;
         const HeadW * head = p.head < 0 ? nullptr : (p.head == 0 ? &m.codec_head : &m.cp_head[p.head - 1]);
-        // next pass' first weight slice (register prefetch across the pass boundary)
-        const __half * next_a0 = nullptr; int next_units = 0; int next_stack = -1;
+        // the next pass' first weight slices are fetched across the pass boundary
+        const StackW * NW = nullptr;
         if (ip + 1 < n_passes) {
-            const PassDesc & np = passes[ip + 1];
-            if (np.xmode != XM_SELECT_ONLY) {
-                next_stack = np.stack;
-                const StackW & NW = np.stack == 0 ? m.talker : m.cp;
-                next_a0 = sl_a(NW, 0, z); next_units = z.a1 - z.a0;
-            }
+            const int nx = passes[ip + 1].xmode, ns = passes[ip + 1].stack;
+            if (nx != XM_SELECT_ONLY) NW = ns == 0 ? &m.talker : &m.cp;
         }
-        run_stack(m, W, p, pos, head, p.process != 0, gs, z, next_a0, next_units, s, bs, w);
-        have_w = next_a0 != nullptr; have_w_stack = next_stack;
+        run_stack(m, W, p, pos, head, p.process != 0, gs, z, NW, s, bs, ws);
         if (head) { pending = p.head; pending_vocab = head->vocab; pending_process = p.process; }
         if (p.stack == 0 && p.pos < 0) ++n_past;
     }
+
+    // drain TMA copies still in flight (early exit on EOS / max_len) before the CTA retires
+    if (ws.pending[0]) wait_fetch(s, ws, 0);
+    if (ws.pending[1]) wait_fetch(s, ws, 1);
 
     // ---- write the state back (CTA 0); barrier epochs are identical in every CTA
     if (blockIdx.x == 0 && t == 0) {
@@ -864,7 +967,7 @@ int lm_max_grid(q3t_ctx * ctx) {
 int lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int frame_mode) {
     if (ctx->grid <= 0) {
         const int g = lm_max_grid(ctx);
-        if (g < LM_MIN_GRID) return set_err(ctx, Q3T_ERR_CUDA, "device cannot co-schedule the persistent decode kernel (needs >= 128 SMs)");
+        if (g < LM_MIN_GRID) return set_err(ctx, Q3T_ERR_CUDA, "device cannot co-schedule the persistent decode kernel (needs >= 140 SMs)");
         ctx->grid = g > 512 ? 512 : g;
     }
     DevModel m = ctx->hm;

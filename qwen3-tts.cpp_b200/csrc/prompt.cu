@@ -18,9 +18,11 @@ __global__ void gather_rows_h(const __half * __restrict__ table, const int * __r
 }
 
 // out[t][n] = act( W[n][:] . X[t][:] + bias[n] );  W, X F16 (X already F16-rounded = the oracle's
-// from_float before an F16 mat-mul), F32 accumulate.  One warp per output row, 8 tokens per sweep
-// so the weight row is streamed once per 8 tokens.  SILU=1 applies x/(1+exp(-x)) and stores the
-// result rounded to F16 (it is the next mat-mul's input); SILU=0 stores F32.
+// from_float before an F16 mat-mul).  One warp per output row; lane = accumulator lane k%32 and
+// the k/32 chain is walked with FMAs, then folded in the oracle's order (bit-exact with
+// ggml_vec_dot_f16, see common.cuh).  8 tokens per sweep so a weight row is streamed once per 8
+// tokens.  SILU=1 applies ggml_v_silu and stores the result rounded to F16 (it is the next
+// mat-mul's input); SILU=0 stores F32.
 template <int SILU>
 __global__ void __launch_bounds__(256)
 proj_rows(const __half * __restrict__ W, const __half * __restrict__ X, const float * __restrict__ bias,
@@ -28,28 +30,26 @@ proj_rows(const __half * __restrict__ W, const __half * __restrict__ X, const fl
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n = blockIdx.x * 8 + warp;
     if (n >= N) return;
-    const uint4 * wrow = reinterpret_cast<const uint4 *>(W + (size_t) n * K);
+    const __half * wrow = W + (size_t) n * K;
     for (int t0 = 0; t0 < T; t0 += 8) {
         float acc[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-        for (int i = lane; i < K / 8; i += 32) {
-            const uint4 wv = ld_weight(wrow + i);
+        for (int c = 0; c < K / 32; ++c) {
+            const float wv = __half2float(wrow[c * 32 + lane]);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                if (t0 + j < T) {
-                    const uint4 xv = *(reinterpret_cast<const uint4 *>(X + (size_t) (t0 + j) * K) + i);
-                    acc[j] = dot8_hh(wv, xv, acc[j]);
-                }
-            }
+            for (int j = 0; j < 8; ++j)
+                if (t0 + j < T) acc[j] = __fmaf_rn(wv, __half2float(X[(size_t) (t0 + j) * K + c * 32 + lane]), acc[j]);
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            float v = warp_sum(acc[j]);
+            float v = reduce32_lanes(acc[j]);
             if (lane == 0 && t0 + j < T) {
-                v += bias[n];
-                if (SILU) { v = v / (1.0f + expf(-v)); out_h[(size_t) (t0 + j) * N + n] = __float2half_rn(v); }
-                else out_f[(size_t) (t0 + j) * N + n] = v;
+                v = __fadd_rn(v, bias[n]);
+                if (SILU) {
+                    v = __fdiv_rn(v, __fadd_rn(1.0f, v_expf(__fsub_rn(0.0f, v))));
+                    out_h[(size_t) (t0 + j) * N + n] = __float2half_rn(v);
+                } else out_f[(size_t) (t0 + j) * N + n] = v;
             }
         }
     }
@@ -83,8 +83,8 @@ __global__ void assemble_prompt(const AsmArgs a) {
             else if (row < a.prefill_len - 1) {
                 const int t = row - 3;                                                 // overlay rows
                 const float ov = (t == L - 2) ? a.proj[0 * H + h] : a.proj[2 * H + h]; // tts_bos : tts_pad
-                v = ov + codec_in(t);
-            } else v = a.proj[(size_t) 6 * H + h] + codec_in(L - 1);                   // first text + codec_bos
+                v = __fadd_rn(ov, codec_in(t));
+            } else v = __fadd_rn(a.proj[(size_t) 6 * H + h], codec_in(L - 1));         // first text + codec_bos
             a.prefill[(size_t) row * H + h] = v;
         } else if (row < a.prefill_len + a.trailing_len) {
             const int t = row - a.prefill_len;
