@@ -1,0 +1,333 @@
+#!/usr/bin/env python3
+"""bench.py — codes-to-audio hot path of qwen3-tts.cpp on B200 (this repo) or on the host CPU
+(the unmodified reference, --impl reference).
+
+One *step* = one utterance through the hot path: prompt prefill, `--frames` greedy 12.5 Hz frames
+(talker decode step + 15-pass code predictor each) and the vocoder over those frames.
+Metric (BASELINE.json): audio-seconds generated per wall-second.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo, N ranks under torchrun for N>1
+    python bench.py --impl reference --steps K --warmup W    # reference ggml-CPU path, bounded sample
+
+Prints ONE JSON line on rank 0.  `value` = device-resident throughput (prompt already staged in
+HBM, CUDA events on the engine stream); `e2e` = the same through TTSTransformer.generate +
+AudioTokenizerDecoder.decode with host buffers; `roofline` = the persistent decode kernel
+(one launch = one frame) against the measured HBM peak; `cpu_baseline` = oracle/_ref timed on
+this box's host cores on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "audio_seconds_per_wall_second"
+UNIT = "audio-s/s"
+FRAME_RATE = 12.5
+
+# algorithmic bytes (SURVEY.md §8d / DESIGN.md §5), F16 weights
+TALKER_STEP_BYTES = {"f16": 887_357_440, "q8_0": 474_480_640}
+CODEPRED_FRAME_BYTES = {"f16": 2_422_963_200, "q8_0": 1_317_043_200}
+KV_BYTES_PER_POS = 114_688
+
+
+def n_samples(frames: int) -> int:
+    return 1920 * frames - 555 if frames > 0 else 0
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.stop_ev, self.th = index, [], threading.Event(), None
+
+    def _loop(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop_ev.is_set():
+            try:
+                r = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=5)
+                f = [x.strip() for x in r.stdout.strip().split(",")]
+                if len(f) >= 6:
+                    self.rows.append(f)
+            except Exception:
+                pass
+            self.stop_ev.wait(0.2)
+
+    def start(self):
+        self.th = threading.Thread(target=self._loop, daemon=True)
+        self.th.start()
+
+    def stop(self):
+        self.stop_ev.set()
+        if self.th:
+            self.th.join(timeout=6)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(int(float(r[0])) for r in self.rows)
+        reasons = []
+        for i, name in enumerate(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]):
+            if any(r[2 + i].lower().startswith("active") for r in self.rows):
+                reasons.append(name)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": int(float(self.rows[0][1])), "reasons": reasons,
+                "samples": len(sm)}
+
+
+def workload(frames):
+    from util import HELLO_FULL
+    rng = np.random.default_rng(2024)
+    spk = (rng.standard_normal(1024) * 0.05).astype(np.float32)     # stands in for the ECAPA x-vector (config 2)
+    return HELLO_FULL, spk, frames
+
+
+# ------------------------------------------------------------------------------ reference arm
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    from oracle import reflib
+    from util import models
+    if not reflib.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libq3t_ref.so was not built"}))
+        return
+    cores = os.cpu_count() or 1
+    reflib.RefLib.get().set_threads(cores)
+    tts_path, voc_path = models("full", args.wtype)
+    tokens, spk, _ = workload(args.frames)
+    sample_frames = args.ref_frames
+    ref = reflib.RefTTS(tts_path)
+    dec = reflib.RefDecoder(voc_path)
+
+    def step():
+        codes = ref.generate(tokens, spk, sample_frames, temperature=0.0)
+        wav = dec.decode(codes)
+        return codes, wav
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        codes, wav = step()
+    dt = time.perf_counter() - t0
+    audio_s = len(wav) / 24000.0 * args.steps
+    v = audio_s / dt
+    sample = f"{sample_frames} greedy frames (generate) + vocoder over them per step, ggml-CPU AVX2 build, {cores} threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f16" if args.wtype == "f16" else "q8_0", "data": "synthetic",
+        "config": {"workload": f"0.6B {args.wtype.upper()} voice-clone-style prompt ('Hello, world!' + 1024-d speaker vector), greedy, "
+                               f"bounded sample of {sample_frames} frames per step on the host CPU", "frames": sample_frames},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ------------------------------------------------------------------------------ this repo
+def cpu_baseline(args):
+    """oracle/_ref on the host cores, bounded sample (rank 0, N=1 only)."""
+    try:
+        from oracle import reflib
+        from util import models
+        if not reflib.available():
+            return None
+        cores = os.cpu_count() or 1
+        reflib.RefLib.get().set_threads(cores)
+        tts_path, voc_path = models("full", args.wtype)
+        tokens, spk, _ = workload(args.frames)
+        n = args.ref_frames
+        ref = reflib.RefTTS(tts_path)
+        dec = reflib.RefDecoder(voc_path)
+        ref.generate(tokens, spk, 2, temperature=0.0)                 # warm the page cache / threadpool
+        t0 = time.perf_counter()
+        codes = ref.generate(tokens, spk, n, temperature=0.0)
+        t1 = time.perf_counter()
+        wav = dec.decode(codes)
+        t2 = time.perf_counter()
+        ref.close(); dec.close()
+        return {"value": (len(wav) / 24000.0) / (t2 - t0), "unit": UNIT, "cores": cores, "kind": "reference",
+                "sample": f"{n} greedy frames + vocoder over them, ggml-CPU AVX2 build at {cores} threads "
+                          f"(generate {(t1 - t0) / n * 1e3:.1f} ms/frame, vocoder {(t2 - t1) / n * 1e3:.1f} ms/frame)"}
+    except Exception as e:                                            # the baseline never takes the bench down
+        return {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference", "sample": f"failed: {e}"}
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — this engine has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    os.environ["QWEN3_TTS_DEVICE"] = str(local_rank)
+
+    from util import pkg, models
+    m = pkg()
+    if rank == 0:
+        models("full", args.wtype)                                     # one rank writes the GGUFs
+    if dist:
+        dist.barrier()
+    tts_path, voc_path = models("full", args.wtype)
+    tokens, spk, frames = workload(args.frames)
+
+    t = m.TTSTransformer()
+    if not t.load_model(tts_path):
+        raise SystemExit("load_model: " + t.get_error())
+    d = m.AudioTokenizerDecoder()
+    have_voc = (not args.no_vocoder) and d.load_model(voc_path)
+    if not have_voc and not args.no_vocoder:
+        raise SystemExit("decoder load_model: " + d.get_error())
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def step_resident():
+        return t.run_staged(frames, repetition_penalty=1.05, temperature=0.0, top_k=0, seed=0, with_vocoder=have_voc)
+
+    def step_e2e():
+        codes = t.generate(tokens, spk, frames, repetition_penalty=1.05, temperature=0.0, top_k=0)
+        if codes is None:
+            raise SystemExit("generate: " + t.get_error())
+        wav = d.decode(codes) if have_voc else np.zeros(n_samples(len(codes)), np.float32)
+        if wav is None:
+            raise SystemExit("decode: " + d.get_error())
+        return codes, wav
+
+    # ---- warm-up (both paths)
+    t.stage_prompt(tokens, spk)
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    step_e2e()
+
+    # ---- timed: device-resident (`value`)
+    t.stage_prompt(tokens, spk)
+    sampler = ClockSampler(local_rank)
+    launches0 = t.timing().kernel_launches
+    sync_all()
+    sampler.start()
+    w0 = time.perf_counter()
+    dev_ms = prefill_ms = frames_ms = voc_ms = 0.0
+    nf = ns = 0
+    for _ in range(args.steps):
+        nf, ns = step_resident()
+        tm = t.timing()
+        prefill_ms += tm.prefill_ms; frames_ms += tm.frames_ms; voc_ms += tm.vocoder_ms
+    sync_all()
+    wall_s = time.perf_counter() - w0
+    clocks = sampler.stop()
+    launches = t.timing().kernel_launches - launches0
+    dev_ms = prefill_ms + frames_ms + voc_ms
+    # the steps run back to back on one stream; the bracketed wall time is the honest whole-step figure
+    step_s = wall_s / args.steps
+    audio_s = (ns if have_voc else n_samples(nf)) / 24000.0
+
+    # ---- timed: end to end through the host classes (`e2e`)
+    sync_all()
+    e0 = time.perf_counter()
+    for _ in range(args.steps):
+        codes, wav = step_e2e()
+    sync_all()
+    e2e_s = (time.perf_counter() - e0) / args.steps
+
+    # ---- talker decode step alone (north-star: HBM GB/s of the batch-1 talker step)
+    n_mid = t.cfg_prefill_len if hasattr(t, "cfg_prefill_len") else 10
+    us_step = t.bench_talker_step(n_mid + frames // 2, 64)
+
+    times = torch.tensor([step_s, e2e_s], dtype=torch.float64, device="cuda")
+    if dist:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    step_s, e2e_s = float(times[0]), float(times[1])
+
+    if rank == 0:
+        peak, peak_kind = measured_peaks()
+        avg_kv = 10 + frames / 2.0
+        frame_bytes = CODEPRED_FRAME_BYTES[args.wtype] + TALKER_STEP_BYTES[args.wtype] + KV_BYTES_PER_POS * (avg_kv + 1)
+        frame_us = frames_ms / args.steps / max(nf, 1) * 1e3
+        achieved = frame_bytes / (frame_us * 1e-6) / 1e9
+        talker_bytes = TALKER_STEP_BYTES[args.wtype] + KV_BYTES_PER_POS * (n_mid + frames // 2 + 1)
+        out = {
+            "metric": METRIC, "value": world * audio_s / step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f16" if args.wtype == "f16" else "q8_0 weights, int8 x int8 / f32 accumulate",
+            "data": "synthetic (seeded random-init GGUF of the real 0.6B shapes; no checkpoint offline)",
+            "config": {"workload": f"0.6B {args.wtype.upper()} voice-clone-style prompt ('Hello, world!' + 1024-d speaker vector), "
+                                   f"greedy, {frames} frames + vocoder, batch 1 per GPU, one utterance per rank per step",
+                       "frames": nf, "samples": ns, "batch_per_gpu": 1, "vocoder": bool(have_voc),
+                       "l2": "weights streamed per frame (3.3 GB) exceed the 126 MB L2; no explicit flush",
+                       "parallelism": f"request-parallel x{world} (no collective)"},
+            "device_ms_per_step": {"prefill": prefill_ms / args.steps, "frames": frames_ms / args.steps,
+                                   "vocoder": voc_ms / args.steps, "events_total": dev_ms / args.steps},
+            "e2e": {"value": world * audio_s / e2e_s, "unit": UNIT,
+                    "h2d_bytes_per_step": int(tokens.nbytes + spk.nbytes + codes.nbytes),
+                    "d2h_bytes_per_step": int(codes.nbytes + wav.nbytes), "ms_per_step": e2e_s * 1e3},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": "lm_kernel (one launch = one frame: 16 code-predictor passes + 1 talker step)",
+                         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "peak_source": peak_kind, "traffic": None, "us_per_launch": frame_us,
+                         "algorithmic_bytes_per_launch": int(frame_bytes)},
+            "talker_step": {"us": us_step, "algorithmic_bytes": int(talker_bytes),
+                            "achieved_gbs": talker_bytes / (us_step * 1e-6) / 1e9,
+                            "frac": talker_bytes / (us_step * 1e-6) / 1e9 / peak, "n_kv": n_mid + frames // 2 + 1},
+            "realtime_factor_per_gpu": audio_s / step_s,
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cb = cpu_baseline(args)
+            if cb:
+                out["cpu_baseline"] = cb
+        print(json.dumps(out))
+    if dist:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--frames", type=int, default=320)
+    ap.add_argument("--ref-frames", type=int, default=96, help="frames per bounded CPU sample")
+    ap.add_argument("--wtype", default="f16", choices=["f16", "q8_0"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-vocoder", action="store_true", help="debug only: codes without the waveform (not a valid bench value)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,87 @@
+#!/usr/bin/env python3
+"""TEST INFRASTRUCTURE — writes the golden vectors under tests/golden/ by running the UNMODIFIED
+reference (oracle/_ref/libq3t_ref.so, built by oracle/Makefile.ref from /root/reference) on the
+seeded random-init GGUFs of tools/make_random_gguf.py.
+
+    make -f oracle/Makefile.ref -j8 && python oracle/gen_golden.py [--full]
+
+The reference build pins AVX2+FMA+F16C, so its F32 summation order — and every vector written
+here — is identical on any x86-64 host with those extensions (checked: build container vs GPU box).
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from oracle import reflib  # noqa: E402
+from util import models, HELLO_TINY, HELLO_FULL, GOLDEN  # noqa: E402
+
+
+def golden_inputs(seed=0):
+    rng = np.random.default_rng(seed)
+    spk = (rng.standard_normal(1024) * 0.05).astype(np.float32)
+    step_x = (rng.standard_normal(1024) * 0.05).astype(np.float32)
+    return spk, step_x
+
+
+def gen_tts(preset, wtype, tokens, n_frames, out):
+    tts, _ = models(preset, wtype)
+    ref = reflib.RefTTS(tts)
+    spk, step_x = golden_inputs()
+    pre, trail, pad = ref.build_prompt(tokens, spk)
+    pre_ns, trail_ns, _ = ref.build_prompt(tokens, None, -1)           # no speaker, no language row
+    ref.init_kv(64)
+    hid, logits = ref.prefill(pre)
+    step_logits, step_hidden = ref.step(step_x, pre.shape[0])
+    cb0 = int(step_logits[:2048].argmax())
+    cp_codes = ref.predict_codes_ar(step_hidden, cb0, 0.0, 0)
+    codes = ref.generate(tokens, spk, n_frames, rep_penalty=1.05, temperature=0.0)
+    codes_nospk = ref.generate(tokens, None, min(n_frames, 8), language_id=-1, rep_penalty=1.0, temperature=0.0)
+    np.savez_compressed(out, tokens=tokens, spk=spk, step_x=step_x,
+                        prefill=pre.astype(np.float32), trailing=trail, pad=pad,
+                        prefill_nospk=pre_ns, trailing_nospk=trail_ns,
+                        prefill_hidden_last=hid[-1], prefill_logits=logits,
+                        step_logits=step_logits, step_hidden=step_hidden,
+                        cp_cb0=np.int32(cb0), cp_codes=cp_codes, codes=codes, codes_nospk=codes_nospk)
+    ref.close()
+    print("wrote", out, "frames", codes.shape)
+    return codes
+
+
+def gen_vocoder(codes, out, T):
+    _, voc = models("tiny", "f16")
+    dec = reflib.RefDecoder(voc)
+    codes = np.ascontiguousarray(codes[:T] % 2048, np.int32)
+    wav = dec.decode(codes)
+    one = dec.decode(codes[:1])
+    np.savez_compressed(out, codes=codes, wav=wav.astype(np.float32), wav_1frame=one.astype(np.float32))
+    dec.close()
+    print("wrote", out, wav.shape, "rms", float(np.sqrt((wav ** 2).mean())), "peak", float(np.abs(wav).max()))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--full", action="store_true", help="also write the full-size (28-layer) goldens")
+    ap.add_argument("--threads", type=int, default=8)
+    a = ap.parse_args()
+    if not reflib.available():
+        sys.exit("oracle/_ref/libq3t_ref.so missing: make -f oracle/Makefile.ref")
+    reflib.RefLib.get().set_threads(a.threads)
+    os.makedirs(GOLDEN, exist_ok=True)
+    codes = gen_tts("tiny", "f16", HELLO_TINY, 16, os.path.join(GOLDEN, "tiny_f16.npz"))
+    gen_tts("tiny", "q8_0", HELLO_TINY, 16, os.path.join(GOLDEN, "tiny_q8_0.npz"))
+    gen_vocoder(codes, os.path.join(GOLDEN, "vocoder_f16.npz"), 6)
+    if a.full:
+        gen_tts("full", "f16", HELLO_FULL, 64, os.path.join(GOLDEN, "full_f16.npz"))
+        gen_tts("full", "q8_0", HELLO_FULL, 64, os.path.join(GOLDEN, "full_q8_0.npz"))
+
+
+if __name__ == "__main__":
+    main()

@@ -121,14 +121,21 @@ ORC_API void orc_linear(const void * W, int wtype, int N, int K, const float * x
         for (int m = 0; m < M; ++m) {
             quant_row_q8_0(x + (size_t) m * K, xq, K);
             for (int n = 0; n < N; ++n) {
+                /* ggml_vec_dot_q8_0_q8_0, AVX2 (arch/x86/quants.c:1029-1046): lane j of the 8-wide
+                 * accumulator takes the int sum of bytes 4j..4j+3 of every block (maddubs + madd),
+                 * acc[j] = fma(dW*dA, (float) sum4, acc[j]); hsum_float_8 (:43-49) folds
+                 * ((a4+a0)+(a6+a2)) + ((a5+a1)+(a7+a3)) */
                 const blk_q8_0 * w = (const blk_q8_0 *) W + (size_t) n * nb;
-                float acc = 0.f;
+                float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
                 for (int b = 0; b < nb; ++b) {
-                    int32_t s = 0;
-                    for (int j = 0; j < 32; ++j) s += (int32_t) w[b].qs[j] * (int32_t) xq[b].qs[j];
-                    acc += (h2f(w[b].d) * h2f(xq[b].d)) * (float) s;
+                    const float d = h2f(w[b].d) * h2f(xq[b].d);
+                    for (int j = 0; j < 8; ++j) {
+                        int32_t s4 = 0;
+                        for (int e = 0; e < 4; ++e) s4 += (int32_t) w[b].qs[4 * j + e] * (int32_t) xq[b].qs[4 * j + e];
+                        a[j] = fmaf(d, (float) s4, a[j]);
+                    }
                 }
-                y[(size_t) m * N + n] = acc;
+                y[(size_t) m * N + n] = ((a[4] + a[0]) + (a[6] + a[2])) + ((a[5] + a[1]) + (a[7] + a[3]));
             }
         }
         free(xq);
@@ -310,18 +317,23 @@ ORC_API void orc_stack_forward(const orc_stack * s, const float * x_in, int M, i
                         o[d] = dot_f32_ff(vt, pr, M);
                     }
                 } else {
+                    /* the graph scores all W = pos0+M cache rows, masks t > pos with -inf
+                     * (diag_mask_inf) and soft-maxes / multiplies rows of length W
+                     * (src/tts_transformer.cpp:1205-1227): W decides which positions go through
+                     * the 8-wide SIMD exp vs the libm tail, and the 32-wide part of the P.V dot */
+                    const int W = pos0 + M;
                     for (int d = 0; d < D; ++d) qh16[d] = f2h(qh[d]);
                     float mx = -INFINITY;
-                    for (int t = 0; t < n_kv; ++t) {
-                        sc[t] = dot_f16_hh(kc + (size_t) t * KN + kvh * D, qh16, D) * kq_scale;
+                    for (int t = 0; t < W; ++t) {
+                        sc[t] = (t < n_kv) ? dot_f16_hh(kc + (size_t) t * KN + kvh * D, qh16, D) * kq_scale : -INFINITY;
                         if (sc[t] > mx) mx = sc[t];
                     }
-                    const double sum = soft_max_vec(pr, sc, n_kv, mx);   /* ops.cpp:5243-5259 */
+                    const double sum = soft_max_vec(pr, sc, W, mx);      /* ops.cpp:5243-5259 */
                     const float inv = (float) (1.0 / sum);
-                    for (int t = 0; t < n_kv; ++t) ph[t] = f2h(pr[t] * inv);
+                    for (int t = 0; t < W; ++t) ph[t] = f2h(pr[t] * inv);
                     for (int d = 0; d < D; ++d) {
-                        for (int t = 0; t < n_kv; ++t) vth[t] = vc[(size_t) t * KN + kvh * D + d];
-                        o[d] = dot_f16_hh(vth, ph, n_kv);
+                        for (int t = 0; t < W; ++t) vth[t] = vc[(size_t) t * KN + kvh * D + d];
+                        o[d] = dot_f16_hh(vth, ph, W);
                     }
                 }
             }

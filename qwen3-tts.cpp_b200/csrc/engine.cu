@@ -414,7 +414,7 @@ static int upload_passes(q3t_ctx * ctx, const std::vector<PassDesc> & v, int off
 static PassDesc make_pass(int stack, int xmode, int arg, int pos, int f32attn, int head, int n_layers, int process) {
     PassDesc p{};
     p.stack = stack; p.xmode = xmode; p.arg = arg; p.pos = pos; p.f32attn = f32attn; p.head = head;
-    p.n_layers = n_layers; p.process = process;
+    p.n_layers = n_layers; p.process = process; p.width = 0;
     p.xsrc = nullptr; p.hidden_dst = nullptr; p.logits_dst = nullptr;
     return p;
 }
@@ -462,6 +462,7 @@ static int run_talker_rows(q3t_ctx * ctx, const float * embd_dev, int n_tokens, 
             const bool last = r == n_tokens - 1;
             PassDesc p = make_pass(0, XM_BUF, 0, n_past + r, 0, (all_heads || last) ? 0 : -1, L, last ? process : 0);
             p.xsrc = embd_dev + (size_t) r * H;
+            p.width = n_past + n_tokens;               // the reference scores the whole prefill block per row
             if (hidden_all_dev && (all_heads || last)) p.hidden_dst = hidden_all_dev + (size_t) r * H;
             v.push_back(p);
         }

@@ -64,6 +64,7 @@ struct PassDesc {
     int head;          // -1 none, 0 talker codec_head, 1..15 -> code_pred.lm_head[head-1]
     int n_layers;      // layers to run (<= stack layers)
     int process;       // 1: apply suppress / repetition penalty to the talker logits before select
+    int width;         // soft-max row width of the reference graph (n_past + n_tokens in a prefill); 0 -> pos + 1
     const float * xsrc;
     float * hidden_dst;   // optional extra copy of the normed hidden (device)
     float * logits_dst;   // optional extra copy of the raw logits (device)

@@ -294,11 +294,16 @@ __device__ __forceinline__ float ld_half_cg(const __half * p) {
     return __half2float(__ushort_as_half(u));
 }
 
-__device__ void attention_phase(const DevModel & m, const StackW & W, int l, int pos, bool f32attn,
+__device__ void attention_phase(const DevModel & m, const StackW & W, int l, int pos, bool f32attn, int width,
                                 Smem & s, BarState & bs) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int g = blockIdx.x % NKV, c = blockIdx.x / NKV;
     const int n_kv = pos + 1;
+    // row width of the reference graph: a prefill scores all n_past + n_tokens cache rows and masks
+    // the future ones with -inf (src/tts_transformer.cpp:1205-1227); masked entries add exact zeros,
+    // but the width decides which positions take the 8-wide SIMD exp vs the libm tail and which
+    // take the 32-lane part of the P.V dot vs its double-precision leftovers.
+    const int wd = width > n_kv ? width : n_kv;
     const int C = attn_splits(n_kv, f32attn);
     const bool active = c < C;
     const float kq_scale = 1.0f / sqrtf((float) HD);
@@ -429,9 +434,10 @@ __device__ void attention_phase(const DevModel & m, const StackW & W, int l, int
         const float * pm = m.part_ms + (size_t) (g * 16 + i) * 2;
         M0 = fmaxf(M0, ld_act(pm)); M1 = fmaxf(M1, ld_act(pm + 1));
     }
-    const int n8 = n_kv >> 3;
+    const int n8 = wd >> 3;                                  // chunks that take the SIMD exp
+    const int n8v = min(n8, (n_kv + 7) >> 3);                // ... of which these hold unmasked positions
     double ds0 = 0.0, ds1 = 0.0;
-    for (int ch = t; ch < n8; ch += LM_THREADS) {          // ggml_vec_soft_max_f32, 8 lanes at a time (vec.cpp:558-568)
+    for (int ch = t; ch < n8v; ch += LM_THREADS) {          // ggml_vec_soft_max_f32, 8 lanes at a time (vec.cpp:558-568)
         float e0[8], e1[8];
         const float4 * p0 = reinterpret_cast<const float4 *>(sb0 + ch * 8);
         const float4 * p1 = reinterpret_cast<const float4 *>(sb1 + ch * 8);
@@ -439,13 +445,17 @@ __device__ void attention_phase(const DevModel & m, const StackW & W, int l, int
         const float xs[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
         const float ys[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { e0[j] = v_expf(__fsub_rn(xs[j], M0)); e1[j] = v_expf(__fsub_rn(ys[j], M1)); }
+        for (int j = 0; j < 8; ++j) {
+            const bool live = ch * 8 + j < n_kv;             // masked: exp(-inf) = +0
+            e0[j] = live ? v_expf(__fsub_rn(xs[j], M0)) : 0.0f;
+            e1[j] = live ? v_expf(__fsub_rn(ys[j], M1)) : 0.0f;
+        }
         ds0 += (double) __fadd_rn(__fadd_rn(__fadd_rn(e0[4], e0[0]), __fadd_rn(e0[6], e0[2])),
                                   __fadd_rn(__fadd_rn(e0[5], e0[1]), __fadd_rn(e0[7], e0[3])));
         ds1 += (double) __fadd_rn(__fadd_rn(__fadd_rn(e1[4], e1[0]), __fadd_rn(e1[6], e1[2])),
                                   __fadd_rn(__fadd_rn(e1[5], e1[1]), __fadd_rn(e1[7], e1[3])));
     }
-    if (t < (n_kv & 7)) {                                   // scalar tail: libm expf
+    if (n8 * 8 + t < n_kv && t < 8) {                       // scalar tail: libm expf
         const int tt = n8 * 8 + t;
         ds0 += (double) tail_expf(__fsub_rn(ld_act(sb0 + tt), M0));
         ds1 += (double) tail_expf(__fsub_rn(ld_act(sb1 + tt), M1));
@@ -468,7 +478,7 @@ __device__ void attention_phase(const DevModel & m, const StackW & W, int l, int
     // ---- stage 2: o[d] for this CTA's nd = 128/C dims, both heads
     const int nd = HD / C, d0 = c * nd;
     const int TB = VT_HALVES / nd;                          // positions per V^T tile (multiple of 32)
-    const int np = n_kv & ~31;
+    const int np = min(wd & ~31, n_kv);                     // positions in the 32-lane part of the dot
     const int ndg = nd >> 3;                                // 16-byte groups per position
     float acc0[8], acc1[8];                                 // up to 8 dims per warp (nd = 128)
 #pragma unroll
@@ -738,7 +748,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         grid_barrier(m, bs);
 
         // ---- phase B: per-head norm + RoPE + KV append + attention
-        attention_phase(m, W, l, pos, p.f32attn != 0, s, bs);
+        attention_phase(m, W, l, pos, p.f32attn != 0, p.width, s, bs);
         grid_barrier(m, bs);
 
         // ---- phase C: attn_output mat-vec (input rounded to F16) + residual
