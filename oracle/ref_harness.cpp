@@ -203,6 +203,17 @@ int ref_tts_trace_step(void * h, const float * embd, int32_t n_past) {
     if (!ok) { g_err = t->get_error(); return -1; }
     return (int) g_trace.size();
 }
+// per-node trace of one vocoder decode (named nodes: vq_output, pre_conv_output, pre_tfm_input, ...)
+int ref_dec_trace(void * h, const int32_t * codes, int32_t n_frames) {
+    auto * d = (AudioTokenizerDecoder *) h;
+    g_trace.clear();
+    ggml_backend_sched_set_eval_callback(d->state_.sched, trace_cb, nullptr);
+    std::vector<float> s;
+    bool ok = d->decode(codes, n_frames, s);
+    ggml_backend_sched_set_eval_callback(d->state_.sched, nullptr, nullptr);
+    if (!ok) { g_err = d->get_error(); return -1; }
+    return (int) g_trace.size();
+}
 int ref_trace_info(int i, char * name, char * op, int64_t * ne, int * type, long * n) {
     if (i < 0 || i >= (int) g_trace.size()) return -1;
     strncpy(name, g_trace[i].name.c_str(), 63); name[63] = 0;

@@ -177,6 +177,30 @@ class RefDecoder:
         return out[:n].copy()
 
 
+def trace_decoder(dec: "RefDecoder", codes):
+    """Debug aid: run one decode with ggml's eval callback and return {node name: float array (ggml order)}."""
+    L = dec.lib.L
+    L.ref_dec_trace.argtypes = [C.c_void_p, _i32p, C.c_int32]
+    L.ref_trace_info.argtypes = [C.c_int, C.c_char_p, C.c_char_p, C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_long)]
+    L.ref_trace_data.argtypes = [C.c_int, _f32p]
+    codes = np.ascontiguousarray(codes, np.int32)
+    n = L.ref_dec_trace(dec.h, _ip(codes), codes.shape[0])
+    if n < 0:
+        raise RuntimeError(dec.lib.err())
+    out = {}
+    for i in range(n):
+        name, op = C.create_string_buffer(64), C.create_string_buffer(32)
+        ne = (C.c_int64 * 4)(); ty = C.c_int(0); cnt = C.c_long(0)
+        L.ref_trace_info(i, name, op, ne, C.byref(ty), C.byref(cnt))
+        nm = name.value.decode()
+        if cnt.value == 0:
+            continue
+        buf = np.zeros(cnt.value, np.float32)
+        L.ref_trace_data(i, _fp(buf))
+        out[f"{i:04d}:{op.value.decode()}:{nm}"] = (buf, [int(x) for x in ne])
+    return out
+
+
 def speaker_embed(tts_model_path: str, samples_24k: np.ndarray) -> np.ndarray:
     lib = RefLib.get()
     s = np.ascontiguousarray(samples_24k, np.float32)

@@ -13,7 +13,7 @@ AudioTokenizerDecoder::~AudioTokenizerDecoder() { unload_model(); }
 void AudioTokenizerDecoder::unload_model() {
     if (engine_) {
         q3t_unload(engine_, 2);
-        release_preferred_backend(engine_);
+        release_preferred_backend(engine_, "AudioTokenizerDecoder");
         engine_ = nullptr;
     }
     loaded_ = false;

@@ -2,17 +2,29 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 namespace qwen3_tts {
 
 namespace {
-struct shared_backend_state {
-    q3t_ctx * backend = nullptr;
-    int32_t ref_count = 0;
+// The reference shares one ggml backend between all components of a process
+// (src/gguf_loader.cpp:10-82).  Here an engine context also owns the model state of at most one
+// transformer and one vocoder (so generate -> decode can stay on the device), hence a small pool:
+// a component takes the first context on its device whose slot of its kind is free.
+enum slot_kind { SLOT_TTS = 0, SLOT_DEC = 1, SLOT_OTHER = 2 };
+struct engine_entry {
+    q3t_ctx * ctx = nullptr;
+    int device = 0;
+    int32_t refs[3] = {0, 0, 0};
 };
-shared_backend_state & get_shared_backend_state() {
-    static shared_backend_state state;
-    return state;
+std::vector<engine_entry> & engine_pool() {
+    static std::vector<engine_entry> pool;
+    return pool;
+}
+slot_kind kind_of(const char * component_name) {
+    if (component_name && strstr(component_name, "TTSTransformer")) return SLOT_TTS;
+    if (component_name && strstr(component_name, "AudioTokenizerDecoder")) return SLOT_DEC;
+    return SLOT_OTHER;
 }
 }
 
@@ -21,10 +33,14 @@ GGUFLoader::~GGUFLoader() { close(); }
 
 q3t_ctx * init_preferred_backend(const char * component_name, std::string * error_msg) {
     if (error_msg) error_msg->clear();
-    auto & shared = get_shared_backend_state();
-    if (shared.backend) { shared.ref_count++; return shared.backend; }
     int device = 0;
     if (const char * e = std::getenv("QWEN3_TTS_DEVICE")) device = std::atoi(e);
+    const slot_kind kind = kind_of(component_name);
+    auto & pool = engine_pool();
+    for (auto & e : pool) {
+        if (e.device != device) continue;
+        if (kind == SLOT_OTHER || e.refs[kind] == 0) { e.refs[kind]++; return e.ctx; }
+    }
     q3t_ctx * ctx = nullptr;
     if (q3t_ctx_create(device, &ctx) != Q3T_OK || !ctx) {
         if (error_msg) {
@@ -33,19 +49,22 @@ q3t_ctx * init_preferred_backend(const char * component_name, std::string * erro
         }
         return nullptr;
     }
-    shared.backend = ctx;
-    shared.ref_count = 1;
+    engine_entry e;
+    e.ctx = ctx; e.device = device; e.refs[kind] = 1;
+    pool.push_back(e);
     return ctx;
 }
 
-void release_preferred_backend(q3t_ctx * backend) {
+void release_preferred_backend(q3t_ctx * backend, const char * component_name) {
     if (!backend) return;
-    auto & shared = get_shared_backend_state();
-    if (shared.backend == backend) {
-        if (--shared.ref_count <= 0) {
-            q3t_ctx_destroy(shared.backend);
-            shared.backend = nullptr;
-            shared.ref_count = 0;
+    const slot_kind kind = kind_of(component_name);
+    auto & pool = engine_pool();
+    for (size_t i = 0; i < pool.size(); ++i) {
+        if (pool[i].ctx != backend) continue;
+        if (pool[i].refs[kind] > 0) pool[i].refs[kind]--;
+        if (pool[i].refs[0] + pool[i].refs[1] + pool[i].refs[2] <= 0) {
+            q3t_ctx_destroy(backend);
+            pool.erase(pool.begin() + (long) i);
         }
         return;
     }

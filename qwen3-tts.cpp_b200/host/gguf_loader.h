@@ -45,10 +45,11 @@ bool load_tensor_data_from_file(const GGUFLoader & loader, q3t_ctx * engine,
                                 const char * const * prefixes, int n_prefixes,
                                 std::string & error_msg, int64_t * n_uploaded = nullptr);
 
-// Process-wide, ref-counted engine context = the reference's shared backend singleton
-// (src/gguf_loader.cpp:10-82).  The CUDA device is taken from QWEN3_TTS_DEVICE (default 0);
+// Process-wide, ref-counted engine contexts = the reference's shared backend singleton
+// (src/gguf_loader.cpp:10-82); one context serves one transformer and one vocoder, further
+// instances of the same component get their own context.  The CUDA device is taken from QWEN3_TTS_DEVICE (default 0);
 // there is no IGPU/ACCEL/CPU fallback chain: without a B200 this returns nullptr.
 q3t_ctx * init_preferred_backend(const char * component_name, std::string * error_msg);
-void release_preferred_backend(q3t_ctx * backend);
+void release_preferred_backend(q3t_ctx * backend, const char * component_name = nullptr);
 
 } // namespace qwen3_tts

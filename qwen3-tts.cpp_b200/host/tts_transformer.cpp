@@ -22,7 +22,7 @@ bool TTSTransformer::fail(int rc) {
 void TTSTransformer::unload_model() {
     if (engine_) {
         q3t_unload(engine_, 1);
-        release_preferred_backend(engine_);
+        release_preferred_backend(engine_, "TTSTransformer");
         engine_ = nullptr;
     }
     loaded_ = false;

@@ -1,0 +1,77 @@
+"""Vocoder parity (AudioTokenizerDecoder::decode, src/audio_tokenizer_decoder.cpp:804-879) — B200 only.
+
+Floating-point path: the bar is BASELINE.json's waveform SNR >= 30 dB against the reference's
+waveform for the SAME codes; the kernels keep the reference's rounding points, so the measured
+SNR is far above that and the tests also assert a tighter internal floor.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from util import GOLDEN, models, snr_db
+
+pytestmark = pytest.mark.gpu
+
+SNR_MIN_DB = 30.0          # north-star tolerance
+SNR_EXPECT_DB = 55.0       # what matching rounding points should give; a regression alarm
+
+
+@pytest.fixture(scope="module")
+def dec(q3t):
+    d = q3t.AudioTokenizerDecoder()
+    assert d.load_model(models("tiny", "f16")[1]), d.get_error()
+    yield d
+    d.close()
+
+
+def test_decode_matches_golden_waveform(dec):
+    g = np.load(os.path.join(GOLDEN, "vocoder_f16.npz"))
+    wav = dec.decode(g["codes"])
+    assert wav is not None, dec.get_error()
+    assert wav.shape == g["wav"].shape == (1920 * 6 - 555,)
+    assert np.abs(wav).max() <= 1.0
+    s = snr_db(g["wav"], wav)
+    assert s >= SNR_MIN_DB and s >= SNR_EXPECT_DB, f"SNR {s:.1f} dB"
+    one = dec.decode(g["codes"][:1])                         # 1-frame decode (tests/test_decoder.cpp:106-116)
+    assert one.shape == g["wav_1frame"].shape == (1365,)
+    assert snr_db(g["wav_1frame"], one) >= SNR_EXPECT_DB
+
+
+def test_causality_prefix_property(dec):
+    """The vocoder is fully causal (left pads only), so decoding a prefix of the codes gives a prefix
+    of the waveform up to the ConvT trims — a size-independent check at a larger T."""
+    rng = np.random.default_rng(9)
+    codes = rng.integers(0, 2048, size=(40, 16), dtype=np.int32)
+    full = dec.decode(codes)
+    part = dec.decode(codes[:17])
+    assert full.shape == (1920 * 40 - 555,) and part.shape == (1920 * 17 - 555,)
+    n = len(part) - 2400                                     # stay clear of the trimmed right edge
+    assert snr_db(full[:n], part[:n]) > 90.0
+
+
+def test_error_behaviour(q3t, dec):
+    assert dec.L.q3t_dec_decode(dec.h, None, 4, None, 0) < 0
+    assert dec.decode(np.zeros((0, 16), np.int32)) is None
+    fresh = q3t.AudioTokenizerDecoder()
+    assert fresh.decode(np.zeros((2, 16), np.int32)) is None and fresh.get_error() == "Model not loaded"
+    assert fresh.load_model(models("tiny", "f16")[0]) is False       # a TTS file has no tok_dec.* tensors
+    assert fresh.get_error() == "No decoder tensors found in model"
+    fresh.close()
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(os.path.dirname(GOLDEN), "..", "oracle", "_ref", "libq3t_ref.so")),
+                    reason="oracle/_ref not shipped")
+@pytest.mark.parametrize("T", [2, 33])
+def test_decode_vs_live_reference(dec, T):
+    from oracle import reflib
+    reflib.RefLib.get().set_threads(min(16, os.cpu_count() or 4))
+    ref = reflib.RefDecoder(models("tiny", "f16")[1])
+    rng = np.random.default_rng(100 + T)
+    codes = rng.integers(0, 2048, size=(T, 16), dtype=np.int32)
+    want = ref.decode(codes)
+    ref.close()
+    got = dec.decode(codes)
+    assert got is not None and got.shape == want.shape
+    s = snr_db(want, got)
+    assert s >= SNR_MIN_DB and s >= SNR_EXPECT_DB, f"T={T}: SNR {s:.1f} dB"
