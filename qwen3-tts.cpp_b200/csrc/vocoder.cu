@@ -189,8 +189,8 @@ __global__ void k_rope_qk(float * __restrict__ qkv, const float * __restrict__ r
         float * p = qkv + (size_t) t * 3 * LATENT + hh * THD;
         const float c = rr[d], s = rr[32 + d];
         const float x0 = p[d], x1 = p[d + 32];
-        p[d] = x0 * c - x1 * s;
-        p[d + 32] = x0 * s + x1 * c;
+        p[d] = __fmaf_rn(x0, c, -__fmul_rn(x1, s));         // contraction of the reference build (g++ -O3 -mfma)
+        p[d + 32] = __fmaf_rn(x0, s, __fmul_rn(x1, c));
     }
 }
 
