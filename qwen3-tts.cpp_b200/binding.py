@@ -98,6 +98,8 @@ def lib() -> C.CDLL:
         "q3t_get_timing": (C.c_int, [vp, C.POINTER(Timing)]), "q3t_weight_bytes": (C.c_int64, [vp, C.c_int32]),
         "q3t_vocoder_n_samples": (C.c_int64, [C.c_int32]), "q3t_kv_n_ctx": (C.c_int, [vp]),
         "q3t_device_info": (C.c_int, [vp, _i32p, _i32p, _i32p]),
+        "q3t_profile_arm": (C.c_int, [vp, C.c_int32, C.c_int32]),
+        "q3t_profile_read": (C.c_int, [vp, C.POINTER(C.c_uint64), C.c_int32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -332,6 +334,17 @@ class TTSTransformer:
         if rc != 0:
             raise Q3TError(self.L.q3t_last_error(self.engine()).decode())
         return us.value
+
+    def profile_arm(self, cta=0, cap=1 << 16):
+        if self.L.q3t_profile_arm(self.engine(), cta, cap) != 0:
+            raise Q3TError("profile_arm failed")
+
+    def profile_read(self, cap=1 << 16):
+        buf = np.zeros(cap, np.uint64)
+        n = self.L.q3t_profile_read(self.engine(), buf.ctypes.data_as(C.POINTER(C.c_uint64)), cap)
+        if n < 0:
+            raise Q3TError("profile_read failed")
+        return (buf[:n] >> np.uint64(8)).astype(np.int64), (buf[:n] & np.uint64(0xff)).astype(np.int64)
 
     def timing(self):
         t = Timing()

@@ -115,6 +115,9 @@ struct DevModel {
     unsigned long long * bar;        // grid barrier counter
     unsigned long long * gbar;       // [8] group barrier counters
     GenState * st;
+    // developer profiling (q3t_profile_arm): thread 0 of CTA prof_cta appends (clock64 << 8 | tag)
+    unsigned long long * prof; int prof_cap; int prof_cta;
+    unsigned int * prof_n;
 };
 
 constexpr int LM_THREADS = 512;
@@ -175,6 +178,7 @@ struct q3t_ctx {
     int last_n_frames = 0;
 
     q3t_timing timing{};
+    unsigned long long * d_prof = nullptr; unsigned int * d_prof_n = nullptr; int prof_cap = 0;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
 };
 

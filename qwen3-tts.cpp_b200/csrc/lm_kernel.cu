@@ -62,6 +62,15 @@ struct __align__(128) Smem {
     unsigned long long mbar[2];    // TMA completion barriers of buf0 / buf1
 };
 
+// ------------------------------------------------------------------------------- phase profiler
+__device__ __forceinline__ void prof_mark(const DevModel & m, int tag) {
+    if (m.prof && threadIdx.x == 0 && (int) blockIdx.x == m.prof_cta) {
+        const unsigned i = atomicAdd(m.prof_n, 1u);
+        if ((int) i < m.prof_cap) m.prof[i] = ((unsigned long long) clock64() << 8) | (unsigned long long) (tag & 0xff);
+    }
+}
+#define PROF(tag) prof_mark(m, tag)
+
 // ------------------------------------------------------------------------------- grid barriers
 struct BarState {
     unsigned long long target;       // grid barrier epoch target
@@ -740,34 +749,47 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
             else if (head) l2_prefetch_range(head->w + (size_t) h0 * H, (size_t) nH * H * 2);
         }
         // ---- phase A: RMSNorm + fused QKV mat-vec
+        PROF(1);
         rmsnorm_to_xf(s, W.attn_norm + (size_t) l * H, m.eps, nullptr);
+        PROF(2);
         wait_fetch(s, ws, 0);
+        PROF(3);
         gemv_chain<4, 1024>(s.buf0, nA, s);
         __syncthreads();
         if (t < nA) m.qkv[z.a0 + t] = s.outv[t];
         issue_fetch(s, ws, 0, sl_gu(W, l, z), 2 * nP, H * 2);
+        PROF(4);
         grid_barrier(m, bs);
+        PROF(5);
 
         // ---- phase B: per-head norm + RoPE + KV append + attention
         attention_phase(m, W, l, pos, p.f32attn != 0, p.width, s, bs);
+        PROF(6);
         grid_barrier(m, bs);
+        PROF(7);
 
         // ---- phase C: attn_output mat-vec (input rounded to F16) + residual
 #pragma unroll
         for (int i = 0; i < 4; ++i) s.xf[t + LM_THREADS * i] = r16(ld_act(m.part_o + t + LM_THREADS * i));
         __syncthreads();
+        PROF(8);
         wait_fetch(s, ws, 1);
+        PROF(9);
         gemv_chain<2, 2048>(s.buf1, nO, s);
         __syncthreads();
         if (t < nO) m.xb[z.o0 + t] = __fadd_rn(s.outv[t], s.xres[z.o0 + t]);
         issue_fetch(s, ws, 1, sl_d(W, l, z), nD, FFN * 2);
+        PROF(10);
         grid_barrier(m, bs);
+        PROF(11);
 
         // ---- phase D: RMSNorm + gate/up mat-vec + SwiGLU
         s.xres[t] = ld_act(m.xb + t); s.xres[t + 512] = ld_act(m.xb + t + 512);
         __syncthreads();
         rmsnorm_to_xf(s, W.ffn_norm + (size_t) l * H, m.eps, nullptr);
+        PROF(12);
         wait_fetch(s, ws, 0);
+        PROF(13);
         gemv_chain<4, 1024>(s.buf0, 2 * nP, s);
         __syncthreads();
         if (t < nP) {
@@ -778,22 +800,29 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         if (!last)      issue_fetch(s, ws, 0, sl_a(W, l + 1, z), nA, H * 2);
         else if (head)  issue_fetch(s, ws, 0, head->w + (size_t) h0 * H, nH, H * 2);
         else if (NW)    issue_fetch(s, ws, 0, sl_a(*NW, 0, z), nA, H * 2);
+        PROF(14);
         grid_barrier(m, bs);
+        PROF(15);
 
         // ---- phase E: ffn_down on F32 activations (weights exact in F32) + residual
 #pragma unroll
         for (int i = 0; i < FFN / LM_THREADS; ++i) s.xf[t + LM_THREADS * i] = ld_act(m.mbuf + t + LM_THREADS * i);
         __syncthreads();
+        PROF(16);
         wait_fetch(s, ws, 1);
+        PROF(17);
         gemv_chain<2, 3072>(s.buf1, nD, s);
         __syncthreads();
         if (t < nD) m.xa[z.d0 + t] = __fadd_rn(s.outv[t], s.xres[z.d0 + t]);
         if (!last)      issue_fetch(s, ws, 1, sl_o(W, l + 1, z), nO, NH * HD * 2);
         else if (NW)    issue_fetch(s, ws, 1, sl_o(*NW, 0, z), nO, NH * HD * 2);
+        PROF(18);
         grid_barrier(m, bs);
+        PROF(19);
         s.xres[t] = ld_act(m.xa + t); s.xres[t + 512] = ld_act(m.xa + t + 512);
         __syncthreads();
     }
+    PROF(20);
 
     if (!head) return;
     // ---- head: final RMSNorm (= hidden_states) + vocabulary mat-vec + per-CTA arg-max candidate
@@ -819,7 +848,9 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         m.cand_val[blockIdx.x] = bv; m.cand_idx[blockIdx.x] = bi;
     }
     if (NW) issue_fetch(s, ws, 0, sl_a(*NW, 0, z), nA, H * 2);
+    PROF(21);
     grid_barrier(m, bs);
+    PROF(22);
 }
 
 // --------------------------------------------------------------------------- the kernel
@@ -863,6 +894,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
     unsigned long long draw = gs.draw;
 
     for (int ip = 0; ip < n_passes; ++ip) {
+        PROF(30);
         if (t == 0) pd = passes[ip];
         __syncthreads();
         const PassDesc p = pd;
@@ -933,6 +965,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
         }
         __syncthreads();
 
+        PROF(31);
         const int pos = p.pos >= 0 ? p.pos : n_past;
         const HeadW * head = p.head < 0 ? nullptr : (p.head == 0 ? &m.codec_head : &m.cp_head[p.head - 1]);
         // the next pass' first weight slices are fetched across the pass boundary
