@@ -193,6 +193,28 @@ static int copy_rows(q3t_ctx * ctx, void * dst, size_t dst_pitch, const void * s
                       "repack copy");
 }
 
+// "chain-major" row layout of every mat-vec weight (private device layout): element k = 32j + a of
+// a row (a = ggml accumulator lane, j = step of its FMA chain) moves to (j/8)*256 + a*8 + j%8, so
+// that a warp reads 512 contiguous bytes and lane a receives 8 consecutive steps of ITS chain.
+__global__ void k_chain_pack(const __half * __restrict__ src, __half * __restrict__ dst, size_t rows, int K) {
+    const size_t n = rows * (size_t) K;
+    for (size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+        const size_t r = i / K; const int k = (int) (i % K);
+        const int j = k >> 5, a = k & 31;
+        dst[r * K + (size_t) ((j >> 3) * 256 + a * 8 + (j & 7))] = src[i];
+    }
+}
+static int chain_pack_inplace(q3t_ctx * ctx, __half * w, size_t rows, int K) {
+    __half * tmp = nullptr;
+    CK(cudaMalloc(&tmp, rows * (size_t) K * 2));
+    k_chain_pack<<<1024, 256, 0, ctx->stream>>>(w, tmp, rows, K);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(w, tmp, rows * (size_t) K * 2, cudaMemcpyDeviceToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaFree(tmp));
+    return Q3T_OK;
+}
+
 static int build_stack(q3t_ctx * ctx, const char * prefix, int n_layers, StackW & W, int64_t & bytes) {
     // dtype of the big matrices follows the file (F16 or Q8_0); all seven must agree
     const q3t_host_tensor * probe = find_raw(ctx, std::string(prefix) + ".blk.0.attn_q.weight");
@@ -239,6 +261,12 @@ static int build_stack(q3t_ctx * ctx, const char * prefix, int n_layers, StackW 
         if ((rc = need(ctx, b + "attn_k_norm.weight", Q3T_TYPE_F32, HD, 1, &t))) return rc;
         if ((rc = copy_rows(ctx, kn + (size_t) l * HD, HD * 4, t->dev, HD * 4, 1))) return rc;
     }
+    for (int l = 0; l < n_layers; ++l) {
+        if ((rc = chain_pack_inplace(ctx, wqkv + (size_t) l * QKV_N * H, QKV_N, H))) return rc;
+        if ((rc = chain_pack_inplace(ctx, wo + (size_t) l * H * NH * HD, H, NH * HD))) return rc;
+        if ((rc = chain_pack_inplace(ctx, wgu + (size_t) l * 2 * FFN * H, 2 * FFN, H))) return rc;
+        if ((rc = chain_pack_inplace(ctx, wdown + (size_t) l * H * FFN, H, FFN))) return rc;
+    }
     W.wqkv = wqkv; W.wo = wo; W.wgu = wgu; W.wdown = wdown;
     W.sqkv = W.so = W.sgu = W.sdown = nullptr;
     W.attn_norm = an; W.ffn_norm = fn; W.q_norm = qn; W.k_norm = kn;
@@ -269,11 +297,13 @@ static int finalize_tts(q3t_ctx * ctx) {
     if ((rc = need(ctx, "code_pred.output_norm.weight", Q3T_TYPE_F32, H, 1, &t))) return rc;
     m.cp.out_norm = (const float *) t->dev;
     if ((rc = need(ctx, "talker.codec_head.weight", Q3T_TYPE_F16, H, c.codec_vocab_size, &t))) return rc;
+    if ((rc = chain_pack_inplace(ctx, (__half *) t->dev, c.codec_vocab_size, H))) return rc;   // only lm_kernel reads the head
     m.codec_head.w = (const __half *) t->dev; m.codec_head.vocab = c.codec_vocab_size;
     if ((rc = need(ctx, "talker.codec_embd.weight", Q3T_TYPE_F16, H, c.codec_vocab_size, &t))) return rc;
     m.codec_embd = (const __half *) t->dev;
     for (int i = 0; i < NCB - 1; ++i) {
         if ((rc = need(ctx, "code_pred.lm_head." + std::to_string(i) + ".weight", Q3T_TYPE_F16, H, c.code_pred_vocab_size, &t))) return rc;
+        if ((rc = chain_pack_inplace(ctx, (__half *) t->dev, c.code_pred_vocab_size, H))) return rc;
         m.cp_head[i].w = (const __half *) t->dev; m.cp_head[i].vocab = c.code_pred_vocab_size;
         if ((rc = need(ctx, "code_pred.codec_embd." + std::to_string(i) + ".weight", Q3T_TYPE_F16, H, c.code_pred_vocab_size, &t))) return rc;
         m.cp_embd[i] = (const __half *) t->dev;

@@ -31,7 +31,7 @@
 namespace q3t {
 
 // ------------------------------------------------------------------------------- shared memory
-constexpr int PAD_B      = 64;                         // row pitch = K*2 + 64 B: conflict-free 64-bit/32-bit row-parallel reads
+constexpr int PAD_B      = 0;                          // rows are dense: chain-major rows are read 512 contiguous bytes per warp
 constexpr int PITCH_1K   = 1024 * 2 + PAD_B;           // 2112
 constexpr int PITCH_2K   = 2048 * 2 + PAD_B;           // 4160
 constexpr int PITCH_3K   = 3072 * 2 + PAD_B;           // 6208
@@ -47,7 +47,7 @@ struct __align__(128) Smem {
     unsigned char buf1[BUF1_BYTES];
     float  xres[H];                // residual stream of the current token (x, then x1)
     float  xf[FFN];                // GEMV input as F32 (already F16-rounded where the oracle rounds)
-    float  outv[64];               // finalised row values of the phase
+    float  outv[96];               // finalised row values of the phase
     // attention
     float  qf[2][HD];              // normed+roped q of the two heads of this kv group (F32)
     float  qr[2][HD];              // same, F16-rounded, as float
@@ -171,65 +171,53 @@ __device__ __forceinline__ void cta_rows(int n_rows, int & r0, int & r1) {
 }
 
 // ------------------------------------------------------------------------------- ordered GEMV
-// rows of F16 weights in shared memory (pitch K*2+64) times the activation vector s.xf (F32 values;
-// already F16-rounded for the F16 mat-vecs, raw F32 for ffn_down).  A task = (row, group of ACC
-// accumulator lanes); each thread walks the k/32 chain with fused multiply-adds exactly like one
-// SIMD lane group of ggml_vec_dot_f16 / ggml_vec_dot_f32, then the lanes of a row are folded in
-// the oracle's order.  Result of row r lands in s.outv[r].
-template <int ACC, int K>
-__device__ __forceinline__ void gemv_chain(const unsigned char * __restrict__ wbuf, int n_rows, Smem & s) {
-    static_assert(ACC == 2 || ACC == 4, "ACC");
-    constexpr int LPR = 32 / ACC;                 // lanes per row
-    constexpr int PITCH = K * 2 + PAD_B;
-    const int task = threadIdx.x;
-    const int r = task / LPR, q = task % LPR;
-    float acc[ACC];
+// Rows of chain-major F16 weights (engine.cu k_chain_pack) in shared memory times the activation
+// vector s.xf (F32 values; already F16-rounded for the F16 mat-vecs, raw F32 for ffn_down).
+// Lane a of a warp IS accumulator lane a of ggml_vec_dot_f16 / ggml_vec_dot_f32 (k % 32 == a): it
+// keeps x[32j + a] for all j in registers and walks its FMA chain over j for R rows at a time
+// (R independent chains per lane hide the FMA latency); one 16-byte shared-memory load brings 8
+// consecutive chain steps, a warp reads 512 contiguous bytes per load (conflict free).  The 32
+// lane sums are folded in the oracle's order (reduce32_lanes).  Result of row r -> s.outv[r].
+template <int K, int R>
+__device__ __forceinline__ void gemv_lane(const unsigned char * __restrict__ wbuf, int n_rows, Smem & s) {
+    constexpr int NJ = K / 32, NU = K / 256;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp >= n_rows) return;
+    float xr[NJ];
 #pragma unroll
-    for (int e = 0; e < ACC; ++e) acc[e] = 0.0f;
-    if (r < n_rows) {
-        const unsigned char * wrow = wbuf + (size_t) r * PITCH + q * ACC * 2;
-        const float * xp = s.xf + q * ACC;
-#pragma unroll 8
-        for (int c = 0; c < K / 32; ++c) {
-            if (ACC == 4) {
-                const uint2 wv = *reinterpret_cast<const uint2 *>(wrow + c * 64);
-                const float4 xv = *reinterpret_cast<const float4 *>(xp + c * 32);
-                const float2 w01 = __half22float2(*reinterpret_cast<const __half2 *>(&wv.x));
-                const float2 w23 = __half22float2(*reinterpret_cast<const __half2 *>(&wv.y));
-                acc[0] = __fmaf_rn(w01.x, xv.x, acc[0]);
-                acc[1] = __fmaf_rn(w01.y, xv.y, acc[1]);
-                acc[2] = __fmaf_rn(w23.x, xv.z, acc[2]);
-                acc[3] = __fmaf_rn(w23.y, xv.w, acc[3]);
-            } else {
-                const unsigned wv = *reinterpret_cast<const unsigned *>(wrow + c * 64);
-                const float2 xv = *reinterpret_cast<const float2 *>(xp + c * 32);
-                const float2 w01 = __half22float2(*reinterpret_cast<const __half2 *>(&wv));
-                acc[0] = __fmaf_rn(w01.x, xv.x, acc[0]);
-                acc[1] = __fmaf_rn(w01.y, xv.y, acc[1]);
+    for (int j = 0; j < NJ; ++j) xr[j] = s.xf[32 * j + lane];
+    for (int r0 = warp; r0 < n_rows; r0 += 16 * R) {
+        float acc[R];
+        const unsigned char * wrow[R];
+#pragma unroll
+        for (int i = 0; i < R; ++i) {
+            acc[i] = 0.0f;
+            const int r = r0 + 16 * i;
+            wrow[i] = wbuf + (size_t) (r < n_rows ? r : r0) * (K * 2) + lane * 16;
+        }
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+            uint4 wv[R];
+#pragma unroll
+            for (int i = 0; i < R; ++i) wv[i] = *reinterpret_cast<const uint4 *>(wrow[i] + u * 512);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+#pragma unroll
+                for (int i = 0; i < R; ++i) {
+                    const unsigned w2 = e == 0 ? wv[i].x : e == 1 ? wv[i].y : e == 2 ? wv[i].z : wv[i].w;
+                    const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&w2));
+                    acc[i] = __fmaf_rn(f.x, xr[8 * u + 2 * e], acc[i]);
+                    acc[i] = __fmaf_rn(f.y, xr[8 * u + 2 * e + 1], acc[i]);
+                }
             }
         }
-    }
-    // fold: accumulator index a = q*ACC + e; oracle order flips a-bits 16, 8, 4, then 1, 2
-    float res;
-    if (ACC == 4) {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 4));
-            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 2));
-            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 1));
+        for (int i = 0; i < R; ++i) {
+            const float res = reduce32_lanes(acc[i]);
+            const int r = r0 + 16 * i;
+            if (lane == 0 && r < n_rows) s.outv[r] = res;
         }
-        res = __fadd_rn(__fadd_rn(acc[0], acc[1]), __fadd_rn(acc[2], acc[3]));
-    } else {
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 8));
-            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 4));
-            acc[e] = __fadd_rn(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], 2));
-        }
-        const float u = __fadd_rn(acc[0], acc[1]);
-        res = __fadd_rn(u, __shfl_xor_sync(0xffffffffu, u, 1));
     }
-    if (r < n_rows && q == 0) s.outv[r] = res;
 }
 
 // ------------------------------------------------------------------------------- RMSNorm
@@ -754,7 +742,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(2);
         wait_fetch(s, ws, 0);
         PROF(3);
-        gemv_chain<4, 1024>(s.buf0, nA, s);
+        gemv_lane<1024, 2>(s.buf0, nA, s);
         __syncthreads();
         if (t < nA) m.qkv[z.a0 + t] = s.outv[t];
         issue_fetch(s, ws, 0, sl_gu(W, l, z), 2 * nP, H * 2);
@@ -775,7 +763,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(8);
         wait_fetch(s, ws, 1);
         PROF(9);
-        gemv_chain<2, 2048>(s.buf1, nO, s);
+        gemv_lane<2048, 1>(s.buf1, nO, s);
         __syncthreads();
         if (t < nO) m.xb[z.o0 + t] = __fadd_rn(s.outv[t], s.xres[z.o0 + t]);
         issue_fetch(s, ws, 1, sl_d(W, l, z), nD, FFN * 2);
@@ -790,7 +778,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(12);
         wait_fetch(s, ws, 0);
         PROF(13);
-        gemv_chain<4, 1024>(s.buf0, 2 * nP, s);
+        gemv_lane<1024, 3>(s.buf0, 2 * nP, s);
         __syncthreads();
         if (t < nP) {
             const float gt = s.outv[2 * t], up = s.outv[2 * t + 1];
@@ -811,7 +799,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(16);
         wait_fetch(s, ws, 1);
         PROF(17);
-        gemv_chain<2, 3072>(s.buf1, nD, s);
+        gemv_lane<3072, 1>(s.buf1, nD, s);
         __syncthreads();
         if (t < nD) m.xa[z.d0 + t] = __fadd_rn(s.outv[t], s.xres[z.d0 + t]);
         if (!last)      issue_fetch(s, ws, 1, sl_o(W, l + 1, z), nO, NH * HD * 2);
@@ -829,7 +817,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
     rmsnorm_to_xf(s, W.out_norm, m.eps, blockIdx.x == 0 ? m.hidden : nullptr);
     if (p.hidden_dst && blockIdx.x == 0) { p.hidden_dst[t] = m.hidden[t]; p.hidden_dst[t + 512] = m.hidden[t + 512]; }
     wait_fetch(s, ws, 0);
-    gemv_chain<4, 1024>(s.buf0, nH, s);
+    gemv_lane<1024, 2>(s.buf0, nH, s);
     __syncthreads();
     float pv = -CUDART_INF_F;
     if (t < nH) {
