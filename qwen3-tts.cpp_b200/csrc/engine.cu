@@ -33,6 +33,8 @@ int cuda_check(q3t_ctx * ctx, cudaError_t e, const char * what) {
 
 #define CK(call) do { int _rc = cuda_check(ctx, (call), #call); if (_rc != Q3T_OK) return _rc; } while (0)
 
+constexpr size_t PKT_TOTAL = QKV_N + NH * HD + H + FFN + H + 3072 + 2 * 512;   // packets of all exchange buffers
+
 template <typename T>
 static int dev_alloc(q3t_ctx * ctx, T ** out, size_t count, bool zero = false, bool owned = true) {
     void * p = nullptr;
@@ -322,20 +324,14 @@ static int finalize_tts(q3t_ctx * ctx) {
     m.cp.kcache = ck; m.cp.vcache = cv; m.cp.kf32 = kf; m.cp.vf32 = vf; m.cp.n_ctx = 16;
 
     // activations / scratch
-    if ((rc = dev_alloc(ctx, &m.xa, H, true))) return rc;
-    if ((rc = dev_alloc(ctx, &m.xb, H, true))) return rc;
-    if ((rc = dev_alloc(ctx, &m.qkv, QKV_N, true))) return rc;
-    if ((rc = dev_alloc(ctx, &m.mbuf, FFN, true))) return rc;
+    // all packet buffers live in one allocation so one memset re-arms them (reset_state)
+    Pkt * pk = nullptr;
+    if ((rc = dev_alloc(ctx, &pk, PKT_TOTAL, true))) return rc;
+    m.x_qkv = pk; m.x_att = m.x_qkv + QKV_N; m.x_x1 = m.x_att + NH * HD; m.x_m = m.x_x1 + H; m.x_x = m.x_m + FFN;
+    m.x_logit = m.x_x + H; m.x_cand = m.x_logit + 3072;
     if ((rc = dev_alloc(ctx, &m.hidden, H, true))) return rc;
     if ((rc = dev_alloc(ctx, &m.logits, 3072, true))) return rc;
-    if ((rc = dev_alloc(ctx, &m.part_ms, NKV * LM_MAXC * 4, true))) return rc;
-    if ((rc = dev_alloc(ctx, &m.part_o, (size_t) NH * HD, true))) return rc;
-    if ((rc = dev_alloc(ctx, &m.sbuf, (size_t) NH * LM_ATT_MAX_KV, true))) return rc;
-    if ((rc = dev_alloc(ctx, &m.cand_val, 512, true))) return rc;
-    if ((rc = dev_alloc(ctx, &m.cand_idx, 512, true))) return rc;
     if ((rc = dev_alloc(ctx, &m.seen, 4096, true))) return rc;
-    if ((rc = dev_alloc(ctx, &m.bar, 1, true))) return rc;
-    if ((rc = dev_alloc(ctx, &m.gbar, NKV, true))) return rc;
     if ((rc = dev_alloc(ctx, &m.st, 1, true))) return rc;
     ctx->passes_cap = 64;
     if ((rc = dev_alloc(ctx, &ctx->d_passes, ctx->passes_cap))) return rc;
@@ -414,11 +410,9 @@ extern "C" int q3t_kv_n_ctx(q3t_ctx * ctx) { return ctx ? ctx->n_ctx : 0; }
 static int reset_state(q3t_ctx * ctx, const GenState & init, bool clear_seen) {
     DevModel & m = ctx->hm;
     GenState st = init;
-    st.bar_base = 0;
-    for (int i = 0; i < 8; ++i) st.gbar_base[i] = 0;
+    st.ep_base = 0; st.pending_ep = 0;
     st.error = 0;
-    CK(cudaMemsetAsync(m.bar, 0, sizeof(unsigned long long), ctx->stream));
-    CK(cudaMemsetAsync(m.gbar, 0, NKV * sizeof(unsigned long long), ctx->stream));
+    CK(cudaMemsetAsync(m.x_qkv, 0, PKT_TOTAL * sizeof(Pkt), ctx->stream));     // epoch 0 = never written
     if (clear_seen) CK(cudaMemsetAsync(m.seen, 0, 4096, ctx->stream));
     CK(cudaMemcpyAsync(m.st, &st, sizeof(GenState), cudaMemcpyHostToDevice, ctx->stream));
     return Q3T_OK;

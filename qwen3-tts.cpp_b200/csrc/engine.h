@@ -83,11 +83,14 @@ struct GenState {
     int error;             // device watchdog
     unsigned long long seed;
     unsigned long long draw;       // sampler draw counter
-    unsigned long long bar_base;   // grid-barrier epoch base (see grid_barrier)
-    unsigned long long gbar_base[NKV > 0 ? 8 : 8];
+    unsigned ep_base;              // packet epoch of the last exchange of the previous launch
+    unsigned pending_ep;           // epoch of the head packets waiting to be selected
     int cur[16];           // codes of the frame being built
     int pending;           // 1: a head result is waiting to be selected
 };
+
+// {value, epoch} activation packet: one aligned 8-byte word (see lm_kernel.cu "LL packets")
+struct __align__(8) Pkt { float v; unsigned e; };
 
 struct DevModel {
     StackW talker, cp;
@@ -99,21 +102,19 @@ struct DevModel {
     int n_rope_pos;
     float eps;
     // activations / scratch (device)
-    float * xa, * xb;                // [1024] each
-    float * qkv;                     // [4096]
-    float * mbuf;                    // [3072]
+    Pkt * x_qkv;                     // [4096] fused q|k|v of the token            (phase A -> B)
+    Pkt * x_att;                     // [2048] attention output                    (B -> C)
+    Pkt * x_x1;                      // [1024] x + attn_output                     (C -> D)
+    Pkt * x_m;                       // [3072] silu(gate) * up                     (D -> E)
+    Pkt * x_x;                       // [1024] layer output                        (E -> next A / head)
+    Pkt * x_logit;                   // [3072] raw head logits                     (head -> select)
+    Pkt * x_cand;                    // [2*grid] per-CTA arg-max candidate {value, index}
     float * hidden;                  // [1024]
     float * logits;                  // [3072]
-    float * part_ms;                 // [8][16][2]  per-split score maxima
-    float * part_o;                  // [16][128]   attention output of the layer
-    float * sbuf;                    // [16][LM_ATT_MAX_KV] attention scores
-    float * cand_val; int * cand_idx;// [grid]
     unsigned char * seen;            // [3072] repetition-penalty set
     const float * trailing;          // [trailing_len][1024]
     const float * pad_embed;         // [1024]
     int * codes_out;                 // [max_len][16]
-    unsigned long long * bar;        // grid barrier counter
-    unsigned long long * gbar;       // [8] group barrier counters
     GenState * st;
     // developer profiling (q3t_profile_arm): thread 0 of CTA prof_cta appends (clock64 << 8 | tag)
     unsigned long long * prof; int prof_cap; int prof_cta;

@@ -4,24 +4,28 @@
 // build_code_pred_step_graph and the host loop that runs 16 dependent ggml graphs per frame
 // (src/tts_transformer.cpp:1268-1411, 1534-1829, 2310-2575, 2664-2804).
 //
-// Design (B200-first, see DESIGN.md §3):
+// Design (B200-first, see DESIGN.md §4.1):
 //   * ONE cooperative launch of `grid` (= #SMs) CTAs x 512 threads runs a whole *program* of
 //     passes (a pass = one token through one layer stack + optional head): a frame is
 //     16 code-predictor passes + 1 talker pass, a prefill is M talker passes.
-//   * Batch-1 decode is HBM/latency bound, so the weight stream is decoupled from the
-//     dependency chain in two stages: one thread per CTA issues TMA-unit bulk L2 prefetches
-//     (cp.async.bulk.prefetch.L2) one layer ahead, and a producer warp issues TMA bulk copies
-//     (cp.async.bulk global->shared, mbarrier complete_tx) of the CTA's weight-row slice of the
-//     phase after next into one of two shared-memory buffers *before* the grid barrier, so
-//     barrier latency is covered by copies in flight and the compute reads only shared memory.
-//   * Every phase boundary is an all-to-all dependency (GEMV output -> next GEMV input); it is
-//     a release/acquire counter barrier in global memory, not a kernel boundary.
-//   * BIT-EXACT with the oracle: F16 rounding points amplify any F32 re-association noise into
-//     ~1e-3 logit differences, enough to flip greedy tokens of a random-init model within a few
-//     hundred steps.  So every dot product is accumulated in the order of ggml-cpu's AVX2+FMA
-//     build (32 accumulator lanes k%32, FMA chain over k/32, fixed reduction tree;
-//     ggml/src/ggml-cpu/vec.cpp:265-390, simd-mappings.h:549-567), exp() is the same
-//     polynomial (vec.h:1230-1267), soft-max sums follow the 8-lane pattern (vec.cpp:558-568).
+//   * Batch-1 decode is a chain of ~600 dependent mat-vecs per frame, so the kernel is built around
+//     the LATENCY of that chain while HBM streams underneath it:
+//       - warp 15 of every CTA is a producer: it walks the (deterministic) schedule of weight
+//         slices of this CTA and keeps a 160 KB shared-memory ring full with TMA bulk copies
+//         (cp.async.bulk global->shared, mbarrier complete_tx), gated only by ring space — the
+//         weight stream never waits for the dependency chain;
+//       - warps 0..14 compute.  Every phase boundary is an all-to-all exchange of a small
+//         activation vector; instead of a grid barrier (fence + atomic + poll + reload = 4 L2 round
+//         trips) activations travel as 8-byte {value, epoch} packets (one store, one polling
+//         load: the value is valid iff its epoch matches) — the NCCL "LL" idea used inside one GPU;
+//       - small parameters (norm weights) are fetched one layer ahead into registers.
+//   * Weights are stored chain-major (engine.cu k_chain_pack) so that lane a of a warp is ggml's
+//     accumulator lane a (k % 32): it keeps x[32j + a] in registers as packed halves and walks its
+//     FMA chain with FHFMA (fma.rn.f32.f16: F16 x F16 + F32 in one instruction, no conversions).
+//   * BIT-EXACT with the oracle: every dot product is accumulated in the order of ggml-cpu's
+//     AVX2+FMA build (32 accumulator lanes k%32, FMA chain over k/32, fixed reduction tree;
+//     ggml/src/ggml-cpu/vec.cpp:265-390, simd-mappings.h:549-567), exp() is the same polynomial
+//     (vec.h:1230-1267), soft-max sums follow the 8-lane pattern (vec.cpp:558-568).
 //     oracle/q3t_oracle.c is the executable statement of these rules.
 #include "common.cuh"
 #include "engine.h"
@@ -31,35 +35,34 @@
 namespace q3t {
 
 // ------------------------------------------------------------------------------- shared memory
-constexpr int PAD_B      = 0;                          // rows are dense: chain-major rows are read 512 contiguous bytes per warp
-constexpr int PITCH_1K   = 1024 * 2 + PAD_B;           // 2112
-constexpr int PITCH_2K   = 2048 * 2 + PAD_B;           // 4160
-constexpr int PITCH_3K   = 3072 * 2 + PAD_B;           // 6208
-constexpr int MAXR_GU    = 44;                         // gate/up rows per CTA   (grid >= 140)
-constexpr int MAXR_H     = 8;                          // rows of a 1024-row matrix per CTA
-constexpr int BUF0_BYTES = MAXR_GU * PITCH_1K;         // qkv / gate-up / head slices     92,928 B
-constexpr int BUF1_BYTES = MAXR_H * PITCH_3K;          // attn_output / ffn_down slices   49,664 B
-constexpr int ATT_MAX_KV = LM_ATT_MAX_KV;              // positions the attention phase can hold (P in F16)
-constexpr int VT_HALVES  = 8192;                       // V^T tile: nd dims x TB positions
+constexpr int NCW        = 15;                         // compute warps (warp 15 is the TMA producer)
+constexpr int NCT        = NCW * 32;                   // 480 compute threads
+constexpr int SLOT_B     = 2048;                       // ring slot = one K=1024 row of F16 weights
+constexpr int NSLOT      = 80;                         // 160 KB ring
+constexpr int NMB        = 8;                          // mbarriers cycling over the slices in flight
+constexpr int ATT_MAX_KV = LM_ATT_MAX_KV;              // positions the attention phase can hold
 
 struct __align__(128) Smem {
-    unsigned char buf0[BUF0_BYTES];
-    unsigned char buf1[BUF1_BYTES];
+    unsigned char ring[NSLOT * SLOT_B];
     float  xres[H];                // residual stream of the current token (x, then x1)
-    float  xf[FFN];                // GEMV input as F32 (already F16-rounded where the oracle rounds)
-    float  outv[96];               // finalised row values of the phase
-    // attention
-    float  qf[2][HD];              // normed+roped q of the two heads of this kv group (F32)
-    float  qr[2][HD];              // same, F16-rounded, as float
+    float  xf[FFN];                // F32 GEMV input (ffn_down) / scratch
+    unsigned xh[H];                // F16 GEMV input, lane-packed: xh[m*32 + a] = {x[64m + a], x[64m + 32 + a]}
+    float  outv[64];               // finalised row values of the phase
+    // attention (one CTA per head)
+    float  sc[ATT_MAX_KV];         // scores, then exp values
+    __half ph[ATT_MAX_KV];         // soft-max probabilities rounded to F16 (oracle D.4)
+    float  qf[HD];                 // normed+roped q (F32)
+    float  qr[HD];                 // same, F16-rounded, as float
     float  knew_f[HD], vnew_f[HD];
-    __half knew_h[HD], vnew_h[HD];
-    __half ph[2][ATT_MAX_KV];      // soft-max probabilities rounded to F16 (oracle D.4)
-    __half vt[VT_HALVES];          // V^T tile [dim][position]
-    double dred[2][16];
+    __half knew_h[HD], vnew_h[HD]; // new token's K and V rounded to F16 (natural dim order)
+    float  o32[HD];
+    __half vt[32 * HD];            // leftover V rows (positions np..n_kv-1)
+    double dred[16];
     float  fred[32];
     int    ired[32];
     int    tok;
-    unsigned long long mbar[2];    // TMA completion barriers of buf0 / buf1
+    unsigned long long mbar[NMB];  // TMA completion barriers of the slices in flight
+    volatile unsigned long long consumed;   // low 32: ring slots released, high 32: slices released
 };
 
 // ------------------------------------------------------------------------------- phase profiler
@@ -71,52 +74,46 @@ __device__ __forceinline__ void prof_mark(const DevModel & m, int tag) {
 }
 #define PROF(tag) prof_mark(m, tag)
 
-// ------------------------------------------------------------------------------- grid barriers
-struct BarState {
-    unsigned long long target;       // grid barrier epoch target
-    unsigned long long gtarget;      // group barrier target of this CTA's kv group
-    bool dead;
-};
+// ------------------------------------------------------------------------------- CTA-level sync
+// barrier among the 480 compute threads only (the producer warp runs free)
+__device__ __forceinline__ void cbar() { asm volatile("bar.sync 1, %0;" :: "n"(NCT) : "memory"); }
 
-__device__ __forceinline__ bool spin_until(const unsigned long long * ctr, unsigned long long target, GenState * st) {
-    long long t0 = clock64();
-    unsigned spins = 0;
-    while (ld_acquire_u64(ctr) < target) {
-        if (((++spins) & 0x3ff) == 0) {
-            if (clock64() - t0 > 4000000000LL) {      // ~2 s: another CTA died; bail out loudly
-                st->error = 1;
-                return false;
-            }
-        }
+// ------------------------------------------------------------------------------- LL packets
+// An activation travels as {float value, u32 epoch} in one aligned 8-byte word: an 8-byte store is
+// single-copy atomic, so a reader that sees the expected epoch also sees the value.  Every exchange
+// point of the program has its own epoch (a counter that advances identically in every CTA).
+struct Watch { long long t0; bool dead; };
+
+__device__ __forceinline__ void pk_store(Pkt * p, float v, unsigned ep) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(p), "r"(__float_as_uint(v)), "r"(ep) : "memory");
+}
+__device__ __forceinline__ bool pk_give_up(const DevModel & m, Watch & w, unsigned & spins) {
+    if (((++spins) & 0x3ff) != 0) return false;
+    if (*reinterpret_cast<volatile int *>(&m.st->error)) { w.dead = true; return true; }
+    if (clock64() - w.t0 > 6000000000LL) { m.st->error = 1; w.dead = true; return true; }   // ~3 s: a CTA died
+    return false;
+}
+__device__ __forceinline__ float pk_poll(const DevModel & m, const Pkt * p, unsigned ep, Watch & w) {
+    unsigned v, e, spins = 0;
+    while (true) {
+        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(p) : "memory");
+        if (e == ep || w.dead) break;
+        if (pk_give_up(m, w, spins)) break;
     }
-    return true;
+    return __uint_as_float(v);
+}
+// two adjacent packets (16-byte aligned) in one load
+__device__ __forceinline__ float2 pk_poll2(const DevModel & m, const Pkt * p, unsigned ep, Watch & w) {
+    unsigned v0, e0, v1, e1, spins = 0;
+    while (true) {
+        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v0), "=r"(e0), "=r"(v1), "=r"(e1) : "l"(p) : "memory");
+        if ((e0 == ep && e1 == ep) || w.dead) break;
+        if (pk_give_up(m, w, spins)) break;
+    }
+    return make_float2(__uint_as_float(v0), __uint_as_float(v1));
 }
 
-__device__ __forceinline__ void grid_barrier(const DevModel & m, BarState & bs) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        bs.target += gridDim.x;
-        __threadfence();
-        red_release_add_u64(m.bar, 1ULL);
-        if (!bs.dead && !spin_until(m.bar, bs.target, m.st)) bs.dead = true;
-    }
-    __syncthreads();
-}
-
-// barrier among the `n` CTAs that share kv group g (attention soft-max statistics exchange)
-__device__ __forceinline__ void group_barrier(const DevModel & m, BarState & bs, int g, int n, bool participate) {
-    bs.gtarget += (unsigned long long) n;
-    if (!participate) return;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        red_release_add_u64(m.gbar + g, 1ULL);
-        if (!bs.dead && !spin_until(m.gbar + g, bs.gtarget, m.st)) bs.dead = true;
-    }
-    __syncthreads();
-}
-
-// ------------------------------------------------------------------------------- TMA weight stream
+// ------------------------------------------------------------------------------- TMA weight ring
 __device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(unsigned long long * bar, uint32_t count) {
@@ -141,227 +138,312 @@ __device__ __forceinline__ void tma_load_1d(void * dst_smem, const void * src_gm
                  :: "r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-struct WStream {                 // per-thread view of the two weight buffers
-    uint32_t parity[2];          // phase parity the next wait on buffer b must observe
-    bool     pending[2];         // a fetch into buffer b has been issued and not yet waited for
-};
-
-// Warp 0 stages `n_rows` rows of `row_bytes` (contiguous in HBM) into buffer `b` with the padded
-// pitch.  Must be called by all threads AFTER a __syncthreads that ends all reads of that buffer.
-__device__ __forceinline__ void issue_fetch(Smem & s, WStream & ws, int b, const void * src, int n_rows, int row_bytes) {
-    ws.pending[b] = true;
-    if (threadIdx.x < 32) {
-        unsigned char * dst = b == 0 ? s.buf0 : s.buf1;
-        const int pitch = row_bytes + PAD_B;
-        if (threadIdx.x == 0) mbar_expect_tx(&s.mbar[b], (uint32_t) (n_rows * row_bytes));
-        __syncwarp();
-        for (int r = threadIdx.x; r < n_rows; r += 32)
-            tma_load_1d(dst + (size_t) r * pitch, (const unsigned char *) src + (size_t) r * row_bytes, (uint32_t) row_bytes, &s.mbar[b]);
-    }
-}
-__device__ __forceinline__ void wait_fetch(Smem & s, WStream & ws, int b) {
-    mbar_wait(&s.mbar[b], ws.parity[b]);
-    ws.parity[b] ^= 1u;
-    ws.pending[b] = false;
-}
-
 __device__ __forceinline__ void cta_rows(int n_rows, int & r0, int & r1) {
     r0 = (int) (((long long) blockIdx.x * n_rows) / gridDim.x);
     r1 = (int) (((long long) (blockIdx.x + 1) * n_rows) / gridDim.x);
 }
 
+struct Slices {            // this CTA's row ranges (fixed for the whole launch)
+    int a0, a1;            // qkv rows            (of 4096, K=1024)
+    int o0, o1;            // attn_output rows    (of 1024, K=2048)
+    int p0, p1;            // gate/up pairs       (of 3072, K=1024, 2 rows per pair)
+    int d0, d1;            // ffn_down rows       (of 1024, K=3072)
+};
+
+// consumer-side cursor over the slice stream (identical bookkeeping runs in the producer)
+struct Ring {
+    unsigned slot_head;    // ring slot (unwrapped) where the next slice starts
+    unsigned slice_idx;    // index of the next slice
+};
+
+__device__ __forceinline__ bool mbar_try(unsigned long long * bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+// wait for the next slice; returns its first ring slot (wrapped)
+__device__ __forceinline__ int ring_acquire(const DevModel & m, Smem & s, const Ring & rg, Watch & w) {
+    unsigned long long * bar = &s.mbar[rg.slice_idx % NMB];
+    const uint32_t parity = (rg.slice_idx / NMB) & 1u;
+    unsigned spins = 0;
+    while (!mbar_try(bar, parity)) {
+        if (w.dead) break;
+        if (pk_give_up(m, w, spins)) break;
+    }
+    return (int) (rg.slot_head % NSLOT);
+}
+// all compute threads are past their last read of the slice (call after a cbar())
+__device__ __forceinline__ void ring_release(Smem & s, Ring & rg, int n_slots) {
+    rg.slot_head += (unsigned) n_slots;
+    rg.slice_idx += 1u;
+    if (threadIdx.x == 0) {
+        __threadfence_block();
+        s.consumed = ((unsigned long long) rg.slice_idx << 32) | (unsigned long long) rg.slot_head;
+    }
+}
+
+// producer: one slice = `n_slots` ring slots filled from `src` (contiguous in HBM); <= 2 bulk copies
+__device__ __forceinline__ void produce_slice(Smem & s, unsigned & p_slot, unsigned & p_idx, const void * src, int n_slots) {
+    if (n_slots <= 0) return;
+    // wait for ring space and for the mbarrier of slice (p_idx - NMB) to be drained by the consumers
+    while (true) {
+        const unsigned long long c = s.consumed;
+        const unsigned c_slot = (unsigned) c, c_idx = (unsigned) (c >> 32);
+        if (p_slot + (unsigned) n_slots - c_slot <= (unsigned) NSLOT && p_idx - c_idx < (unsigned) NMB) break;
+        __nanosleep(20);
+    }
+    unsigned long long * bar = &s.mbar[p_idx % NMB];
+    const int w0 = (int) (p_slot % NSLOT);
+    const int n0 = min(n_slots, NSLOT - w0);
+    // order the consumers' generic-proxy reads of the recycled slots before the async-proxy writes
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    mbar_expect_tx(bar, (uint32_t) n_slots * SLOT_B);
+    tma_load_1d(s.ring + (size_t) w0 * SLOT_B, src, (uint32_t) n0 * SLOT_B, bar);
+    if (n0 < n_slots)
+        tma_load_1d(s.ring, (const unsigned char *) src + (size_t) n0 * SLOT_B, (uint32_t) (n_slots - n0) * SLOT_B, bar);
+    p_slot += (unsigned) n_slots;
+    p_idx  += 1u;
+}
+
+__device__ __forceinline__ const __half * sl_a(const StackW & W, int l, const Slices & z) {
+    return reinterpret_cast<const __half *>(W.wqkv) + ((size_t) l * QKV_N + z.a0) * H;
+}
+__device__ __forceinline__ const __half * sl_o(const StackW & W, int l, const Slices & z) {
+    return reinterpret_cast<const __half *>(W.wo) + ((size_t) l * H + z.o0) * (NH * HD);
+}
+__device__ __forceinline__ const __half * sl_gu(const StackW & W, int l, const Slices & z) {
+    return reinterpret_cast<const __half *>(W.wgu) + ((size_t) l * 2 * FFN + 2 * z.p0) * H;
+}
+__device__ __forceinline__ const __half * sl_d(const StackW & W, int l, const Slices & z) {
+    return reinterpret_cast<const __half *>(W.wdown) + ((size_t) l * H + z.d0) * FFN;
+}
+
 // ------------------------------------------------------------------------------- ordered GEMV
-// Rows of chain-major F16 weights (engine.cu k_chain_pack) in shared memory times the activation
-// vector s.xf (F32 values; already F16-rounded for the F16 mat-vecs, raw F32 for ffn_down).
-// Lane a of a warp IS accumulator lane a of ggml_vec_dot_f16 / ggml_vec_dot_f32 (k % 32 == a): it
-// keeps x[32j + a] for all j in registers and walks its FMA chain over j for R rows at a time
-// (R independent chains per lane hide the FMA latency); one 16-byte shared-memory load brings 8
-// consecutive chain steps, a warp reads 512 contiguous bytes per load (conflict free).  The 32
-// lane sums are folded in the oracle's order (reduce32_lanes).  Result of row r -> s.outv[r].
-template <int K, int R>
-__device__ __forceinline__ void gemv_lane(const unsigned char * __restrict__ wbuf, int n_rows, Smem & s) {
-    constexpr int NJ = K / 32, NU = K / 256;
+// fma.rn.f32.f16 (SASS FHFMA, sm_100+): d = f32(a) * f32(b) + c with a, b F16 and one rounding —
+// exactly ggml's F16C-convert + vfmadd lane step, in one instruction.
+__device__ __forceinline__ float fhfma_lo(unsigned w, unsigned x, float acc) {
+    asm("{.reg .b16 wl, wh, xl, xh; mov.b32 {wl, wh}, %1; mov.b32 {xl, xh}, %2; fma.rn.f32.f16 %0, wl, xl, %0;}" : "+f"(acc) : "r"(w), "r"(x));
+    return acc;
+}
+__device__ __forceinline__ float fhfma_hi(unsigned w, unsigned x, float acc) {
+    asm("{.reg .b16 wl, wh, xl, xh; mov.b32 {wl, wh}, %1; mov.b32 {xl, xh}, %2; fma.rn.f32.f16 %0, wh, xh, %0;}" : "+f"(acc) : "r"(w), "r"(x));
+    return acc;
+}
+__device__ __forceinline__ unsigned u4_get(const uint4 & v, int e) { return e == 0 ? v.x : e == 1 ? v.y : e == 2 ? v.z : v.w; }
+
+// Rows of chain-major F16 weights in the shared-memory ring (slice starting at slot s0, K/1024 slots
+// per row) times the activation vector.  Lane a of a warp IS accumulator lane a of
+// ggml_vec_dot_f16 / ggml_vec_dot_f32 (k % 32 == a): it holds x[32j + a] for all j in registers
+// (packed halves from s.xh for the F16 mat-vecs, floats from s.xf for ffn_down) and walks its FMA
+// chain over j for R rows at a time; one 16-byte load brings 8 consecutive chain steps and a warp
+// reads 512 contiguous bytes per load.  The 32 lane sums are folded in the oracle's order
+// (reduce32_lanes).  Result of row r -> s.outv[r].
+template <int K, int R, bool XF32>
+__device__ __forceinline__ void gemv_ring(Smem & s, int s0, int n_rows) {
+    constexpr int SPR = K / 1024, NU = K / 256, NJ = K / 32;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (warp >= n_rows) return;
-    float xr[NJ];
+    if (warp * R >= n_rows) return;
+    float    xr[XF32 ? NJ : 1];
+    unsigned xp[XF32 ? 1 : NJ / 2];
+    if (XF32) {
 #pragma unroll
-    for (int j = 0; j < NJ; ++j) xr[j] = s.xf[32 * j + lane];
-    for (int r0 = warp; r0 < n_rows; r0 += 16 * R) {
+        for (int j = 0; j < NJ; ++j) xr[j] = s.xf[32 * j + lane];
+    } else {
+#pragma unroll
+        for (int m2 = 0; m2 < NJ / 2; ++m2) xp[m2] = s.xh[m2 * 32 + lane];
+    }
+    for (int rb = warp * R; rb < n_rows; rb += NCW * R) {
         float acc[R];
-        const unsigned char * wrow[R];
+        int   sb[R];
 #pragma unroll
         for (int i = 0; i < R; ++i) {
             acc[i] = 0.0f;
-            const int r = r0 + 16 * i;
-            wrow[i] = wbuf + (size_t) (r < n_rows ? r : r0) * (K * 2) + lane * 16;
+            const int r = rb + i < n_rows ? rb + i : rb;
+            sb[i] = s0 + r * SPR;
         }
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
             uint4 wv[R];
 #pragma unroll
-            for (int i = 0; i < R; ++i) wv[i] = *reinterpret_cast<const uint4 *>(wrow[i] + u * 512);
+            for (int i = 0; i < R; ++i) {
+                int slot = sb[i] + (u >> 2);
+                if (slot >= NSLOT) slot -= NSLOT;
+                wv[i] = *reinterpret_cast<const uint4 *>(s.ring + (size_t) slot * SLOT_B + (u & 3) * 512 + lane * 16);
+            }
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
 #pragma unroll
                 for (int i = 0; i < R; ++i) {
-                    const unsigned w2 = e == 0 ? wv[i].x : e == 1 ? wv[i].y : e == 2 ? wv[i].z : wv[i].w;
-                    const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&w2));
-                    acc[i] = __fmaf_rn(f.x, xr[8 * u + 2 * e], acc[i]);
-                    acc[i] = __fmaf_rn(f.y, xr[8 * u + 2 * e + 1], acc[i]);
+                    const unsigned w2 = u4_get(wv[i], e);
+                    if (XF32) {
+                        const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&w2));
+                        acc[i] = __fmaf_rn(f.x, xr[8 * u + 2 * e], acc[i]);
+                        acc[i] = __fmaf_rn(f.y, xr[8 * u + 2 * e + 1], acc[i]);
+                    } else {
+                        acc[i] = fhfma_lo(w2, xp[4 * u + e], acc[i]);
+                        acc[i] = fhfma_hi(w2, xp[4 * u + e], acc[i]);
+                    }
                 }
             }
         }
 #pragma unroll
         for (int i = 0; i < R; ++i) {
             const float res = reduce32_lanes(acc[i]);
-            const int r = r0 + 16 * i;
-            if (lane == 0 && r < n_rows) s.outv[r] = res;
+            if (lane == 0 && rb + i < n_rows) s.outv[rb + i] = res;
         }
     }
 }
 
+// write x[k] rounded to F16 into the lane-packed GEMV input (see Smem::xh)
+__device__ __forceinline__ void xh_put(Smem & s, int k, float v) {
+    reinterpret_cast<__half *>(s.xh)[(((k >> 6) * 32 + (k & 31)) << 1) + ((k >> 5) & 1)] = __float2half_rn(v);
+}
+
 // ------------------------------------------------------------------------------- RMSNorm
 // y = (x * rsqrt(mean(x^2)+eps)) * gamma; sum of squares in double (oracle D.5,
-// ggml/src/ggml-cpu/ops.cpp:3666-3691).  Writes float(r16(y)) to s.xf (the F16 mat-vec input)
-// and optionally the unrounded y (the `hidden_states` output).
-__device__ __forceinline__ void rmsnorm_to_xf(Smem & s, const float * __restrict__ gamma, float eps, float * y_out) {
+// ggml/src/ggml-cpu/ops.cpp:3666-3691).  x = s.xres; thread t owns elements t, t+480, t+960.
+// Writes F16(y) into s.xh (the F16 mat-vec input) and optionally the unrounded y (hidden states).
+// gamma values come in registers (fetched a layer ahead).  Ends with a cbar().
+struct Gam { float g[3]; };
+__device__ __forceinline__ Gam load_gamma(const float * __restrict__ gamma) {
+    Gam r;
+    const int t = threadIdx.x;
+    r.g[0] = __ldg(gamma + t); r.g[1] = __ldg(gamma + t + NCT);
+    r.g[2] = (t + 2 * NCT < H) ? __ldg(gamma + t + 2 * NCT) : 0.0f;
+    return r;
+}
+__device__ __forceinline__ void rmsnorm_to_xh(Smem & s, const Gam & gm, float eps, float * y_out, float * y_out2) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const float a = s.xres[t], b = s.xres[t + 512];
-    double sq = (double) __fmul_rn(a, a) + (double) __fmul_rn(b, b);
+    const bool has3 = t + 2 * NCT < H;
+    const float a = s.xres[t], b = s.xres[t + NCT], c = has3 ? s.xres[t + 2 * NCT] : 0.0f;
+    double sq = (double) __fmul_rn(a, a) + (double) __fmul_rn(b, b) + (double) __fmul_rn(c, c);
     sq = warp_sum_d(sq);
-    if (lane == 0) s.dred[0][warp] = sq;
-    __syncthreads();
-    double tot = 0.0;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) tot += s.dred[0][i];
+    if (lane == 0) s.dred[warp] = sq;
+    cbar();
+    double t0 = s.dred[0] + s.dred[1], t1 = s.dred[2] + s.dred[3], t2 = s.dred[4] + s.dred[5], t3 = s.dred[6] + s.dred[7];
+    t0 += s.dred[8] + s.dred[9]; t1 += s.dred[10] + s.dred[11]; t2 += s.dred[12] + s.dred[13]; t3 += s.dred[14];
+    const double tot = (t0 + t1) + (t2 + t3);
     const float mean  = (float) (tot / (double) H);
     const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
-    const float ya = __fmul_rn(__fmul_rn(a, scale), __ldg(gamma + t));
-    const float yb = __fmul_rn(__fmul_rn(b, scale), __ldg(gamma + t + 512));
-    s.xf[t] = r16(ya); s.xf[t + 512] = r16(yb);
-    if (y_out) { y_out[t] = ya; y_out[t + 512] = yb; }
-    __syncthreads();
+    const float ya = __fmul_rn(__fmul_rn(a, scale), gm.g[0]);
+    const float yb = __fmul_rn(__fmul_rn(b, scale), gm.g[1]);
+    xh_put(s, t, ya); xh_put(s, t + NCT, yb);
+    if (y_out)  { y_out[t] = ya;  y_out[t + NCT] = yb; }
+    if (y_out2) { y_out2[t] = ya; y_out2[t + NCT] = yb; }
+    if (has3) {
+        const float yc = __fmul_rn(__fmul_rn(c, scale), gm.g[2]);
+        xh_put(s, t + 2 * NCT, yc);
+        if (y_out)  y_out[t + 2 * NCT] = yc;
+        if (y_out2) y_out2[t + 2 * NCT] = yc;
+    }
+    cbar();
 }
 
 // per-head RMSNorm(128)*gamma then NEOX RoPE (FMA-contracted like the reference build), one warp;
-// lane l owns dims {l, l+32, l+64, l+96}; rope row = cos[64] | sin[64] (oracle D.7)
-__device__ __forceinline__ void head_norm_rope(const float * __restrict__ raw, const float * __restrict__ gamma,
-                                               const float * __restrict__ rope_row, float eps, bool do_norm,
-                                               float (&out)[4]) {
-    const int lane = threadIdx.x & 31;
-    float v[4];
+// lane l owns dims {l, l+32, l+64, l+96}; rope values c0,s0 (dim l) and c1,s1 (dim l+32) (oracle D.7)
+__device__ __forceinline__ void head_norm_rope(float (&v)[4], const float (&gn)[4], const float (&rp)[4], float eps) {
+    double sq = 0.0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) v[i] = ld_act(raw + lane + 32 * i);
-    if (do_norm) {
-        double sq = 0.0;
+    for (int i = 0; i < 4; ++i) sq += (double) __fmul_rn(v[i], v[i]);
+    sq = warp_sum_d(sq);
+    const float mean  = (float) (sq / (double) HD);
+    const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
 #pragma unroll
-        for (int i = 0; i < 4; ++i) sq += (double) __fmul_rn(v[i], v[i]);
-        sq = warp_sum_d(sq);
-        const float mean  = (float) (sq / (double) HD);
-        const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
-#pragma unroll
-        for (int i = 0; i < 4; ++i) v[i] = __fmul_rn(__fmul_rn(v[i], scale), __ldg(gamma + lane + 32 * i));
-        const float c0 = __ldg(rope_row + lane),      s0 = __ldg(rope_row + 64 + lane);
-        const float c1 = __ldg(rope_row + lane + 32), s1 = __ldg(rope_row + 64 + lane + 32);
-        // the reference build (g++ -O3 -mfma) contracts the rotation: fmsub(x0,c,x1*s), fmadd(x0,s,x1*c)
-        out[0] = __fmaf_rn(v[0], c0, -__fmul_rn(v[2], s0));
-        out[2] = __fmaf_rn(v[0], s0,  __fmul_rn(v[2], c0));
-        out[1] = __fmaf_rn(v[1], c1, -__fmul_rn(v[3], s1));
-        out[3] = __fmaf_rn(v[1], s1,  __fmul_rn(v[3], c1));
-    } else {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) out[i] = v[i];
-    }
+    for (int i = 0; i < 4; ++i) v[i] = __fmul_rn(__fmul_rn(v[i], scale), gn[i]);
+    const float c0 = rp[0], s0 = rp[1], c1 = rp[2], s1 = rp[3];
+    // the reference build (g++ -O3 -mfma) contracts the rotation: fmsub(x0,c,x1*s), fmadd(x0,s,x1*c)
+    const float o0 = __fmaf_rn(v[0], c0, -__fmul_rn(v[2], s0));
+    const float o2 = __fmaf_rn(v[0], s0,  __fmul_rn(v[2], c0));
+    const float o1 = __fmaf_rn(v[1], c1, -__fmul_rn(v[3], s1));
+    const float o3 = __fmaf_rn(v[1], s1,  __fmul_rn(v[3], c1));
+    v[0] = o0; v[1] = o1; v[2] = o2; v[3] = o3;
 }
 
 // ------------------------------------------------------------------------------- attention (phase B)
-// CTA role: kv group g = blockIdx % 8 (q heads 2g, 2g+1 share kv head g — GQA by broadcast,
-// ggml-cpu.c:1160-1199), split index c = blockIdx / 8 of C.  Stage 1 splits the positions for the
-// scores, stage 2 splits the head dimension for P.V, so every dot product keeps the oracle's
-// accumulation order (D.4): s_t = dot_f16(K_t, r16(q)) * scale ; P = softmax ; o_d =
-// dot_f16(V^T_d, r16(P)) over positions (32 accumulator lanes t%32 + double-precision leftovers).
-__device__ __forceinline__ int attn_splits(int n_kv, bool f32attn) {
-    if (f32attn || n_kv <= 48) return 1;
-    if (n_kv <= 192) return 4;
-    if (n_kv <= 1024) return 8;
-    return 16;
-}
+// CTA h (< 16) owns query head h of every layer (kv head h/2 — GQA by broadcast, ggml-cpu.c:1160-1199;
+// the even head of a pair appends K/V to the cache).  Every dot product keeps the oracle's order
+// (D.4): s_t = dot_f16(K_t, r16(q)) * scale ; P = softmax ; o_d = dot_f16(V^T_d, r16(P)) over
+// positions (32 accumulator lanes t%32 + double-precision leftovers).
+// K cache rows are chain-major (element d = 32i + a at a*4 + i: one 8-byte load per lane), V rows natural.
+struct AttnRegs {          // per-lane parameters fetched ahead of use (warps 0 and 1)
+    float gn[4];           // q_norm (warp 0) / k_norm (warp 1) of the layer
+    float rp[4];           // RoPE c0, s0, c1, s1 of the position
+};
 
-__device__ __forceinline__ float ld_half_cg(const __half * p) {
-    const unsigned short u = __ldcg(reinterpret_cast<const unsigned short *>(p));
-    return __half2float(__ushort_as_half(u));
-}
+__device__ __forceinline__ uint2 ld_cg_u2(const void * p) { return __ldcg(reinterpret_cast<const uint2 *>(p)); }
 
-__device__ void attention_phase(const DevModel & m, const StackW & W, int l, int pos, bool f32attn, int width,
-                                Smem & s, BarState & bs) {
+__device__ void attention_head(const DevModel & m, const StackW & W, int l, int h, int pos, bool f32attn, int width,
+                               const AttnRegs & ar, unsigned ep_in, unsigned ep_out, Smem & s, Watch & wd_) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const int g = blockIdx.x % NKV, c = blockIdx.x / NKV;
+    const int g = h >> 1;
+    const bool writer = (h & 1) == 0;
     const int n_kv = pos + 1;
     // row width of the reference graph: a prefill scores all n_past + n_tokens cache rows and masks
     // the future ones with -inf (src/tts_transformer.cpp:1205-1227); masked entries add exact zeros,
     // but the width decides which positions take the 8-wide SIMD exp vs the libm tail and which
     // take the 32-lane part of the P.V dot vs its double-precision leftovers.
     const int wd = width > n_kv ? width : n_kv;
-    const int C = attn_splits(n_kv, f32attn);
-    const bool active = c < C;
     const float kq_scale = 1.0f / sqrtf((float) HD);
     const size_t kv_head_base = ((size_t) (l * NKV + g) * W.n_ctx) * HD;
-    float * ao = m.part_o;                                   // [16 heads][128] attention output
+    Pkt * att = m.x_att + h * HD;
 
-    if (!active) {
-        if (C > 1) group_barrier(m, bs, g, C, false);
-        return;
-    }
-    // ---- prologue: q (2 heads), k, v of the new token; the CTA with c == 0 appends K/V to the cache
-    if (warp < 4) {
-        const float * rope_row = m.rope + (size_t) pos * HD;
-        float o[4];
-        if (warp < 2) {
-            head_norm_rope(m.qkv + (2 * g + warp) * HD, W.q_norm + l * HD, rope_row, m.eps, true, o);
+    // ---- prologue: q, k, v of the new token (warps 0, 1, 2)
+    if (warp < 3) {
+        const Pkt * src = m.x_qkv + (warp == 0 ? h * HD : warp == 1 ? NH * HD + g * HD : (NH + NKV) * HD + g * HD);
+        float v[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { s.qf[warp][lane + 32 * i] = o[i]; s.qr[warp][lane + 32 * i] = r16(o[i]); }
-        } else if (warp == 2) {
-            head_norm_rope(m.qkv + NH * HD + g * HD, W.k_norm + l * HD, rope_row, m.eps, true, o);
+        for (int i = 0; i < 4; ++i) v[i] = pk_poll(m, src + lane + 32 * i, ep_in, wd_);
+        if (warp == 0) {
+            head_norm_rope(v, ar.gn, ar.rp, m.eps);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int d = lane + 32 * i;
-                const __half hv = __float2half_rn(o[i]);
-                s.knew_f[d] = o[i]; s.knew_h[d] = hv;
-                if (c == 0) {
-                    W.kcache[kv_head_base + (size_t) pos * HD + d] = hv;
-                    if (W.kf32 && pos < 2) W.kf32[((size_t) (l * 2 + pos) * NKV + g) * HD + d] = o[i];
+            for (int i = 0; i < 4; ++i) { s.qf[lane + 32 * i] = v[i]; s.qr[lane + 32 * i] = r16(v[i]); }
+        } else if (warp == 1) {
+            head_norm_rope(v, ar.gn, ar.rp, m.eps);
+            __half hv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { hv[i] = __float2half_rn(v[i]); s.knew_f[lane + 32 * i] = v[i]; s.knew_h[lane + 32 * i] = hv[i]; }
+            if (writer) {
+                uint2 pk;
+                pk.x = (unsigned) __half_as_ushort(hv[0]) | ((unsigned) __half_as_ushort(hv[1]) << 16);
+                pk.y = (unsigned) __half_as_ushort(hv[2]) | ((unsigned) __half_as_ushort(hv[3]) << 16);
+                *reinterpret_cast<uint2 *>(W.kcache + kv_head_base + (size_t) pos * HD + lane * 4) = pk;
+                if (W.kf32 && pos < 2) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) W.kf32[((size_t) (l * 2 + pos) * NKV + g) * HD + lane + 32 * i] = v[i];
                 }
+                __threadfence();
             }
         } else {
-            head_norm_rope(m.qkv + (NH + NKV) * HD + g * HD, nullptr, rope_row, m.eps, false, o);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int d = lane + 32 * i;
-                const __half hv = __float2half_rn(o[i]);
-                s.vnew_f[d] = o[i]; s.vnew_h[d] = hv;
-                if (c == 0) {
+                const __half hv = __float2half_rn(v[i]);
+                s.vnew_f[d] = v[i]; s.vnew_h[d] = hv;
+                if (writer) {
                     W.vcache[kv_head_base + (size_t) pos * HD + d] = hv;
-                    if (W.vf32 && pos < 2) W.vf32[((size_t) (l * 2 + pos) * NKV + g) * HD + d] = o[i];
+                    if (W.vf32 && pos < 2) W.vf32[((size_t) (l * 2 + pos) * NKV + g) * HD + d] = v[i];
                 }
             }
+            if (writer) __threadfence();
         }
     }
-    __syncthreads();
+    cbar();
 
     if (f32attn) {
         // code-predictor prefill numerics: the reference graph multiplies the fresh F32 Kcur/Vcur/Q
         // and does not round P (src/tts_transformer.cpp:1624-1635): ggml_vec_dot_f32 order.
-        if (warp < 2) {
+        if (warp == 0) {
             float sc_t[2];
             float mx = -CUDART_INF_F;
             const int n = pos + 1 < 2 ? pos + 1 : 2;
             for (int tt = 0; tt < n; ++tt) {
-                const float * krow = (tt == pos) ? s.knew_f : (W.kf32 + ((size_t) (l * 2 + tt) * NKV + g) * HD);
+                const float * krow = W.kf32 + ((size_t) (l * 2 + tt) * NKV + g) * HD;
                 float acc = 0.0f;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const float kv = (tt == pos) ? krow[lane + 32 * i] : ld_act(krow + lane + 32 * i);
-                    acc = __fmaf_rn(kv, s.qf[warp][lane + 32 * i], acc);
+                    const float kv = (tt == pos) ? s.knew_f[lane + 32 * i] : ld_act(krow + lane + 32 * i);
+                    acc = __fmaf_rn(kv, s.qf[lane + 32 * i], acc);
                 }
                 sc_t[tt] = __fmul_rn(reduce32_lanes(acc), kq_scale);
                 mx = fmaxf(mx, sc_t[tt]);
@@ -371,176 +453,154 @@ __device__ void attention_phase(const DevModel & m, const StackW & W, int l, int
             const float inv = (float) (1.0 / sum);
             float o[4] = {0.f, 0.f, 0.f, 0.f};
             for (int tt = 0; tt < n; ++tt) {
-                const float * vrow = (tt == pos) ? s.vnew_f : (W.vf32 + ((size_t) (l * 2 + tt) * NKV + g) * HD);
+                const float * vrow = W.vf32 + ((size_t) (l * 2 + tt) * NKV + g) * HD;
                 const float p = __fmul_rn(sc_t[tt], inv);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const float vv = (tt == pos) ? vrow[lane + 32 * i] : ld_act(vrow + lane + 32 * i);
+                    const float vv = (tt == pos) ? s.vnew_f[lane + 32 * i] : ld_act(vrow + lane + 32 * i);
                     o[i] = __fmaf_rn(vv, p, o[i]);
                 }
             }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) ao[(2 * g + warp) * HD + lane + 32 * i] = o[i];
+            for (int i = 0; i < 4; ++i) pk_store(att + lane + 32 * i, o[i], ep_out);
         }
         return;
     }
 
-    float * sb0 = m.sbuf + (size_t) (2 * g) * ATT_MAX_KV;
-    float * sb1 = sb0 + ATT_MAX_KV;
-    // ---- stage 1: scores of this CTA's position chunk
+    // ---- scores: warp w takes positions w, w+15, ...; lane a walks chain a (4 steps) of dot_f16(K_t, q)
     {
-        const int Lc = (n_kv + C - 1) / C;
-        const int t0 = min(c * Lc, n_kv), t1 = min(n_kv, t0 + Lc);
-        float q0[4], q1[4];
+        float q[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { q0[i] = s.qr[0][lane + 32 * i]; q1[i] = s.qr[1][lane + 32 * i]; }
-        float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F;
-        for (int tt = t0 + warp; tt < t1; tt += 16) {
-            float kv[4];
-            if (tt == pos) {
+        for (int i = 0; i < 4; ++i) q[i] = s.qr[lane + 32 * i];
+        const __half * kbase = W.kcache + kv_head_base;
+        float mx = -CUDART_INF_F;
+        for (int t0 = warp; t0 < n_kv; t0 += 4 * NCW) {
+            uint2 kk[4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) kv[i] = __half2float(s.knew_h[lane + 32 * i]);
-            } else {
-                const __half * krow = W.kcache + kv_head_base + (size_t) tt * HD;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) kv[i] = ld_half_cg(krow + lane + 32 * i);
+            for (int j = 0; j < 4; ++j) {
+                const int tt = t0 + j * NCW;
+                if (tt < n_kv && tt != pos) kk[j] = ld_cg_u2(kbase + (size_t) tt * HD + lane * 4);
             }
-            float a0 = 0.0f, a1 = 0.0f;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { a0 = __fmaf_rn(kv[i], q0[i], a0); a1 = __fmaf_rn(kv[i], q1[i], a1); }
-            const float s0 = __fmul_rn(reduce32_lanes(a0), kq_scale);
-            const float s1 = __fmul_rn(reduce32_lanes(a1), kq_scale);
-            mx0 = fmaxf(mx0, s0); mx1 = fmaxf(mx1, s1);
-            if (lane == 0) { sb0[tt] = s0; sb1[tt] = s1; }
-        }
-        if (lane == 0) { s.fred[warp] = mx0; s.fred[16 + warp] = mx1; }
-        __threadfence_block();
-        __syncthreads();
-        if (t == 0) {
-            float a = s.fred[0], b = s.fred[16];
-            for (int i = 1; i < 16; ++i) { a = fmaxf(a, s.fred[i]); b = fmaxf(b, s.fred[16 + i]); }
-            float * pm = m.part_ms + (size_t) (g * 16 + c) * 2;
-            pm[0] = a; pm[1] = b;
-        }
-    }
-    if (C > 1) group_barrier(m, bs, g, C, true);
-    else { __threadfence_block(); __syncthreads(); }
-
-    // ---- soft-max over all n_kv positions (every CTA of the group, redundantly)
-    float M0 = -CUDART_INF_F, M1 = -CUDART_INF_F;
-    for (int i = 0; i < C; ++i) {
-        const float * pm = m.part_ms + (size_t) (g * 16 + i) * 2;
-        M0 = fmaxf(M0, ld_act(pm)); M1 = fmaxf(M1, ld_act(pm + 1));
-    }
-    const int n8 = wd >> 3;                                  // chunks that take the SIMD exp
-    const int n8v = min(n8, (n_kv + 7) >> 3);                // ... of which these hold unmasked positions
-    double ds0 = 0.0, ds1 = 0.0;
-    for (int ch = t; ch < n8v; ch += LM_THREADS) {          // ggml_vec_soft_max_f32, 8 lanes at a time (vec.cpp:558-568)
-        float e0[8], e1[8];
-        const float4 * p0 = reinterpret_cast<const float4 *>(sb0 + ch * 8);
-        const float4 * p1 = reinterpret_cast<const float4 *>(sb1 + ch * 8);
-        const float4 x0 = __ldcg(p0), x1 = __ldcg(p0 + 1), y0 = __ldcg(p1), y1 = __ldcg(p1 + 1);
-        const float xs[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
-        const float ys[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const bool live = ch * 8 + j < n_kv;             // masked: exp(-inf) = +0
-            e0[j] = live ? v_expf(__fsub_rn(xs[j], M0)) : 0.0f;
-            e1[j] = live ? v_expf(__fsub_rn(ys[j], M1)) : 0.0f;
-        }
-        ds0 += (double) __fadd_rn(__fadd_rn(__fadd_rn(e0[4], e0[0]), __fadd_rn(e0[6], e0[2])),
-                                  __fadd_rn(__fadd_rn(e0[5], e0[1]), __fadd_rn(e0[7], e0[3])));
-        ds1 += (double) __fadd_rn(__fadd_rn(__fadd_rn(e1[4], e1[0]), __fadd_rn(e1[6], e1[2])),
-                                  __fadd_rn(__fadd_rn(e1[5], e1[1]), __fadd_rn(e1[7], e1[3])));
-    }
-    if (n8 * 8 + t < n_kv && t < 8) {                       // scalar tail: libm expf
-        const int tt = n8 * 8 + t;
-        ds0 += (double) tail_expf(__fsub_rn(ld_act(sb0 + tt), M0));
-        ds1 += (double) tail_expf(__fsub_rn(ld_act(sb1 + tt), M1));
-    }
-    ds0 = warp_sum_d(ds0); ds1 = warp_sum_d(ds1);
-    if (lane == 0) { s.dred[0][warp] = ds0; s.dred[1][warp] = ds1; }
-    __syncthreads();
-    double S0 = 0.0, S1 = 0.0;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) { S0 += s.dred[0][i]; S1 += s.dred[1][i]; }
-    const float inv0 = (float) (1.0 / S0), inv1 = (float) (1.0 / S1);
-    for (int tt = t; tt < n_kv; tt += LM_THREADS) {
-        const float x = __fsub_rn(ld_act(sb0 + tt), M0), y = __fsub_rn(ld_act(sb1 + tt), M1);
-        const bool simd = tt < n8 * 8;
-        s.ph[0][tt] = __float2half_rn(__fmul_rn(simd ? v_expf(x) : tail_expf(x), inv0));
-        s.ph[1][tt] = __float2half_rn(__fmul_rn(simd ? v_expf(y) : tail_expf(y), inv1));
-    }
-    __syncthreads();
-
-    // ---- stage 2: o[d] for this CTA's nd = 128/C dims, both heads
-    const int nd = HD / C, d0 = c * nd;
-    const int TB = VT_HALVES / nd;                          // positions per V^T tile (multiple of 32)
-    const int np = min(wd & ~31, n_kv);                     // positions in the 32-lane part of the dot
-    const int ndg = nd >> 3;                                // 16-byte groups per position
-    float acc0[8], acc1[8];                                 // up to 8 dims per warp (nd = 128)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { acc0[j] = 0.0f; acc1[j] = 0.0f; }
-    const __half * vbase = W.vcache + kv_head_base;
-    for (int tb0 = 0; tb0 < np; tb0 += TB) {
-        const int tbn = min(TB, np - tb0);
-        for (int idx = t; idx < tbn * ndg; idx += LM_THREADS) {
-            const int tt = idx / ndg, dg = idx % ndg;
-            const int tg = tb0 + tt;
-            uint4 v;
-            if (tg == pos) v = *reinterpret_cast<const uint4 *>(s.vnew_h + d0 + dg * 8);
-            else v = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tg * HD + d0 + dg * 8));
-            const __half * vh = reinterpret_cast<const __half *>(&v);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) s.vt[(dg * 8 + e) * TB + tt] = vh[e];
-        }
-        __syncthreads();
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int dl = warp + 16 * j;
-            if (dl < nd) {
-                for (int tt = lane; tt < tbn; tt += 32) {
-                    const float vv = __half2float(s.vt[dl * TB + tt]);
-                    acc0[j] = __fmaf_rn(vv, __half2float(s.ph[0][tb0 + tt]), acc0[j]);
-                    acc1[j] = __fmaf_rn(vv, __half2float(s.ph[1][tb0 + tt]), acc1[j]);
+            for (int j = 0; j < 4; ++j) {
+                const int tt = t0 + j * NCW;
+                if (tt < n_kv) {
+                    float k0, k1, k2, k3;
+                    if (tt == pos) {
+                        k0 = __half2float(s.knew_h[lane]);      k1 = __half2float(s.knew_h[lane + 32]);
+                        k2 = __half2float(s.knew_h[lane + 64]); k3 = __half2float(s.knew_h[lane + 96]);
+                    } else {
+                        const float2 f01 = __half22float2(*reinterpret_cast<const __half2 *>(&kk[j].x));
+                        const float2 f23 = __half22float2(*reinterpret_cast<const __half2 *>(&kk[j].y));
+                        k0 = f01.x; k1 = f01.y; k2 = f23.x; k3 = f23.y;
+                    }
+                    float a = __fmaf_rn(k0, q[0], 0.0f);
+                    a = __fmaf_rn(k1, q[1], a); a = __fmaf_rn(k2, q[2], a); a = __fmaf_rn(k3, q[3], a);
+                    const float sv = __fmul_rn(reduce32_lanes(a), kq_scale);
+                    mx = fmaxf(mx, sv);
+                    if (lane == 0) s.sc[tt] = sv;
                 }
             }
         }
-        __syncthreads();
+        if (lane == 0) s.fred[warp] = mx;
     }
-    // leftovers t in [np, n_kv): staged into the tile, then one thread per (head, dim) adds them
-    // sequentially in double like ggml_vec_dot_f16's scalar tail (vec.cpp:381-384)
+    cbar();
+    float M = s.fred[0];
+#pragma unroll
+    for (int i = 1; i < NCW; ++i) M = fmaxf(M, s.fred[i]);
+
+    // ---- soft-max over the row (ggml_vec_soft_max_f32: 8 lanes at a time, libm tail; vec.cpp:548-617)
+    const int n8  = wd >> 3;                                 // chunks that take the SIMD exp
+    const int n8v = min(n8, (n_kv + 7) >> 3);                // ... of which these hold unmasked positions
+    double ds = 0.0;
+    for (int ch = t; ch < n8v; ch += NCT) {
+        float e[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int tt = ch * 8 + j;
+            e[j] = tt < n_kv ? v_expf(__fsub_rn(s.sc[tt], M)) : 0.0f;     // masked: exp(-inf) = +0
+        }
+        ds += (double) __fadd_rn(__fadd_rn(__fadd_rn(e[4], e[0]), __fadd_rn(e[6], e[2])),
+                                 __fadd_rn(__fadd_rn(e[5], e[1]), __fadd_rn(e[7], e[3])));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (ch * 8 + j < n_kv) s.sc[ch * 8 + j] = e[j];
+    }
+    if (t < 8 && n8 * 8 + t < n_kv) {                        // scalar tail: libm expf
+        const int tt = n8 * 8 + t;
+        const float e = tail_expf(__fsub_rn(s.sc[tt], M));
+        ds += (double) e;
+        s.sc[tt] = e;
+    }
+    ds = warp_sum_d(ds);
+    if (lane == 0) s.dred[warp] = ds;
+    cbar();
+    double S = 0.0;
+#pragma unroll
+    for (int i = 0; i < NCW; ++i) S += s.dred[i];
+    const float inv = (float) (1.0 / S);
+    for (int tt = t; tt < n_kv; tt += NCT) s.ph[tt] = __float2half_rn(__fmul_rn(s.sc[tt], inv));
+
+    // ---- P.V: warps 0..7 own 16 dims each, lane a = accumulator lane a (position % 32);
+    //      warps 8..14 stage the leftover rows (positions np..n_kv-1) for the double-precision tail
+    const int np = min(wd & ~31, n_kv);                      // positions in the 32-lane part of the dot
     const int nleft = n_kv - np;
-    for (int idx = t; idx < nleft * ndg; idx += LM_THREADS) {
-        const int tt = idx / ndg, dg = idx % ndg;
-        const int tg = np + tt;
-        uint4 v;
-        if (tg == pos) v = *reinterpret_cast<const uint4 *>(s.vnew_h + d0 + dg * 8);
-        else v = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tg * HD + d0 + dg * 8));
-        const __half * vh = reinterpret_cast<const __half *>(&v);
+    const __half * vbase = W.vcache + kv_head_base;
+    cbar();
+    if (warp < 8) {
+        const int d0 = warp * 16;
+        float acc[16];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) s.vt[(dg * 8 + e) * TB + tt] = vh[e];
-    }
+        for (int e = 0; e < 16; ++e) acc[e] = 0.0f;
+        for (int tb = 0; tb < np; tb += 32) {
+            const int tt = tb + lane;
+            uint4 v0, v1;
+            if (tt == pos) {
+                v0 = *reinterpret_cast<const uint4 *>(s.vnew_h + d0);
+                v1 = *reinterpret_cast<const uint4 *>(s.vnew_h + d0 + 8);
+            } else {
+                v0 = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tt * HD + d0));
+                v1 = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tt * HD + d0 + 8));
+            }
+            const unsigned pu = (unsigned) __half_as_ushort(s.ph[tt]);
+            const unsigned p2 = pu | (pu << 16);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const int dl = warp + 16 * j;
-        const float r0 = reduce32_lanes(acc0[j]), r1 = reduce32_lanes(acc1[j]);
-        if (dl < nd && lane == 0) { s.xf[dl] = r0; s.xf[HD + dl] = r1; }      // xf is free during phase B
+            for (int e = 0; e < 4; ++e) {
+                acc[2 * e]         = fhfma_lo(u4_get(v0, e), p2, acc[2 * e]);
+                acc[2 * e + 1]     = fhfma_hi(u4_get(v0, e), p2, acc[2 * e + 1]);
+                acc[8 + 2 * e]     = fhfma_lo(u4_get(v1, e), p2, acc[8 + 2 * e]);
+                acc[8 + 2 * e + 1] = fhfma_hi(u4_get(v1, e), p2, acc[8 + 2 * e + 1]);
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            const float r = reduce32_lanes(acc[e]);
+            if (lane == 0) s.o32[d0 + e] = r;
+        }
+    } else {
+        for (int idx = t - 8 * 32; idx < nleft * (HD / 8); idx += (NCW - 8) * 32) {
+            const int i = idx >> 4, dg = idx & 15;
+            const int tg = np + i;
+            uint4 v;
+            if (tg == pos) v = *reinterpret_cast<const uint4 *>(s.vnew_h + dg * 8);
+            else v = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tg * HD + dg * 8));
+            *reinterpret_cast<uint4 *>(s.vt + i * HD + dg * 8) = v;
+        }
     }
-    __syncthreads();
-    if (t < 2 * nd) {
-        const int h = t / nd, dl = t % nd;
-        double sumf = (double) s.xf[h * HD + dl];
+    cbar();
+    // leftovers: one thread per dim adds them sequentially in double like ggml_vec_dot_f16's scalar
+    // tail (vec.cpp:381-384)
+    if (t < HD) {
+        double sumf = (double) s.o32[t];
         for (int i = 0; i < nleft; ++i)
-            sumf += (double) __fmul_rn(__half2float(s.vt[dl * TB + i]), __half2float(s.ph[h][np + i]));
-        ao[(2 * g + h) * HD + d0 + dl] = (float) sumf;
+            sumf += (double) __fmul_rn(__half2float(s.vt[i * HD + t]), __half2float(s.ph[np + i]));
+        pk_store(att + t, (float) sumf, ep_out);
     }
 }
 
 // --------------------------------------------------------------------------- token selection
 // Reference: host argmax (src/tts_transformer.cpp:2182-2192: first maximum wins) and the
 // sample_or_argmax lambda / cb0 post-processing (:2349-2387, :2664-2722).  Every CTA evaluates
-// the selection redundantly on identical global data, so no extra barrier is needed.
+// the selection redundantly on the same packets, so no extra exchange is needed.
 __device__ __forceinline__ float proc_logit(const DevModel & m, float raw, int i, bool process,
                                             int suppress_start, int eos_id, float rep_penalty) {
     if (!process) return raw;
@@ -549,10 +609,13 @@ __device__ __forceinline__ float proc_logit(const DevModel & m, float raw, int i
     return raw;
 }
 
-__device__ int select_greedy(const DevModel & m, Smem & s) {
+__device__ int select_greedy(const DevModel & m, Smem & s, unsigned ep, Watch & w) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     float v = -CUDART_INF_F; int idx = 0x7fffffff;
-    if (t < (int) gridDim.x) { v = ld_act(m.cand_val + t); idx = ld_act_i(m.cand_idx + t); }
+    if (t < (int) gridDim.x) {
+        const float2 c = pk_poll2(m, m.x_cand + 2 * t, ep, w);
+        v = c.x; idx = __float_as_int(c.y);
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const float ov = __shfl_xor_sync(0xffffffffu, v, o);
@@ -560,14 +623,14 @@ __device__ int select_greedy(const DevModel & m, Smem & s) {
         if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
     }
     if (lane == 0) { s.fred[warp] = v; s.ired[warp] = idx; }
-    __syncthreads();
+    cbar();
     v = s.fred[0]; idx = s.ired[0];
 #pragma unroll
-    for (int i = 1; i < 16; ++i) {
+    for (int i = 1; i < NCW; ++i) {
         const float ov = s.fred[i]; const int oi = s.ired[i];
         if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
     }
-    __syncthreads();
+    cbar();
     return idx;
 }
 
@@ -587,17 +650,17 @@ __device__ __forceinline__ double u01(unsigned long long seed, unsigned long lon
 }
 
 // temperature -> top-k threshold (ties kept, `<` test) -> softmax (double sum) -> inverse CDF draw
-__device__ int select_sample(const DevModel & m, Smem & s, int vocab, bool process, int suppress_start,
+__device__ int select_sample(const DevModel & m, Smem & s, unsigned ep, Watch & w, int vocab, bool process, int suppress_start,
                              int eos_id, float rep_penalty, float temperature, int top_k,
                              unsigned long long seed, unsigned long long draw) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    constexpr int PER = 6;                       // 512 * 6 = 3072 >= vocab
+    constexpr int PER = 7;                       // 480 * 7 = 3360 >= vocab
     float l[PER];
 #pragma unroll
     for (int i = 0; i < PER; ++i) {
         const int idx = t * PER + i;
         l[i] = -CUDART_INF_F;
-        if (idx < vocab) l[i] = proc_logit(m, ld_act(m.logits + idx), idx, process, suppress_start, eos_id, rep_penalty) / temperature;
+        if (idx < vocab) l[i] = proc_logit(m, pk_poll(m, m.x_logit + idx, ep, w), idx, process, suppress_start, eos_id, rep_penalty) / temperature;
     }
     int * hist = reinterpret_cast<int *>(s.vt);              // 256 bins + 2 control words
     if (top_k > 0 && top_k < vocab) {
@@ -606,7 +669,7 @@ __device__ int select_sample(const DevModel & m, Smem & s, int vocab, bool proce
         for (int pass = 0; pass < 4; ++pass) {
             const int shift = 24 - 8 * pass;
             if (t < 256) hist[t] = 0;
-            __syncthreads();
+            cbar();
 #pragma unroll
             for (int i = 0; i < PER; ++i) {
                 if (t * PER + i < vocab) {
@@ -614,17 +677,17 @@ __device__ int select_sample(const DevModel & m, Smem & s, int vocab, bool proce
                     if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255], 1);
                 }
             }
-            __syncthreads();
+            cbar();
             if (t == 0) {
                 int acc = 0, d = 255;
                 for (; d > 0; --d) { if (acc + hist[d] >= k_rem) break; acc += hist[d]; }
                 hist[256] = d; hist[257] = k_rem - acc;
             }
-            __syncthreads();
+            cbar();
             prefix |= ((unsigned int) hist[256]) << shift;
             mask   |= 0xffu << shift;
             k_rem   = hist[257];
-            __syncthreads();
+            cbar();
         }
         const float thr = key2f(prefix);
 #pragma unroll
@@ -635,10 +698,10 @@ __device__ int select_sample(const DevModel & m, Smem & s, int vocab, bool proce
     for (int i = 0; i < PER; ++i) mx = fmaxf(mx, l[i]);
     mx = warp_max(mx);
     if (lane == 0) s.fred[warp] = mx;
-    __syncthreads();
+    cbar();
     mx = s.fred[0];
 #pragma unroll
-    for (int i = 1; i < 16; ++i) mx = fmaxf(mx, s.fred[i]);
+    for (int i = 1; i < NCW; ++i) mx = fmaxf(mx, s.fred[i]);
     float e[PER];
     double loc = 0.0;
 #pragma unroll
@@ -647,16 +710,16 @@ __device__ int select_sample(const DevModel & m, Smem & s, int vocab, bool proce
     double inc = loc;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const double v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
-    __syncthreads();
-    if (lane == 31) s.dred[0][warp] = inc;
-    __syncthreads();
+    cbar();
+    if (lane == 31) s.dred[warp] = inc;
+    cbar();
     double woff = 0.0, total = 0.0;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) { if (i < warp) woff += s.dred[0][i]; total += s.dred[0][i]; }
+    for (int i = 0; i < NCW; ++i) { if (i < warp) woff += s.dred[i]; total += s.dred[i]; }
     inc += woff;
     const double target = u01(seed, draw) * total;
     if (t == 0) s.tok = -1;
-    __syncthreads();
+    cbar();
     const double exc = inc - loc;
     if (target >= exc && target < inc) {
         double a = exc; int pick = -1;
@@ -665,180 +728,228 @@ __device__ int select_sample(const DevModel & m, Smem & s, int vocab, bool proce
         if (pick < 0) { for (int i = PER - 1; i >= 0; --i) if (e[i] > 0.0f) { pick = t * PER + i; break; } }
         if (pick >= 0) s.tok = pick;
     }
-    __syncthreads();
+    cbar();
     if (s.tok < 0) {            // rounding at the very end of the CDF: fall back to the arg-max element
         if (t == 0) s.tok = 0;
-        __syncthreads();
+        cbar();
 #pragma unroll
         for (int i = 0; i < PER; ++i) if (t * PER + i < vocab && l[i] == mx) s.tok = t * PER + i;
-        __syncthreads();
+        cbar();
     }
     const int tok = s.tok;
-    __syncthreads();
+    cbar();
     return tok;
 }
 
-
-// ------------------------------------------------------------------------------- weight slices
-struct Slices {            // this CTA's row ranges (fixed for the whole launch)
-    int a0, a1;            // qkv rows            (of 4096, K=1024)
-    int o0, o1;            // attn_output rows    (of 1024, K=2048)
-    int p0, p1;            // gate/up pairs       (of 3072, K=1024, 2 rows per pair)
-    int d0, d1;            // ffn_down rows       (of 1024, K=3072)
+// ------------------------------------------------------------------------------- one pass (compute warps)
+struct PassRegs {          // parameters fetched ahead of use; carried across layers and passes
+    Gam ga, gf;            // attn_norm / ffn_norm of the layer about to run
+    float gn[4];           // q_norm (warp 0) / k_norm (warp 1) of that layer (attention CTAs)
 };
 
-__device__ __forceinline__ const __half * sl_a(const StackW & W, int l, const Slices & z) {
-    return reinterpret_cast<const __half *>(W.wqkv) + ((size_t) l * QKV_N + z.a0) * H;
-}
-__device__ __forceinline__ const __half * sl_o(const StackW & W, int l, const Slices & z) {
-    return reinterpret_cast<const __half *>(W.wo) + ((size_t) l * H + z.o0) * (NH * HD);
-}
-__device__ __forceinline__ const __half * sl_gu(const StackW & W, int l, const Slices & z) {
-    return reinterpret_cast<const __half *>(W.wgu) + ((size_t) l * 2 * FFN + 2 * z.p0) * H;
-}
-__device__ __forceinline__ const __half * sl_d(const StackW & W, int l, const Slices & z) {
-    return reinterpret_cast<const __half *>(W.wdown) + ((size_t) l * H + z.d0) * FFN;
-}
-
-__device__ __forceinline__ void l2_prefetch_range(const void * p, size_t bytes) {
-    const char * c = reinterpret_cast<const char *>(p);
-    while (bytes > 0) {
-        const uint32_t n = bytes > 32768 ? 32768u : (uint32_t) bytes;
-        l2_prefetch_bulk(c, n);
-        c += n; bytes -= n;
+__device__ __forceinline__ void prefetch_layer_params(const StackW & W, int l, PassRegs & r) {
+    r.ga = load_gamma(W.attn_norm + (size_t) l * H);
+    r.gf = load_gamma(W.ffn_norm + (size_t) l * H);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if ((int) blockIdx.x < NH && warp < 2) {
+        const float * g = (warp == 0 ? W.q_norm : W.k_norm) + (size_t) l * HD;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) r.gn[i] = __ldg(g + lane + 32 * i);
     }
 }
-// one thread: pull this CTA's slices of layer l of stack W towards L2 (TMA-unit bulk prefetch)
-__device__ __forceinline__ void l2_prefetch_layer(const StackW & W, int l, const Slices & z) {
-    l2_prefetch_range(sl_a(W, l, z),  (size_t) (z.a1 - z.a0) * H * 2);
-    l2_prefetch_range(sl_o(W, l, z),  (size_t) (z.o1 - z.o0) * NH * HD * 2);
-    l2_prefetch_range(sl_gu(W, l, z), (size_t) (z.p1 - z.p0) * 2 * H * 2);
-    l2_prefetch_range(sl_d(W, l, z),  (size_t) (z.d1 - z.d0) * FFN * 2);
+
+// poll n packets (n even, multiple of 2) from src into dst (float) — all compute threads
+__device__ __forceinline__ void poll_vec(const DevModel & m, const Pkt * src, int n, unsigned ep, float * dst, Watch & w) {
+    for (int i = threadIdx.x; i < n / 2; i += NCT) {
+        const float2 f = pk_poll2(m, src + 2 * i, ep, w);
+        dst[2 * i] = f.x; dst[2 * i + 1] = f.y;
+    }
 }
 
-// ------------------------------------------------------------------------------- one pass
-// One token through `n_layers` layers of stack W (+ optional head).  s.xres holds x on entry;
-// the TMA fetches of A(0) -> buf0 and C(0) -> buf1 have been issued by the caller.  On exit the
-// fetches of the next pass' A(0)/C(0) (stack NW, if any) are in flight.
+// One token through `n_layers` layers of stack W (+ optional head).  s.xres holds x on entry (and a
+// cbar() has made it visible); pr holds layer 0's parameters.  On exit pr holds layer 0's parameters
+// of the next pass' stack NW (if any).
 __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc & p, int pos,
                           const HeadW * head, bool process, const GenState & gs,
                           const Slices & z, const StackW * NW,
-                          Smem & s, BarState & bs, WStream & ws) {
+                          Smem & s, Ring & rg, unsigned & ep, PassRegs & pr, Watch & w) {
     const int t = threadIdx.x;
     const int nA = z.a1 - z.a0, nO = z.o1 - z.o0, nP = z.p1 - z.p0, nD = z.d1 - z.d0;
     int h0 = 0, h1 = 0;
     if (head) cta_rows(head->vocab, h0, h1);
     const int nH = h1 - h0;
+    const bool attn_cta = (int) blockIdx.x < NH;
+
+    AttnRegs ar;
+    if (attn_cta && t < 64) {                                // RoPE row of this position (warps 0, 1)
+        const float * rope_row = m.rope + (size_t) pos * HD;
+        const int lane = t & 31;
+        ar.rp[0] = __ldg(rope_row + lane);      ar.rp[1] = __ldg(rope_row + 64 + lane);
+        ar.rp[2] = __ldg(rope_row + lane + 32); ar.rp[3] = __ldg(rope_row + 64 + lane + 32);
+    }
+    Gam gh;                                                  // out_norm for the head
+    gh.g[0] = gh.g[1] = gh.g[2] = 0.0f;
 
     for (int l = 0; l < p.n_layers; ++l) {
         const bool last = l + 1 == p.n_layers;
-        if (t == 0) {
-            if (!last) l2_prefetch_layer(W, l + 1, z);
-            else if (head) l2_prefetch_range(head->w + (size_t) h0 * H, (size_t) nH * H * 2);
+        const unsigned e_qkv = ep + 1, e_att = ep + 2, e_x1 = ep + 3, e_m = ep + 4, e_x = ep + 5;
+        // this layer's parameters are in registers; start fetching the next ones
+        const Gam ga = pr.ga, gf = pr.gf;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) ar.gn[i] = pr.gn[i];
+        if (!last) prefetch_layer_params(W, l + 1, pr);
+        else {
+            if (head) gh = load_gamma(W.out_norm);
+            if (NW) prefetch_layer_params(*NW, 0, pr);
         }
+
         // ---- phase A: RMSNorm + fused QKV mat-vec
         PROF(1);
-        rmsnorm_to_xf(s, W.attn_norm + (size_t) l * H, m.eps, nullptr);
+        if (l > 0) { poll_vec(m, m.x_x, H, ep, s.xres, w); cbar(); }
         PROF(2);
-        wait_fetch(s, ws, 0);
+        rmsnorm_to_xh(s, ga, m.eps, nullptr, nullptr);
         PROF(3);
-        gemv_lane<1024, 2>(s.buf0, nA, s);
-        __syncthreads();
-        if (t < nA) m.qkv[z.a0 + t] = s.outv[t];
-        issue_fetch(s, ws, 0, sl_gu(W, l, z), 2 * nP, H * 2);
+        int s0 = ring_acquire(m, s, rg, w);
         PROF(4);
-        grid_barrier(m, bs);
+        gemv_ring<1024, 2, false>(s, s0, nA);
+        cbar();
+        if (t < nA) pk_store(m.x_qkv + z.a0 + t, s.outv[t], e_qkv);
+        ring_release(s, rg, nA);
         PROF(5);
 
-        // ---- phase B: per-head norm + RoPE + KV append + attention
-        attention_phase(m, W, l, pos, p.f32attn != 0, p.width, s, bs);
+        // ---- phase B: per-head norm + RoPE + KV append + attention (CTA h owns head h)
+        if (attn_cta) attention_head(m, W, l, (int) blockIdx.x, pos, p.f32attn != 0, p.width, ar, e_qkv, e_att, s, w);
         PROF(6);
-        grid_barrier(m, bs);
-        PROF(7);
 
         // ---- phase C: attn_output mat-vec (input rounded to F16) + residual
-#pragma unroll
-        for (int i = 0; i < 4; ++i) s.xf[t + LM_THREADS * i] = r16(ld_act(m.part_o + t + LM_THREADS * i));
-        __syncthreads();
+        for (int i = t; i < NH * HD / 2; i += NCT) {
+            const float2 f = pk_poll2(m, m.x_att + 2 * i, e_att, w);
+            xh_put(s, 2 * i, f.x); xh_put(s, 2 * i + 1, f.y);
+        }
+        cbar();
+        PROF(7);
+        s0 = ring_acquire(m, s, rg, w);
         PROF(8);
-        wait_fetch(s, ws, 1);
+        gemv_ring<2048, 1, false>(s, s0, nO);
+        cbar();
+        if (t < nO) pk_store(m.x_x1 + z.o0 + t, __fadd_rn(s.outv[t], s.xres[z.o0 + t]), e_x1);
+        ring_release(s, rg, nO * 2);
         PROF(9);
-        gemv_lane<2048, 1>(s.buf1, nO, s);
-        __syncthreads();
-        if (t < nO) m.xb[z.o0 + t] = __fadd_rn(s.outv[t], s.xres[z.o0 + t]);
-        issue_fetch(s, ws, 1, sl_d(W, l, z), nD, FFN * 2);
-        PROF(10);
-        grid_barrier(m, bs);
-        PROF(11);
 
         // ---- phase D: RMSNorm + gate/up mat-vec + SwiGLU
-        s.xres[t] = ld_act(m.xb + t); s.xres[t + 512] = ld_act(m.xb + t + 512);
-        __syncthreads();
-        rmsnorm_to_xf(s, W.ffn_norm + (size_t) l * H, m.eps, nullptr);
+        poll_vec(m, m.x_x1, H, e_x1, s.xres, w);
+        cbar();
+        PROF(10);
+        rmsnorm_to_xh(s, gf, m.eps, nullptr, nullptr);
+        PROF(11);
+        s0 = ring_acquire(m, s, rg, w);
         PROF(12);
-        wait_fetch(s, ws, 0);
-        PROF(13);
-        gemv_lane<1024, 3>(s.buf0, 2 * nP, s);
-        __syncthreads();
+        gemv_ring<1024, 3, false>(s, s0, 2 * nP);
+        cbar();
         if (t < nP) {
             const float gt = s.outv[2 * t], up = s.outv[2 * t + 1];
             const float sl = __fdiv_rn(gt, __fadd_rn(1.0f, v_expf(__fsub_rn(0.0f, gt))));   // ggml_v_silu
-            m.mbuf[z.p0 + t] = __fmul_rn(sl, up);
+            pk_store(m.x_m + z.p0 + t, __fmul_rn(sl, up), e_m);
         }
-        if (!last)      issue_fetch(s, ws, 0, sl_a(W, l + 1, z), nA, H * 2);
-        else if (head)  issue_fetch(s, ws, 0, head->w + (size_t) h0 * H, nH, H * 2);
-        else if (NW)    issue_fetch(s, ws, 0, sl_a(*NW, 0, z), nA, H * 2);
-        PROF(14);
-        grid_barrier(m, bs);
-        PROF(15);
+        ring_release(s, rg, 2 * nP);
+        PROF(13);
 
         // ---- phase E: ffn_down on F32 activations (weights exact in F32) + residual
-#pragma unroll
-        for (int i = 0; i < FFN / LM_THREADS; ++i) s.xf[t + LM_THREADS * i] = ld_act(m.mbuf + t + LM_THREADS * i);
-        __syncthreads();
+        poll_vec(m, m.x_m, FFN, e_m, s.xf, w);
+        cbar();
+        PROF(14);
+        s0 = ring_acquire(m, s, rg, w);
+        PROF(15);
+        gemv_ring<3072, 1, true>(s, s0, nD);
+        cbar();
+        if (t < nD) pk_store(m.x_x + z.d0 + t, __fadd_rn(s.outv[t], s.xres[z.d0 + t]), e_x);
+        ring_release(s, rg, nD * 3);
         PROF(16);
-        wait_fetch(s, ws, 1);
-        PROF(17);
-        gemv_lane<3072, 1>(s.buf1, nD, s);
-        __syncthreads();
-        if (t < nD) m.xa[z.d0 + t] = __fadd_rn(s.outv[t], s.xres[z.d0 + t]);
-        if (!last)      issue_fetch(s, ws, 1, sl_o(W, l + 1, z), nO, NH * HD * 2);
-        else if (NW)    issue_fetch(s, ws, 1, sl_o(*NW, 0, z), nO, NH * HD * 2);
-        PROF(18);
-        grid_barrier(m, bs);
-        PROF(19);
-        s.xres[t] = ld_act(m.xa + t); s.xres[t + 512] = ld_act(m.xa + t + 512);
-        __syncthreads();
+        ep += 5;
     }
-    PROF(20);
 
     if (!head) return;
     // ---- head: final RMSNorm (= hidden_states) + vocabulary mat-vec + per-CTA arg-max candidate
-    rmsnorm_to_xf(s, W.out_norm, m.eps, blockIdx.x == 0 ? m.hidden : nullptr);
-    if (p.hidden_dst && blockIdx.x == 0) { p.hidden_dst[t] = m.hidden[t]; p.hidden_dst[t + 512] = m.hidden[t + 512]; }
-    wait_fetch(s, ws, 0);
-    gemv_lane<1024, 2>(s.buf0, nH, s);
-    __syncthreads();
+    const unsigned e_head = ep + 1;
+    poll_vec(m, m.x_x, H, ep, s.xres, w);
+    cbar();
+    rmsnorm_to_xh(s, gh, m.eps, blockIdx.x == 0 ? m.hidden : nullptr, blockIdx.x == 0 ? p.hidden_dst : nullptr);
+    PROF(20);
+    const int s0 = ring_acquire(m, s, rg, w);
+    gemv_ring<1024, 2, false>(s, s0, nH);
+    cbar();
     float pv = -CUDART_INF_F;
     if (t < nH) {
         const float raw = s.outv[t];
         m.logits[h0 + t] = raw;
         if (p.logits_dst) p.logits_dst[h0 + t] = raw;
+        pk_store(m.x_logit + h0 + t, raw, e_head);
         pv = proc_logit(m, raw, h0 + t, process, gs.suppress_start, gs.eos_id, gs.rep_penalty);
     }
-    __syncthreads();
+    cbar();
     if (t < nH) s.outv[t] = pv;
-    __syncthreads();
+    ring_release(s, rg, nH);
+    cbar();
     if (t == 0) {
         float bv = -CUDART_INF_F; int bi = 0x7fffffff;
         for (int i = 0; i < nH; ++i) if (s.outv[i] > bv) { bv = s.outv[i]; bi = h0 + i; }
         if (nH > 0 && bi == 0x7fffffff) bi = h0;       // all -inf: keep first-index semantics
-        m.cand_val[blockIdx.x] = bv; m.cand_idx[blockIdx.x] = bi;
+        pk_store(m.x_cand + 2 * blockIdx.x, bv, e_head);
+        pk_store(m.x_cand + 2 * blockIdx.x + 1, __int_as_float(bi), e_head);
     }
-    if (NW) issue_fetch(s, ws, 0, sl_a(*NW, 0, z), nA, H * 2);
+    ep += 1;
     PROF(21);
-    grid_barrier(m, bs);
-    PROF(22);
+}
+
+// ------------------------------------------------------------------------------- producer warp
+// Walks the same pass / layer / slice order as run_stack and keeps the ring full.  s_go: -1 until
+// the compute warps know how many passes of the program will run (EOS / max_len), then that count.
+__device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ passes, int n_passes,
+                              const Slices & z, Smem & s, volatile int * s_go) {
+    unsigned p_slot = 0, p_idx = 0;
+    const int nA = z.a1 - z.a0, nO = z.o1 - z.o0, nP = z.p1 - z.p0, nD = z.d1 - z.d0;
+    bool aborted = false;
+    for (int ip = 0; ip < n_passes && !aborted; ++ip) {
+        int go = *s_go;
+        while (go < 0 && ip > 0) { __nanosleep(64); go = *s_go; }     // pass 0 is produced optimistically
+        if (go >= 0 && ip >= go) break;
+        const int xmode = passes[ip].xmode;
+        if (xmode == XM_SELECT_ONLY) continue;
+        const StackW & W = passes[ip].stack == 0 ? m.talker : m.cp;
+        const int n_layers = passes[ip].n_layers, hd = passes[ip].head;
+        for (int l = 0; l < n_layers && !aborted; ++l) {
+            for (int k = 0; k < 4; ++k) {
+                const void * src = k == 0 ? (const void *) sl_a(W, l, z) : k == 1 ? (const void *) sl_o(W, l, z)
+                                 : k == 2 ? (const void *) sl_gu(W, l, z) : (const void *) sl_d(W, l, z);
+                const int n_slots = k == 0 ? nA : k == 1 ? nO * 2 : k == 2 ? nP * 2 : nD * 3;
+                // ring-space wait with an abort check (EOS decided while pass 0 is being produced)
+                while (true) {
+                    const unsigned long long c = s.consumed;
+                    if (p_slot + (unsigned) n_slots - (unsigned) c <= (unsigned) NSLOT && p_idx - (unsigned) (c >> 32) < (unsigned) NMB) break;
+                    if (*s_go == 0) { aborted = true; break; }
+                    __nanosleep(20);
+                }
+                if (aborted) break;
+                produce_slice(s, p_slot, p_idx, src, n_slots);
+            }
+        }
+        if (hd >= 0 && !aborted) {
+            const HeadW & hw = hd == 0 ? m.codec_head : m.cp_head[hd - 1];
+            int h0, h1; cta_rows(hw.vocab, h0, h1);
+            while (true) {
+                const unsigned long long c = s.consumed;
+                if (p_slot + (unsigned) (h1 - h0) - (unsigned) c <= (unsigned) NSLOT && p_idx - (unsigned) (c >> 32) < (unsigned) NMB) break;
+                if (*s_go == 0) { aborted = true; break; }
+                __nanosleep(20);
+            }
+            if (!aborted) produce_slice(s, p_slot, p_idx, hw.w + (size_t) h0 * H, h1 - h0);
+        }
+    }
+    if (*s_go == 0 || aborted) {
+        // the compute warps stopped consuming: wait for the copies already issued before the CTA retires
+        const unsigned c_idx = (unsigned) (s.consumed >> 32);
+        for (unsigned i = c_idx; i < p_idx; ++i) mbar_wait(&s.mbar[i % NMB], (i / NMB) & 1u);
+    }
 }
 
 // --------------------------------------------------------------------------- the kernel
@@ -851,16 +962,19 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
     Smem & s = *reinterpret_cast<Smem *>(smem_raw);
     __shared__ GenState gs;
     __shared__ PassDesc pd;
+    __shared__ int s_go_raw;
+    volatile int * s_go = &s_go_raw;
     const int t = threadIdx.x;
 
-    if (t == 0) gs = *m.st;
+    if (t == 0) {
+        gs = *m.st;
+        s_go_raw = frame_mode ? -1 : n_passes;
+        s.consumed = 0ULL;
+        for (int i = 0; i < NMB; ++i) mbar_init(&s.mbar[i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncthreads();
     if (frame_mode && gs.done) return;
-
-    BarState bs;
-    bs.target  = gs.bar_base;
-    bs.gtarget = gs.gbar_base[blockIdx.x % NKV];
-    bs.dead    = false;
 
     Slices z;
     cta_rows(QKV_N, z.a0, z.a1);
@@ -868,118 +982,111 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
     cta_rows(FFN,   z.p0, z.p1);
     cta_rows(H,     z.d0, z.d1);
 
-    WStream ws;
-    ws.parity[0] = ws.parity[1] = 0u;
-    ws.pending[0] = ws.pending[1] = false;
-    if (t == 0) {
-        mbar_init(&s.mbar[0], 1);
-        mbar_init(&s.mbar[1], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    if (t >= NCT) {                                   // ---- producer warp: one thread drives the TMA unit
+        if (t == NCT) producer_loop(m, passes, n_passes, z, s, s_go);
+        return;
     }
-    __syncthreads();
+
+    // ---- compute warps
+    Watch w; w.t0 = clock64(); w.dead = false;
+    Ring rg; rg.slot_head = 0; rg.slice_idx = 0;
+    unsigned ep = gs.ep_base;
+    unsigned pending_ep = gs.pending_ep;
     int frame = gs.frame, n_past = gs.n_past, done = gs.done, pending = gs.pending;
     int pending_vocab = gs.codec_vocab, pending_process = 1;
     unsigned long long draw = gs.draw;
+    PassRegs pr;
+    bool pr_valid = false;
 
     for (int ip = 0; ip < n_passes; ++ip) {
         PROF(30);
         if (t == 0) pd = passes[ip];
-        __syncthreads();
+        cbar();
         const PassDesc p = pd;
         const StackW & W = p.stack == 0 ? m.talker : m.cp;
-
-        // start pulling layer 0 of this stack towards L2 / shared memory before the (serial) selection
-        if (p.xmode != XM_SELECT_ONLY) {
-            if (t == 0) l2_prefetch_layer(W, 0, z);
-            if (!ws.pending[0]) issue_fetch(s, ws, 0, sl_a(W, 0, z), z.a1 - z.a0, H * 2);
-            if (!ws.pending[1]) issue_fetch(s, ws, 1, sl_o(W, 0, z), z.o1 - z.o0, NH * HD * 2);
-        }
+        if (!pr_valid && p.xmode != XM_SELECT_ONLY) { prefetch_layer_params(W, 0, pr); pr_valid = true; }
 
         // ---- select the token produced by the previous head, if one is waiting
         const bool needs_select = p.xmode == XM_HIDDEN || p.xmode == XM_CP_EMBD ||
                                   p.xmode == XM_TALKER_NEXT || p.xmode == XM_SELECT_ONLY;
         if (needs_select && pending >= 0) {
             int tok;
-            if (gs.temperature <= 0.0f) tok = select_greedy(m, s);
-            else tok = select_sample(m, s, pending_vocab, pending == 0 && pending_process, gs.suppress_start, gs.eos_id,
+            if (gs.temperature <= 0.0f) tok = select_greedy(m, s, pending_ep, w);
+            else tok = select_sample(m, s, pending_ep, w, pending_vocab, pending == 0 && pending_process, gs.suppress_start, gs.eos_id,
                                      gs.rep_penalty, gs.temperature, gs.top_k, gs.seed, draw++);
             if (t == 0) gs.cur[pending] = tok;
-            __syncthreads();
+            cbar();
             pending = -1;
         }
         if (p.xmode == XM_SELECT_ONLY) continue;
 
         if (p.xmode == XM_HIDDEN && frame_mode) {
             // src/tts_transformer.cpp:2724-2729: EOS stops before a frame is emitted
-            if (gs.cur[0] == gs.eos_id) { done = 1; break; }
-            if (blockIdx.x == 0 && t == 0) m.seen[gs.cur[0]] = 1;
+            if (gs.cur[0] == gs.eos_id) { done = 1; if (t == 0) *s_go = 0; break; }
+            if (blockIdx.x == 0 && t == 0) { m.seen[gs.cur[0]] = 1; __threadfence(); }
+        }
+        if (ip == 0 && frame_mode && t == 0) {
+            // :2755-2757 no talker step after the last frame: the producer must not stream it either
+            const bool trunc = passes[n_passes - 1].xmode == XM_TALKER_NEXT && frame + 1 >= gs.max_len;
+            *s_go = trunc ? n_passes - 1 : n_passes;
         }
         if (p.xmode == XM_TALKER_NEXT && frame_mode) {
             if (blockIdx.x == 0 && t < NCB) m.codes_out[(size_t) frame * NCB + t] = gs.cur[t];
             ++frame;
-            if (frame >= gs.max_len) { done = 1; break; }     // :2755-2757 no talker step after the last frame
+            if (frame >= gs.max_len) { done = 1; break; }
         }
 
-        // ---- form x in shared memory
-        {
-            float xa = 0.f, xb = 0.f;
+        // ---- form x in shared memory (elements t, t+480, t+960)
+        for (int k = t; k < H; k += NCT) {
+            float xv = 0.f;
             switch (p.xmode) {
-                case XM_BUF:    xa = ld_act(p.xsrc + t); xb = ld_act(p.xsrc + t + 512); break;
-                case XM_HIDDEN: xa = ld_act(m.hidden + t); xb = ld_act(m.hidden + t + 512); break;
-                case XM_CB0_EMBD: {
-                    const __half * r = m.codec_embd + (size_t) gs.cur[0] * H;
-                    xa = __half2float(r[t]); xb = __half2float(r[t + 512]);
-                } break;
-                case XM_CP_EMBD: {
-                    const __half * r = m.cp_embd[p.arg - 1] + (size_t) gs.cur[p.arg] * H;
-                    xa = __half2float(r[t]); xb = __half2float(r[t + 512]);
-                } break;
+                case XM_BUF:    xv = ld_act(p.xsrc + k); break;
+                case XM_HIDDEN: xv = ld_act(m.hidden + k); break;
+                case XM_CB0_EMBD: xv = __half2float(m.codec_embd[(size_t) gs.cur[0] * H + k]); break;
+                case XM_CP_EMBD:  xv = __half2float(m.cp_embd[p.arg - 1][(size_t) gs.cur[p.arg] * H + k]); break;
                 case XM_TALKER_NEXT: {
                     // :2759-2790  codec_embd[cb0] + sum_i code_pred_embd[i-1][c_i] + trailing/pad, F32 in this order
-                    const __half * r = m.codec_embd + (size_t) gs.cur[0] * H;
-                    xa = __half2float(r[t]); xb = __half2float(r[t + 512]);
+                    float hv[NCB];
+                    hv[0] = __half2float(m.codec_embd[(size_t) gs.cur[0] * H + k]);
 #pragma unroll
-                    for (int cb = 1; cb < NCB; ++cb) {
-                        const __half * q = m.cp_embd[cb - 1] + (size_t) gs.cur[cb] * H;
-                        xa = __fadd_rn(xa, __half2float(q[t])); xb = __fadd_rn(xb, __half2float(q[t + 512]));
-                    }
+                    for (int cb = 1; cb < NCB; ++cb) hv[cb] = __half2float(m.cp_embd[cb - 1][(size_t) gs.cur[cb] * H + k]);
                     const int fr = frame - 1;      // the frame just emitted
                     const float * tr = (fr < gs.trailing_len) ? (m.trailing + (size_t) fr * H) : m.pad_embed;
-                    xa = __fadd_rn(xa, ld_act(tr + t)); xb = __fadd_rn(xb, ld_act(tr + t + 512));
+                    const float tv = ld_act(tr + k);
+                    xv = hv[0];
+#pragma unroll
+                    for (int cb = 1; cb < NCB; ++cb) xv = __fadd_rn(xv, hv[cb]);
+                    xv = __fadd_rn(xv, tv);
                 } break;
                 default: break;
             }
-            s.xres[t] = xa; s.xres[t + 512] = xb;
+            s.xres[k] = xv;
         }
-        __syncthreads();
-
+        cbar();
         PROF(31);
+
         const int pos = p.pos >= 0 ? p.pos : n_past;
         const HeadW * head = p.head < 0 ? nullptr : (p.head == 0 ? &m.codec_head : &m.cp_head[p.head - 1]);
-        // the next pass' first weight slices are fetched across the pass boundary
+        // the next pass' first-layer parameters are fetched across the pass boundary
         const StackW * NW = nullptr;
         if (ip + 1 < n_passes) {
             const int nx = passes[ip + 1].xmode, ns = passes[ip + 1].stack;
             if (nx != XM_SELECT_ONLY) NW = ns == 0 ? &m.talker : &m.cp;
         }
-        run_stack(m, W, p, pos, head, p.process != 0, gs, z, NW, s, bs, ws);
-        if (head) { pending = p.head; pending_vocab = head->vocab; pending_process = p.process; }
+        if (!NW) pr_valid = false;
+        run_stack(m, W, p, pos, head, p.process != 0, gs, z, NW, s, rg, ep, pr, w);
+        if (head) { pending = p.head; pending_vocab = head->vocab; pending_process = p.process; pending_ep = ep; }
         if (p.stack == 0 && p.pos < 0) ++n_past;
     }
 
-    // drain TMA copies still in flight (early exit on EOS / max_len) before the CTA retires
-    if (ws.pending[0]) wait_fetch(s, ws, 0);
-    if (ws.pending[1]) wait_fetch(s, ws, 1);
-
-    // ---- write the state back (CTA 0); barrier epochs are identical in every CTA
+    // ---- write the state back (CTA 0); epochs are identical in every CTA
     if (blockIdx.x == 0 && t == 0) {
         GenState * st = m.st;
         st->frame = frame; st->n_past = n_past; st->done = done; st->pending = pending;
         st->draw = draw;
         for (int i = 0; i < NCB; ++i) st->cur[i] = gs.cur[i];
-        st->bar_base = bs.target;
+        st->ep_base = ep; st->pending_ep = pending_ep;
     }
-    if (blockIdx.x < NKV && t == 0) m.st->gbar_base[blockIdx.x] = bs.gtarget;
 }
 
 // --------------------------------------------------------------------------- host launch
@@ -1000,7 +1107,7 @@ int lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int fram
     if (ctx->grid <= 0) {
         const int g = lm_max_grid(ctx);
         if (g < LM_MIN_GRID) return set_err(ctx, Q3T_ERR_CUDA, "device cannot co-schedule the persistent decode kernel (needs >= 140 SMs)");
-        ctx->grid = g > 512 ? 512 : g;
+        ctx->grid = g > 480 ? 480 : g;
     }
     DevModel m = ctx->hm;
     void * args[] = { (void *) &m, (void *) &passes_dev, (void *) &n_passes, (void *) &frame_mode };
