@@ -100,6 +100,7 @@ def lib() -> C.CDLL:
         "q3t_device_info": (C.c_int, [vp, _i32p, _i32p, _i32p]),
         "q3t_profile_arm": (C.c_int, [vp, C.c_int32, C.c_int32]),
         "q3t_profile_read": (C.c_int, [vp, C.POINTER(C.c_uint64), C.c_int32]),
+        "q3t_profile_select": (C.c_int, [vp, C.c_int32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -339,7 +340,9 @@ class TTSTransformer:
         if self.L.q3t_profile_arm(self.engine(), cta, cap) != 0:
             raise Q3TError("profile_arm failed")
 
-    def profile_read(self, cap=1 << 16):
+    def profile_read(self, cap=1 << 16, cta=None):
+        if cta is not None:
+            self.L.q3t_profile_select(self.engine(), cta)
         buf = np.zeros(cap, np.uint64)
         n = self.L.q3t_profile_read(self.engine(), buf.ctypes.data_as(C.POINTER(C.c_uint64)), cap)
         if n < 0:

@@ -794,24 +794,29 @@ extern "C" int q3t_profile_arm(q3t_ctx * ctx, int32_t cta, int32_t cap) {
     if (ctx->d_prof) { cudaFree(ctx->d_prof); cudaFree(ctx->d_prof_n); ctx->d_prof = nullptr; ctx->d_prof_n = nullptr; ctx->prof_cap = 0; }
     ctx->hm.prof = nullptr; ctx->hm.prof_n = nullptr; ctx->hm.prof_cap = 0; ctx->hm.prof_cta = 0;
     if (cap <= 0) return Q3T_OK;
-    CK(cudaMalloc(&ctx->d_prof, (size_t) cap * 8));
-    CK(cudaMalloc(&ctx->d_prof_n, 4));
-    CK(cudaMemset(ctx->d_prof_n, 0, 4));
+    CK(cudaMalloc(&ctx->d_prof, (size_t) cap * 8 * 512));
+    CK(cudaMalloc(&ctx->d_prof_n, 4 * 512));
+    CK(cudaMemset(ctx->d_prof_n, 0, 4 * 512));
     ctx->prof_cap = cap;
     ctx->hm.prof = ctx->d_prof; ctx->hm.prof_n = ctx->d_prof_n; ctx->hm.prof_cap = cap; ctx->hm.prof_cta = cta;
     return Q3T_OK;
 }
-// copies the records (clock64 << 8 | tag) out and resets the counter; returns the record count
+// copies the records (clock64 << 8 | tag) of the selected CTA for the LAST launch out; returns the count
 extern "C" int q3t_profile_read(q3t_ctx * ctx, uint64_t * out, int32_t cap) {
     if (!ctx || !ctx->d_prof) return Q3T_ERR_STATE;
     CK(cudaStreamSynchronize(ctx->stream));
+    const int cta = ctx->hm.prof_cta;
     unsigned n = 0;
-    CK(cudaMemcpy(&n, ctx->d_prof_n, 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(&n, ctx->d_prof_n + cta, 4, cudaMemcpyDeviceToHost));
     if ((int) n > ctx->prof_cap) n = ctx->prof_cap;
     if ((int) n > cap) n = cap;
-    if (n) CK(cudaMemcpy(out, ctx->d_prof, (size_t) n * 8, cudaMemcpyDeviceToHost));
-    CK(cudaMemset(ctx->d_prof_n, 0, 4));
+    if (n) CK(cudaMemcpy(out, ctx->d_prof + (size_t) cta * ctx->prof_cap, (size_t) n * 8, cudaMemcpyDeviceToHost));
     return (int) n;
+}
+extern "C" int q3t_profile_select(q3t_ctx * ctx, int32_t cta) {
+    if (!ctx || !ctx->d_prof || cta < 0 || cta >= 512) return Q3T_ERR_STATE;
+    ctx->hm.prof_cta = cta;
+    return Q3T_OK;
 }
 
 extern "C" int q3t_get_timing(q3t_ctx * ctx, q3t_timing * out) {

@@ -61,18 +61,25 @@ struct __align__(128) Smem {
     float  fred[32];
     int    ired[32];
     int    tok;
+    int    prof_cnt;
     unsigned long long mbar[NMB];  // TMA completion barriers of the slices in flight
     volatile unsigned long long consumed;   // low 32: ring slots released, high 32: slices released
 };
 
 // ------------------------------------------------------------------------------- phase profiler
-__device__ __forceinline__ void prof_mark(const DevModel & m, int tag) {
-    if (m.prof && threadIdx.x == 0 && (int) blockIdx.x == m.prof_cta) {
-        const unsigned i = atomicAdd(m.prof_n, 1u);
-        if ((int) i < m.prof_cap) m.prof[i] = ((unsigned long long) clock64() << 8) | (unsigned long long) (tag & 0xff);
+// thread 0 of EVERY CTA appends (clock64 << 8 | tag) to its own region of m.prof with plain stores
+// (no round trip: the marks do not perturb the chain); the count lives in shared memory and is
+// written to m.prof_n[cta] when the kernel ends, so the buffer holds the last launch.
+__device__ __forceinline__ void prof_mark(const DevModel & m, int * cnt, int tag) {
+    if (m.prof && threadIdx.x == 0) {
+        const int i = *cnt;
+        if (i < m.prof_cap) {
+            m.prof[(size_t) blockIdx.x * m.prof_cap + i] = ((unsigned long long) clock64() << 8) | (unsigned long long) (tag & 0xff);
+            *cnt = i + 1;
+        }
     }
 }
-#define PROF(tag) prof_mark(m, tag)
+#define PROF(tag) prof_mark(m, &s.prof_cnt, tag)
 
 // ------------------------------------------------------------------------------- CTA-level sync
 // barrier among the 480 compute threads only (the producer warp runs free)
@@ -85,7 +92,9 @@ __device__ __forceinline__ void cbar() { asm volatile("bar.sync 1, %0;" :: "n"(N
 struct Watch { long long t0; bool dead; };
 
 __device__ __forceinline__ void pk_store(Pkt * p, float v, unsigned ep) {
-    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(p), "r"(__float_as_uint(v)), "r"(ep) : "memory");
+    // gpu-scope relaxed (SASS .STRONG.GPU): `volatile` would be system scope, which is far slower
+    const unsigned long long u = (unsigned long long) __float_as_uint(v) | ((unsigned long long) ep << 32);
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(u) : "memory");
 }
 __device__ __forceinline__ bool pk_give_up(const DevModel & m, Watch & w, unsigned & spins) {
     if (((++spins) & 0x3ff) != 0) return false;
@@ -94,23 +103,25 @@ __device__ __forceinline__ bool pk_give_up(const DevModel & m, Watch & w, unsign
     return false;
 }
 __device__ __forceinline__ float pk_poll(const DevModel & m, const Pkt * p, unsigned ep, Watch & w) {
-    unsigned v, e, spins = 0;
+    unsigned long long u;
+    unsigned spins = 0;
     while (true) {
-        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(p) : "memory");
-        if (e == ep || w.dead) break;
+        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(u) : "l"(p) : "memory");
+        if ((unsigned) (u >> 32) == ep || w.dead) break;
         if (pk_give_up(m, w, spins)) break;
     }
-    return __uint_as_float(v);
+    return __uint_as_float((unsigned) u);
 }
 // two adjacent packets (16-byte aligned) in one load
 __device__ __forceinline__ float2 pk_poll2(const DevModel & m, const Pkt * p, unsigned ep, Watch & w) {
-    unsigned v0, e0, v1, e1, spins = 0;
+    unsigned long long u0, u1;
+    unsigned spins = 0;
     while (true) {
-        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v0), "=r"(e0), "=r"(v1), "=r"(e1) : "l"(p) : "memory");
-        if ((e0 == ep && e1 == ep) || w.dead) break;
+        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(u0), "=l"(u1) : "l"(p) : "memory");
+        if (((unsigned) (u0 >> 32) == ep && (unsigned) (u1 >> 32) == ep) || w.dead) break;
         if (pk_give_up(m, w, spins)) break;
     }
-    return make_float2(__uint_as_float(v0), __uint_as_float(v1));
+    return make_float2(__uint_as_float((unsigned) u0), __uint_as_float((unsigned) u1));
 }
 
 // ------------------------------------------------------------------------------- TMA weight ring
@@ -812,8 +823,11 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         int s0 = ring_acquire(m, s, rg, w);
         PROF(4);
         gemv_ring<1024, 2, false>(s, s0, nA);
+        PROF(40);
         cbar();
+        PROF(41);
         if (t < nA) pk_store(m.x_qkv + z.a0 + t, s.outv[t], e_qkv);
+        PROF(42);
         ring_release(s, rg, nA);
         PROF(5);
 
@@ -970,6 +984,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
         gs = *m.st;
         s_go_raw = frame_mode ? -1 : n_passes;
         s.consumed = 0ULL;
+        s.prof_cnt = 0;
         for (int i = 0; i < NMB; ++i) mbar_init(&s.mbar[i], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -1079,6 +1094,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
         if (p.stack == 0 && p.pos < 0) ++n_past;
     }
 
+    if (m.prof && t == 0) m.prof_n[blockIdx.x] = (unsigned) s.prof_cnt;
     // ---- write the state back (CTA 0); epochs are identical in every CTA
     if (blockIdx.x == 0 && t == 0) {
         GenState * st = m.st;
