@@ -117,6 +117,7 @@ struct DevModel {
     int * codes_out;                 // [max_len][16]
     GenState * st;
     // developer profiling (q3t_profile_arm): thread 0 of CTA prof_cta appends (clock64 << 8 | tag)
+    int poll_d0, poll_d1;            // tuning: cycles before the first poll of a vector / between polls
     unsigned long long * prof; int prof_cap; int prof_cta;
     unsigned int * prof_n;
 };

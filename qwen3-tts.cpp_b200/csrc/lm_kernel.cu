@@ -31,6 +31,7 @@
 #include "engine.h"
 
 #include <math_constants.h>
+#include <stdlib.h>
 
 namespace q3t {
 
@@ -64,6 +65,7 @@ struct __align__(128) Smem {
     int    prof_cnt;
     unsigned long long mbar[NMB];  // TMA completion barriers of the slices in flight
     volatile unsigned long long consumed;   // low 32: ring slots released, high 32: slices released
+    volatile unsigned tokens;               // exchanges completed by the compute warps (paces the producer's bursts)
 };
 
 // ------------------------------------------------------------------------------- phase profiler
@@ -95,6 +97,11 @@ __device__ __forceinline__ void pk_store(Pkt * p, float v, unsigned ep) {
     // gpu-scope relaxed (SASS .STRONG.GPU): `volatile` would be system scope, which is far slower
     const unsigned long long u = (unsigned long long) __float_as_uint(v) | ((unsigned long long) ep << 32);
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(u) : "memory");
+}
+__device__ __forceinline__ void spin_cycles(int n) {
+    if (n <= 0) return;
+    const long long t0 = clock64();
+    while (clock64() - t0 < n) { }
 }
 __device__ __forceinline__ bool pk_give_up(const DevModel & m, Watch & w, unsigned & spins) {
     if (((++spins) & 0x3ff) != 0) return false;
@@ -202,7 +209,6 @@ __device__ __forceinline__ void produce_slice(Smem & s, unsigned & p_slot, unsig
         const unsigned long long c = s.consumed;
         const unsigned c_slot = (unsigned) c, c_idx = (unsigned) (c >> 32);
         if (p_slot + (unsigned) n_slots - c_slot <= (unsigned) NSLOT && p_idx - c_idx < (unsigned) NMB) break;
-        __nanosleep(20);
     }
     unsigned long long * bar = &s.mbar[p_idx % NMB];
     const int w0 = (int) (p_slot % NSLOT);
@@ -399,6 +405,27 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     const size_t kv_head_base = ((size_t) (l * NKV + g) * W.n_ctx) * HD;
     Pkt * att = m.x_att + h * HD;
 
+    // ---- stage 0 (before the new token arrives): everything that depends only on history is put in
+    //      flight now so its L2 latency hides behind the packet wait: the K rows of this warp's first
+    //      positions (registers) and the V rows of the double-precision leftover part (shared memory)
+    const int np = min(wd & ~31, n_kv);                      // positions in the 32-lane part of the P.V dot
+    const int nleft = n_kv - np;
+    const __half * kbase = W.kcache + kv_head_base;
+    const __half * vbase = W.vcache + kv_head_base;
+    uint2 kk0[4];
+    if (!f32attn) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int tt = warp + j * NCW;
+            if (tt < n_kv && tt != pos) kk0[j] = ld_cg_u2(kbase + (size_t) tt * HD + lane * 4);
+        }
+        for (int idx = t; idx < nleft * (HD / 8); idx += NCT) {
+            const int i = idx >> 4, dg = idx & 15;
+            const int tg = np + i;
+            if (tg != pos) *reinterpret_cast<uint4 *>(s.vt + i * HD + dg * 8) = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tg * HD + dg * 8));
+        }
+    }
+
     // ---- prologue: q, k, v of the new token (warps 0, 1, 2)
     if (warp < 3) {
         const Pkt * src = m.x_qkv + (warp == 0 ? h * HD : warp == 1 ? NH * HD + g * HD : (NH + NKV) * HD + g * HD);
@@ -423,7 +450,6 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
 #pragma unroll
                     for (int i = 0; i < 4; ++i) W.kf32[((size_t) (l * 2 + pos) * NKV + g) * HD + lane + 32 * i] = v[i];
                 }
-                __threadfence();
             }
         } else {
 #pragma unroll
@@ -435,8 +461,8 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
                     W.vcache[kv_head_base + (size_t) pos * HD + d] = hv;
                     if (W.vf32 && pos < 2) W.vf32[((size_t) (l * 2 + pos) * NKV + g) * HD + d] = v[i];
                 }
+                if (pos >= np) s.vt[(pos - np) * HD + d] = hv;          // the new token is a leftover row
             }
-            if (writer) __threadfence();
         }
     }
     cbar();
@@ -475,6 +501,9 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
 #pragma unroll
             for (int i = 0; i < 4; ++i) pk_store(att + lane + 32 * i, o[i], ep_out);
         }
+        // the K/V rows appended above are read by other CTAs one pass later: publish them before this
+        // CTA's next packets (off the critical path: after the attention output has left)
+        if (writer && (warp == 1 || warp == 2)) __threadfence();
         return;
     }
 
@@ -483,14 +512,14 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
         float q[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) q[i] = s.qr[lane + 32 * i];
-        const __half * kbase = W.kcache + kv_head_base;
         float mx = -CUDART_INF_F;
         for (int t0 = warp; t0 < n_kv; t0 += 4 * NCW) {
             uint2 kk[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int tt = t0 + j * NCW;
-                if (tt < n_kv && tt != pos) kk[j] = ld_cg_u2(kbase + (size_t) tt * HD + lane * 4);
+                if (t0 == warp) kk[j] = kk0[j];
+                else if (tt < n_kv && tt != pos) kk[j] = ld_cg_u2(kbase + (size_t) tt * HD + lane * 4);
             }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -551,11 +580,8 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     const float inv = (float) (1.0 / S);
     for (int tt = t; tt < n_kv; tt += NCT) s.ph[tt] = __float2half_rn(__fmul_rn(s.sc[tt], inv));
 
-    // ---- P.V: warps 0..7 own 16 dims each, lane a = accumulator lane a (position % 32);
-    //      warps 8..14 stage the leftover rows (positions np..n_kv-1) for the double-precision tail
-    const int np = min(wd & ~31, n_kv);                      // positions in the 32-lane part of the dot
-    const int nleft = n_kv - np;
-    const __half * vbase = W.vcache + kv_head_base;
+    // ---- P.V: warps 0..7 own 16 dims each, lane a = accumulator lane a (position % 32); the leftover
+    //      rows (positions np..n_kv-1) were staged into s.vt in stage 0 / the prologue
     cbar();
     if (warp < 8) {
         const int d0 = warp * 16;
@@ -582,30 +608,24 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
                 acc[8 + 2 * e + 1] = fhfma_hi(u4_get(v1, e), p2, acc[8 + 2 * e + 1]);
             }
         }
+        if (np > 0) {
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
-            const float r = reduce32_lanes(acc[e]);
-            if (lane == 0) s.o32[d0 + e] = r;
-        }
-    } else {
-        for (int idx = t - 8 * 32; idx < nleft * (HD / 8); idx += (NCW - 8) * 32) {
-            const int i = idx >> 4, dg = idx & 15;
-            const int tg = np + i;
-            uint4 v;
-            if (tg == pos) v = *reinterpret_cast<const uint4 *>(s.vnew_h + dg * 8);
-            else v = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tg * HD + dg * 8));
-            *reinterpret_cast<uint4 *>(s.vt + i * HD + dg * 8) = v;
+            for (int e = 0; e < 16; ++e) {
+                const float r = reduce32_lanes(acc[e]);
+                if (lane == 0) s.o32[d0 + e] = r;
+            }
+            asm volatile("bar.sync 2, 256;" ::: "memory");    // warps 0..7: o32 complete before the tail below
         }
     }
-    cbar();
     // leftovers: one thread per dim adds them sequentially in double like ggml_vec_dot_f16's scalar
     // tail (vec.cpp:381-384)
     if (t < HD) {
-        double sumf = (double) s.o32[t];
+        double sumf = np > 0 ? (double) s.o32[t] : 0.0;
         for (int i = 0; i < nleft; ++i)
             sumf += (double) __fmul_rn(__half2float(s.vt[i * HD + t]), __half2float(s.ph[np + i]));
         pk_store(att + t, (float) sumf, ep_out);
     }
+    if (writer && (warp == 1 || warp == 2)) __threadfence();   // publish the appended K/V rows (see above)
 }
 
 // --------------------------------------------------------------------------- token selection
@@ -752,6 +772,10 @@ __device__ int select_sample(const DevModel & m, Smem & s, unsigned ep, Watch & 
     return tok;
 }
 
+// the compute warps have just finished an exchange: the SM's return path is idle, a good moment for the
+// producer to start its next bulk copy (keeps the weight stream from delaying the latency-critical polls)
+__device__ __forceinline__ void token(Smem & s) { if (threadIdx.x == 0) s.tokens = s.tokens + 1u; }
+
 // ------------------------------------------------------------------------------- one pass (compute warps)
 struct PassRegs {          // parameters fetched ahead of use; carried across layers and passes
     Gam ga, gf;            // attn_norm / ffn_norm of the layer about to run
@@ -771,6 +795,7 @@ __device__ __forceinline__ void prefetch_layer_params(const StackW & W, int l, P
 
 // poll n packets (n even, multiple of 2) from src into dst (float) — all compute threads
 __device__ __forceinline__ void poll_vec(const DevModel & m, const Pkt * src, int n, unsigned ep, float * dst, Watch & w) {
+    spin_cycles(m.poll_d0);
     for (int i = threadIdx.x; i < n / 2; i += NCT) {
         const float2 f = pk_poll2(m, src + 2 * i, ep, w);
         dst[2 * i] = f.x; dst[2 * i + 1] = f.y;
@@ -817,6 +842,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         // ---- phase A: RMSNorm + fused QKV mat-vec
         PROF(1);
         if (l > 0) { poll_vec(m, m.x_x, H, ep, s.xres, w); cbar(); }
+        token(s);
         PROF(2);
         rmsnorm_to_xh(s, ga, m.eps, nullptr, nullptr);
         PROF(3);
@@ -836,11 +862,13 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(6);
 
         // ---- phase C: attn_output mat-vec (input rounded to F16) + residual
+        spin_cycles(m.poll_d0);
         for (int i = t; i < NH * HD / 2; i += NCT) {
             const float2 f = pk_poll2(m, m.x_att + 2 * i, e_att, w);
             xh_put(s, 2 * i, f.x); xh_put(s, 2 * i + 1, f.y);
         }
         cbar();
+        token(s);
         PROF(7);
         s0 = ring_acquire(m, s, rg, w);
         PROF(8);
@@ -853,6 +881,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         // ---- phase D: RMSNorm + gate/up mat-vec + SwiGLU
         poll_vec(m, m.x_x1, H, e_x1, s.xres, w);
         cbar();
+        token(s);
         PROF(10);
         rmsnorm_to_xh(s, gf, m.eps, nullptr, nullptr);
         PROF(11);
@@ -871,6 +900,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         // ---- phase E: ffn_down on F32 activations (weights exact in F32) + residual
         poll_vec(m, m.x_m, FFN, e_m, s.xf, w);
         cbar();
+        token(s);
         PROF(14);
         s0 = ring_acquire(m, s, rg, w);
         PROF(15);
@@ -887,6 +917,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
     const unsigned e_head = ep + 1;
     poll_vec(m, m.x_x, H, ep, s.xres, w);
     cbar();
+    token(s);
     rmsnorm_to_xh(s, gh, m.eps, blockIdx.x == 0 ? m.hidden : nullptr, blockIdx.x == 0 ? p.hidden_dst : nullptr);
     PROF(20);
     const int s0 = ring_acquire(m, s, rg, w);
@@ -923,9 +954,15 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
     unsigned p_slot = 0, p_idx = 0;
     const int nA = z.a1 - z.a0, nO = z.o1 - z.o0, nP = z.p1 - z.p0, nD = z.d1 - z.d0;
     bool aborted = false;
+    const long long t_start = clock64();
+    unsigned pspins = 0;
     for (int ip = 0; ip < n_passes && !aborted; ++ip) {
         int go = *s_go;
-        while (go < 0 && ip > 0) { __nanosleep(64); go = *s_go; }     // pass 0 is produced optimistically
+        while (go < 0 && ip > 0) {                                    // pass 0 is produced optimistically
+            __nanosleep(64); go = *s_go;
+            if (((++pspins) & 0xfff) == 0 && clock64() - t_start > 8000000000LL) { m.st->error = 1; aborted = true; break; }
+        }
+        if (aborted) break;
         if (go >= 0 && ip >= go) break;
         const int xmode = passes[ip].xmode;
         if (xmode == XM_SELECT_ONLY) continue;
@@ -939,9 +976,10 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
                 // ring-space wait with an abort check (EOS decided while pass 0 is being produced)
                 while (true) {
                     const unsigned long long c = s.consumed;
-                    if (p_slot + (unsigned) n_slots - (unsigned) c <= (unsigned) NSLOT && p_idx - (unsigned) (c >> 32) < (unsigned) NMB) break;
+                    if (p_slot + (unsigned) n_slots - (unsigned) c <= (unsigned) NSLOT && p_idx - (unsigned) (c >> 32) < (unsigned) NMB &&
+                        (m.poll_d1 <= 0 || (int) (p_idx - s.tokens) < m.poll_d1)) break;
                     if (*s_go == 0) { aborted = true; break; }
-                    __nanosleep(20);
+                    if (((++pspins) & 0xfff) == 0 && clock64() - t_start > 8000000000LL) { m.st->error = 1; aborted = true; break; }   // watchdog
                 }
                 if (aborted) break;
                 produce_slice(s, p_slot, p_idx, src, n_slots);
@@ -954,7 +992,7 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
                 const unsigned long long c = s.consumed;
                 if (p_slot + (unsigned) (h1 - h0) - (unsigned) c <= (unsigned) NSLOT && p_idx - (unsigned) (c >> 32) < (unsigned) NMB) break;
                 if (*s_go == 0) { aborted = true; break; }
-                __nanosleep(20);
+                if (((++pspins) & 0xfff) == 0 && clock64() - t_start > 8000000000LL) { m.st->error = 1; aborted = true; break; }
             }
             if (!aborted) produce_slice(s, p_slot, p_idx, hw.w + (size_t) h0 * H, h1 - h0);
         }
@@ -984,12 +1022,13 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
         gs = *m.st;
         s_go_raw = frame_mode ? -1 : n_passes;
         s.consumed = 0ULL;
+        s.tokens = 0u;
         s.prof_cnt = 0;
         for (int i = 0; i < NMB; ++i) mbar_init(&s.mbar[i], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    if (frame_mode && gs.done) return;
+    if ((frame_mode && gs.done) || gs.error) return;      // a tripped watchdog makes every later launch a no-op
 
     Slices z;
     cta_rows(QKV_N, z.a0, z.a1);
@@ -1126,6 +1165,9 @@ int lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int fram
         ctx->grid = g > 480 ? 480 : g;
     }
     DevModel m = ctx->hm;
+    static int d0 = -1, d1 = -1;
+    if (d0 < 0) { const char * e0 = getenv("Q3T_POLL_D0"), * e1 = getenv("Q3T_POLL_D1"); d0 = e0 ? atoi(e0) : 0; d1 = e1 ? atoi(e1) : 0; }
+    m.poll_d0 = d0; m.poll_d1 = d1;
     void * args[] = { (void *) &m, (void *) &passes_dev, (void *) &n_passes, (void *) &frame_mode };
     cudaError_t e = cudaLaunchCooperativeKernel((const void *) lm_kernel, dim3(ctx->grid), dim3(LM_THREADS),
                                                 args, sizeof(Smem), ctx->stream);

@@ -8,6 +8,7 @@ sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 from util import pkg, models, HELLO_FULL
 
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 40
+print("POLL_D0", os.environ.get("Q3T_POLL_D0"))
 m = pkg()
 t = m.TTSTransformer()
 assert t.load_model(models("full", "f16")[0]), t.get_error()
