@@ -164,8 +164,8 @@ Q3T_API int64_t q3t_fetch_samples(q3t_ctx * ctx, float * samples_out, int64_t ca
 Q3T_API int  q3t_bench_talker_step(q3t_ctx * ctx, int32_t n_past, int32_t iters, float * us_per_step);
 Q3T_API int  q3t_get_timing(q3t_ctx * ctx, q3t_timing * out);
 /* Developer aid (no reference counterpart): in-kernel phase profiler of the persistent decode
- * kernel.  arm: thread 0 of every CTA keeps up to `cap` (clock64 << 8 | tag) records of the LAST
- * launch, cap <= 0 disarms; read: copies the records of the selected CTA out, returns the count. */
+ * kernel.  arm: thread 0 of every CTA keeps up to `cap` (clock64 << 8 | tag) records of the launch
+ * whose frame counter equals `cta` (< 0: the last launch), cap <= 0 disarms; read: copies the records of the selected CTA out, returns the count. */
 Q3T_API int  q3t_profile_arm(q3t_ctx * ctx, int32_t cta, int32_t cap);
 Q3T_API int  q3t_profile_read(q3t_ctx * ctx, uint64_t * out, int32_t cap);
 Q3T_API int  q3t_profile_select(q3t_ctx * ctx, int32_t cta);   /* which CTA q3t_profile_read returns */

@@ -798,7 +798,7 @@ extern "C" int q3t_profile_arm(q3t_ctx * ctx, int32_t cta, int32_t cap) {
     CK(cudaMalloc(&ctx->d_prof_n, 4 * 512));
     CK(cudaMemset(ctx->d_prof_n, 0, 4 * 512));
     ctx->prof_cap = cap;
-    ctx->hm.prof = ctx->d_prof; ctx->hm.prof_n = ctx->d_prof_n; ctx->hm.prof_cap = cap; ctx->hm.prof_cta = cta;
+    ctx->hm.prof = ctx->d_prof; ctx->hm.prof_n = ctx->d_prof_n; ctx->hm.prof_cap = cap; ctx->hm.prof_cta = 0; ctx->hm.prof_frame = cta;
     return Q3T_OK;
 }
 // copies the records (clock64 << 8 | tag) of the selected CTA for the LAST launch out; returns the count

@@ -118,11 +118,11 @@ struct DevModel {
     GenState * st;
     // developer profiling (q3t_profile_arm): thread 0 of CTA prof_cta appends (clock64 << 8 | tag)
     int poll_d0, poll_d1;            // tuning: cycles before the first poll of a vector / between polls
-    unsigned long long * prof; int prof_cap; int prof_cta;
+    unsigned long long * prof; int prof_cap; int prof_cta; int prof_frame;
     unsigned int * prof_n;
 };
 
-constexpr int LM_THREADS = 512;
+constexpr int LM_THREADS = 384;       // 11 compute warps + 1 producer warp; 168 registers per thread
 constexpr int LM_MAXC    = 18;       // max KV chunks per kv-head in the attention phase
 constexpr int LM_MIN_GRID = 140;
 constexpr int LM_ATT_MAX_KV = 4608;  // KV positions the attention phase supports (P kept in shared memory)

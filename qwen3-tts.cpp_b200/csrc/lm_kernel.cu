@@ -36,8 +36,8 @@
 namespace q3t {
 
 // ------------------------------------------------------------------------------- shared memory
-constexpr int NCW        = 15;                         // compute warps (warp 15 is the TMA producer)
-constexpr int NCT        = NCW * 32;                   // 480 compute threads
+constexpr int NCW        = LM_THREADS / 32 - 1;        // compute warps (the last warp is the TMA producer)
+constexpr int NCT        = NCW * 32;                   // compute threads
 constexpr int SLOT_B     = 2048;                       // ring slot = one K=1024 row of F16 weights
 constexpr int NSLOT      = 80;                         // 160 KB ring
 constexpr int NMB        = 8;                          // mbarriers cycling over the slices in flight
@@ -73,7 +73,7 @@ struct __align__(128) Smem {
 // (no round trip: the marks do not perturb the chain); the count lives in shared memory and is
 // written to m.prof_n[cta] when the kernel ends, so the buffer holds the last launch.
 __device__ __forceinline__ void prof_mark(const DevModel & m, int * cnt, int tag) {
-    if (m.prof && threadIdx.x == 0) {
+    if (m.prof && threadIdx.x == 0 && *cnt >= 0) {
         const int i = *cnt;
         if (i < m.prof_cap) {
             m.prof[(size_t) blockIdx.x * m.prof_cap + i] = ((unsigned long long) clock64() << 8) | (unsigned long long) (tag & 0xff);
@@ -338,10 +338,11 @@ __device__ __forceinline__ void rmsnorm_to_xh(Smem & s, const Gam & gm, float ep
     sq = warp_sum_d(sq);
     if (lane == 0) s.dred[warp] = sq;
     cbar();
-    double t0 = s.dred[0] + s.dred[1], t1 = s.dred[2] + s.dred[3], t2 = s.dred[4] + s.dred[5], t3 = s.dred[6] + s.dred[7];
-    t0 += s.dred[8] + s.dred[9]; t1 += s.dred[10] + s.dred[11]; t2 += s.dred[12] + s.dred[13]; t3 += s.dred[14];
-    const double tot = (t0 + t1) + (t2 + t3);
-    const float mean  = (float) (tot / (double) H);
+    double ts[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int i = 0; i < NCW; ++i) ts[i & 3] += s.dred[i];
+    const double tot = (ts[0] + ts[1]) + (ts[2] + ts[3]);
+    const float mean  = (float) (tot * (1.0 / (double) H));       // H is a power of two: same value as tot / H
     const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
     const float ya = __fmul_rn(__fmul_rn(a, scale), gm.g[0]);
     const float yb = __fmul_rn(__fmul_rn(b, scale), gm.g[1]);
@@ -364,7 +365,7 @@ __device__ __forceinline__ void head_norm_rope(float (&v)[4], const float (&gn)[
 #pragma unroll
     for (int i = 0; i < 4; ++i) sq += (double) __fmul_rn(v[i], v[i]);
     sq = warp_sum_d(sq);
-    const float mean  = (float) (sq / (double) HD);
+    const float mean  = (float) (sq * (1.0 / (double) HD));
     const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
 #pragma unroll
     for (int i = 0; i < 4; ++i) v[i] = __fmul_rn(__fmul_rn(v[i], scale), gn[i]);
@@ -419,13 +420,16 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
             const int tt = warp + j * NCW;
             if (tt < n_kv && tt != pos) kk0[j] = ld_cg_u2(kbase + (size_t) tt * HD + lane * 4);
         }
+        // cp.async (LDGSTS): global -> shared without passing through registers, completes in the background
         for (int idx = t; idx < nleft * (HD / 8); idx += NCT) {
-            const int i = idx >> 4, dg = idx & 15;
-            const int tg = np + i;
-            if (tg != pos) *reinterpret_cast<uint4 *>(s.vt + i * HD + dg * 8) = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tg * HD + dg * 8));
+            const int tg = np + (idx >> 4);
+            if (tg != pos)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_u32(s.vt + (idx >> 4) * HD + (idx & 15) * 8)),
+                             "l"(vbase + (size_t) tg * HD + (idx & 15) * 8) : "memory");
         }
     }
 
+    PROF(50);
     // ---- prologue: q, k, v of the new token (warps 0, 1, 2)
     if (warp < 3) {
         const Pkt * src = m.x_qkv + (warp == 0 ? h * HD : warp == 1 ? NH * HD + g * HD : (NH + NKV) * HD + g * HD);
@@ -465,7 +469,10 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
             }
         }
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    PROF(51);
     cbar();
+    PROF(52);
 
     if (f32attn) {
         // code-predictor prefill numerics: the reference graph multiplies the fresh F32 Kcur/Vcur/Q
@@ -545,6 +552,7 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
         if (lane == 0) s.fred[warp] = mx;
     }
     cbar();
+    PROF(53);
     float M = s.fred[0];
 #pragma unroll
     for (int i = 1; i < NCW; ++i) M = fmaxf(M, s.fred[i]);
@@ -552,6 +560,35 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     // ---- soft-max over the row (ggml_vec_soft_max_f32: 8 lanes at a time, libm tail; vec.cpp:548-617)
     const int n8  = wd >> 3;                                 // chunks that take the SIMD exp
     const int n8v = min(n8, (n_kv + 7) >> 3);                // ... of which these hold unmasked positions
+    if (wd <= 32) {
+        // short rows (the code predictor, early talker steps): one warp, no block-level reductions
+        if (warp == 0) {
+            const bool live = lane < n_kv;
+            const bool simd = lane < n8 * 8;
+            const float x = live ? __fsub_rn(s.sc[lane], M) : 0.0f;
+            float e = 0.0f;
+            if (live) e = simd ? v_expf(x) : tail_expf(x);
+            // chunk sums in the oracle's order: ((e4+e0)+(e6+e2)) + ((e5+e1)+(e7+e3)) per 8 lanes
+            float c = simd || !live ? e : 0.0f;              // masked lanes of a SIMD chunk add +0
+            c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 4));
+            c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 2));
+            c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 1));
+            double S = 0.0;
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch) {
+                const float cs = __shfl_sync(0xffffffffu, c, ch * 8);
+                if (ch < n8v) S += (double) cs;
+            }
+#pragma unroll
+            for (int i = 0; i < 7; ++i) {                    // scalar tail, in order
+                const int tt = n8 * 8 + i;
+                const float ev = __shfl_sync(0xffffffffu, e, tt & 31);
+                if (tt < n_kv) S += (double) ev;
+            }
+            const float inv = (float) (1.0 / S);
+            if (live) s.ph[lane] = __float2half_rn(__fmul_rn(e, inv));
+        }
+    } else {
     double ds = 0.0;
     for (int ch = t; ch < n8v; ch += NCT) {
         float e[8];
@@ -579,10 +616,12 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     for (int i = 0; i < NCW; ++i) S += s.dred[i];
     const float inv = (float) (1.0 / S);
     for (int tt = t; tt < n_kv; tt += NCT) s.ph[tt] = __float2half_rn(__fmul_rn(s.sc[tt], inv));
+    }
 
     // ---- P.V: warps 0..7 own 16 dims each, lane a = accumulator lane a (position % 32); the leftover
     //      rows (positions np..n_kv-1) were staged into s.vt in stage 0 / the prologue
     cbar();
+    PROF(54);
     if (warp < 8) {
         const int d0 = warp * 16;
         float acc[16];
@@ -640,7 +679,7 @@ __device__ __forceinline__ float proc_logit(const DevModel & m, float raw, int i
     return raw;
 }
 
-__device__ int select_greedy(const DevModel & m, Smem & s, unsigned ep, Watch & w) {
+__device__ __noinline__ int select_greedy(const DevModel & m, Smem & s, unsigned ep, Watch & w) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     float v = -CUDART_INF_F; int idx = 0x7fffffff;
     if (t < (int) gridDim.x) {
@@ -681,11 +720,11 @@ __device__ __forceinline__ double u01(unsigned long long seed, unsigned long lon
 }
 
 // temperature -> top-k threshold (ties kept, `<` test) -> softmax (double sum) -> inverse CDF draw
-__device__ int select_sample(const DevModel & m, Smem & s, unsigned ep, Watch & w, int vocab, bool process, int suppress_start,
+__device__ __noinline__ int select_sample(const DevModel & m, Smem & s, unsigned ep, Watch & w, int vocab, bool process, int suppress_start,
                              int eos_id, float rep_penalty, float temperature, int top_k,
                              unsigned long long seed, unsigned long long draw) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    constexpr int PER = 7;                       // 480 * 7 = 3360 >= vocab
+    constexpr int PER = (3072 + NCT - 1) / NCT;  // NCT * PER >= vocab
     float l[PER];
 #pragma unroll
     for (int i = 0; i < PER; ++i) {
@@ -848,7 +887,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(3);
         int s0 = ring_acquire(m, s, rg, w);
         PROF(4);
-        gemv_ring<1024, 2, false>(s, s0, nA);
+        gemv_ring<1024, 3, false>(s, s0, nA);
         PROF(40);
         cbar();
         PROF(41);
@@ -887,7 +926,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(11);
         s0 = ring_acquire(m, s, rg, w);
         PROF(12);
-        gemv_ring<1024, 3, false>(s, s0, 2 * nP);
+        gemv_ring<1024, 4, false>(s, s0, 2 * nP);
         cbar();
         if (t < nP) {
             const float gt = s.outv[2 * t], up = s.outv[2 * t + 1];
@@ -1023,7 +1062,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
         s_go_raw = frame_mode ? -1 : n_passes;
         s.consumed = 0ULL;
         s.tokens = 0u;
-        s.prof_cnt = 0;
+        s.prof_cnt = (m.prof_frame < 0 || m.prof_frame == gs.frame) ? 0 : -1;    // record one chosen frame only
         for (int i = 0; i < NMB; ++i) mbar_init(&s.mbar[i], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -1133,7 +1172,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
         if (p.stack == 0 && p.pos < 0) ++n_past;
     }
 
-    if (m.prof && t == 0) m.prof_n[blockIdx.x] = (unsigned) s.prof_cnt;
+    if (m.prof && t == 0 && s.prof_cnt >= 0) m.prof_n[blockIdx.x] = (unsigned) s.prof_cnt;
     // ---- write the state back (CTA 0); epochs are identical in every CTA
     if (blockIdx.x == 0 && t == 0) {
         GenState * st = m.st;
