@@ -131,6 +131,53 @@ __device__ __forceinline__ float2 pk_poll2(const DevModel & m, const Pkt * p, un
     return make_float2(__uint_as_float((unsigned) u0), __uint_as_float((unsigned) u1));
 }
 
+// N packets per thread with every load in flight at once: a thread that polls its packets one after
+// the other pays one L2 round trip per packet even when all of them have already arrived.
+template <int N>
+__device__ __forceinline__ void pk_poll_n(const DevModel & m, const Pkt * p, int stride, int n_valid, unsigned ep,
+                                          float (&v)[N], Watch & w) {
+    unsigned long long u[N];
+    unsigned pending = n_valid >= N ? (1u << N) - 1u : (1u << n_valid) - 1u;
+    unsigned spins = 0;
+#pragma unroll
+    for (int j = 0; j < N; ++j) u[j] = 0ull;
+    while (pending) {
+#pragma unroll
+        for (int j = 0; j < N; ++j)
+            asm volatile("{ .reg .pred q; setp.ne.u32 q, %2, 0; @q ld.relaxed.gpu.global.u64 %0, [%1]; }"
+                         : "+l"(u[j]) : "l"(p + (size_t) j * stride), "r"(pending & (1u << j)) : "memory");
+#pragma unroll
+        for (int j = 0; j < N; ++j) if ((unsigned) (u[j] >> 32) == ep) pending &= ~(1u << j);
+        if (w.dead) break;
+        if (pending && pk_give_up(m, w, spins)) break;
+    }
+#pragma unroll
+    for (int j = 0; j < N; ++j) v[j] = __uint_as_float((unsigned) u[j]);
+}
+// same for N adjacent pairs (16-byte loads); pair j of the thread is at p + 2 * j * stride_pairs
+template <int N>
+__device__ __forceinline__ void pk_poll2_n(const DevModel & m, const Pkt * p, int stride_pairs, int n_valid, unsigned ep,
+                                           float2 (&v)[N], Watch & w) {
+    unsigned long long u0[N], u1[N];
+    unsigned pending = n_valid >= N ? (1u << N) - 1u : (1u << n_valid) - 1u;
+    unsigned spins = 0;
+#pragma unroll
+    for (int j = 0; j < N; ++j) { u0[j] = 0ull; u1[j] = 0ull; }
+    while (pending) {
+#pragma unroll
+        for (int j = 0; j < N; ++j)
+            asm volatile("{ .reg .pred q; setp.ne.u32 q, %3, 0; @q ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2]; }"
+                         : "+l"(u0[j]), "+l"(u1[j]) : "l"(p + (size_t) 2 * j * stride_pairs), "r"(pending & (1u << j)) : "memory");
+#pragma unroll
+        for (int j = 0; j < N; ++j)
+            if ((unsigned) (u0[j] >> 32) == ep && (unsigned) (u1[j] >> 32) == ep) pending &= ~(1u << j);
+        if (w.dead) break;
+        if (pending && pk_give_up(m, w, spins)) break;
+    }
+#pragma unroll
+    for (int j = 0; j < N; ++j) v[j] = make_float2(__uint_as_float((unsigned) u0[j]), __uint_as_float((unsigned) u1[j]));
+}
+
 // ------------------------------------------------------------------------------- TMA weight ring
 __device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
 
@@ -434,8 +481,7 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     if (warp < 3) {
         const Pkt * src = m.x_qkv + (warp == 0 ? h * HD : warp == 1 ? NH * HD + g * HD : (NH + NKV) * HD + g * HD);
         float v[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) v[i] = pk_poll(m, src + lane + 32 * i, ep_in, wd_);
+        pk_poll_n<4>(m, src + lane, 32, 4, ep_in, v, wd_);
         if (warp == 0) {
             head_norm_rope(v, ar.gn, ar.rp, m.eps);
 #pragma unroll
@@ -726,11 +772,14 @@ __device__ __noinline__ int select_sample(const DevModel & m, Smem & s, unsigned
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     constexpr int PER = (3072 + NCT - 1) / NCT;  // NCT * PER >= vocab
     float l[PER];
+    {
+        const int have = min(max(vocab - t * PER, 0), PER);
+        pk_poll_n<PER>(m, m.x_logit + t * PER, 1, have, ep, l, w);
+    }
 #pragma unroll
     for (int i = 0; i < PER; ++i) {
         const int idx = t * PER + i;
-        l[i] = -CUDART_INF_F;
-        if (idx < vocab) l[i] = proc_logit(m, pk_poll(m, m.x_logit + idx, ep, w), idx, process, suppress_start, eos_id, rep_penalty) / temperature;
+        l[i] = idx < vocab ? proc_logit(m, l[i], idx, process, suppress_start, eos_id, rep_penalty) / temperature : -CUDART_INF_F;
     }
     int * hist = reinterpret_cast<int *>(s.vt);              // 256 bins + 2 control words
     if (top_k > 0 && top_k < vocab) {
@@ -832,13 +881,17 @@ __device__ __forceinline__ void prefetch_layer_params(const StackW & W, int l, P
     }
 }
 
-// poll n packets (n even, multiple of 2) from src into dst (float) — all compute threads
-__device__ __forceinline__ void poll_vec(const DevModel & m, const Pkt * src, int n, unsigned ep, float * dst, Watch & w) {
-    spin_cycles(m.poll_d0);
-    for (int i = threadIdx.x; i < n / 2; i += NCT) {
-        const float2 f = pk_poll2(m, src + 2 * i, ep, w);
-        dst[2 * i] = f.x; dst[2 * i + 1] = f.y;
-    }
+// poll N packets (N even) from src into dst (float) — all compute threads, every load of a thread in flight at once
+template <int N>
+__device__ __forceinline__ void poll_vec(const DevModel & m, const Pkt * src, unsigned ep, float * dst, Watch & w) {
+    constexpr int PER = (N / 2 + NCT - 1) / NCT;
+    const int t = threadIdx.x;
+    const int mine = t < N / 2 ? (N / 2 - 1 - t) / NCT + 1 : 0;
+    float2 f[PER];
+    pk_poll2_n<PER>(m, src + 2 * t, NCT, mine, ep, f, w);
+#pragma unroll
+    for (int j = 0; j < PER; ++j)
+        if (j < mine) { dst[2 * (t + j * NCT)] = f[j].x; dst[2 * (t + j * NCT) + 1] = f[j].y; }
 }
 
 // One token through `n_layers` layers of stack W (+ optional head).  s.xres holds x on entry (and a
@@ -880,7 +933,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
 
         // ---- phase A: RMSNorm + fused QKV mat-vec
         PROF(1);
-        if (l > 0) { poll_vec(m, m.x_x, H, ep, s.xres, w); cbar(); }
+        if (l > 0) { poll_vec<H>(m, m.x_x, ep, s.xres, w); cbar(); }
         token(s);
         PROF(2);
         rmsnorm_to_xh(s, ga, m.eps, nullptr, nullptr);
@@ -901,10 +954,14 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(6);
 
         // ---- phase C: attn_output mat-vec (input rounded to F16) + residual
-        spin_cycles(m.poll_d0);
-        for (int i = t; i < NH * HD / 2; i += NCT) {
-            const float2 f = pk_poll2(m, m.x_att + 2 * i, e_att, w);
-            xh_put(s, 2 * i, f.x); xh_put(s, 2 * i + 1, f.y);
+        {
+            constexpr int NP = NH * HD / 2, PER = (NP + NCT - 1) / NCT;
+            const int mine = t < NP ? (NP - 1 - t) / NCT + 1 : 0;
+            float2 f[PER];
+            pk_poll2_n<PER>(m, m.x_att + 2 * t, NCT, mine, e_att, f, w);
+#pragma unroll
+            for (int j = 0; j < PER; ++j)
+                if (j < mine) { xh_put(s, 2 * (t + j * NCT), f[j].x); xh_put(s, 2 * (t + j * NCT) + 1, f[j].y); }
         }
         cbar();
         token(s);
@@ -918,7 +975,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(9);
 
         // ---- phase D: RMSNorm + gate/up mat-vec + SwiGLU
-        poll_vec(m, m.x_x1, H, e_x1, s.xres, w);
+        poll_vec<H>(m, m.x_x1, e_x1, s.xres, w);
         cbar();
         token(s);
         PROF(10);
@@ -937,7 +994,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(13);
 
         // ---- phase E: ffn_down on F32 activations (weights exact in F32) + residual
-        poll_vec(m, m.x_m, FFN, e_m, s.xf, w);
+        poll_vec<FFN>(m, m.x_m, e_m, s.xf, w);
         cbar();
         token(s);
         PROF(14);
@@ -954,7 +1011,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
     if (!head) return;
     // ---- head: final RMSNorm (= hidden_states) + vocabulary mat-vec + per-CTA arg-max candidate
     const unsigned e_head = ep + 1;
-    poll_vec(m, m.x_x, H, ep, s.xres, w);
+    poll_vec<H>(m, m.x_x, ep, s.xres, w);
     cbar();
     token(s);
     rmsnorm_to_xh(s, gh, m.eps, blockIdx.x == 0 ? m.hidden : nullptr, blockIdx.x == 0 ? p.hidden_dst : nullptr);
