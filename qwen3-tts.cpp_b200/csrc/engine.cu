@@ -217,12 +217,91 @@ static int chain_pack_inplace(q3t_ctx * ctx, __half * w, size_t rows, int K) {
     return Q3T_OK;
 }
 
+// Q8_0 rows (34-byte blocks {half d; int8 qs[32]}, ggml/src/ggml-common.h:219-224) -> ring records of
+// 1024 weights: [1024 int8][32 F16 block scales] = 1088 B, K/1024 records per row, rows at
+// dst_row0 + r * dst_row_step (fused q|k|v planes, gate/up interleave).
+//   mode 0 (int8 dot, lm_kernel.cu gemv_q8):      value e of block b -> (b/4)*128 + (e/4)*16 + (b%4)*4 + e%4
+//   mode 1 (F32 chain, lm_kernel.cu gemv_q8_f32): value e of block b -> (b/8)*256 + e*8 + b%8
+__global__ void k_q8_pack(const unsigned char * __restrict__ raw, unsigned char * __restrict__ dst, size_t n_rows, int K,
+                          size_t dst_row0, int dst_row_step, int mode) {
+    const int nb = K / 32;
+    const size_t n = n_rows * (size_t) nb;
+    for (size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+        const size_t r = i / nb; const int b = (int) (i % nb);
+        const unsigned char * src = raw + i * 34;
+        unsigned char * rec = dst + ((dst_row0 + r * (size_t) dst_row_step) * (size_t) (K / 1024) + (size_t) (b >> 5)) * 1088;
+        const int bl = b & 31;
+        rec[1024 + bl * 2] = src[0]; rec[1024 + bl * 2 + 1] = src[1];
+        for (int e = 0; e < 32; ++e) {
+            const int off = mode == 0 ? (bl >> 2) * 128 + (e >> 2) * 16 + (bl & 3) * 4 + (e & 3)
+                                      : (bl >> 3) * 256 + e * 8 + (bl & 7);
+            rec[off] = src[2 + e];
+        }
+    }
+}
+static int q8_pack(q3t_ctx * ctx, const q3t_host_tensor * t, unsigned char * plane, size_t n_rows, int K,
+                   size_t dst_row0, int dst_row_step, int mode) {
+    k_q8_pack<<<1024, 256, 0, ctx->stream>>>((const unsigned char *) t->dev, plane, n_rows, K, dst_row0, dst_row_step, mode);
+    return cuda_check(ctx, cudaGetLastError(), "q8 repack");
+}
+
+static int build_stack_q8(q3t_ctx * ctx, const char * prefix, int n_layers, StackW & W, int64_t & bytes) {
+    const int32_t wt = Q3T_TYPE_Q8_0;
+    const size_t REC = 1088;
+    unsigned char * wqkv, * wo, * wgu, * wdown;
+    float * an, * fn, * qn, * kn;
+    int rc;
+    if ((rc = dev_alloc(ctx, &wqkv,  (size_t) n_layers * QKV_N * REC))) return rc;
+    if ((rc = dev_alloc(ctx, &wo,    (size_t) n_layers * H * 2 * REC))) return rc;
+    if ((rc = dev_alloc(ctx, &wgu,   (size_t) n_layers * 2 * FFN * REC))) return rc;
+    if ((rc = dev_alloc(ctx, &wdown, (size_t) n_layers * H * 3 * REC))) return rc;
+    if ((rc = dev_alloc(ctx, &an, (size_t) n_layers * H))) return rc;
+    if ((rc = dev_alloc(ctx, &fn, (size_t) n_layers * H))) return rc;
+    if ((rc = dev_alloc(ctx, &qn, (size_t) n_layers * HD))) return rc;
+    if ((rc = dev_alloc(ctx, &kn, (size_t) n_layers * HD))) return rc;
+    for (int l = 0; l < n_layers; ++l) {
+        const std::string b = std::string(prefix) + ".blk." + std::to_string(l) + ".";
+        const q3t_host_tensor * q, * k, * v, * o, * g, * u, * d, * t;
+        if ((rc = need(ctx, b + "attn_q.weight", wt, H, NH * HD, &q))) return rc;
+        if ((rc = need(ctx, b + "attn_k.weight", wt, H, NKV * HD, &k))) return rc;
+        if ((rc = need(ctx, b + "attn_v.weight", wt, H, NKV * HD, &v))) return rc;
+        if ((rc = need(ctx, b + "attn_output.weight", wt, NH * HD, H, &o))) return rc;
+        if ((rc = need(ctx, b + "ffn_gate.weight", wt, H, FFN, &g))) return rc;
+        if ((rc = need(ctx, b + "ffn_up.weight", wt, H, FFN, &u))) return rc;
+        if ((rc = need(ctx, b + "ffn_down.weight", wt, FFN, H, &d))) return rc;
+        const size_t a0 = (size_t) l * QKV_N;
+        if ((rc = q8_pack(ctx, q, wqkv, NH * HD,  H, a0, 1, 0))) return rc;
+        if ((rc = q8_pack(ctx, k, wqkv, NKV * HD, H, a0 + NH * HD, 1, 0))) return rc;
+        if ((rc = q8_pack(ctx, v, wqkv, NKV * HD, H, a0 + (NH + NKV) * HD, 1, 0))) return rc;
+        if ((rc = q8_pack(ctx, o, wo, H, NH * HD, (size_t) l * H, 1, 0))) return rc;
+        if ((rc = q8_pack(ctx, g, wgu, FFN, H, (size_t) l * 2 * FFN, 2, 0))) return rc;          // even rows: gate
+        if ((rc = q8_pack(ctx, u, wgu, FFN, H, (size_t) l * 2 * FFN + 1, 2, 0))) return rc;      // odd rows: up
+        if ((rc = q8_pack(ctx, d, wdown, H, FFN, (size_t) l * H, 1, 1))) return rc;
+        if ((rc = need(ctx, b + "attn_norm.weight", Q3T_TYPE_F32, H, 1, &t))) return rc;
+        if ((rc = copy_rows(ctx, an + (size_t) l * H, H * 4, t->dev, H * 4, 1))) return rc;
+        if ((rc = need(ctx, b + "ffn_norm.weight", Q3T_TYPE_F32, H, 1, &t))) return rc;
+        if ((rc = copy_rows(ctx, fn + (size_t) l * H, H * 4, t->dev, H * 4, 1))) return rc;
+        if ((rc = need(ctx, b + "attn_q_norm.weight", Q3T_TYPE_F32, HD, 1, &t))) return rc;
+        if ((rc = copy_rows(ctx, qn + (size_t) l * HD, HD * 4, t->dev, HD * 4, 1))) return rc;
+        if ((rc = need(ctx, b + "attn_k_norm.weight", Q3T_TYPE_F32, HD, 1, &t))) return rc;
+        if ((rc = copy_rows(ctx, kn + (size_t) l * HD, HD * 4, t->dev, HD * 4, 1))) return rc;
+    }
+    W.n_layers = n_layers; W.wtype = wt;
+    W.wqkv = wqkv; W.wo = wo; W.wgu = wgu; W.wdown = wdown;
+    W.sqkv = W.so = W.sgu = W.sdown = nullptr;      // block scales travel inside the records
+    W.attn_norm = an; W.ffn_norm = fn; W.q_norm = qn; W.k_norm = kn;
+    bytes = (int64_t) n_layers * ((int64_t) QKV_N + 2 * H + 2LL * FFN + 3 * H) * (int64_t) REC
+          + (int64_t) n_layers * (2 * H + 2 * HD) * 4;
+    return Q3T_OK;
+}
+
 static int build_stack(q3t_ctx * ctx, const char * prefix, int n_layers, StackW & W, int64_t & bytes) {
     // dtype of the big matrices follows the file (F16 or Q8_0); all seven must agree
     const q3t_host_tensor * probe = find_raw(ctx, std::string(prefix) + ".blk.0.attn_q.weight");
     if (!probe) return set_err(ctx, Q3T_ERR_FORMAT, std::string("missing tensor: ") + prefix + ".blk.0.attn_q.weight");
     const int32_t wt = probe->type;
-    if (wt != Q3T_TYPE_F16) return set_err(ctx, Q3T_ERR_FORMAT, "only F16 layer weights are wired up in this build");
+    if (wt == Q3T_TYPE_Q8_0) return build_stack_q8(ctx, prefix, n_layers, W, bytes);
+    if (wt != Q3T_TYPE_F16) return set_err(ctx, Q3T_ERR_FORMAT, "layer weights must be F16 or Q8_0");
     W.n_layers = n_layers; W.wtype = wt;
     __half * wqkv, * wo, * wgu, * wdown;
     float * an, * fn, * qn, * kn;
@@ -293,6 +372,8 @@ static int finalize_tts(q3t_ctx * ctx) {
     drop_stack_raw(ctx, "talker");
     if ((rc = build_stack(ctx, "code_pred", c.code_pred_layers, m.cp, ctx->cp_bytes))) return rc;
     drop_stack_raw(ctx, "code_pred");
+    if (m.talker.wtype != m.cp.wtype)
+        return set_err(ctx, Q3T_ERR_FORMAT, "talker and code predictor layer weights must share one dtype (F16 or Q8_0)");
     const q3t_host_tensor * t;
     if ((rc = need(ctx, "talker.output_norm.weight", Q3T_TYPE_F32, H, 1, &t))) return rc;
     m.talker.out_norm = (const float *) t->dev;

@@ -40,6 +40,7 @@ constexpr int NCW        = LM_THREADS / 32 - 1;        // compute warps (the las
 constexpr int NCT        = NCW * 32;                   // compute threads
 constexpr int SLOT_B     = 2048;                       // ring slot = one K=1024 row of F16 weights
 constexpr int NSLOT      = 80;                         // 160 KB ring
+constexpr int SLOT_Q8    = 1088;                       // Q8_0 record of 1024 weights: 1024 int8 + 32 F16 block scales
 constexpr int NMB        = 8;                          // mbarriers cycling over the slices in flight
 constexpr int ATT_MAX_KV = LM_ATT_MAX_KV;              // positions the attention phase can hold
 
@@ -49,6 +50,8 @@ struct __align__(128) Smem {
     float  xf[FFN];                // F32 GEMV input (ffn_down) / scratch
     unsigned xh[H];                // F16 GEMV input, lane-packed: xh[m*32 + a] = {x[64m + a], x[64m + 32 + a]}
     float  outv[64];               // finalised row values of the phase
+    signed char xq[2048];          // Q8_0 mat-vec input: int8 values, lane-major per group of 4 blocks (see gemv_q8)
+    float  xd[64];                 // ... and its block scales (F16-rounded, as float)
     // attention (one CTA per head)
     float  sc[ATT_MAX_KV];         // scores, then exp values
     __half ph[ATT_MAX_KV];         // soft-max probabilities rounded to F16 (oracle D.4)
@@ -149,7 +152,7 @@ __device__ __forceinline__ void pk_poll_n(const DevModel & m, const Pkt * p, int
 #pragma unroll
         for (int j = 0; j < N; ++j) if ((unsigned) (u[j] >> 32) == ep) pending &= ~(1u << j);
         if (w.dead) break;
-        if (pending && pk_give_up(m, w, spins)) break;
+        if (pending) { if (pk_give_up(m, w, spins)) break; spin_cycles(m.poll_d1); }
     }
 #pragma unroll
     for (int j = 0; j < N; ++j) v[j] = __uint_as_float((unsigned) u[j]);
@@ -172,7 +175,7 @@ __device__ __forceinline__ void pk_poll2_n(const DevModel & m, const Pkt * p, in
         for (int j = 0; j < N; ++j)
             if ((unsigned) (u0[j] >> 32) == ep && (unsigned) (u1[j] >> 32) == ep) pending &= ~(1u << j);
         if (w.dead) break;
-        if (pending && pk_give_up(m, w, spins)) break;
+        if (pending) { if (pk_give_up(m, w, spins)) break; spin_cycles(m.poll_d1); }
     }
 #pragma unroll
     for (int j = 0; j < N; ++j) v[j] = make_float2(__uint_as_float((unsigned) u0[j]), __uint_as_float((unsigned) u1[j]));
@@ -232,10 +235,15 @@ __device__ __forceinline__ int ring_acquire(const DevModel & m, Smem & s, const 
     unsigned long long * bar = &s.mbar[rg.slice_idx % NMB];
     const uint32_t parity = (rg.slice_idx / NMB) & 1u;
     unsigned spins = 0;
-    while (!mbar_try(bar, parity)) {
-        if (w.dead) break;
-        if (pk_give_up(m, w, spins)) break;
+    // one lane per warp waits (every thread hitting the same mbarrier serialises for ~1 cycle each);
+    // __syncwarp orders the other lanes' reads of the slice after the observed completion
+    if ((threadIdx.x & 31) == 0) {
+        while (!mbar_try(bar, parity)) {
+            if (w.dead) break;
+            if (pk_give_up(m, w, spins)) break;
+        }
     }
+    __syncwarp();
     return (int) (rg.slot_head % NSLOT);
 }
 // all compute threads are past their last read of the slice (call after a cbar())
@@ -249,7 +257,8 @@ __device__ __forceinline__ void ring_release(Smem & s, Ring & rg, int n_slots) {
 }
 
 // producer: one slice = `n_slots` ring slots filled from `src` (contiguous in HBM); <= 2 bulk copies
-__device__ __forceinline__ void produce_slice(Smem & s, unsigned & p_slot, unsigned & p_idx, const void * src, int n_slots) {
+__device__ __forceinline__ void produce_slice(Smem & s, unsigned & p_slot, unsigned & p_idx, const void * src, int n_slots,
+                                              int slot_bytes = SLOT_B) {
     if (n_slots <= 0) return;
     // wait for ring space and for the mbarrier of slice (p_idx - NMB) to be drained by the consumers
     while (true) {
@@ -262,25 +271,37 @@ __device__ __forceinline__ void produce_slice(Smem & s, unsigned & p_slot, unsig
     const int n0 = min(n_slots, NSLOT - w0);
     // order the consumers' generic-proxy reads of the recycled slots before the async-proxy writes
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    mbar_expect_tx(bar, (uint32_t) n_slots * SLOT_B);
-    tma_load_1d(s.ring + (size_t) w0 * SLOT_B, src, (uint32_t) n0 * SLOT_B, bar);
-    if (n0 < n_slots)
-        tma_load_1d(s.ring, (const unsigned char *) src + (size_t) n0 * SLOT_B, (uint32_t) (n_slots - n0) * SLOT_B, bar);
+    mbar_expect_tx(bar, (uint32_t) n_slots * (uint32_t) slot_bytes);
+    if (slot_bytes == SLOT_B) {
+        tma_load_1d(s.ring + (size_t) w0 * SLOT_B, src, (uint32_t) n0 * SLOT_B, bar);
+        if (n0 < n_slots)
+            tma_load_1d(s.ring, (const unsigned char *) src + (size_t) n0 * SLOT_B, (uint32_t) (n_slots - n0) * SLOT_B, bar);
+    } else {
+        // compact records in HBM (pitch slot_bytes) land at the start of 2 KB ring slots: one copy per slot
+        for (int i = 0; i < n_slots; ++i) {
+            int slot = w0 + i; if (slot >= NSLOT) slot -= NSLOT;
+            tma_load_1d(s.ring + (size_t) slot * SLOT_B, (const unsigned char *) src + (size_t) i * slot_bytes, (uint32_t) slot_bytes, bar);
+        }
+    }
     p_slot += (unsigned) n_slots;
     p_idx  += 1u;
 }
 
-__device__ __forceinline__ const __half * sl_a(const StackW & W, int l, const Slices & z) {
-    return reinterpret_cast<const __half *>(W.wqkv) + ((size_t) l * QKV_N + z.a0) * H;
+// first byte of this CTA's rows of layer l (F16: 2048 B per 1024 weights, Q8_0: 1088 B records)
+__device__ __forceinline__ const unsigned char * sl_rows(const void * plane, int wtype, size_t row, int spr) {
+    return reinterpret_cast<const unsigned char *>(plane) + row * (size_t) spr * (wtype == Q3T_TYPE_Q8_0 ? SLOT_Q8 : SLOT_B);
 }
-__device__ __forceinline__ const __half * sl_o(const StackW & W, int l, const Slices & z) {
-    return reinterpret_cast<const __half *>(W.wo) + ((size_t) l * H + z.o0) * (NH * HD);
+__device__ __forceinline__ const void * sl_a(const StackW & W, int l, const Slices & z) {
+    return sl_rows(W.wqkv, W.wtype, (size_t) l * QKV_N + z.a0, 1);
 }
-__device__ __forceinline__ const __half * sl_gu(const StackW & W, int l, const Slices & z) {
-    return reinterpret_cast<const __half *>(W.wgu) + ((size_t) l * 2 * FFN + 2 * z.p0) * H;
+__device__ __forceinline__ const void * sl_o(const StackW & W, int l, const Slices & z) {
+    return sl_rows(W.wo, W.wtype, (size_t) l * H + z.o0, 2);
 }
-__device__ __forceinline__ const __half * sl_d(const StackW & W, int l, const Slices & z) {
-    return reinterpret_cast<const __half *>(W.wdown) + ((size_t) l * H + z.d0) * FFN;
+__device__ __forceinline__ const void * sl_gu(const StackW & W, int l, const Slices & z) {
+    return sl_rows(W.wgu, W.wtype, (size_t) l * 2 * FFN + 2 * z.p0, 1);
+}
+__device__ __forceinline__ const void * sl_d(const StackW & W, int l, const Slices & z) {
+    return sl_rows(W.wdown, W.wtype, (size_t) l * H + z.d0, 3);
 }
 
 // ------------------------------------------------------------------------------- ordered GEMV
@@ -359,6 +380,102 @@ __device__ __forceinline__ void gemv_ring(Smem & s, int s0, int n_rows) {
     }
 }
 
+// ------------------------------------------------------------------------------- Q8_0 mat-vecs
+// Activation quantisation of ggml's AVX2 quantize_row_q8_0 (arch/x86/quants.c:290-385): per block
+// of 32, d = amax / 127 (stored as F16), q = round-half-even(x * (127 / amax)).  One warp per block.
+// s.xf[0..K) -> s.xq (int8) + s.xd (scale as float).  Layout of s.xq per 1024 values: group c of 4
+// blocks is 128 bytes, lane l (0..7) owns bytes [c*128 + l*16, +16) = its 4 values (4l..4l+3) of each
+// of the 4 blocks -- the operand order of one dp4a per block in gemv_q8.  Ends with a cbar().
+template <int K>
+__device__ __forceinline__ void quant_q8(Smem & s) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int b = warp; b < K / 32; b += NCW) {
+        const float v = s.xf[b * 32 + lane];
+        float amax = fabsf(v);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        const float d  = __fdiv_rn(amax, 127.0f);
+        const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
+        const int q = __float2int_rn(__fmul_rn(v, id));
+        const int bl = b & 31;
+        s.xq[(b >> 5) * 1024 + (bl >> 2) * 128 + (lane >> 2) * 16 + (bl & 3) * 4 + (lane & 3)] = (signed char) q;
+        if (lane == 0) s.xd[b] = __half2float(__float2half_rn(d));
+    }
+    cbar();
+}
+
+// ggml_vec_dot_q8_0_q8_0, AVX2 (arch/x86/quants.c:1029-1046): accumulator lane j (0..7) takes the
+// int sum of bytes 4j..4j+3 of every block: acc_j = fma(dW*dX, (float) sum4, acc_j) over the blocks
+// in order, then hsum_float_8 (:43-49).  8 lanes per row, 4 rows per warp step; the ring record of
+// 1024 weights is [8 groups x 128 B lane-major int8][32 F16 block scales] (engine.cu k_q8_pack).
+template <int K>
+__device__ __forceinline__ void gemv_q8(Smem & s, int s0, int n_rows) {
+    constexpr int SPR = K / 1024;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 3, l = lane & 7;
+    for (int rb = warp * 4; rb < n_rows; rb += NCW * 4) {
+        const int r = rb + g < n_rows ? rb + g : rb;
+        float acc = 0.0f;
+#pragma unroll
+        for (int ch = 0; ch < SPR; ++ch) {
+            int slot = s0 + r * SPR + ch;
+            slot %= NSLOT;
+            const unsigned char * rec = s.ring + (size_t) slot * SLOT_B;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint4  wq = *reinterpret_cast<const uint4 *>(rec + c * 128 + l * 16);
+                const uint4  xq = *reinterpret_cast<const uint4 *>(s.xq + ch * 1024 + c * 128 + l * 16);
+                const uint2  ws = *reinterpret_cast<const uint2 *>(rec + 1024 + c * 8);
+                const float4 xs = *reinterpret_cast<const float4 *>(s.xd + ch * 32 + c * 4);
+                const float2 w01 = __half22float2(*reinterpret_cast<const __half2 *>(&ws.x));
+                const float2 w23 = __half22float2(*reinterpret_cast<const __half2 *>(&ws.y));
+                acc = __fmaf_rn(__fmul_rn(w01.x, xs.x), (float) __dp4a((int) wq.x, (int) xq.x, 0), acc);
+                acc = __fmaf_rn(__fmul_rn(w01.y, xs.y), (float) __dp4a((int) wq.y, (int) xq.y, 0), acc);
+                acc = __fmaf_rn(__fmul_rn(w23.x, xs.z), (float) __dp4a((int) wq.z, (int) xq.z, 0), acc);
+                acc = __fmaf_rn(__fmul_rn(w23.y, xs.w), (float) __dp4a((int) wq.w, (int) xq.w, 0), acc);
+            }
+        }
+        acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, 4));
+        acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, 2));
+        acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, 1));
+        if (l == 0 && rb + g < n_rows) s.outv[rb + g] = acc;
+    }
+}
+
+// ffn_down with Q8_0 weights: the reference casts W to F32 (dequantize_row_q8_0: (float) q * d) and
+// runs ggml_vec_dot_f32 on un-rounded activations (src/tts_transformer.cpp:1389-1390).  Lane a is
+// accumulator lane a; the record keeps the int8 values chain-major ((j/8)*256 + a*8 + j%8 for block
+// j of the 1024-chunk) so one 8-byte load brings 8 chain steps, and the 32 block scales behind them.
+template <int K>
+__device__ __forceinline__ void gemv_q8_f32(Smem & s, int s0, int n_rows) {
+    constexpr int SPR = K / 1024, NU = K / 256, NJ = K / 32;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp >= n_rows) return;
+    float xr[NJ];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) xr[j] = s.xf[32 * j + lane];
+    for (int r = warp; r < n_rows; r += NCW) {
+        float acc = 0.0f;
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+            int slot = s0 + r * SPR + (u >> 2);
+            slot %= NSLOT;
+            const unsigned char * rec = s.ring + (size_t) slot * SLOT_B;
+            const uint2 q8 = *reinterpret_cast<const uint2 *>(rec + (u & 3) * 256 + lane * 8);
+            const uint4 sc = *reinterpret_cast<const uint4 *>(rec + 1024 + (u & 3) * 16);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const unsigned word = e < 4 ? q8.x : q8.y;
+                const int qv = (int) (signed char) ((word >> (8 * (e & 3))) & 0xffu);
+                const unsigned sw = u4_get(sc, e >> 1);
+                const float d = __half2float(__ushort_as_half((unsigned short) ((e & 1) ? (sw >> 16) : (sw & 0xffffu))));
+                acc = __fmaf_rn(__fmul_rn((float) qv, d), xr[8 * u + e], acc);
+            }
+        }
+        const float res = reduce32_lanes(acc);
+        if (lane == 0) s.outv[r] = res;
+    }
+}
+
 // write x[k] rounded to F16 into the lane-packed GEMV input (see Smem::xh)
 __device__ __forceinline__ void xh_put(Smem & s, int k, float v) {
     reinterpret_cast<__half *>(s.xh)[(((k >> 6) * 32 + (k & 31)) << 1) + ((k >> 5) & 1)] = __float2half_rn(v);
@@ -377,6 +494,7 @@ __device__ __forceinline__ Gam load_gamma(const float * __restrict__ gamma) {
     r.g[2] = (t + 2 * NCT < H) ? __ldg(gamma + t + 2 * NCT) : 0.0f;
     return r;
 }
+template <bool Q8 = false>
 __device__ __forceinline__ void rmsnorm_to_xh(Smem & s, const Gam & gm, float eps, float * y_out, float * y_out2) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const bool has3 = t + 2 * NCT < H;
@@ -393,16 +511,17 @@ __device__ __forceinline__ void rmsnorm_to_xh(Smem & s, const Gam & gm, float ep
     const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
     const float ya = __fmul_rn(__fmul_rn(a, scale), gm.g[0]);
     const float yb = __fmul_rn(__fmul_rn(b, scale), gm.g[1]);
-    xh_put(s, t, ya); xh_put(s, t + NCT, yb);
+    if (Q8) { s.xf[t] = ya; s.xf[t + NCT] = yb; } else { xh_put(s, t, ya); xh_put(s, t + NCT, yb); }
     if (y_out)  { y_out[t] = ya;  y_out[t + NCT] = yb; }
     if (y_out2) { y_out2[t] = ya; y_out2[t + NCT] = yb; }
     if (has3) {
         const float yc = __fmul_rn(__fmul_rn(c, scale), gm.g[2]);
-        xh_put(s, t + 2 * NCT, yc);
+        if (Q8) s.xf[t + 2 * NCT] = yc; else xh_put(s, t + 2 * NCT, yc);
         if (y_out)  y_out[t + 2 * NCT] = yc;
         if (y_out2) y_out2[t + 2 * NCT] = yc;
     }
     cbar();
+    if (Q8) quant_q8<H>(s);
 }
 
 // per-head RMSNorm(128)*gamma then NEOX RoPE (FMA-contracted like the reference build), one warp;
@@ -888,6 +1007,7 @@ __device__ __forceinline__ void poll_vec(const DevModel & m, const Pkt * src, un
     const int t = threadIdx.x;
     const int mine = t < N / 2 ? (N / 2 - 1 - t) / NCT + 1 : 0;
     float2 f[PER];
+    spin_cycles(m.poll_d0);
     pk_poll2_n<PER>(m, src + 2 * t, NCT, mine, ep, f, w);
 #pragma unroll
     for (int j = 0; j < PER; ++j)
@@ -897,6 +1017,7 @@ __device__ __forceinline__ void poll_vec(const DevModel & m, const Pkt * src, un
 // One token through `n_layers` layers of stack W (+ optional head).  s.xres holds x on entry (and a
 // cbar() has made it visible); pr holds layer 0's parameters.  On exit pr holds layer 0's parameters
 // of the next pass' stack NW (if any).
+template <bool Q8>
 __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc & p, int pos,
                           const HeadW * head, bool process, const GenState & gs,
                           const Slices & z, const StackW * NW,
@@ -936,11 +1057,11 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         if (l > 0) { poll_vec<H>(m, m.x_x, ep, s.xres, w); cbar(); }
         token(s);
         PROF(2);
-        rmsnorm_to_xh(s, ga, m.eps, nullptr, nullptr);
+        rmsnorm_to_xh<Q8>(s, ga, m.eps, nullptr, nullptr);
         PROF(3);
         int s0 = ring_acquire(m, s, rg, w);
         PROF(4);
-        gemv_ring<1024, 3, false>(s, s0, nA);
+        if (Q8) gemv_q8<1024>(s, s0, nA); else gemv_ring<1024, 3, false>(s, s0, nA);
         PROF(40);
         cbar();
         PROF(41);
@@ -958,17 +1079,22 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
             constexpr int NP = NH * HD / 2, PER = (NP + NCT - 1) / NCT;
             const int mine = t < NP ? (NP - 1 - t) / NCT + 1 : 0;
             float2 f[PER];
+            spin_cycles(m.poll_d0);
             pk_poll2_n<PER>(m, m.x_att + 2 * t, NCT, mine, e_att, f, w);
 #pragma unroll
             for (int j = 0; j < PER; ++j)
-                if (j < mine) { xh_put(s, 2 * (t + j * NCT), f[j].x); xh_put(s, 2 * (t + j * NCT) + 1, f[j].y); }
+                if (j < mine) {
+                    if (Q8) { s.xf[2 * (t + j * NCT)] = f[j].x; s.xf[2 * (t + j * NCT) + 1] = f[j].y; }
+                    else    { xh_put(s, 2 * (t + j * NCT), f[j].x); xh_put(s, 2 * (t + j * NCT) + 1, f[j].y); }
+                }
         }
         cbar();
+        if (Q8) quant_q8<NH * HD>(s);
         token(s);
         PROF(7);
         s0 = ring_acquire(m, s, rg, w);
         PROF(8);
-        gemv_ring<2048, 1, false>(s, s0, nO);
+        if (Q8) gemv_q8<2048>(s, s0, nO); else gemv_ring<2048, 1, false>(s, s0, nO);
         cbar();
         if (t < nO) pk_store(m.x_x1 + z.o0 + t, __fadd_rn(s.outv[t], s.xres[z.o0 + t]), e_x1);
         ring_release(s, rg, nO * 2);
@@ -979,11 +1105,11 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         cbar();
         token(s);
         PROF(10);
-        rmsnorm_to_xh(s, gf, m.eps, nullptr, nullptr);
+        rmsnorm_to_xh<Q8>(s, gf, m.eps, nullptr, nullptr);
         PROF(11);
         s0 = ring_acquire(m, s, rg, w);
         PROF(12);
-        gemv_ring<1024, 4, false>(s, s0, 2 * nP);
+        if (Q8) gemv_q8<1024>(s, s0, 2 * nP); else gemv_ring<1024, 4, false>(s, s0, 2 * nP);
         cbar();
         if (t < nP) {
             const float gt = s.outv[2 * t], up = s.outv[2 * t + 1];
@@ -1000,7 +1126,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(14);
         s0 = ring_acquire(m, s, rg, w);
         PROF(15);
-        gemv_ring<3072, 1, true>(s, s0, nD);
+        if (Q8) gemv_q8_f32<3072>(s, s0, nD); else gemv_ring<3072, 1, true>(s, s0, nD);
         cbar();
         if (t < nD) pk_store(m.x_x + z.d0 + t, __fadd_rn(s.outv[t], s.xres[z.d0 + t]), e_x);
         ring_release(s, rg, nD * 3);
@@ -1066,19 +1192,18 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
         const int n_layers = passes[ip].n_layers, hd = passes[ip].head;
         for (int l = 0; l < n_layers && !aborted; ++l) {
             for (int k = 0; k < 4; ++k) {
-                const void * src = k == 0 ? (const void *) sl_a(W, l, z) : k == 1 ? (const void *) sl_o(W, l, z)
-                                 : k == 2 ? (const void *) sl_gu(W, l, z) : (const void *) sl_d(W, l, z);
+                const void * src = k == 0 ? sl_a(W, l, z) : k == 1 ? sl_o(W, l, z) : k == 2 ? sl_gu(W, l, z) : sl_d(W, l, z);
                 const int n_slots = k == 0 ? nA : k == 1 ? nO * 2 : k == 2 ? nP * 2 : nD * 3;
                 // ring-space wait with an abort check (EOS decided while pass 0 is being produced)
                 while (true) {
                     const unsigned long long c = s.consumed;
                     if (p_slot + (unsigned) n_slots - (unsigned) c <= (unsigned) NSLOT && p_idx - (unsigned) (c >> 32) < (unsigned) NMB &&
-                        (m.poll_d1 <= 0 || (int) (p_idx - s.tokens) < m.poll_d1)) break;
+                        true) break;
                     if (*s_go == 0) { aborted = true; break; }
                     if (((++pspins) & 0xfff) == 0 && clock64() - t_start > 8000000000LL) { m.st->error = 1; aborted = true; break; }   // watchdog
                 }
                 if (aborted) break;
-                produce_slice(s, p_slot, p_idx, src, n_slots);
+                produce_slice(s, p_slot, p_idx, src, n_slots, W.wtype == Q3T_TYPE_Q8_0 ? SLOT_Q8 : SLOT_B);
             }
         }
         if (hd >= 0 && !aborted) {
@@ -1104,6 +1229,7 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
 // frame_mode = 1: `passes` is the 17-pass frame program; the kernel owns the generate-loop
 // bookkeeping of src/tts_transformer.cpp:2664-2804 (EOS test, code emission, repetition set,
 // n_past) in GenState so the identical launch can be replayed once per frame.
+template <bool Q8>
 __global__ void __launch_bounds__(LM_THREADS, 1)
 lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ passes, int n_passes, int frame_mode) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -1224,7 +1350,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
             if (nx != XM_SELECT_ONLY) NW = ns == 0 ? &m.talker : &m.cp;
         }
         if (!NW) pr_valid = false;
-        run_stack(m, W, p, pos, head, p.process != 0, gs, z, NW, s, rg, ep, pr, w);
+        run_stack<Q8>(m, W, p, pos, head, p.process != 0, gs, z, NW, s, rg, ep, pr, w);
         if (head) { pending = p.head; pending_vocab = head->vocab; pending_process = p.process; pending_ep = ep; }
         if (p.stack == 0 && p.pos < 0) ++n_past;
     }
@@ -1245,12 +1371,14 @@ int lm_max_grid(q3t_ctx * ctx) {
     static bool attr_set = false;
     const size_t smem = sizeof(Smem);
     if (!attr_set) {
-        if (cudaFuncSetAttribute(lm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem) != cudaSuccess) return -1;
+        if (cudaFuncSetAttribute(lm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem) != cudaSuccess) return -1;
+        if (cudaFuncSetAttribute(lm_kernel<true>,  cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem) != cudaSuccess) return -1;
         attr_set = true;
     }
-    int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_kernel, LM_THREADS, smem) != cudaSuccess) return -1;
-    if (per_sm < 1) return 0;
+    int per_sm = 0, per_sm_q = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_kernel<false>, LM_THREADS, smem) != cudaSuccess) return -1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_q, lm_kernel<true>, LM_THREADS, smem) != cudaSuccess) return -1;
+    if (per_sm < 1 || per_sm_q < 1) return 0;
     return ctx->sm_count;          // one persistent CTA per SM
 }
 
@@ -1262,11 +1390,13 @@ int lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int fram
     }
     DevModel m = ctx->hm;
     static int d0 = -1, d1 = -1;
-    if (d0 < 0) { const char * e0 = getenv("Q3T_POLL_D0"), * e1 = getenv("Q3T_POLL_D1"); d0 = e0 ? atoi(e0) : 0; d1 = e1 ? atoi(e1) : 0; }
+    if (d0 < 0) { const char * e0 = getenv("Q3T_POLL_D0"), * e1 = getenv("Q3T_POLL_D1"); d0 = e0 ? atoi(e0) : 300; d1 = e1 ? atoi(e1) : 0; }
     m.poll_d0 = d0; m.poll_d1 = d1;
     void * args[] = { (void *) &m, (void *) &passes_dev, (void *) &n_passes, (void *) &frame_mode };
-    cudaError_t e = cudaLaunchCooperativeKernel((const void *) lm_kernel, dim3(ctx->grid), dim3(LM_THREADS),
-                                                args, sizeof(Smem), ctx->stream);
+    // both stacks of a model share the weight type (the converter quantises them together)
+    const bool q8 = m.talker.wtype == Q3T_TYPE_Q8_0;
+    cudaError_t e = cudaLaunchCooperativeKernel(q8 ? (const void *) lm_kernel<true> : (const void *) lm_kernel<false>,
+                                                dim3(ctx->grid), dim3(LM_THREADS), args, sizeof(Smem), ctx->stream);
     ctx->timing.kernel_launches++;
     return cuda_check(ctx, e, "lm_kernel launch");
 }

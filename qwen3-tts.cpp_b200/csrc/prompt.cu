@@ -55,6 +55,60 @@ proj_rows(const __half * __restrict__ W, const __half * __restrict__ X, const fl
     }
 }
 
+// ---- Q8_0 text projection (fc1/fc2 quantised by scripts/convert_tts_to_gguf.py:244-270)
+// activation rows -> Q8_0 (quantize_row_q8_0, AVX2 flavour: d = amax/127 as F16, q = rne(x * 127/amax));
+// one warp per block of 32
+template <typename T>
+__global__ void quant_rows_q8(const T * __restrict__ X, int K, signed char * __restrict__ xq, float * __restrict__ xd) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const size_t row = blockIdx.x;
+    for (int b = warp; b < K / 32; b += nw) {
+        const float v = (float) X[row * K + b * 32 + lane];
+        float amax = fabsf(v);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        const float d  = __fdiv_rn(amax, 127.0f);
+        const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
+        xq[row * K + b * 32 + lane] = (signed char) __float2int_rn(__fmul_rn(v, id));
+        if (lane == 0) xd[row * (K / 32) + b] = __half2float(__float2half_rn(d));
+    }
+}
+
+// out[t][n] = act( q8dot(W[n], X[t]) + bias[n] ) in the order of ggml_vec_dot_q8_0_q8_0 (AVX2,
+// arch/x86/quants.c:1029-1046): accumulator lane j takes bytes 4j..4j+3 of every block.  One warp
+// per output row: lane = (token slot g = lane/8, accumulator lane j = lane%8), 4 tokens per sweep.
+// W is the raw GGUF tensor (34-byte blocks, 2-byte aligned).
+template <int SILU>
+__global__ void __launch_bounds__(256)
+proj_rows_q8(const unsigned char * __restrict__ W, const signed char * __restrict__ xq, const float * __restrict__ xd,
+             const float * __restrict__ bias, int N, int K, int T, float * __restrict__ out) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 3, j = lane & 7;
+    const int n = blockIdx.x * 8 + warp;
+    if (n >= N) return;
+    const int nb = K / 32;
+    const unsigned char * wrow = W + (size_t) n * nb * 34;
+    for (int t0 = 0; t0 < T; t0 += 4) {
+        const int t = t0 + g < T ? t0 + g : T - 1;
+        float acc = 0.0f;
+        for (int b = 0; b < nb; ++b) {
+            const unsigned short * wb = reinterpret_cast<const unsigned short *>(wrow + (size_t) b * 34);
+            const float dw = __half2float(__ushort_as_half(wb[0]));
+            const unsigned wq = (unsigned) wb[1 + 2 * j] | ((unsigned) wb[2 + 2 * j] << 16);
+            const unsigned xv = *reinterpret_cast<const unsigned *>(xq + (size_t) t * K + b * 32 + 4 * j);
+            const float d = __fmul_rn(dw, xd[(size_t) t * nb + b]);
+            acc = __fmaf_rn(d, (float) __dp4a((int) wq, (int) xv, 0), acc);
+        }
+        acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, 4));
+        acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, 2));
+        acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, 1));
+        if (j == 0 && t0 + g < T) {
+            float v = __fadd_rn(acc, bias[n]);
+            if (SILU) v = __fdiv_rn(v, __fadd_rn(1.0f, v_expf(__fsub_rn(0.0f, v))));
+            out[(size_t) (t0 + g) * N + n] = v;
+        }
+    }
+}
+
 struct AsmArgs {
     const float * proj;       // [7 + tc][H]: bos, eos, pad, role0..2, first_text, trailing...
     const __half * codec_embd;
@@ -116,8 +170,9 @@ static int project_ids(q3t_ctx * ctx, const int * ids_dev, int T, float * out_de
     const q3t_host_tensor * w1 = get("talker.text_proj.fc1.weight"), * b1 = get("talker.text_proj.fc1.bias");
     const q3t_host_tensor * w2 = get("talker.text_proj.fc2.weight"), * b2 = get("talker.text_proj.fc2.bias");
     if (!emb || !w1 || !b1 || !w2 || !b2) return set_err(ctx, Q3T_ERR_FORMAT, "missing text embedding / projection tensors");
-    if (emb->type != Q3T_TYPE_F16 || w1->type != Q3T_TYPE_F16 || w2->type != Q3T_TYPE_F16)
-        return set_err(ctx, Q3T_ERR_FORMAT, "text projection: only F16 weights are wired up in this build");
+    const bool q8 = w1->type == Q3T_TYPE_Q8_0;
+    if (emb->type != Q3T_TYPE_F16 || (w1->type != Q3T_TYPE_F16 && !q8) || w2->type != w1->type)
+        return set_err(ctx, Q3T_ERR_FORMAT, "text projection: text_embd must be F16, fc1/fc2 both F16 or both Q8_0");
     if (K % 8 != 0 || emb->ne[0] != K || w1->ne[0] != K || w1->ne[1] != K || w2->ne[0] != K || w2->ne[1] != H)
         return set_err(ctx, Q3T_ERR_FORMAT, "unexpected text projection shapes");
     __half * xh = nullptr, * hh = nullptr;
@@ -126,12 +181,26 @@ static int project_ids(q3t_ctx * ctx, const int * ids_dev, int T, float * out_de
     rc = cuda_check(ctx, cudaMalloc(&hh, (size_t) T * K * 2), "cudaMalloc");
     if (rc) { cudaFree(xh); return rc; }
     gather_rows_h<<<T, 128, 0, ctx->stream>>>((const __half *) emb->dev, ids_dev, K, xh);
-    proj_rows<1><<<(K + 7) / 8, 256, 0, ctx->stream>>>((const __half *) w1->dev, xh, (const float *) b1->dev, K, K, T, nullptr, hh);
-    proj_rows<0><<<(H + 7) / 8, 256, 0, ctx->stream>>>((const __half *) w2->dev, hh, (const float *) b2->dev, H, K, T, out_dev, nullptr);
-    ctx->timing.kernel_launches += 3;
-    rc = cuda_check(ctx, cudaGetLastError(), "text projection launch");
+    signed char * xq = nullptr; float * xd = nullptr, * hf = nullptr;
+    if (!q8) {
+        proj_rows<1><<<(K + 7) / 8, 256, 0, ctx->stream>>>((const __half *) w1->dev, xh, (const float *) b1->dev, K, K, T, nullptr, hh);
+        proj_rows<0><<<(H + 7) / 8, 256, 0, ctx->stream>>>((const __half *) w2->dev, hh, (const float *) b2->dev, H, K, T, out_dev, nullptr);
+        ctx->timing.kernel_launches += 3;
+    } else {
+        rc = cuda_check(ctx, cudaMalloc(&xq, (size_t) T * K), "cudaMalloc");
+        if (!rc) rc = cuda_check(ctx, cudaMalloc(&xd, (size_t) T * (K / 32) * 4), "cudaMalloc");
+        if (!rc) rc = cuda_check(ctx, cudaMalloc(&hf, (size_t) T * K * 4), "cudaMalloc");
+        if (!rc) {
+            quant_rows_q8<__half><<<T, 256, 0, ctx->stream>>>(xh, K, xq, xd);
+            proj_rows_q8<1><<<(K + 7) / 8, 256, 0, ctx->stream>>>((const unsigned char *) w1->dev, xq, xd, (const float *) b1->dev, K, K, T, hf);
+            quant_rows_q8<float><<<T, 256, 0, ctx->stream>>>(hf, K, xq, xd);
+            proj_rows_q8<0><<<(H + 7) / 8, 256, 0, ctx->stream>>>((const unsigned char *) w2->dev, xq, xd, (const float *) b2->dev, H, K, T, out_dev);
+            ctx->timing.kernel_launches += 5;
+        }
+    }
+    if (!rc) rc = cuda_check(ctx, cudaGetLastError(), "text projection launch");
     cudaStreamSynchronize(ctx->stream);
-    cudaFree(xh); cudaFree(hh);
+    cudaFree(xh); cudaFree(hh); cudaFree(xq); cudaFree(xd); cudaFree(hf);
     return rc;
 }
 

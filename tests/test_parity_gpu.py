@@ -40,6 +40,26 @@ def tts_full(q3t):
     t.close()
 
 
+@pytest.fixture(scope="module")
+def tts_tiny_q8(q3t):
+    t = q3t.TTSTransformer()
+    assert t.load_model(models("tiny", "q8_0")[0]), t.get_error()
+    yield t
+    t.close()
+
+
+@pytest.fixture(scope="module")
+def tts_full_q8(q3t):
+    t = q3t.TTSTransformer()
+    assert t.load_model(models("full", "q8_0")[0]), t.get_error()
+    yield t
+    t.close()
+
+
+def _fixture_for(request, preset, wtype):
+    return request.getfixturevalue("tts_" + preset + ("_q8" if wtype == "q8_0" else ""))
+
+
 def test_native_library_loaded(q3t):
     """The CUDA extension is the thing that runs: the in-tree .so is mapped into this process."""
     q3t.lib()
@@ -47,10 +67,11 @@ def test_native_library_loaded(q3t):
     assert "libq3t_b200.so" in maps
 
 
+@pytest.mark.parametrize("wtype", ["f16", "q8_0"])
 @pytest.mark.parametrize("preset", ["tiny", "full"])
-def test_prompt_prefill_step_codepred_vs_golden(q3t, preset, request):
-    t = request.getfixturevalue("tts_" + preset)
-    g = _gold(f"{preset}_f16.npz")
+def test_prompt_prefill_step_codepred_vs_golden(q3t, preset, wtype, request):
+    t = _fixture_for(request, preset, wtype)
+    g = _gold(f"{preset}_{wtype}.npz")
     pre, trail, pad = t.build_prompt(g["tokens"], g["spk"])
     assert np.array_equal(pre, g["prefill"]) and np.array_equal(trail, g["trailing"]) and np.array_equal(pad, g["pad"])
     pre_ns, trail_ns, _ = t.build_prompt(g["tokens"], None, -1)
@@ -76,10 +97,11 @@ def test_prompt_prefill_step_codepred_vs_golden(q3t, preset, request):
     assert np.array_equal(codes, g["cp_codes"])
 
 
+@pytest.mark.parametrize("wtype", ["f16", "q8_0"])
 @pytest.mark.parametrize("preset,n", [("tiny", 16), ("full", 64)])
-def test_generate_greedy_codes_identical_vs_golden(q3t, preset, n, request):
-    t = request.getfixturevalue("tts_" + preset)
-    g = _gold(f"{preset}_f16.npz")
+def test_generate_greedy_codes_identical_vs_golden(q3t, preset, n, wtype, request):
+    t = _fixture_for(request, preset, wtype)
+    g = _gold(f"{preset}_{wtype}.npz")
     codes = t.generate(g["tokens"], g["spk"], n, repetition_penalty=1.05, temperature=0.0, top_k=0)
     assert codes is not None, t.get_error()
     assert codes.shape == g["codes"].shape
@@ -101,10 +123,12 @@ def test_generate_is_prefix_stable_and_repeatable(tts_full):
     assert a[:, 1:].max() < 2048 and a.min() >= 0
 
 
-def test_step_vs_c_oracle_fresh_inputs(tts_tiny):
+@pytest.mark.parametrize("wtype", ["f16", "q8_0"])
+def test_step_vs_c_oracle_fresh_inputs(wtype, request):
     from oracle import port
-    p = port.PortTTS(models("tiny", "f16")[0])
-    g = _gold("tiny_f16.npz")
+    tts_tiny = _fixture_for(request, "tiny", wtype)
+    p = port.PortTTS(models("tiny", wtype)[0])
+    g = _gold(f"tiny_{wtype}.npz")
     rng = np.random.default_rng(11)
     p.init_kv(64)
     assert tts_tiny.init_kv_cache(64)
@@ -195,6 +219,24 @@ def test_generate_320_frames_identical_to_live_reference(tts_full):
     want = ref.generate(HELLO_FULL, spk, 320, temperature=0.0)
     ref.close()
     got = tts_full.generate(HELLO_FULL, spk, 320, temperature=0.0)
+    assert got is not None and got.shape == want.shape
+    neq = np.argwhere(got != want)
+    assert len(neq) == 0, f"first mismatch at frame/codebook {neq[0]}"
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(os.path.dirname(GOLDEN), "..", "oracle", "_ref", "libq3t_ref.so")),
+                    reason="oracle/_ref not shipped")
+def test_generate_q8_0_160_frames_identical_to_live_reference(tts_full_q8):
+    """Q8_0 layer weights (config 3's model): int8 x int8 block dots, activations re-quantised per
+    mat-vec, ffn_down on de-quantised weights — greedy codes identical to the reference's ggml-CPU run."""
+    from oracle import reflib
+    reflib.RefLib.get().set_threads(min(16, os.cpu_count() or 4))
+    ref = reflib.RefTTS(models("full", "q8_0")[0])
+    rng = np.random.default_rng(4)
+    spk = (rng.standard_normal(1024) * 0.05).astype(np.float32)
+    want = ref.generate(HELLO_FULL, spk, 160, temperature=0.0)
+    ref.close()
+    got = tts_full_q8.generate(HELLO_FULL, spk, 160, temperature=0.0)
     assert got is not None and got.shape == want.shape
     neq = np.argwhere(got != want)
     assert len(neq) == 0, f"first mismatch at frame/codebook {neq[0]}"
