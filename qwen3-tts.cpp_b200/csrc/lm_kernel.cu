@@ -40,6 +40,7 @@ constexpr int NCW        = LM_THREADS / 32 - 1;        // compute warps (the las
 constexpr int NCT        = NCW * 32;                   // compute threads
 constexpr int SLOT_B     = 2048;                       // ring slot = one K=1024 row of F16 weights
 constexpr int NSLOT      = 80;                         // 160 KB ring
+constexpr int KV_CH      = 128;                        // K/V history rows per ring slice (16 slots)
 constexpr int SLOT_Q8    = 1088;                       // Q8_0 record of 1024 weights: 1024 int8 + 32 F16 block scales
 constexpr int NMB        = 8;                          // mbarriers cycling over the slices in flight
 constexpr int ATT_MAX_KV = LM_ATT_MAX_KV;              // positions the attention phase can hold
@@ -258,7 +259,7 @@ __device__ __forceinline__ void ring_release(Smem & s, Ring & rg, int n_slots) {
 
 // producer: one slice = `n_slots` ring slots filled from `src` (contiguous in HBM); <= 2 bulk copies
 __device__ __forceinline__ void produce_slice(Smem & s, unsigned & p_slot, unsigned & p_idx, const void * src, int n_slots,
-                                              int slot_bytes = SLOT_B) {
+                                              int slot_bytes = SLOT_B, int tail_bytes = SLOT_B) {
     if (n_slots <= 0) return;
     // wait for ring space and for the mbarrier of slice (p_idx - NMB) to be drained by the consumers
     while (true) {
@@ -271,12 +272,15 @@ __device__ __forceinline__ void produce_slice(Smem & s, unsigned & p_slot, unsig
     const int n0 = min(n_slots, NSLOT - w0);
     // order the consumers' generic-proxy reads of the recycled slots before the async-proxy writes
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    mbar_expect_tx(bar, (uint32_t) n_slots * (uint32_t) slot_bytes);
     if (slot_bytes == SLOT_B) {
-        tma_load_1d(s.ring + (size_t) w0 * SLOT_B, src, (uint32_t) n0 * SLOT_B, bar);
-        if (n0 < n_slots)
-            tma_load_1d(s.ring, (const unsigned char *) src + (size_t) n0 * SLOT_B, (uint32_t) (n_slots - n0) * SLOT_B, bar);
+        // contiguous source; the last slot may be partly filled (tail_bytes, multiple of 16)
+        const uint32_t total = (uint32_t) (n_slots - 1) * SLOT_B + (uint32_t) tail_bytes;
+        const uint32_t first = min(total, (uint32_t) n0 * SLOT_B);
+        mbar_expect_tx(bar, total);
+        tma_load_1d(s.ring + (size_t) w0 * SLOT_B, src, first, bar);
+        if (total > first) tma_load_1d(s.ring, (const unsigned char *) src + first, total - first, bar);
     } else {
+        mbar_expect_tx(bar, (uint32_t) n_slots * (uint32_t) slot_bytes);
         // compact records in HBM (pitch slot_bytes) land at the start of 2 KB ring slots: one copy per slot
         for (int i = 0; i < n_slots; ++i) {
             int slot = w0 + i; if (slot >= NSLOT) slot -= NSLOT;
@@ -557,8 +561,15 @@ struct AttnRegs {          // per-lane parameters fetched ahead of use (warps 0 
 
 __device__ __forceinline__ uint2 ld_cg_u2(const void * p) { return __ldcg(reinterpret_cast<const uint2 *>(p)); }
 
+// address of history row r (0..KV_CH) of a K/V slice that starts at ring slot s0
+__device__ __forceinline__ const unsigned char * kv_row(const Smem & s, int s0, int r) {
+    int slot = s0 + (r >> 3);
+    if (slot >= NSLOT) slot -= NSLOT;
+    return s.ring + (size_t) slot * SLOT_B + (r & 7) * (HD * 2);
+}
+
 __device__ void attention_head(const DevModel & m, const StackW & W, int l, int h, int pos, bool f32attn, int width,
-                               const AttnRegs & ar, unsigned ep_in, unsigned ep_out, Smem & s, Watch & wd_) {
+                               const AttnRegs & ar, unsigned ep_in, unsigned ep_out, Smem & s, Ring & rg, Watch & wd_) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int g = h >> 1;
     const bool writer = (h & 1) == 0;
@@ -571,29 +582,8 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     const float kq_scale = 1.0f / sqrtf((float) HD);
     const size_t kv_head_base = ((size_t) (l * NKV + g) * W.n_ctx) * HD;
     Pkt * att = m.x_att + h * HD;
-
-    // ---- stage 0 (before the new token arrives): everything that depends only on history is put in
-    //      flight now so its L2 latency hides behind the packet wait: the K rows of this warp's first
-    //      positions (registers) and the V rows of the double-precision leftover part (shared memory)
     const int np = min(wd & ~31, n_kv);                      // positions in the 32-lane part of the P.V dot
-    const int nleft = n_kv - np;
-    const __half * kbase = W.kcache + kv_head_base;
-    const __half * vbase = W.vcache + kv_head_base;
-    uint2 kk0[4];
-    if (!f32attn) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int tt = warp + j * NCW;
-            if (tt < n_kv && tt != pos) kk0[j] = ld_cg_u2(kbase + (size_t) tt * HD + lane * 4);
-        }
-        // cp.async (LDGSTS): global -> shared without passing through registers, completes in the background
-        for (int idx = t; idx < nleft * (HD / 8); idx += NCT) {
-            const int tg = np + (idx >> 4);
-            if (tg != pos)
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_u32(s.vt + (idx >> 4) * HD + (idx & 15) * 8)),
-                             "l"(vbase + (size_t) tg * HD + (idx & 15) * 8) : "memory");
-        }
-    }
+    const int nck = f32attn ? 0 : (pos + KV_CH - 1) / KV_CH; // history slices (K, then V) the producer streams
 
     PROF(50);
     // ---- prologue: q, k, v of the new token (warps 0, 1, 2)
@@ -630,11 +620,9 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
                     W.vcache[kv_head_base + (size_t) pos * HD + d] = hv;
                     if (W.vf32 && pos < 2) W.vf32[((size_t) (l * 2 + pos) * NKV + g) * HD + d] = v[i];
                 }
-                if (pos >= np) s.vt[(pos - np) * HD + d] = hv;          // the new token is a leftover row
             }
         }
     }
-    asm volatile("cp.async.wait_all;" ::: "memory");
     PROF(51);
     cbar();
     PROF(52);
@@ -675,44 +663,42 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
         }
         // the K/V rows appended above are read by other CTAs one pass later: publish them before this
         // CTA's next packets (off the critical path: after the attention output has left)
-        if (writer && (warp == 1 || warp == 2)) __threadfence();
+        if (writer && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }
         return;
     }
 
-    // ---- scores: warp w takes positions w, w+15, ...; lane a walks chain a (4 steps) of dot_f16(K_t, q)
+    // ---- scores: the K history arrives in the ring (chain-major rows: element d = 32i + a at a*4 + i);
+    //      warp w takes rows w, w+11, ... of a slice; lane a walks chain a (4 steps) of dot_f16(K_t, q)
     {
         float q[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) q[i] = s.qr[lane + 32 * i];
         float mx = -CUDART_INF_F;
-        for (int t0 = warp; t0 < n_kv; t0 += 4 * NCW) {
-            uint2 kk[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int tt = t0 + j * NCW;
-                if (t0 == warp) kk[j] = kk0[j];
-                else if (tt < n_kv && tt != pos) kk[j] = ld_cg_u2(kbase + (size_t) tt * HD + lane * 4);
+        for (int c = 0; c < nck; ++c) {
+            const int s0 = ring_acquire(m, s, rg, wd_);
+            const int rows = min(KV_CH, pos - c * KV_CH);
+#pragma unroll 2
+            for (int r = warp; r < rows; r += NCW) {
+                const uint2 kk = *reinterpret_cast<const uint2 *>(kv_row(s, s0, r) + lane * 8);
+                const float2 f01 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.x));
+                const float2 f23 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.y));
+                float a = __fmaf_rn(f01.x, q[0], 0.0f);
+                a = __fmaf_rn(f01.y, q[1], a); a = __fmaf_rn(f23.x, q[2], a); a = __fmaf_rn(f23.y, q[3], a);
+                const float sv = __fmul_rn(reduce32_lanes(a), kq_scale);
+                mx = fmaxf(mx, sv);
+                if (lane == 0) s.sc[c * KV_CH + r] = sv;
             }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int tt = t0 + j * NCW;
-                if (tt < n_kv) {
-                    float k0, k1, k2, k3;
-                    if (tt == pos) {
-                        k0 = __half2float(s.knew_h[lane]);      k1 = __half2float(s.knew_h[lane + 32]);
-                        k2 = __half2float(s.knew_h[lane + 64]); k3 = __half2float(s.knew_h[lane + 96]);
-                    } else {
-                        const float2 f01 = __half22float2(*reinterpret_cast<const __half2 *>(&kk[j].x));
-                        const float2 f23 = __half22float2(*reinterpret_cast<const __half2 *>(&kk[j].y));
-                        k0 = f01.x; k1 = f01.y; k2 = f23.x; k3 = f23.y;
-                    }
-                    float a = __fmaf_rn(k0, q[0], 0.0f);
-                    a = __fmaf_rn(k1, q[1], a); a = __fmaf_rn(k2, q[2], a); a = __fmaf_rn(k3, q[3], a);
-                    const float sv = __fmul_rn(reduce32_lanes(a), kq_scale);
-                    mx = fmaxf(mx, sv);
-                    if (lane == 0) s.sc[tt] = sv;
-                }
-            }
+            cbar();
+            ring_release(s, rg, (rows + 7) >> 3);
+        }
+        if (warp == NCW - 1) {                               // the new token's row comes from shared memory
+            float a = __fmaf_rn(__half2float(s.knew_h[lane]), q[0], 0.0f);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 32]), q[1], a);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 64]), q[2], a);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 96]), q[3], a);
+            const float sv = __fmul_rn(reduce32_lanes(a), kq_scale);
+            mx = fmaxf(mx, sv);
+            if (lane == 0) s.sc[pos] = sv;
         }
         if (lane == 0) s.fred[warp] = mx;
     }
@@ -754,82 +740,111 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
             if (live) s.ph[lane] = __float2half_rn(__fmul_rn(e, inv));
         }
     } else {
-    double ds = 0.0;
-    for (int ch = t; ch < n8v; ch += NCT) {
-        float e[8];
+        double ds = 0.0;
+        for (int ch = t; ch < n8v; ch += NCT) {
+            float e[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int tt = ch * 8 + j;
-            e[j] = tt < n_kv ? v_expf(__fsub_rn(s.sc[tt], M)) : 0.0f;     // masked: exp(-inf) = +0
+            for (int j = 0; j < 8; ++j) {
+                const int tt = ch * 8 + j;
+                e[j] = tt < n_kv ? v_expf(__fsub_rn(s.sc[tt], M)) : 0.0f;     // masked: exp(-inf) = +0
+            }
+            ds += (double) __fadd_rn(__fadd_rn(__fadd_rn(e[4], e[0]), __fadd_rn(e[6], e[2])),
+                                     __fadd_rn(__fadd_rn(e[5], e[1]), __fadd_rn(e[7], e[3])));
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (ch * 8 + j < n_kv) s.sc[ch * 8 + j] = e[j];
         }
-        ds += (double) __fadd_rn(__fadd_rn(__fadd_rn(e[4], e[0]), __fadd_rn(e[6], e[2])),
-                                 __fadd_rn(__fadd_rn(e[5], e[1]), __fadd_rn(e[7], e[3])));
+        if (t < 8 && n8 * 8 + t < n_kv) {                        // scalar tail: libm expf
+            const int tt = n8 * 8 + t;
+            const float e = tail_expf(__fsub_rn(s.sc[tt], M));
+            ds += (double) e;
+            s.sc[tt] = e;
+        }
+        ds = warp_sum_d(ds);
+        if (lane == 0) s.dred[warp] = ds;
+        cbar();
+        double S = 0.0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) if (ch * 8 + j < n_kv) s.sc[ch * 8 + j] = e[j];
+        for (int i = 0; i < NCW; ++i) S += s.dred[i];
+        const float inv = (float) (1.0 / S);
+        for (int tt = t; tt < n_kv; tt += NCT) s.ph[tt] = __float2half_rn(__fmul_rn(s.sc[tt], inv));
     }
-    if (t < 8 && n8 * 8 + t < n_kv) {                        // scalar tail: libm expf
-        const int tt = n8 * 8 + t;
-        const float e = tail_expf(__fsub_rn(s.sc[tt], M));
-        ds += (double) e;
-        s.sc[tt] = e;
-    }
-    ds = warp_sum_d(ds);
-    if (lane == 0) s.dred[warp] = ds;
-    cbar();
-    double S = 0.0;
-#pragma unroll
-    for (int i = 0; i < NCW; ++i) S += s.dred[i];
-    const float inv = (float) (1.0 / S);
-    for (int tt = t; tt < n_kv; tt += NCT) s.ph[tt] = __float2half_rn(__fmul_rn(s.sc[tt], inv));
-    }
-
-    // ---- P.V: warps 0..7 own 16 dims each, lane a = accumulator lane a (position % 32); the leftover
-    //      rows (positions np..n_kv-1) were staged into s.vt in stage 0 / the prologue
     cbar();
     PROF(54);
-    if (warp < 8) {
-        const int d0 = warp * 16;
-        float acc[16];
+
+    // ---- P.V (dot_f16(V^T_d, P) over positions): accumulator lane a = position % 32.  Warp w < 8 owns
+    //      accumulator lanes 4w..4w+3, its lane owns dims 4*lane..4*lane+3, so a row read is 256
+    //      contiguous bytes of the ring.  The 32 partial sums of a dim are folded in the oracle's order
+    //      through shared memory (the score buffer is free again); positions >= np are the
+    //      double-precision leftovers of ggml_vec_dot_f16 (vec.cpp:381-384), one thread per dim.
+    float acc[4][4];
 #pragma unroll
-        for (int e = 0; e < 16; ++e) acc[e] = 0.0f;
-        for (int tb = 0; tb < np; tb += 32) {
-            const int tt = tb + lane;
-            uint4 v0, v1;
-            if (tt == pos) {
-                v0 = *reinterpret_cast<const uint4 *>(s.vnew_h + d0);
-                v1 = *reinterpret_cast<const uint4 *>(s.vnew_h + d0 + 8);
-            } else {
-                v0 = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tt * HD + d0));
-                v1 = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t) tt * HD + d0 + 8));
-            }
-            const unsigned pu = (unsigned) __half_as_ushort(s.ph[tt]);
-            const unsigned p2 = pu | (pu << 16);
+    for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                acc[2 * e]         = fhfma_lo(u4_get(v0, e), p2, acc[2 * e]);
-                acc[2 * e + 1]     = fhfma_hi(u4_get(v0, e), p2, acc[2 * e + 1]);
-                acc[8 + 2 * e]     = fhfma_lo(u4_get(v1, e), p2, acc[8 + 2 * e]);
-                acc[8 + 2 * e + 1] = fhfma_hi(u4_get(v1, e), p2, acc[8 + 2 * e + 1]);
+        for (int k = 0; k < 4; ++k) acc[i][k] = 0.0f;
+    int s0_last = 0, rows_last = 0;
+    for (int c = 0; c < nck; ++c) {
+        const int s0 = ring_acquire(m, s, rg, wd_);
+        const int rows = min(KV_CH, pos - c * KV_CH);
+        if (warp < 8) {
+#pragma unroll
+            for (int gq = 0; gq < KV_CH / 32; ++gq) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int r = gq * 32 + 4 * warp + i;
+                    const int tt = c * KV_CH + r;
+                    if (r < rows && tt < np) {
+                        const uint2 vv = *reinterpret_cast<const uint2 *>(kv_row(s, s0, r) + lane * 8);
+                        const unsigned pu = (unsigned) __half_as_ushort(s.ph[tt]);
+                        const unsigned p2 = pu | (pu << 16);
+                        acc[i][0] = fhfma_lo(vv.x, p2, acc[i][0]); acc[i][1] = fhfma_hi(vv.x, p2, acc[i][1]);
+                        acc[i][2] = fhfma_lo(vv.y, p2, acc[i][2]); acc[i][3] = fhfma_hi(vv.y, p2, acc[i][3]);
+                    }
+                }
             }
         }
-        if (np > 0) {
-#pragma unroll
-            for (int e = 0; e < 16; ++e) {
-                const float r = reduce32_lanes(acc[e]);
-                if (lane == 0) s.o32[d0 + e] = r;
-            }
-            asm volatile("bar.sync 2, 256;" ::: "memory");    // warps 0..7: o32 complete before the tail below
-        }
+        if (c + 1 < nck) { cbar(); ring_release(s, rg, (rows + 7) >> 3); }
+        else { s0_last = s0; rows_last = rows; }             // the last slice also holds the leftover rows
     }
-    // leftovers: one thread per dim adds them sequentially in double like ggml_vec_dot_f16's scalar
-    // tail (vec.cpp:381-384)
+    if (np > 0) {
+        if (warp < 8) {
+            if (pos < np && ((pos & 31) >> 2) == warp) {     // the new token is the last step of its chain
+                const int i = pos & 3;
+                const uint2 vv = *reinterpret_cast<const uint2 *>(s.vnew_h + lane * 4);
+                const unsigned pu = (unsigned) __half_as_ushort(s.ph[pos]);
+                const unsigned p2 = pu | (pu << 16);
+#pragma unroll
+                for (int ii = 0; ii < 4; ++ii)
+                    if (ii == i) {
+                        acc[ii][0] = fhfma_lo(vv.x, p2, acc[ii][0]); acc[ii][1] = fhfma_hi(vv.x, p2, acc[ii][1]);
+                        acc[ii][2] = fhfma_lo(vv.y, p2, acc[ii][2]); acc[ii][3] = fhfma_hi(vv.y, p2, acc[ii][3]);
+                    }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                *reinterpret_cast<float4 *>(s.sc + (4 * warp + i) * HD + 4 * lane) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        }
+        cbar();
+    }
     if (t < HD) {
-        double sumf = np > 0 ? (double) s.o32[t] : 0.0;
-        for (int i = 0; i < nleft; ++i)
-            sumf += (double) __fmul_rn(__half2float(s.vt[i * HD + t]), __half2float(s.ph[np + i]));
+        double sumf = 0.0;
+        if (np > 0) {
+            float lq[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                lq[i] = __fadd_rn(__fadd_rn(s.sc[i * HD + t], s.sc[(16 + i) * HD + t]), __fadd_rn(s.sc[(8 + i) * HD + t], s.sc[(24 + i) * HD + t]));
+            const float t0 = __fadd_rn(lq[0], lq[4]), t1 = __fadd_rn(lq[1], lq[5]), t2 = __fadd_rn(lq[2], lq[6]), t3 = __fadd_rn(lq[3], lq[7]);
+            sumf = (double) __fadd_rn(__fadd_rn(t0, t1), __fadd_rn(t2, t3));
+        }
+        const int c_last = nck - 1;
+        for (int tt = np; tt < n_kv; ++tt) {
+            const __half vv = tt == pos ? s.vnew_h[t]
+                            : *reinterpret_cast<const __half *>(kv_row(s, s0_last, tt - c_last * KV_CH) + t * 2);
+            sumf += (double) __fmul_rn(__half2float(vv), __half2float(s.ph[tt]));
+        }
         pk_store(att + t, (float) sumf, ep_out);
     }
-    if (writer && (warp == 1 || warp == 2)) __threadfence();   // publish the appended K/V rows (see above)
+    if (nck > 0) { cbar(); ring_release(s, rg, (rows_last + 7) >> 3); }
+    if (writer && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }   // publish the appended K/V rows (see above)
 }
 
 // --------------------------------------------------------------------------- token selection
@@ -1071,7 +1086,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(5);
 
         // ---- phase B: per-head norm + RoPE + KV append + attention (CTA h owns head h)
-        if (attn_cta) attention_head(m, W, l, (int) blockIdx.x, pos, p.f32attn != 0, p.width, ar, e_qkv, e_att, s, w);
+        if (attn_cta) attention_head(m, W, l, (int) blockIdx.x, pos, p.f32attn != 0, p.width, ar, e_qkv, e_att, s, rg, w);
         PROF(6);
 
         // ---- phase C: attn_output mat-vec (input rounded to F16) + residual
@@ -1172,12 +1187,14 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
 // Walks the same pass / layer / slice order as run_stack and keeps the ring full.  s_go: -1 until
 // the compute warps know how many passes of the program will run (EOS / max_len), then that count.
 __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ passes, int n_passes,
-                              const Slices & z, Smem & s, volatile int * s_go) {
+                              const Slices & z, Smem & s, volatile int * s_go, int n_past0) {
     unsigned p_slot = 0, p_idx = 0;
     const int nA = z.a1 - z.a0, nO = z.o1 - z.o0, nP = z.p1 - z.p0, nD = z.d1 - z.d0;
     bool aborted = false;
     const long long t_start = clock64();
     unsigned pspins = 0;
+    int n_past = n_past0;
+    const bool attn_cta = (int) blockIdx.x < NH;
     for (int ip = 0; ip < n_passes && !aborted; ++ip) {
         int go = *s_go;
         while (go < 0 && ip > 0) {                                    // pass 0 is produced optimistically
@@ -1190,10 +1207,25 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
         if (xmode == XM_SELECT_ONLY) continue;
         const StackW & W = passes[ip].stack == 0 ? m.talker : m.cp;
         const int n_layers = passes[ip].n_layers, hd = passes[ip].head;
+        const int pos = passes[ip].pos >= 0 ? passes[ip].pos : n_past;
+        if (passes[ip].stack == 0 && passes[ip].pos < 0) ++n_past;
+        // attention CTAs: the K then V history of the head (rows 0..pos-1) follows the QKV slice, KV_CH rows per slice
+        const int n_kvs = (attn_cta && !passes[ip].f32attn) ? (pos + KV_CH - 1) / KV_CH : 0;
         for (int l = 0; l < n_layers && !aborted; ++l) {
-            for (int k = 0; k < 4; ++k) {
-                const void * src = k == 0 ? sl_a(W, l, z) : k == 1 ? sl_o(W, l, z) : k == 2 ? sl_gu(W, l, z) : sl_d(W, l, z);
-                const int n_slots = k == 0 ? nA : k == 1 ? nO * 2 : k == 2 ? nP * 2 : nD * 3;
+            for (int k = 0; k < 4 + 2 * n_kvs; ++k) {
+                const void * src; int n_slots, slot_bytes = W.wtype == Q3T_TYPE_Q8_0 ? SLOT_Q8 : SLOT_B, tail = SLOT_B;
+                if (k == 0) { src = sl_a(W, l, z); n_slots = nA; }
+                else if (k <= 2 * n_kvs) {
+                    const int c = (k - 1) % n_kvs;
+                    const int rows = min(KV_CH, pos - c * KV_CH);
+                    const __half * base = (k - 1 < n_kvs ? W.kcache : W.vcache)
+                                        + ((size_t) (l * NKV + ((int) blockIdx.x >> 1)) * W.n_ctx + (size_t) c * KV_CH) * HD;
+                    src = base; n_slots = (rows + 7) >> 3; slot_bytes = SLOT_B; tail = (rows - (n_slots - 1) * 8) * HD * 2;
+                } else {
+                    const int kk = k - 2 * n_kvs;
+                    src = kk == 1 ? sl_o(W, l, z) : kk == 2 ? sl_gu(W, l, z) : sl_d(W, l, z);
+                    n_slots = kk == 1 ? nO * 2 : kk == 2 ? nP * 2 : nD * 3;
+                }
                 // ring-space wait with an abort check (EOS decided while pass 0 is being produced)
                 while (true) {
                     const unsigned long long c = s.consumed;
@@ -1203,7 +1235,7 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
                     if (((++pspins) & 0xfff) == 0 && clock64() - t_start > 8000000000LL) { m.st->error = 1; aborted = true; break; }   // watchdog
                 }
                 if (aborted) break;
-                produce_slice(s, p_slot, p_idx, src, n_slots, W.wtype == Q3T_TYPE_Q8_0 ? SLOT_Q8 : SLOT_B);
+                produce_slice(s, p_slot, p_idx, src, n_slots, slot_bytes, tail);
             }
         }
         if (hd >= 0 && !aborted) {
@@ -1259,7 +1291,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
     cta_rows(H,     z.d0, z.d1);
 
     if (t >= NCT) {                                   // ---- producer warp: one thread drives the TMA unit
-        if (t == NCT) producer_loop(m, passes, n_passes, z, s, s_go);
+        if (t == NCT) producer_loop(m, passes, n_passes, z, s, s_go, gs.n_past);
         return;
     }
 
