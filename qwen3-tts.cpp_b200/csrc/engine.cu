@@ -114,6 +114,7 @@ extern "C" void q3t_ctx_destroy(q3t_ctx * ctx) {
     for (auto & kv : ctx->raw) cudaFree(kv.second.dev);
     ctx->raw.clear();
     for (auto & ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    if (ctx->h_done) cudaFreeHost(ctx->h_done);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -774,8 +775,8 @@ static int run_generate(q3t_ctx * ctx, int max_len, float rep_penalty, float tem
 
     // enqueue frames in batches; poll `done` one batch behind so the GPU never idles on the host
     const int BATCH = 32;
-    int * h_done = nullptr;
-    CK(cudaMallocHost(&h_done, 2 * sizeof(int)));
+    if (!ctx->h_done) CK(cudaMallocHost(&ctx->h_done, 2 * sizeof(int)));   // pinned once: page-locking per call stalls for 100s of ms now and then
+    int * h_done = ctx->h_done;
     h_done[0] = h_done[1] = 0;
     cudaEvent_t evs[2];
     cudaEventCreateWithFlags(&evs[0], cudaEventDisableTiming);
@@ -801,7 +802,6 @@ static int run_generate(q3t_ctx * ctx, int max_len, float rep_penalty, float tem
     GenState out;
     if (!rc) rc = cuda_check(ctx, cudaMemcpyAsync(&out, ctx->hm.st, sizeof(GenState), cudaMemcpyDeviceToHost, ctx->stream), "D2H state");
     if (!rc) rc = cuda_check(ctx, cudaStreamSynchronize(ctx->stream), "generate sync");
-    cudaFreeHost(h_done);
     if (rc) return rc;
     if (out.error) return set_err(ctx, Q3T_ERR_DEVICE, "device watchdog: a grid barrier timed out inside lm_kernel");
     float ms = 0.f;

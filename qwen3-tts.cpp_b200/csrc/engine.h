@@ -180,6 +180,7 @@ struct q3t_ctx {
     int last_n_frames = 0;
 
     q3t_timing timing{};
+    int * h_done = nullptr;           // pinned flag pair polled by the generate loop
     unsigned long long * d_prof = nullptr; unsigned int * d_prof_n = nullptr; int prof_cap = 0;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
 };
