@@ -41,6 +41,15 @@ CODEPRED_FRAME_BYTES = {"f16": 2_422_963_200, "q8_0": 1_317_043_200}
 KV_BYTES_PER_POS = 114_688
 
 
+def ncu_traffic(wtype: str):
+    """dram bytes per lm_kernel launch from the committed ncu --set full capture (None if not captured for this dtype)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "lm_kernel_traffic.json")))[wtype]
+        return int(t["dram_bytes_read"]) + int(t["dram_bytes_write"])
+    except Exception:
+        return None
+
+
 def n_samples(frames: int) -> int:
     return 1920 * frames - 555 if frames > 0 else 0
 
@@ -293,7 +302,7 @@ def run_ours(args, rank, world, local_rank):
             "gpu_launches": int(launches),
             "roofline": {"kernel": "lm_kernel (one launch = one frame: 16 code-predictor passes + 1 talker step)",
                          "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "peak_source": peak_kind, "traffic": None, "us_per_launch": frame_us,
+                         "peak_source": peak_kind, "traffic": ncu_traffic(args.wtype), "us_per_launch": frame_us,
                          "algorithmic_bytes_per_launch": int(frame_bytes)},
             "talker_step": {"us": us_step, "algorithmic_bytes": int(talker_bytes),
                             "achieved_gbs": talker_bytes / (us_step * 1e-6) / 1e9,
