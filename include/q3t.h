@@ -140,6 +140,15 @@ Q3T_API int  q3t_generate(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_
                           float repetition_penalty, float temperature, int32_t top_k, uint64_t seed,
                           int32_t * codes_out, int32_t * n_frames_out);
 
+/* Batched generate (extension; SURVEY.md §8b "batched variants take n_seq + per-seq arrays"): n_seq
+ * independent utterances, greedy, same semantics per utterance as q3t_generate with temperature 0
+ * (src/tts_transformer.cpp:2577-2851).  Sequences advance in lock-step, up to 8 per kernel launch;
+ * codes_out[i] int32[max_len*n_codebooks], n_frames_out[i] = frames of utterance i.
+ * speaker_embd may be null (no speaker for any utterance) or hold per-utterance pointers (null entries allowed). */
+Q3T_API int  q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * const * text_tokens, const int32_t * n_tokens,
+                                const float * const * speaker_embd, int32_t max_len, int32_t language_id,
+                                float repetition_penalty, int32_t * const * codes_out, int32_t * n_frames_out);
+
 /* AudioTokenizerDecoder::decode (src/audio_tokenizer_decoder.cpp:804-879):
  * codes int32[n_frames*16] frame-major -> samples f32; returns sample count
  * (1920*n_frames-555) or a negative status.  cap = capacity of samples_out in floats. */
@@ -209,6 +218,10 @@ Q3T_API int  q3t_tts_generate(q3t_tts * t, const int32_t * text_tokens, int32_t 
                               const float * speaker_embd, int32_t max_len,
                               int32_t * codes_out, int32_t * n_frames_out,
                               int32_t language_id, float repetition_penalty, float temperature, int32_t top_k);
+Q3T_API int  q3t_tts_generate_batch(q3t_tts * t, int32_t n, const int32_t * const * text_tokens, const int32_t * n_tokens,
+                                    const float * const * speaker_embd, int32_t max_len,
+                                    int32_t * const * codes_out, int32_t * n_frames_out,
+                                    int32_t language_id, float repetition_penalty);   /* extension: batched greedy generate */
 Q3T_API void q3t_tts_set_seed(q3t_tts * t, uint64_t seed);   /* extension: the reference has no seed API */
 Q3T_API int  q3t_tts_get_config(q3t_tts * t, q3t_tts_config * out);
 Q3T_API const char * q3t_tts_get_error(q3t_tts * t);

@@ -834,6 +834,148 @@ extern "C" int q3t_generate(q3t_ctx * ctx, const int32_t * text_tokens, int32_t 
     return Q3T_OK;
 }
 
+// ------------------------------------------------------------------------------ batched generate
+// n_seq independent utterances, greedy, in waves of Q3T_MAX_BATCH sequences that advance in lock-step
+// through lm_batch_kernel (lm_batch.inc).  Each sequence gets its own packet block, KV caches, state,
+// repetition set, trailing rows and code buffer; the prompt and the prefill of a sequence run through
+// the batch-1 path into those buffers (once per utterance, ~4 ms), then the frames are batched.
+struct BatchSeqBuf {
+    Pkt * pk = nullptr; float * hidden = nullptr, * logits = nullptr; unsigned char * seen = nullptr;
+    GenState * st = nullptr; int * codes = nullptr; float * trailing = nullptr;
+    __half * kv = nullptr;          // talker K then V
+    __half * ck = nullptr, * cv = nullptr; float * kf = nullptr, * vf = nullptr;
+    void release() {
+        cudaFree(pk); cudaFree(hidden); cudaFree(logits); cudaFree(seen); cudaFree(st); cudaFree(codes);
+        cudaFree(trailing); cudaFree(kv); cudaFree(ck); cudaFree(cv); cudaFree(kf); cudaFree(vf);
+        *this = BatchSeqBuf{};
+    }
+};
+
+static int rope_table(q3t_ctx * ctx, int n_rope, float ** out_dev) {
+    std::vector<float> tab((size_t) n_rope * HD);
+    const float theta_scale = powf(ctx->cfg.rope_theta, -2.0f / (float) HD);
+    for (int p = 0; p < n_rope; ++p) {
+        float theta = (float) p;
+        for (int i = 0; i < HD / 2; ++i) {
+            tab[(size_t) p * HD + i]          = cosf(theta);
+            tab[(size_t) p * HD + HD / 2 + i] = sinf(theta);
+            theta *= theta_scale;
+        }
+    }
+    CK(cudaMalloc(out_dev, tab.size() * sizeof(float)));
+    CK(cudaMemcpyAsync(*out_dev, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return Q3T_OK;
+}
+
+extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * const * text_tokens, const int32_t * n_tokens,
+                                  const float * const * speaker_embd, int32_t max_len, int32_t language_id,
+                                  float repetition_penalty, int32_t * const * codes_out, int32_t * n_frames_out) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (n_seq <= 0 || !text_tokens || !n_tokens || !codes_out || !n_frames_out) return set_err(ctx, Q3T_ERR_ARG, "null argument");
+    if (ctx->hm.talker.wtype != Q3T_TYPE_F16) return set_err(ctx, Q3T_ERR_STATE, "batched generation is wired up for F16 layer weights only");
+    for (int i = 0; i < n_seq; ++i) n_frames_out[i] = 0;
+    if (max_len <= 0) return Q3T_OK;
+    cudaSetDevice(ctx->device);
+    const q3t_tts_config & c = ctx->cfg;
+    const int L = c.n_layers, L2 = c.code_pred_layers;
+    const DevModel saved = ctx->hm;
+    int rc = Q3T_OK;
+    const int n_ctx = 16 + max_len + 8;                              // prefill is <= 10 rows (src/tts_transformer.cpp:2630)
+    float * rope = nullptr;
+    if ((rc = rope_table(ctx, std::max(n_ctx, 16), &rope))) return rc;
+    BatchSeqBuf buf[Q3T_MAX_BATCH];
+    DevModel views[Q3T_MAX_BATCH];
+    const size_t per = (size_t) L * NKV * n_ctx * HD;
+    float ms_frames = 0.f, ms_prefill = 0.f;
+    auto fail = [&](int code) { for (auto & b : buf) b.release(); cudaFree(rope); ctx->hm = saved; return code; };
+
+    for (int w0 = 0; w0 < n_seq && !rc; w0 += Q3T_MAX_BATCH) {
+        const int nb = std::min(Q3T_MAX_BATCH, n_seq - w0);
+        cudaEventRecord(ctx->ev[0], ctx->stream);
+        for (int q = 0; q < nb && !rc; ++q) {
+            BatchSeqBuf & b = buf[q];
+            if (!b.pk) {
+                bool ok = cudaMalloc(&b.pk, PKT_TOTAL * sizeof(Pkt)) == cudaSuccess && cudaMalloc(&b.hidden, H * 4) == cudaSuccess &&
+                          cudaMalloc(&b.logits, 3072 * 4) == cudaSuccess && cudaMalloc(&b.seen, 4096) == cudaSuccess &&
+                          cudaMalloc(&b.st, sizeof(GenState)) == cudaSuccess && cudaMalloc(&b.codes, (size_t) max_len * NCB * 4) == cudaSuccess &&
+                          cudaMalloc(&b.trailing, (size_t) 4096 * H * 4) == cudaSuccess && cudaMalloc(&b.kv, per * 2 * sizeof(__half)) == cudaSuccess &&
+                          cudaMalloc(&b.ck, (size_t) L2 * NKV * 16 * HD * 2) == cudaSuccess && cudaMalloc(&b.cv, (size_t) L2 * NKV * 16 * HD * 2) == cudaSuccess &&
+                          cudaMalloc(&b.kf, (size_t) L2 * 2 * NKV * HD * 4) == cudaSuccess && cudaMalloc(&b.vf, (size_t) L2 * 2 * NKV * HD * 4) == cudaSuccess;
+                if (!ok) return fail(set_err(ctx, Q3T_ERR_CUDA, "cudaMalloc failed (batch buffers)"));
+            }
+            const int i = w0 + q;
+            if ((rc = q3t_stage_prompt(ctx, text_tokens[i], n_tokens[i], speaker_embd ? speaker_embd[i] : nullptr, language_id))) break;
+            const int M = ctx->staged_prefill_len, TL = ctx->staged_trailing_len;
+            if (M > 16 || TL > 4096) { rc = set_err(ctx, Q3T_ERR_ARG, "prompt too long for the batched path"); break; }
+            cudaMemcpyAsync(b.trailing, ctx->d_trailing, (size_t) TL * H * 4, cudaMemcpyDeviceToDevice, ctx->stream);
+            cudaMemsetAsync(b.kv, 0, per * 2 * sizeof(__half), ctx->stream);
+            cudaMemsetAsync(b.ck, 0, (size_t) L2 * NKV * 16 * HD * 2, ctx->stream);
+            cudaMemsetAsync(b.cv, 0, (size_t) L2 * NKV * 16 * HD * 2, ctx->stream);
+            // view of the model for this sequence
+            DevModel & m = ctx->hm;
+            m = saved;
+            m.x_qkv = b.pk; m.x_att = m.x_qkv + QKV_N; m.x_x1 = m.x_att + NH * HD; m.x_m = m.x_x1 + H; m.x_x = m.x_m + FFN;
+            m.x_logit = m.x_x + H; m.x_cand = m.x_logit + 3072;
+            m.hidden = b.hidden; m.logits = b.logits; m.seen = b.seen; m.st = b.st; m.codes_out = b.codes;
+            m.trailing = b.trailing; m.pad_embed = ctx->d_pad;
+            m.talker.kcache = b.kv; m.talker.vcache = b.kv + per; m.talker.kf32 = nullptr; m.talker.vf32 = nullptr; m.talker.n_ctx = n_ctx;
+            m.cp.kcache = b.ck; m.cp.vcache = b.cv; m.cp.kf32 = b.kf; m.cp.vf32 = b.vf; m.cp.n_ctx = 16;
+            m.rope = rope; m.n_rope_pos = std::max(n_ctx, 16);
+            m.prof = nullptr; m.prof_n = nullptr; m.prof_cap = 0;
+            GenState st = default_state(ctx);
+            st.max_len = max_len; st.n_past = M; st.trailing_len = TL;
+            st.rep_penalty = repetition_penalty; st.temperature = 0.0f; st.top_k = 0; st.seed = 0;
+            if ((rc = reset_state(ctx, st, true))) break;
+            const int saved_nctx = ctx->n_ctx;
+            ctx->n_ctx = n_ctx;                                     // run_talker_rows checks the context bound
+            rc = run_talker_rows(ctx, ctx->d_prefill, M, 0, false, 1, nullptr);
+            ctx->n_ctx = saved_nctx;
+            views[q] = m;
+        }
+        ctx->hm = saved;
+        if (rc) break;
+        cudaEventRecord(ctx->ev[1], ctx->stream);
+
+        std::vector<PassDesc> v;
+        append_codepred(ctx, v, XM_HIDDEN, nullptr);
+        v.push_back(make_pass(0, XM_TALKER_NEXT, 0, -1, 0, 0, L, 1));
+        if ((rc = upload_passes(ctx, v))) break;
+        // frames: every launch advances all live sequences by one frame; poll `done` every 32 launches
+        std::vector<GenState> hst(nb);
+        int launched = 0;
+        bool all_done = false;
+        while (launched < max_len && !all_done && !rc) {
+            const int n = std::min(32, max_len - launched);
+            for (int k = 0; k < n && !rc; ++k) rc = lm_launch_batch(ctx, views, nb, ctx->d_passes, (int) v.size());
+            launched += n;
+            if (rc) break;
+            for (int q = 0; q < nb; ++q) cudaMemcpyAsync(&hst[q], buf[q].st, sizeof(GenState), cudaMemcpyDeviceToHost, ctx->stream);
+            if ((rc = cuda_check(ctx, cudaStreamSynchronize(ctx->stream), "batch sync"))) break;
+            all_done = true;
+            for (int q = 0; q < nb; ++q) {
+                if (hst[q].error) rc = set_err(ctx, Q3T_ERR_DEVICE, "device watchdog: an exchange timed out inside lm_batch_kernel");
+                all_done = all_done && hst[q].done;
+            }
+        }
+        if (rc) break;
+        cudaEventRecord(ctx->ev[2], ctx->stream);
+        for (int q = 0; q < nb; ++q) {
+            const int nf = hst[q].frame;
+            n_frames_out[w0 + q] = nf;
+            if (nf > 0 && codes_out[w0 + q])
+                cudaMemcpyAsync(codes_out[w0 + q], buf[q].codes, (size_t) nf * NCB * 4, cudaMemcpyDeviceToHost, ctx->stream);
+        }
+        if ((rc = cuda_check(ctx, cudaStreamSynchronize(ctx->stream), "batch sync"))) break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ms_prefill += ms;
+        cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); ms_frames += ms;
+    }
+    ctx->timing.prefill_ms = ms_prefill; ctx->timing.frames_ms = ms_frames;
+    return fail(rc);
+}
+
 extern "C" int q3t_run_staged(q3t_ctx * ctx, int32_t max_len, float repetition_penalty, float temperature, int32_t top_k,
                               uint64_t seed, int32_t with_vocoder, int32_t * n_frames_out, int64_t * n_samples_out) {
     if (!ctx) return Q3T_ERR_ARG;

@@ -123,6 +123,7 @@ struct DevModel {
 };
 
 constexpr int LM_THREADS = 384;       // 11 compute warps + 1 producer warp; 168 registers per thread
+constexpr int Q3T_MAX_BATCH = 8;    // sequences per batched frame launch (lm_batch.inc)
 constexpr int LM_MAXC    = 18;       // max KV chunks per kv-head in the attention phase
 constexpr int LM_MIN_GRID = 140;
 constexpr int LM_ATT_MAX_KV = 4608;  // KV positions the attention phase supports (P kept in shared memory)
@@ -191,6 +192,7 @@ int  set_err(q3t_ctx * ctx, int code, const std::string & msg);
 int  cuda_check(q3t_ctx * ctx, cudaError_t e, const char * what);
 int  lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int frame_mode);
 int  lm_max_grid(q3t_ctx * ctx);
+int  lm_launch_batch(q3t_ctx * ctx, const DevModel * seqs, int nb, const PassDesc * passes_dev, int n_passes);
 int  prompt_build(q3t_ctx * ctx, const int32_t * tokens_dev, int n_tokens, const float * spk_dev,
                   int language_id, float * prefill_dev, int * prefill_len, float * trailing_dev,
                   int * trailing_len, float * pad_dev);

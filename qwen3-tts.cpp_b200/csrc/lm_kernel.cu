@@ -46,6 +46,7 @@ constexpr int NMB        = 8;                          // mbarriers cycling over
 constexpr int ATT_MAX_KV = LM_ATT_MAX_KV;              // positions the attention phase can hold
 
 struct __align__(128) Smem {
+    static constexpr int NSLOTS = NSLOT;
     unsigned char ring[NSLOT * SLOT_B];
     float  xres[H];                // residual stream of the current token (x, then x1)
     float  xf[FFN];                // F32 GEMV input (ffn_down) / scratch
@@ -95,7 +96,7 @@ __device__ __forceinline__ void cbar() { asm volatile("bar.sync 1, %0;" :: "n"(N
 // An activation travels as {float value, u32 epoch} in one aligned 8-byte word: an 8-byte store is
 // single-copy atomic, so a reader that sees the expected epoch also sees the value.  Every exchange
 // point of the program has its own epoch (a counter that advances identically in every CTA).
-struct Watch { long long t0; bool dead; };
+struct Watch { long long t0; bool dead; int * err; };   // err: the launch's device error flag (GenState::error)
 
 __device__ __forceinline__ void pk_store(Pkt * p, float v, unsigned ep) {
     // gpu-scope relaxed (SASS .STRONG.GPU): `volatile` would be system scope, which is far slower
@@ -109,8 +110,8 @@ __device__ __forceinline__ void spin_cycles(int n) {
 }
 __device__ __forceinline__ bool pk_give_up(const DevModel & m, Watch & w, unsigned & spins) {
     if (((++spins) & 0x3ff) != 0) return false;
-    if (*reinterpret_cast<volatile int *>(&m.st->error)) { w.dead = true; return true; }
-    if (clock64() - w.t0 > 6000000000LL) { m.st->error = 1; w.dead = true; return true; }   // ~3 s: a CTA died
+    if (*reinterpret_cast<volatile int *>(w.err)) { w.dead = true; return true; }
+    if (clock64() - w.t0 > 6000000000LL) { *w.err = 1; w.dead = true; return true; }   // ~3 s: a CTA died
     return false;
 }
 __device__ __forceinline__ float pk_poll(const DevModel & m, const Pkt * p, unsigned ep, Watch & w) {
@@ -232,7 +233,8 @@ __device__ __forceinline__ bool mbar_try(unsigned long long * bar, uint32_t pari
     return ok != 0;
 }
 // wait for the next slice; returns its first ring slot (wrapped)
-__device__ __forceinline__ int ring_acquire(const DevModel & m, Smem & s, const Ring & rg, Watch & w) {
+template <class SM>
+__device__ __forceinline__ int ring_acquire(const DevModel & m, SM & s, const Ring & rg, Watch & w) {
     unsigned long long * bar = &s.mbar[rg.slice_idx % NMB];
     const uint32_t parity = (rg.slice_idx / NMB) & 1u;
     unsigned spins = 0;
@@ -245,10 +247,11 @@ __device__ __forceinline__ int ring_acquire(const DevModel & m, Smem & s, const 
         }
     }
     __syncwarp();
-    return (int) (rg.slot_head % NSLOT);
+    return (int) (rg.slot_head % SM::NSLOTS);
 }
 // all compute threads are past their last read of the slice (call after a cbar())
-__device__ __forceinline__ void ring_release(Smem & s, Ring & rg, int n_slots) {
+template <class SM>
+__device__ __forceinline__ void ring_release(SM & s, Ring & rg, int n_slots) {
     rg.slot_head += (unsigned) n_slots;
     rg.slice_idx += 1u;
     if (threadIdx.x == 0) {
@@ -258,18 +261,19 @@ __device__ __forceinline__ void ring_release(Smem & s, Ring & rg, int n_slots) {
 }
 
 // producer: one slice = `n_slots` ring slots filled from `src` (contiguous in HBM); <= 2 bulk copies
-__device__ __forceinline__ void produce_slice(Smem & s, unsigned & p_slot, unsigned & p_idx, const void * src, int n_slots,
+template <class SM>
+__device__ __forceinline__ void produce_slice(SM & s, unsigned & p_slot, unsigned & p_idx, const void * src, int n_slots,
                                               int slot_bytes = SLOT_B, int tail_bytes = SLOT_B) {
     if (n_slots <= 0) return;
     // wait for ring space and for the mbarrier of slice (p_idx - NMB) to be drained by the consumers
     while (true) {
         const unsigned long long c = s.consumed;
         const unsigned c_slot = (unsigned) c, c_idx = (unsigned) (c >> 32);
-        if (p_slot + (unsigned) n_slots - c_slot <= (unsigned) NSLOT && p_idx - c_idx < (unsigned) NMB) break;
+        if (p_slot + (unsigned) n_slots - c_slot <= (unsigned) SM::NSLOTS && p_idx - c_idx < (unsigned) NMB) break;
     }
     unsigned long long * bar = &s.mbar[p_idx % NMB];
-    const int w0 = (int) (p_slot % NSLOT);
-    const int n0 = min(n_slots, NSLOT - w0);
+    const int w0 = (int) (p_slot % SM::NSLOTS);
+    const int n0 = min(n_slots, SM::NSLOTS - w0);
     // order the consumers' generic-proxy reads of the recycled slots before the async-proxy writes
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     if (slot_bytes == SLOT_B) {
@@ -283,7 +287,7 @@ __device__ __forceinline__ void produce_slice(Smem & s, unsigned & p_slot, unsig
         mbar_expect_tx(bar, (uint32_t) n_slots * (uint32_t) slot_bytes);
         // compact records in HBM (pitch slot_bytes) land at the start of 2 KB ring slots: one copy per slot
         for (int i = 0; i < n_slots; ++i) {
-            int slot = w0 + i; if (slot >= NSLOT) slot -= NSLOT;
+            int slot = w0 + i; if (slot >= SM::NSLOTS) slot -= SM::NSLOTS;
             tma_load_1d(s.ring + (size_t) slot * SLOT_B, (const unsigned char *) src + (size_t) i * slot_bytes, (uint32_t) slot_bytes, bar);
         }
     }
@@ -562,14 +566,16 @@ struct AttnRegs {          // per-lane parameters fetched ahead of use (warps 0 
 __device__ __forceinline__ uint2 ld_cg_u2(const void * p) { return __ldcg(reinterpret_cast<const uint2 *>(p)); }
 
 // address of history row r (0..KV_CH) of a K/V slice that starts at ring slot s0
-__device__ __forceinline__ const unsigned char * kv_row(const Smem & s, int s0, int r) {
+template <class SM>
+__device__ __forceinline__ const unsigned char * kv_row(const SM & s, int s0, int r) {
     int slot = s0 + (r >> 3);
-    if (slot >= NSLOT) slot -= NSLOT;
+    if (slot >= SM::NSLOTS) slot -= SM::NSLOTS;
     return s.ring + (size_t) slot * SLOT_B + (r & 7) * (HD * 2);
 }
 
+template <class SM>
 __device__ void attention_head(const DevModel & m, const StackW & W, int l, int h, int pos, bool f32attn, int width,
-                               const AttnRegs & ar, unsigned ep_in, unsigned ep_out, Smem & s, Ring & rg, Watch & wd_) {
+                               const AttnRegs & ar, unsigned ep_in, unsigned ep_out, SM & s, Ring & rg, Watch & wd_) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int g = h >> 1;
     const bool writer = (h & 1) == 0;
@@ -996,7 +1002,8 @@ __device__ __noinline__ int select_sample(const DevModel & m, Smem & s, unsigned
 
 // the compute warps have just finished an exchange: the SM's return path is idle, a good moment for the
 // producer to start its next bulk copy (keeps the weight stream from delaying the latency-critical polls)
-__device__ __forceinline__ void token(Smem & s) { if (threadIdx.x == 0) s.tokens = s.tokens + 1u; }
+template <class SM>
+__device__ __forceinline__ void token(SM & s) { if (threadIdx.x == 0) s.tokens = s.tokens + 1u; }
 
 // ------------------------------------------------------------------------------- one pass (compute warps)
 struct PassRegs {          // parameters fetched ahead of use; carried across layers and passes
@@ -1296,7 +1303,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
     }
 
     // ---- compute warps
-    Watch w; w.t0 = clock64(); w.dead = false;
+    Watch w; w.t0 = clock64(); w.dead = false; w.err = &m.st->error;
     Ring rg; rg.slot_head = 0; rg.slice_idx = 0;
     unsigned ep = gs.ep_base;
     unsigned pending_ep = gs.pending_ep;
@@ -1398,6 +1405,8 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
     }
 }
 
+#include "lm_batch.inc"
+
 // --------------------------------------------------------------------------- host launch
 int lm_max_grid(q3t_ctx * ctx) {
     static bool attr_set = false;
@@ -1431,6 +1440,38 @@ int lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int fram
                                                 dim3(ctx->grid), dim3(LM_THREADS), args, sizeof(Smem), ctx->stream);
     ctx->timing.kernel_launches++;
     return cuda_check(ctx, e, "lm_kernel launch");
+}
+
+// batched frame launch: nb sequences (views in `seqs`), instantiation = smallest NB >= nb
+template <int NB>
+static cudaError_t launch_batch_t(q3t_ctx * ctx, const BatchModel & bm, const PassDesc * passes_dev, int n_passes) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(lm_batch_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(BSmem<NB>));
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    void * args[] = { (void *) &bm, (void *) &passes_dev, (void *) &n_passes };
+    return cudaLaunchCooperativeKernel((const void *) lm_batch_kernel<NB>, dim3(ctx->grid), dim3(LM_THREADS), args,
+                                       sizeof(BSmem<NB>), ctx->stream);
+}
+
+int lm_launch_batch(q3t_ctx * ctx, const DevModel * seqs, int nb, const PassDesc * passes_dev, int n_passes) {
+    if (nb < 1 || nb > Q3T_MAX_BATCH) return set_err(ctx, Q3T_ERR_ARG, "batch size out of range");
+    if (ctx->grid <= 0) {
+        const int g = lm_max_grid(ctx);
+        if (g < LM_MIN_GRID) return set_err(ctx, Q3T_ERR_CUDA, "device cannot co-schedule the persistent decode kernel (needs >= 140 SMs)");
+        ctx->grid = g > 480 ? 480 : g;
+    }
+    if (NH * nb > ctx->grid) return set_err(ctx, Q3T_ERR_ARG, "batch needs one CTA per (sequence, head) attention unit");
+    BatchModel bm;
+    bm.nb = nb;
+    for (int q = 0; q < Q3T_MAX_BATCH; ++q) bm.seq[q] = seqs[q < nb ? q : 0];
+    cudaError_t e = nb <= 2 ? launch_batch_t<2>(ctx, bm, passes_dev, n_passes)
+                  : nb <= 4 ? launch_batch_t<4>(ctx, bm, passes_dev, n_passes)
+                            : launch_batch_t<8>(ctx, bm, passes_dev, n_passes);
+    ctx->timing.kernel_launches++;
+    return cuda_check(ctx, e, "lm_batch_kernel launch");
 }
 
 } // namespace q3t

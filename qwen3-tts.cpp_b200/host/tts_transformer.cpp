@@ -224,6 +224,38 @@ bool TTSTransformer::generate(const int32_t * text_tokens, int32_t n_tokens, con
     return true;
 }
 
+bool TTSTransformer::generate_batch(const std::vector<const int32_t *> & text_tokens, const std::vector<int32_t> & n_tokens,
+                                    const std::vector<const float *> & speaker_embd, int32_t max_len,
+                                    std::vector<std::vector<int32_t>> & outputs, int32_t language_id, float repetition_penalty) {
+    const auto t0 = std::chrono::high_resolution_clock::now();
+    if (!loaded_) { error_msg_ = "Model not loaded"; return false; }
+    const size_t n = text_tokens.size();
+    if (n == 0 || n_tokens.size() != n || (!speaker_embd.empty() && speaker_embd.size() != n)) { error_msg_ = "batch arrays disagree"; return false; }
+    for (size_t i = 0; i < n; ++i) {
+        if (!text_tokens[i]) { error_msg_ = "text_tokens is null"; return false; }
+        if (n_tokens[i] < 4) { error_msg_ = "Need at least 4 text tokens for generation"; return false; }
+    }
+    outputs.assign(n, {});
+    if (max_len <= 0) return true;
+    std::vector<int32_t *> outp(n);
+    std::vector<int32_t> nf(n, 0);
+    for (size_t i = 0; i < n; ++i) { outputs[i].resize((size_t) max_len * config_.n_codebooks); outp[i] = outputs[i].data(); }
+    if (fail(q3t_generate_batch(engine_, (int32_t) n, text_tokens.data(), n_tokens.data(),
+                                speaker_embd.empty() ? nullptr : speaker_embd.data(), max_len, language_id,
+                                repetition_penalty, outp.data(), nf.data()))) {
+        outputs.assign(n, {});
+        return false;
+    }
+    for (size_t i = 0; i < n; ++i) outputs[i].resize((size_t) nf[i] * config_.n_codebooks);
+    q3t_timing tm{};
+    q3t_get_timing(engine_, &tm);
+    timing_.t_prefill_forward_ms = tm.prefill_ms;
+    timing_.t_talker_forward_ms = tm.frames_ms;
+    timing_.kernel_launches = tm.kernel_launches;
+    timing_.t_generate_total_ms = std::chrono::duration<double, std::milli>(std::chrono::high_resolution_clock::now() - t0).count();
+    return true;
+}
+
 bool TTSTransformer::forward(const int32_t * tokens, int32_t n_tokens, int32_t n_past, std::vector<float> & output) {
     return forward_text(tokens, n_tokens, nullptr, n_past, output);
 }

@@ -107,6 +107,12 @@ public:
                             std::vector<float> & output);
 
     // ---- extensions (not in the reference) --------------------------------------------------
+    // n independent utterances, greedy, batched on the device (up to 8 sequences per kernel launch);
+    // outputs[i] receives what generate(..., temperature = 0) returns for utterance i
+    bool generate_batch(const std::vector<const int32_t *> & text_tokens, const std::vector<int32_t> & n_tokens,
+                        const std::vector<const float *> & speaker_embd, int32_t max_len,
+                        std::vector<std::vector<int32_t>> & outputs,
+                        int32_t language_id = 2050, float repetition_penalty = 1.05f);
     void set_seed(uint64_t seed) { seed_ = seed; }        // the reference's rng_ cannot be seeded
     q3t_ctx * engine() const { return engine_; }
     const tts_timing & last_timing() const { return timing_; }
