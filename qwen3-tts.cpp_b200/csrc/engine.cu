@@ -923,7 +923,6 @@ extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * 
             m.talker.kcache = b.kv; m.talker.vcache = b.kv + per; m.talker.kf32 = nullptr; m.talker.vf32 = nullptr; m.talker.n_ctx = n_ctx;
             m.cp.kcache = b.ck; m.cp.vcache = b.cv; m.cp.kf32 = b.kf; m.cp.vf32 = b.vf; m.cp.n_ctx = 16;
             m.rope = rope; m.n_rope_pos = std::max(n_ctx, 16);
-            m.prof = nullptr; m.prof_n = nullptr; m.prof_cap = 0;
             GenState st = default_state(ctx);
             st.max_len = max_len; st.n_past = M; st.trailing_len = TL;
             st.rep_penalty = repetition_penalty; st.temperature = 0.0f; st.top_k = 0; st.seed = 0;

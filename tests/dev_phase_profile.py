@@ -14,11 +14,18 @@ t = m.TTSTransformer()
 assert t.load_model(models("full", "f16")[0]), t.get_error()
 rng = np.random.default_rng(2024)
 spk = (rng.standard_normal(1024) * 0.05).astype(np.float32)
-t.stage_prompt(HELLO_FULL, spk)
-t.run_staged(frames, with_vocoder=False)            # warm
-t.stage_prompt(HELLO_FULL, spk)
-t.profile_arm(frames // 2, 4096)
-t.run_staged(frames, with_vocoder=False)
+nbatch = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+if nbatch:
+    utts = [(HELLO_FULL, (rng.standard_normal(1024) * 0.05).astype(np.float32)) for _ in range(nbatch)]
+    t.generate_batch(utts, frames)
+    t.profile_arm(-1, 4096)
+    t.generate_batch(utts, frames)
+else:
+    t.stage_prompt(HELLO_FULL, spk)
+    t.run_staged(frames, with_vocoder=False)            # warm
+    t.stage_prompt(HELLO_FULL, spk)
+    t.profile_arm(frames // 2, 4096)
+    t.run_staged(frames, with_vocoder=False)
 print("frames_ms", t.timing().frames_ms, "ms/frame", t.timing().frames_ms / frames)
 names = {1: "layer start", 2: "x polled", 3: "rmsnormA done", 4: "sliceA ready", 5: "gemvA+store", 6: "attention done",
          7: "att polled", 8: "sliceO ready", 9: "gemvC+store", 10: "x1 polled", 11: "rmsnormD done", 12: "sliceGU ready",
