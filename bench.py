@@ -335,15 +335,27 @@ def run_sharded_workload(args, rank, world, local_rank, t, d, have_voc, dist, sy
         wav = d.decode(codes) if have_voc else np.zeros(n_samples(len(codes)), np.float32)
         return codes, wav
 
+    def synth_batch(mine):
+        lens = {u.max_len for u in mine}
+        if len(lens) != 1:
+            raise SystemExit("config 4 uses one max_len for all utterances")
+        codes = t.generate_batch([(u.tokens, u.spk) for u in mine], mine[0].max_len, repetition_penalty=1.05)
+        if codes is None:
+            raise SystemExit("generate_batch: " + t.get_error())
+        return [(c, d.decode(c) if have_voc else np.zeros(n_samples(len(c)), np.float32)) for c in codes]
+
+    batched = not args.no_batch
+    run = (lambda: disp.run_sharded(utts, None, rank, world, dist, synth_batch=synth_batch)) if batched else \
+          (lambda: disp.run_sharded(utts, synth, rank, world, dist))
     for _ in range(max(1, min(args.warmup, 1))):
-        disp.run_sharded(utts, synth, rank, world, dist)
+        run()
     sampler = ClockSampler(local_rank)
     launches0 = t.timing().kernel_launches
     sync_all()
     sampler.start()
     w0 = time.perf_counter()
     for _ in range(args.steps):
-        local, merged = disp.run_sharded(utts, synth, rank, world, dist)
+        local, merged = run()
     sync_all()
     step_s = (time.perf_counter() - w0) / args.steps
     clocks = sampler.stop()
@@ -360,7 +372,7 @@ def run_sharded_workload(args, rank, world, local_rank, t, d, have_voc, dist, sy
             "warmup": 1, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f16", "data": "synthetic (seeded random-init GGUF of the real 0.6B shapes)",
             "config": {"workload": f"config 4: {args.utterances} utterances (8-64 byte texts, seed 4), greedy, {args.frames} frames each + vocoder, "
-                                   f"utterance i -> rank i mod {world}, one utterance at a time per GPU (batch-1 engine)",
+                                   f"utterance i -> rank i mod {world}, " + ("8 sequences in lock-step per kernel launch on each GPU (lm_batch_kernel)" if batched else "one utterance at a time per GPU (batch-1 engine)"),
                        "utterances": args.utterances, "frames": args.frames, "parallelism": f"request-parallel x{world} (no collective)",
                        "l2": "weights streamed per frame (3.3 GB) exceed the 126 MB L2; no explicit flush"},
             "e2e": {"value": audio_s / step_s, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
@@ -382,6 +394,7 @@ def main():
     ap.add_argument("--wtype", default="f16", choices=["f16", "q8_0"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-vocoder", action="store_true", help="debug only: codes without the waveform (not a valid bench value)")
+    ap.add_argument("--no-batch", action="store_true", help="config 4 through the batch-1 engine, one utterance at a time")
     ap.add_argument("--utterances", type=int, default=0,
                     help="config 4: this many independent utterances (8-64 byte texts) per step, dealt i mod G to the ranks; "
                          "0 = the default config-2 workload (one utterance per rank per step)")

@@ -52,16 +52,25 @@ def make_workload(n_utt: int, seed: int = 4, max_len: int = 320) -> List[Utteran
     return out
 
 
-def run_sharded(utts: Sequence[Utterance], synth: Callable, rank: int = 0, world: int = 1, dist=None):
+def run_sharded(utts: Sequence[Utterance], synth: Optional[Callable], rank: int = 0, world: int = 1, dist=None,
+                synth_batch: Optional[Callable] = None):
     """Synthesise this rank's share; gather {uid: (n_frames, n_samples, checksum)} on rank 0.
 
+    `synth(tokens, spk, max_len) -> (codes, wav)` handles one utterance at a time;
+    `synth_batch([Utterance, ...]) -> [(codes, wav), ...]` (preferred when given) hands the rank's whole
+    share to the engine at once so it can batch the sequences on the device (lm_batch_kernel).
     Returns (local_results, gathered) where gathered is None on ranks != 0.  The per-utterance
     checksum (sum of codes) lets rank 0 verify that every utterance was produced exactly once.
     """
     local = {}
-    for i in my_share(utts, rank, world):
-        u = utts[i]
-        codes, wav = synth(u.tokens, u.spk, u.max_len)
+    mine = [utts[i] for i in my_share(utts, rank, world)]
+    if synth_batch is not None and mine:
+        outs = synth_batch(mine)
+        if len(outs) != len(mine):
+            raise RuntimeError("synth_batch returned a different number of results")
+    else:
+        outs = [synth(u.tokens, u.spk, u.max_len) for u in mine]
+    for u, (codes, wav) in zip(mine, outs):
         local[u.uid] = (int(codes.shape[0]), int(len(wav)), int(np.asarray(codes, np.int64).sum()))
     if dist is None or world == 1:
         return local, dict(local)

@@ -46,6 +46,25 @@ def test_single_rank_runs_everything():
     assert sorted(merged) == list(range(7)) and merged == local
 
 
+def test_batched_hand_over_gives_the_same_summaries():
+    """synth_batch receives the rank's whole share at once (the engine batches it on the device)."""
+    d = _load_dispatch()
+    utts = d.make_workload(7, seed=2, max_len=4)
+    seen = []
+
+    def fake_batch(mine):
+        seen.append([u.uid for u in mine])
+        return [_fake_synth(u.tokens, u.spk, u.max_len) for u in mine]
+
+    _, one = d.run_sharded(utts, _fake_synth)
+    _, bat = d.run_sharded(utts, None, synth_batch=fake_batch)
+    assert bat == one and seen == [list(range(7))]
+    _, part = d.run_sharded(utts, None, 1, 2, None, synth_batch=fake_batch)        # rank 1 of 2, no gather
+    assert seen[-1] == [1, 3, 5] and sorted(part) == [1, 3, 5]
+    with pytest.raises(RuntimeError):
+        d.run_sharded(utts, None, synth_batch=lambda mine: [])
+
+
 def _worker(rank, world, port, q):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
