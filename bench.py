@@ -310,6 +310,8 @@ def run_ours(args, rank, world, local_rank):
             "realtime_factor_per_gpu": audio_s / step_s,
             "clocks": clocks,
         }
+        if world == 1 and not args.no_batch:
+            out["batch64"] = batch64_line(args, t, d, have_voc)
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_baseline(args)
             if cb:
@@ -318,6 +320,37 @@ def run_ours(args, rank, world, local_rank):
     if dist:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def batch64_line(args, t, d, have_voc):
+    """BASELINE.json's second metric point: audio-s per wall-s with 64 concurrent utterances on this GPU
+    (config 4 on one GPU): generate_batch advances 8 sequences in lock-step per launch (lm_batch_kernel),
+    the vocoder then decodes each utterance.  Host buffers in, host buffers out, wall clock."""
+    import importlib
+    import torch
+    disp = importlib.import_module("q3t_b200.dispatch")
+    utts = disp.make_workload(64, seed=4, max_len=args.frames)
+    pairs = [(u.tokens, u.spk) for u in utts]
+    if t.generate_batch(pairs[:8], 8) is None:                      # warm-up (instantiation, buffers)
+        return {"error": t.get_error()}
+    torch.cuda.synchronize()
+    w0 = time.perf_counter()
+    codes = t.generate_batch(pairs, args.frames, repetition_penalty=1.05)
+    if codes is None:
+        return {"error": t.get_error()}
+    tm = t.timing()
+    w1 = time.perf_counter()
+    ns = 0
+    for c in codes:
+        wav = d.decode(c) if have_voc else np.zeros(n_samples(len(c)), np.float32)
+        ns += len(wav)
+    torch.cuda.synchronize()
+    w2 = time.perf_counter()
+    nf = sum(len(c) for c in codes)
+    return {"utterances": 64, "frames_each": args.frames, "sequences_per_launch": 8, "value": ns / 24000.0 / (w2 - w0), "unit": UNIT,
+            "generate_s": w1 - w0, "vocoder_s": w2 - w1, "ms_per_batched_frame": tm.frames_ms / max(nf / 8.0, 1.0),
+            "codes_only_audio_s_per_s": nf / FRAME_RATE / (w1 - w0),
+            "workload": "config 4 on one GPU: 64 utterances (8-64 byte texts, seed 4), greedy, host buffers in/out"}
 
 
 def run_sharded_workload(args, rank, world, local_rank, t, d, have_voc, dist, sync_all, m):
