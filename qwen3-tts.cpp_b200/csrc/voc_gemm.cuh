@@ -132,7 +132,165 @@ vgemm_simt(const VGemm p) {
     }
 }
 
+// ---- v2: 5th-generation tensor cores.  128 x BN output tile per CTA, accumulator in TMEM (128 lanes x BN
+// columns of F32), operands staged in shared memory by cp.async in the no-swizzle K-major UMMA layout
+//   offset(row, k16B) = (row / 8) * SBO + k16B * LBO + (row % 8) * 16      (core matrix = 8 rows x 16 bytes)
+// and consumed by tcgen05.mma.kind::f16 (F16 x F16 -> F32) issued by one thread.  The A tile of tap t is the
+// activation matrix read at row offset tap_off[t]; rows outside [0, a_rows) are zero-filled by cp.async
+// (= the causal left padding of the reference), so no im2col buffer exists.  4-stage ring: the loads of step
+// i + 3 are in flight while the MMAs of step i run; tcgen05.commit on a per-stage mbarrier frees the stage.
+// Epilogue: tcgen05.ld (each warp owns its 32 TMEM lanes = 32 output rows), fused bias / layer-scale /
+// residual / snake / gelu / swiglu as in vgemm_epilogue_pair.
+constexpr int VU_BM = 128, VU_BK = 32, VU_STAGES = 4, VU_THREADS = 128;
+constexpr int VU_LBO = 128, VU_SBO = (VU_BK / 8) * 128;            // bytes: 4 k-chunks of 16 B per 8-row group
+constexpr int VU_A_STAGE = VU_BM * VU_BK * 2;                       // 8 KB
+__host__ __device__ constexpr int vu_b_stage(int bn) { return bn * VU_BK * 2; }
+
+__device__ __forceinline__ uint32_t vu_smem(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint64_t vu_desc(uint32_t saddr) {
+    // SmemDescriptor (cute/arch/mma_sm100_desc.hpp): start >> 4 [0,14), LBO >> 4 [16,30), SBO >> 4 [32,46),
+    // version 1 [46,48), layout type SWIZZLE_NONE [61,64)
+    return (uint64_t) ((saddr & 0x3FFFFu) >> 4) | ((uint64_t) (VU_LBO >> 4) << 16) | ((uint64_t) (VU_SBO >> 4) << 32) | (1ull << 46);
+}
+__device__ __forceinline__ void vu_cp16(uint32_t dst, const void * src, bool ok) {
+    const int n = ok ? 16 : 0;                                      // src-size 0: the 16 bytes are zero-filled
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(n) : "memory");
+}
+
+__global__ void __launch_bounds__(VU_THREADS)
+vgemm_umma(const VGemm p, const int BN) {
+    extern __shared__ __align__(1024) unsigned char vu_sm[];
+    __shared__ unsigned long long mbar[VU_STAGES];
+    __shared__ unsigned long long mbar_done;
+    __shared__ uint32_t tmem_base_s;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long m0 = (long) blockIdx.x * VU_BM;
+    const int n0 = blockIdx.y * BN;
+    const int b_stage = vu_b_stage(BN);
+    unsigned char * smA = vu_sm;                                    // [stage][128 x 32 halves]
+    unsigned char * smB = vu_sm + VU_STAGES * VU_A_STAGE;           // [stage][BN x 32 halves]
+    const int tmem_cols = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+
+    if (tid == 0) {
+        for (int i = 0; i < VU_STAGES; ++i)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(vu_smem(&mbar[i])));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(vu_smem(&mbar_done)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(vu_smem(&tmem_base_s)), "r"(tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_s;
+
+    const int kpt = p.Kc / VU_BK;                                    // k steps per tap
+    const int n_steps = p.ntaps * kpt;
+    const int Ktot = p.ntaps * p.Kc;
+    // instruction descriptor (kind::f16): D = F32 [4,6) = 1, A = B = F16, both K-major, N >> 3 [17,23), M >> 4 [24,29)
+    const uint32_t idesc = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (VU_BM >> 4) << 24);
+
+    auto load_step = [&](int step) {
+        const int stage = step % VU_STAGES;
+        const int tap = step / kpt, k0 = (step - tap * kpt) * VU_BK;
+        const uint32_t a_dst = vu_smem(smA + stage * VU_A_STAGE), b_dst = vu_smem(smB + stage * b_stage);
+        // A: 128 rows x 4 chunks; thread -> (row = idx / 4, chunk = idx % 4)
+#pragma unroll
+        for (int it = 0; it < (VU_BM * 4) / VU_THREADS; ++it) {
+            const int idx = tid + it * VU_THREADS, r = idx >> 2, kc = idx & 3;
+            const long arow = m0 + r + p.tap_off[tap];
+            const bool ok = arow >= 0 && arow < p.a_rows && m0 + r < p.M;
+            vu_cp16(a_dst + (r >> 3) * VU_SBO + kc * VU_LBO + (r & 7) * 16, p.A + (size_t) (ok ? arow : 0) * p.lda + k0 + kc * 8, ok);
+        }
+        for (int idx = tid; idx < BN * 4; idx += VU_THREADS) {
+            const int r = idx >> 2, kc = idx & 3;
+            const bool ok = n0 + r < p.N;
+            vu_cp16(b_dst + (r >> 3) * VU_SBO + kc * VU_LBO + (r & 7) * 16, p.W + (size_t) (ok ? n0 + r : 0) * Ktot + (size_t) tap * p.Kc + k0 + kc * 8, ok);
+        }
+    };
+
+    // prologue: S - 1 steps in flight
+    for (int s = 0; s < VU_STAGES - 1; ++s) {
+        if (s < n_steps) load_step(s);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    for (int step = 0; step < n_steps; ++step) {
+        const int stage = step % VU_STAGES;
+        asm volatile("cp.async.wait_group %0;" :: "n"(VU_STAGES - 2) : "memory");      // this thread's part of `step` landed
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                  // generic-proxy writes -> async proxy (UMMA)
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t a_base = vu_smem(smA + stage * VU_A_STAGE), b_base = vu_smem(smB + stage * b_stage);
+#pragma unroll
+            for (int kk = 0; kk < VU_BK / 16; ++kk) {
+                const uint64_t ad = vu_desc(a_base + kk * 2 * VU_LBO), bd = vu_desc(b_base + kk * 2 * VU_LBO);
+                const uint32_t accum = (step > 0 || kk > 0) ? 1u : 0u;
+                asm volatile("{ .reg .pred q; setp.ne.b32 q, %4, 0; tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, q; }"
+                             :: "r"(tmem_d), "l"(ad), "l"(bd), "r"(idesc), "r"(accum) : "memory");
+            }
+            // frees this stage when the MMAs above (and all earlier ones) have read their operands
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(vu_smem(&mbar[stage])) : "memory");
+            if (step == n_steps - 1)
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(vu_smem(&mbar_done)) : "memory");
+        }
+        // refill the stage used by step - 1 with step + S - 1 once its MMAs are done
+        const int nxt = step + VU_STAGES - 1;
+        if (nxt < n_steps) {
+            if (step >= 1) {
+                const int ps = (step - 1) % VU_STAGES;
+                const uint32_t parity = ((step - 1) / VU_STAGES) & 1;
+                asm volatile("{ .reg .pred q; W_%=: mbarrier.try_wait.parity.shared::cta.b64 q, [%0], %1; @q bra D_%=; bra W_%=; D_%=: }"
+                             :: "r"(vu_smem(&mbar[ps])), "r"(parity) : "memory");
+            }
+            load_step(nxt);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    // ---- epilogue
+    asm volatile("{ .reg .pred q; W_%=: mbarrier.try_wait.parity.shared::cta.b64 q, [%0], 0; @q bra D_%=; bra W_%=; D_%=: }"
+                 :: "r"(vu_smem(&mbar_done)) : "memory");
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const size_t m = (size_t) m0 + warp * 32 + lane;                  // TMEM lane = output row
+    for (int c0 = 0; c0 < BN; c0 += 16) {
+        uint32_t v[16];
+        const uint32_t taddr = tmem_d + ((uint32_t) (warp * 32) << 16) + (uint32_t) c0;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                     : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                       "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                     : "r"(taddr) : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (m < (size_t) p.M) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 2) {
+                const int n = n0 + c0 + j;
+                if (n < p.N) vgemm_epilogue_pair(p, m, n, __uint_as_float(v[j]), __uint_as_float(v[j + 1]), n + 1 < p.N);
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_d), "r"(tmem_cols) : "memory");
+}
+
+inline bool voc_use_umma() {
+    static int v = -1;
+    if (v < 0) { const char * e = getenv("Q3T_VOC_SIMT"); v = (e && atoi(e)) ? 0 : 1; }
+    return v != 0;
+}
+
 inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
+    if (voc_use_umma() && p.Kc % VU_BK == 0 && p.N >= 16 && p.N % 2 == 0 && p.lda % 8 == 0) {
+        const int BN = p.N >= 128 ? 128 : ((p.N + 15) / 16) * 16;
+        const int smem = VU_STAGES * (VU_A_STAGE + vu_b_stage(BN));
+        static bool attr = false;
+        if (!attr) { cudaFuncSetAttribute(vgemm_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, VU_STAGES * (VU_A_STAGE + vu_b_stage(128))); attr = true; }
+        dim3 grid((unsigned) ((p.M + VU_BM - 1) / VU_BM), (unsigned) ((p.N + BN - 1) / BN));
+        vgemm_umma<<<grid, VU_THREADS, smem, ctx->stream>>>(p, BN);
+        return;
+    }
     dim3 grid((unsigned) ((p.M + VG_BM - 1) / VG_BM), (unsigned) ((p.N + VG_BN - 1) / VG_BN));
     vgemm_simt<<<grid, 256, 0, ctx->stream>>>(p);
 }

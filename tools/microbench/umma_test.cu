@@ -1,0 +1,81 @@
+// Standalone check of the tcgen05 tap-GEMM (vgemm_umma) against the CUDA-core tile kernel (vgemm_simt)
+// on random data: shapes of the vocoder (taps with negative row offsets, N = 96, ragged M), plus timing.
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+#include <cmath>
+#include "../../qwen3-tts.cpp_b200/csrc/voc_gemm.cuh"
+using namespace q3t;
+namespace q3t { int set_err(q3t_ctx *, int c, const std::string &) { return c; } int cuda_check(q3t_ctx *, cudaError_t e, const char *) { return e != cudaSuccess; } }
+
+static float frand() { return (float) rand() / RAND_MAX * 2.f - 1.f; }
+
+static bool run_case(q3t_ctx * ctx, int M, int N, int Kc, int ntaps, const int * offs, int a_rows, bool bias, bool time_it) {
+    const int Ktot = ntaps * Kc;
+    std::vector<__half> hA((size_t) a_rows * Kc), hW((size_t) N * Ktot);
+    for (auto & x : hA) x = __float2half(frand() * 0.5f);
+    for (auto & x : hW) x = __float2half(frand() * 0.1f);
+    std::vector<float> hb(N);
+    for (auto & x : hb) x = frand();
+    __half * dA, * dW; float * db, * o1, * o2;
+    cudaMalloc(&dA, hA.size() * 2); cudaMalloc(&dW, hW.size() * 2); cudaMalloc(&db, N * 4);
+    cudaMalloc(&o1, (size_t) M * N * 4); cudaMalloc(&o2, (size_t) M * N * 4);
+    cudaMemcpy(dA, hA.data(), hA.size() * 2, cudaMemcpyHostToDevice);
+    cudaMemcpy(dW, hW.data(), hW.size() * 2, cudaMemcpyHostToDevice);
+    cudaMemcpy(db, hb.data(), N * 4, cudaMemcpyHostToDevice);
+    cudaMemset(o1, 0xff, (size_t) M * N * 4); cudaMemset(o2, 0xff, (size_t) M * N * 4);
+    VGemm p{};
+    p.A = dA; p.lda = Kc; p.a_rows = a_rows; p.M = M; p.N = N; p.ntaps = ntaps; p.Kc = Kc;
+    for (int i = 0; i < ntaps; ++i) p.tap_off[i] = offs[i];
+    p.W = dW; p.bias = bias ? db : nullptr; p.pmod = N; p.out32 = o1; p.ld32 = N;
+    dim3 grid((M + VG_BM - 1) / VG_BM, (N + VG_BN - 1) / VG_BN);
+    vgemm_simt<<<grid, 256>>>(p);
+    p.out32 = o2;
+    setenv("Q3T_VOC_SIMT", "0", 1);
+    voc_gemm(ctx, p);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { printf("CUDA error: %s\n", cudaGetErrorString(e)); return false; }
+    std::vector<float> r1((size_t) M * N), r2((size_t) M * N);
+    cudaMemcpy(r1.data(), o1, r1.size() * 4, cudaMemcpyDeviceToHost);
+    cudaMemcpy(r2.data(), o2, r2.size() * 4, cudaMemcpyDeviceToHost);
+    double maxd = 0, maxv = 0; size_t bad = 0;
+    for (size_t i = 0; i < r1.size(); ++i) {
+        const double d = fabs((double) r1[i] - (double) r2[i]);
+        if (!(d <= 1e-3 * (1.0 + fabs(r1[i])))) ++bad;
+        if (d > maxd) maxd = d;
+        if (fabs(r1[i]) > maxv) maxv = fabs(r1[i]);
+    }
+    printf("M=%7d N=%4d Kc=%4d taps=%d: max|diff| %.3g (max|ref| %.3g) mismatches %zu %s\n", M, N, Kc, ntaps, maxd, maxv, bad, bad ? "FAIL" : "ok");
+    if (time_it && !bad) {
+        cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+        for (int k = 0; k < 2; ++k) {
+            cudaEventRecord(a);
+            for (int i = 0; i < 10; ++i) { if (k == 0) vgemm_simt<<<grid, 256>>>(p); else voc_gemm(ctx, p); }
+            cudaEventRecord(b); cudaEventSynchronize(b);
+            float ms; cudaEventElapsedTime(&ms, a, b);
+            printf("    %-5s %8.3f ms  %7.1f TFLOP/s\n", k == 0 ? "simt" : "umma", ms / 10, 2.0 * M * N * Ktot / (ms / 10 * 1e-3) / 1e12);
+        }
+    }
+    cudaFree(dA); cudaFree(dW); cudaFree(db); cudaFree(o1); cudaFree(o2);
+    return bad == 0;
+}
+
+int main() {
+    q3t_ctx ctx; ctx.stream = nullptr;
+    bool ok = true;
+    const int o1[1] = {0}, o7[7] = {-6, -5, -4, -3, -2, -1, 0}, o2[2] = {0, 1}, o7d[7] = {-18, -15, -12, -9, -6, -3, 0};
+    ok &= run_case(&ctx, 128, 128, 64, 1, o1, 128, false, false);
+    ok &= run_case(&ctx, 300, 96, 96, 1, o1, 300, true, false);
+    ok &= run_case(&ctx, 1000, 1536, 512, 1, o1, 1000, true, false);
+    ok &= run_case(&ctx, 777, 768, 768, 7, o7, 777, true, false);
+    ok &= run_case(&ctx, 2559, 768, 1536, 2, o2, 2560, false, false);
+    ok &= run_case(&ctx, 5000, 192, 192, 7, o7d, 5000, true, false);
+    if (ok) {
+        run_case(&ctx, 20480, 768, 768, 7, o7, 20480, true, true);
+        run_case(&ctx, 102400, 384, 384, 7, o7, 102400, true, true);
+        run_case(&ctx, 409600, 192, 192, 7, o7, 409600, true, true);
+        run_case(&ctx, 614400, 96, 96, 7, o7, 614400, true, true);
+    }
+    printf(ok ? "ALL OK\n" : "FAILED\n");
+    return ok ? 0 : 1;
+}
