@@ -12,6 +12,7 @@
 //   swiglu: columns (2i, 2i+1) = (gate_i, up_i) -> out16[m][i] = F16(silu(gate) * up)
 #pragma once
 
+#include <algorithm>
 #include "common.cuh"
 #include "engine.h"
 
@@ -69,6 +70,51 @@ __device__ __forceinline__ void vgemm_epilogue_pair(const VGemm & p, size_t m, i
             else if (p.act == VACT_GELU) x = gelu_f16_table(x);
             p.out16[m * p.ld16 + nn] = __float2half_rn(x);
         }
+    }
+}
+
+// the same epilogue with the per-column parameters of the pair (n, n+1) fetched once (a thread of the
+// tensor-core kernel keeps its column pair for all rows of the tile)
+struct VEpiCols { float bias[2], gamma[2], ea[2], eb[2]; };
+__device__ __forceinline__ void vgemm_epi_cols(const VGemm & p, int n, bool ok1, VEpiCols & c) {
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+        const int pi = (n + ((e == 1 && ok1) ? 1 : 0)) % p.pmod;
+        c.bias[e]  = p.bias ? p.bias[pi] : 0.0f;
+        c.gamma[e] = p.gamma ? p.gamma[pi] : 1.0f;
+        c.ea[e] = (p.act == VACT_SNAKE && p.out16) ? p.ea[pi] : 0.0f;
+        c.eb[e] = (p.act == VACT_SNAKE && p.out16) ? p.eb[pi] : 0.0f;
+    }
+}
+__device__ __forceinline__ void vgemm_epilogue_cols(const VGemm & p, size_t m, int n, float v0, float v1, bool ok1, const VEpiCols & c) {
+    if (p.swiglu) {
+        p.out16[m * p.ld16 + (n >> 1)] = __float2half_rn(silu_f(v0) * v1);
+        return;
+    }
+    float x[2] = {v0, v1};
+    float r[2] = {0.0f, 0.0f};
+    if (p.res) {
+        if (ok1 && ((p.ldres & 1) == 0)) { const float2 rr = *reinterpret_cast<const float2 *>(p.res + m * p.ldres + n); r[0] = rr.x; r[1] = rr.y; }
+        else { r[0] = p.res[m * p.ldres + n]; if (ok1) r[1] = p.res[m * p.ldres + n + 1]; }
+    }
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+        if (p.bias)  x[e] += c.bias[e];
+        if (p.gamma) x[e] *= c.gamma[e];
+        if (p.res)   x[e] += r[e];
+    }
+    if (p.out32) {
+        if (ok1 && ((p.ld32 & 1) == 0)) *reinterpret_cast<float2 *>(p.out32 + m * p.ld32 + n) = make_float2(x[0], x[1]);
+        else { p.out32[m * p.ld32 + n] = x[0]; if (ok1) p.out32[m * p.ld32 + n + 1] = x[1]; }
+    }
+    if (p.out16) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            if (p.act == VACT_SNAKE) x[e] = snake_f(x[e], c.ea[e], c.eb[e]);
+            else if (p.act == VACT_GELU) x[e] = gelu_f16_table(x[e]);
+        }
+        if (ok1 && ((p.ld16 & 1) == 0)) *reinterpret_cast<__half2 *>(p.out16 + m * p.ld16 + n) = __floats2half2_rn(x[0], x[1]);
+        else { p.out16[m * p.ld16 + n] = __float2half_rn(x[0]); if (ok1) p.out16[m * p.ld16 + n + 1] = __float2half_rn(x[1]); }
     }
 }
 
@@ -163,7 +209,7 @@ vgemm_umma(const VGemm p, const int BN) {
     __shared__ unsigned long long mbar[VU_STAGES];
     __shared__ unsigned long long mbar_done;
     __shared__ uint32_t tmem_base_s;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = tid >> 5;
     const long m0 = (long) blockIdx.x * VU_BM;
     const int n0 = blockIdx.y * BN;
     const int b_stage = vu_b_stage(BN);
@@ -249,11 +295,13 @@ vgemm_umma(const VGemm p, const int BN) {
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
-    // ---- epilogue
+    // ---- epilogue: TMEM -> registers (thread = output row) -> shared memory (padded rows) -> coalesced fused
+    //      epilogue (consecutive threads = consecutive column pairs; per-column parameters live in registers)
     asm volatile("{ .reg .pred q; W_%=: mbarrier.try_wait.parity.shared::cta.b64 q, [%0], 0; @q bra D_%=; bra W_%=; D_%=: }"
                  :: "r"(vu_smem(&mbar_done)) : "memory");
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const size_t m = (size_t) m0 + warp * 32 + lane;                  // TMEM lane = output row
+    float * stg = reinterpret_cast<float *>(vu_sm);                   // the operand ring is idle now
+    const int sld = BN + 4;                                           // row stride (floats): 16-byte aligned, conflict-free float4 rows
     for (int c0 = 0; c0 < BN; c0 += 16) {
         uint32_t v[16];
         const uint32_t taddr = tmem_d + ((uint32_t) (warp * 32) << 16) + (uint32_t) c0;
@@ -262,16 +310,31 @@ vgemm_umma(const VGemm p, const int BN) {
                        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
                      : "r"(taddr) : "memory");
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        if (m < (size_t) p.M) {
+        float4 * dst = reinterpret_cast<float4 *>(stg + (size_t) tid * sld + c0);
 #pragma unroll
-            for (int j = 0; j < 16; j += 2) {
-                const int n = n0 + c0 + j;
-                if (n < p.N) vgemm_epilogue_pair(p, m, n, __uint_as_float(v[j]), __uint_as_float(v[j + 1]), n + 1 < p.N);
-            }
-        }
+        for (int j = 0; j < 4; ++j)
+            dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    {
+        const int npairs = BN >> 1, rpp = VU_THREADS / npairs;        // rows handled per sweep
+        if (tid < rpp * npairs) {
+            const int pr = tid % npairs, r0 = tid / npairs;
+            const int n = n0 + 2 * pr;
+            if (n < p.N) {
+                const bool ok1 = n + 1 < p.N;
+                VEpiCols ec;
+                vgemm_epi_cols(p, n, ok1, ec);
+                for (int r = r0; r < VU_BM; r += rpp) {
+                    const size_t m = (size_t) m0 + r;
+                    if (m >= (size_t) p.M) break;
+                    const float2 v = *reinterpret_cast<const float2 *>(stg + (size_t) r * sld + 2 * pr);
+                    vgemm_epilogue_cols(p, m, n, v.x, v.y, ok1, ec);
+                }
+            }
+        }
+    }
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_d), "r"(tmem_cols) : "memory");
 }
 
@@ -283,10 +346,12 @@ inline bool voc_use_umma() {
 
 inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
     if (voc_use_umma() && p.Kc % VU_BK == 0 && p.N >= 16 && p.N % 2 == 0 && p.lda % 8 == 0) {
-        const int BN = p.N >= 128 ? 128 : ((p.N + 15) / 16) * 16;
-        const int smem = VU_STAGES * (VU_A_STAGE + vu_b_stage(BN));
+        // widest tile <= 128 columns that divides N (no half-empty last tile), else 128 / N rounded up to 16
+        int BN = p.N >= 128 ? 128 : ((p.N + 15) / 16) * 16;
+        for (int c = 128; c >= 64; c -= 16) if (p.N % c == 0) { BN = c; break; }
+        const int smem = std::max(VU_STAGES * (VU_A_STAGE + vu_b_stage(BN)), VU_BM * (BN + 4) * 4);
         static bool attr = false;
-        if (!attr) { cudaFuncSetAttribute(vgemm_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, VU_STAGES * (VU_A_STAGE + vu_b_stage(128))); attr = true; }
+        if (!attr) { cudaFuncSetAttribute(vgemm_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(VU_STAGES * (VU_A_STAGE + vu_b_stage(128)), VU_BM * (128 + 4) * 4)); attr = true; }
         dim3 grid((unsigned) ((p.M + VU_BM - 1) / VU_BM), (unsigned) ((p.N + BN - 1) / BN));
         vgemm_umma<<<grid, VU_THREADS, smem, ctx->stream>>>(p, BN);
         return;
