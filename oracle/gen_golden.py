@@ -66,18 +66,42 @@ def gen_vocoder(codes, out, T):
     print("wrote", out, wav.shape, "rms", float(np.sqrt((wav ** 2).mean())), "peak", float(np.abs(wav).max()))
 
 
+def gen_legacy(out):
+    """predict_codes (legacy parallel-heads graph, src/tts_transformer.cpp:2130-2180): logits of the 15
+    heads for a seeded hidden vector, with and without previous codes, F16 and Q8_0 tiny models.  Only
+    every 8th logit of each head is stored (bit patterns) to keep the fixture small."""
+    rng = np.random.default_rng(77)
+    hidden = (rng.standard_normal(1024) * 0.5).astype(np.float32)
+    d = dict(hidden=hidden)
+    for wtype in ("f16", "q8_0"):
+        tts, _ = models("tiny", wtype)
+        ref = reflib.RefTTS(tts)
+        prev = rng.integers(0, ref.CPV, size=15).astype(np.int32)
+        d[f"prev_{wtype}"] = prev
+        d[f"logits_{wtype}"] = ref.predict_codes(hidden, prev)[:, ::8].copy()
+        d[f"logits_noprev_{wtype}"] = ref.predict_codes(hidden, None)[:, ::8].copy()
+        ref.close()
+    np.savez_compressed(out, **d)
+    print("wrote", out)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--full", action="store_true", help="also write the full-size (28-layer) goldens")
     ap.add_argument("--threads", type=int, default=8)
+    ap.add_argument("--only-legacy", action="store_true", help="write only legacy_predict_codes.npz")
     a = ap.parse_args()
     if not reflib.available():
         sys.exit("oracle/_ref/libq3t_ref.so missing: make -f oracle/Makefile.ref")
     reflib.RefLib.get().set_threads(a.threads)
     os.makedirs(GOLDEN, exist_ok=True)
+    if a.only_legacy:
+        gen_legacy(os.path.join(GOLDEN, "legacy_predict_codes.npz"))
+        return
     codes = gen_tts("tiny", "f16", HELLO_TINY, 16, os.path.join(GOLDEN, "tiny_f16.npz"))
     gen_tts("tiny", "q8_0", HELLO_TINY, 16, os.path.join(GOLDEN, "tiny_q8_0.npz"))
     gen_vocoder(codes, os.path.join(GOLDEN, "vocoder_f16.npz"), 6)
+    gen_legacy(os.path.join(GOLDEN, "legacy_predict_codes.npz"))
     if a.full:
         gen_tts("full", "f16", HELLO_FULL, 64, os.path.join(GOLDEN, "full_f16.npz"))
         gen_tts("full", "q8_0", HELLO_FULL, 64, os.path.join(GOLDEN, "full_q8_0.npz"))

@@ -216,6 +216,23 @@ class PortTTS:
             out[s] = int(self.L.orc_argmax(_fp(logits), self.cp_vocab))
         return out
 
+    # predict_codes, the legacy parallel-heads graph (:2130-2180, build_code_pred_graph :1413-1532): one token,
+    # no RoPE / cache (a one-key soft-max is exactly 1, so the mixed value is the token's un-rounded V row =
+    # the F32-attention numerics at position 0), no output norm, all 15 heads on the same layer output
+    def predict_codes(self, hidden, prev_codes=None):
+        x = np.asarray(hidden, np.float32).copy()
+        if prev_codes is not None:
+            for cb in range(15):
+                x = x + self._rows(f"code_pred.codec_embd.{cb}.weight", [int(prev_codes[cb])], self.H)[0]
+        s = self.cp["s"]
+        keep = s.out_norm
+        s.out_norm = None
+        try:
+            h = self._forward(self.cp, x, 0, f32_attn=1)[0]
+        finally:
+            s.out_norm = keep
+        return np.stack([self._linear(f"code_pred.lm_head.{cb}.weight", h, self.cp_vocab, self.H)[0] for cb in range(15)])
+
     # generate, greedy (:2577-2851)
     def generate(self, tokens, spk, max_len, language_id=2050, rep_penalty=1.05):
         if max_len <= 0:

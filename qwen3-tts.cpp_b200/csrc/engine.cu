@@ -520,7 +520,7 @@ static int upload_passes(q3t_ctx * ctx, const std::vector<PassDesc> & v, int off
 static PassDesc make_pass(int stack, int xmode, int arg, int pos, int f32attn, int head, int n_layers, int process) {
     PassDesc p{};
     p.stack = stack; p.xmode = xmode; p.arg = arg; p.pos = pos; p.f32attn = f32attn; p.head = head;
-    p.n_layers = n_layers; p.process = process; p.width = 0;
+    p.n_layers = n_layers; p.process = process; p.width = 0; p.nonorm = 0;
     p.xsrc = nullptr; p.hidden_dst = nullptr; p.logits_dst = nullptr;
     return p;
 }
@@ -644,6 +644,52 @@ extern "C" int q3t_codepred_frame(q3t_ctx * ctx, const float * hidden, int32_t c
     if (out.error) return set_err(ctx, Q3T_ERR_DEVICE, "device watchdog: a grid barrier timed out inside lm_kernel");
     for (int i = 0; i < NCB - 1; ++i) codes15_out[i] = out.cur[i + 1];
     return Q3T_OK;
+}
+
+// ------------------------------------------------------------------------------ legacy predict_codes
+// src/tts_transformer.cpp:2130-2180 + build_code_pred_graph :1413-1532: ONE token through the five
+// code-predictor layers without RoPE or KV cache, then all 15 heads on the un-normed layer output.
+// With a single key the soft-max is exactly 1.0 and the mixed value is the token's own un-rounded V
+// row, which is what the F32-attention pass numerics give at position 0 (the q/k-norm and the
+// rotation cannot change a one-element soft-max).  Input: hidden + sum_cb f32(code_pred_embd[cb][prev[cb]])
+// added in codebook order (:1445-1451).  Not on the timed path: the stack is simply re-run per head.
+extern "C" int q3t_codepred_parallel(q3t_ctx * ctx, const float * hidden, const int32_t * prev_codes, float * logits_out) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (!hidden || !logits_out) return set_err(ctx, Q3T_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->device);
+    int rc;
+    if (ctx->n_ctx == 0 && (rc = q3t_kv_init(ctx, 256))) return rc;     // the RoPE table lives with the KV allocation
+    const int V = ctx->cfg.code_pred_vocab_size;
+    std::vector<float> x(hidden, hidden + H);
+    if (prev_codes) {
+        std::vector<__half> row(H);
+        for (int cb = 0; cb < NCB - 1; ++cb) {
+            if (prev_codes[cb] < 0 || prev_codes[cb] >= V) return set_err(ctx, Q3T_ERR_ARG, "Embedding token ID out of range");
+            CK(cudaMemcpyAsync(row.data(), ctx->hm.cp_embd[cb] + (size_t) prev_codes[cb] * H, H * 2, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));
+            for (int k = 0; k < H; ++k) x[k] = x[k] + __half2float(row[k]);
+        }
+    }
+    float * d_log = nullptr;
+    CK(cudaMalloc(&d_log, (size_t) (NCB - 1) * V * 4));
+    rc = cuda_check(ctx, cudaMemcpyAsync(ctx->d_tmp, x.data(), H * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D");
+    if (!rc) rc = reset_state(ctx, default_state(ctx), false);
+    if (!rc) {
+        std::vector<PassDesc> v;
+        for (int cb = 0; cb < NCB - 1; ++cb) {
+            PassDesc p = make_pass(1, XM_BUF, 0, 0, 1, cb + 1, ctx->cfg.code_pred_layers, 0);
+            p.xsrc = ctx->d_tmp; p.nonorm = 1; p.logits_dst = d_log + (size_t) cb * V;
+            v.push_back(p);
+        }
+        rc = upload_passes(ctx, v);
+        if (!rc) rc = lm_launch(ctx, ctx->d_passes, (int) v.size(), 0);
+    }
+    if (!rc) rc = cuda_check(ctx, cudaMemcpyAsync(logits_out, d_log, (size_t) (NCB - 1) * V * 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H");
+    if (!rc) rc = check_device_error(ctx);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_log);
+    return rc;
 }
 
 // ------------------------------------------------------------------------------ prompt staging

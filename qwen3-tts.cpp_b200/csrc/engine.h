@@ -65,6 +65,7 @@ struct PassDesc {
     int n_layers;      // layers to run (<= stack layers)
     int process;       // 1: apply suppress / repetition penalty to the talker logits before select
     int width;         // soft-max row width of the reference graph (n_past + n_tokens in a prefill); 0 -> pos + 1
+    int nonorm;        // 1: the head reads the raw stack output (no out_norm): legacy predict_codes graph
     const float * xsrc;
     float * hidden_dst;   // optional extra copy of the normed hidden (device)
     float * logits_dst;   // optional extra copy of the raw logits (device)

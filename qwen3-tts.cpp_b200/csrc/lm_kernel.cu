@@ -1162,7 +1162,17 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
     poll_vec<H>(m, m.x_x, ep, s.xres, w);
     cbar();
     token(s);
-    rmsnorm_to_xh(s, gh, m.eps, blockIdx.x == 0 ? m.hidden : nullptr, blockIdx.x == 0 ? p.hidden_dst : nullptr);
+    if (p.nonorm) {
+        // legacy predict_codes graph (src/tts_transformer.cpp:1517-1524): the heads multiply the un-normed
+        // output of the last layer; the mat-vec rounds it to F16 like any F16-weight ggml_mul_mat
+        for (int k = t; k < H; k += NCT) {
+            xh_put(s, k, s.xres[k]);
+            if (blockIdx.x == 0 && p.hidden_dst) p.hidden_dst[k] = s.xres[k];
+        }
+        cbar();
+    } else {
+        rmsnorm_to_xh(s, gh, m.eps, blockIdx.x == 0 ? m.hidden : nullptr, blockIdx.x == 0 ? p.hidden_dst : nullptr);
+    }
     PROF(20);
     const int s0 = ring_acquire(m, s, rg, w);
     gemv_ring<1024, 2, false>(s, s0, nH);

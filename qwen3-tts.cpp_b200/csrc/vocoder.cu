@@ -739,6 +739,3 @@ extern "C" int64_t q3t_fetch_samples(q3t_ctx * ctx, float * samples_out, int64_t
     return rc ? rc : n;
 }
 
-extern "C" int q3t_codepred_parallel(q3t_ctx * ctx, const float *, const int32_t *, float *) {
-    return q3t::set_err(ctx, Q3T_ERR_STATE, "predict_codes (legacy parallel heads) is not built yet");
-}

@@ -110,3 +110,15 @@ def test_live_reference_agrees_with_golden_and_oracle(orc_tiny):
     b = orc_tiny.step(x, 10)
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
     ref.close()
+
+
+@pytest.mark.parametrize("wtype", ["f16", "q8_0"])
+def test_legacy_predict_codes_matches_golden(wtype):
+    """predict_codes (legacy parallel-heads graph, src/tts_transformer.cpp:2130-2180): every 8th logit of
+    the 15 heads, with and without previous codes, bit-exact against the reference's output."""
+    g = _gold("legacy_predict_codes.npz")
+    t = port.PortTTS(models("tiny", wtype)[0])
+    a = t.predict_codes(g["hidden"], g[f"prev_{wtype}"])
+    assert a.shape == (15, 2048)
+    assert np.array_equal(a[:, ::8], g[f"logits_{wtype}"])
+    assert np.array_equal(t.predict_codes(g["hidden"], None)[:, ::8], g[f"logits_noprev_{wtype}"])

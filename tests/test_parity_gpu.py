@@ -240,3 +240,35 @@ def test_generate_q8_0_160_frames_identical_to_live_reference(tts_full_q8):
     assert got is not None and got.shape == want.shape
     neq = np.argwhere(got != want)
     assert len(neq) == 0, f"first mismatch at frame/codebook {neq[0]}"
+
+
+@pytest.mark.parametrize("wtype", ["f16", "q8_0"])
+def test_legacy_predict_codes_vs_golden_and_oracle(wtype, request):
+    """predict_codes (src/tts_transformer.cpp:2130-2180, graph :1413-1532): 15 x 2048 logits,
+    bit-exact against the reference's golden subset and against the C oracle on every logit, for the tiny
+    and the full-size models; the call must leave the engine usable for generate()."""
+    from oracle import port
+    g = _gold("legacy_predict_codes.npz")
+    t = _fixture_for(request, "tiny", wtype)
+    a = t.predict_codes(g["hidden"], g[f"prev_{wtype}"])
+    assert a is not None, t.get_error()
+    assert a.shape == (15, 2048)
+    assert np.array_equal(a[:, ::8], g[f"logits_{wtype}"])
+    b = t.predict_codes(g["hidden"], None)
+    assert np.array_equal(b[:, ::8], g[f"logits_noprev_{wtype}"])
+    o = port.PortTTS(models("tiny", wtype)[0])
+    assert np.array_equal(a, o.predict_codes(g["hidden"], g[f"prev_{wtype}"]))
+    # full-size model, fresh inputs, against the oracle
+    tf = _fixture_for(request, "full", wtype)
+    of = port.PortTTS(models("full", wtype)[0])
+    rng = np.random.default_rng(5)
+    hid = (rng.standard_normal(1024) * 0.7).astype(np.float32)
+    prev = rng.integers(0, 2048, size=15).astype(np.int32)
+    got = tf.predict_codes(hid, prev)
+    assert got is not None, tf.get_error()
+    assert np.array_equal(got, of.predict_codes(hid, prev))
+    bad = prev.copy(); bad[3] = 5000
+    assert tf.predict_codes(hid, bad) is None and "out of range" in tf.get_error()
+    gg = _gold(f"full_{wtype}.npz")
+    codes = tf.generate(gg["tokens"], gg["spk"], 4, temperature=0.0)
+    assert np.array_equal(codes, gg["codes"][:4])
