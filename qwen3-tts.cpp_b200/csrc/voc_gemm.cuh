@@ -38,6 +38,16 @@ __device__ __forceinline__ float snake_f(float x, float ea, float eb) {
     const float s = sinf(x * ea);
     return x + (s * s) * eb;
 }
+// tensor-core epilogue variant: two-term Cody-Waite reduction to [-pi, pi] and the SFU sine (abs. error
+// < 5e-7 there); the result is rounded to F16 (2^-11 relative) right after, and the waveform bar is an SNR.
+__device__ __forceinline__ float snake_fast(float x, float ea, float eb) {
+    const float y = x * ea;
+    const float k = rintf(y * 0.15915494309189535f);
+    float r = fmaf(k, -6.28318548202514648f, y);
+    r = fmaf(k, 1.7484555e-7f, r);
+    const float sn = __sinf(r);
+    return x + (sn * sn) * eb;
+}
 // ggml_vec_gelu_f32 with GGML_GELU_FP16 (ggml/src/ggml-cpu/vec.h:996-1009): table lookup on F16(x),
 // table entry = F16(gelu_f32(F32(F16(x))))
 __device__ __forceinline__ float gelu_f16_table(float x) {
@@ -86,17 +96,22 @@ __device__ __forceinline__ void vgemm_epi_cols(const VGemm & p, int n, bool ok1,
         c.eb[e] = (p.act == VACT_SNAKE && p.out16) ? p.eb[pi] : 0.0f;
     }
 }
-__device__ __forceinline__ void vgemm_epilogue_cols(const VGemm & p, size_t m, int n, float v0, float v1, bool ok1, const VEpiCols & c) {
+// residual of the pair (issued early so that several rows' loads are in flight)
+__device__ __forceinline__ float2 vgemm_load_res(const VGemm & p, size_t m, int n, bool ok1) {
+    float2 r = make_float2(0.0f, 0.0f);
+    if (p.res) {
+        if (ok1 && ((p.ldres & 1) == 0)) r = *reinterpret_cast<const float2 *>(p.res + m * p.ldres + n);
+        else { r.x = p.res[m * p.ldres + n]; if (ok1) r.y = p.res[m * p.ldres + n + 1]; }
+    }
+    return r;
+}
+__device__ __forceinline__ void vgemm_epilogue_cols(const VGemm & p, size_t m, int n, float v0, float v1, bool ok1, const VEpiCols & c, float2 rr) {
     if (p.swiglu) {
         p.out16[m * p.ld16 + (n >> 1)] = __float2half_rn(silu_f(v0) * v1);
         return;
     }
     float x[2] = {v0, v1};
-    float r[2] = {0.0f, 0.0f};
-    if (p.res) {
-        if (ok1 && ((p.ldres & 1) == 0)) { const float2 rr = *reinterpret_cast<const float2 *>(p.res + m * p.ldres + n); r[0] = rr.x; r[1] = rr.y; }
-        else { r[0] = p.res[m * p.ldres + n]; if (ok1) r[1] = p.res[m * p.ldres + n + 1]; }
-    }
+    const float r[2] = {rr.x, rr.y};
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
         if (p.bias)  x[e] += c.bias[e];
@@ -110,7 +125,7 @@ __device__ __forceinline__ void vgemm_epilogue_cols(const VGemm & p, size_t m, i
     if (p.out16) {
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-            if (p.act == VACT_SNAKE) x[e] = snake_f(x[e], c.ea[e], c.eb[e]);
+            if (p.act == VACT_SNAKE) x[e] = snake_fast(x[e], c.ea[e], c.eb[e]);
             else if (p.act == VACT_GELU) x[e] = gelu_f16_table(x[e]);
         }
         if (ok1 && ((p.ld16 & 1) == 0)) *reinterpret_cast<__half2 *>(p.out16 + m * p.ld16 + n) = __floats2half2_rn(x[0], x[1]);
@@ -187,7 +202,7 @@ vgemm_simt(const VGemm p) {
 // i + 3 are in flight while the MMAs of step i run; tcgen05.commit on a per-stage mbarrier frees the stage.
 // Epilogue: tcgen05.ld (each warp owns its 32 TMEM lanes = 32 output rows), fused bias / layer-scale /
 // residual / snake / gelu / swiglu as in vgemm_epilogue_pair.
-constexpr int VU_BM = 128, VU_BK = 32, VU_STAGES = 4, VU_THREADS = 128;
+constexpr int VU_BM = 128, VU_BK = 32, VU_STAGES = 4, VU_THREADS = 256;
 constexpr int VU_LBO = 128, VU_SBO = (VU_BK / 8) * 128;            // bytes: 4 k-chunks of 16 B per 8-row group
 constexpr int VU_A_STAGE = VU_BM * VU_BK * 2;                       // 8 KB
 __host__ __device__ constexpr int vu_b_stage(int bn) { return bn * VU_BK * 2; }
@@ -302,18 +317,24 @@ vgemm_umma(const VGemm p, const int BN) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     float * stg = reinterpret_cast<float *>(vu_sm);                   // the operand ring is idle now
     const int sld = BN + 4;                                           // row stride (floats): 16-byte aligned, conflict-free float4 rows
-    for (int c0 = 0; c0 < BN; c0 += 16) {
-        uint32_t v[16];
-        const uint32_t taddr = tmem_d + ((uint32_t) (warp * 32) << 16) + (uint32_t) c0;
-        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-                     : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                       "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-                     : "r"(taddr) : "memory");
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        float4 * dst = reinterpret_cast<float4 *>(stg + (size_t) tid * sld + c0);
+    {
+        // a warp may touch TMEM lanes 32 * (warp % 4) .. + 31 only: warps w and w + 4 share a lane quadrant and
+        // take alternate 16-column chunks
+        const int quad = warp & 3, lane = tid & 31;
+        const int row = quad * 32 + lane;
+        for (int c0 = (warp >> 2) * 16; c0 < BN; c0 += 32) {
+            uint32_t v[16];
+            const uint32_t taddr = tmem_d + ((uint32_t) (quad * 32) << 16) + (uint32_t) c0;
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                         : "r"(taddr) : "memory");
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            float4 * dst = reinterpret_cast<float4 *>(stg + (size_t) row * sld + c0);
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-            dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+            for (int j = 0; j < 4; ++j)
+                dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+        }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -326,11 +347,25 @@ vgemm_umma(const VGemm p, const int BN) {
                 const bool ok1 = n + 1 < p.N;
                 VEpiCols ec;
                 vgemm_epi_cols(p, n, ok1, ec);
-                for (int r = r0; r < VU_BM; r += rpp) {
-                    const size_t m = (size_t) m0 + r;
-                    if (m >= (size_t) p.M) break;
-                    const float2 v = *reinterpret_cast<const float2 *>(stg + (size_t) r * sld + 2 * pr);
-                    vgemm_epilogue_cols(p, m, n, v.x, v.y, ok1, ec);
+                // a thread reads and writes only its own elements (the residual may alias out32), so the
+                // residual loads of the next rows can be issued ahead of the stores of the current ones
+                constexpr int U = 4;
+                for (int rb = r0; rb < VU_BM; rb += rpp * U) {
+                    float2 rr[U];
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        const size_t m = (size_t) m0 + rb + u * rpp;
+                        rr[u] = (rb + u * rpp < VU_BM && m < (size_t) p.M) ? vgemm_load_res(p, m, n, ok1) : make_float2(0.0f, 0.0f);
+                    }
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        const int r = rb + u * rpp;
+                        const size_t m = (size_t) m0 + r;
+                        if (r < VU_BM && m < (size_t) p.M) {
+                            const float2 v = *reinterpret_cast<const float2 *>(stg + (size_t) r * sld + 2 * pr);
+                            vgemm_epilogue_cols(p, m, n, v.x, v.y, ok1, ec, rr[u]);
+                        }
+                    }
                 }
             }
         }
