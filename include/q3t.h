@@ -155,6 +155,14 @@ Q3T_API int  q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * co
 Q3T_API int64_t q3t_vocoder_decode(q3t_ctx * ctx, const int32_t * codes, int32_t n_frames,
                                    float * samples_out, int64_t cap);
 Q3T_API int64_t q3t_vocoder_n_samples(int32_t n_frames);
+/* Streaming form of the same decode (the reference pipeline decodes once per utterance,
+ * src/qwen3_tts.cpp:384-396).  `codes` holds ALL n_frames frames received so far, n_done of which were
+ * decoded by earlier calls; samples_out receives the samples that became final, i.e. global samples
+ * [n(n_done), n(n_frames)) with n(T) = 1920*T-555, n(0) = 0.  Every layer of the decoder is causal
+ * (src/audio_tokenizer_decoder.cpp:455,511,562,706,759), so the concatenation over the calls is the
+ * waveform decode() returns for the whole utterance.  Returns the sample count or a negative status. */
+Q3T_API int64_t q3t_vocoder_decode_from(q3t_ctx * ctx, const int32_t * codes, int32_t n_frames, int32_t n_done,
+                                        float * samples_out, int64_t cap);
 
 /* Device-resident variants used by bench.py `value` (inputs already in HBM):
  * run generate+decode for a prompt that was staged with q3t_stage_prompt, leave the
@@ -233,6 +241,9 @@ Q3T_API void      q3t_dec_delete(q3t_dec * d);
 Q3T_API int  q3t_dec_load_model(q3t_dec * d, const char * model_path);
 Q3T_API void q3t_dec_unload_model(q3t_dec * d);
 Q3T_API int64_t q3t_dec_decode(q3t_dec * d, const int32_t * codes, int32_t n_frames, float * samples_out, int64_t cap);
+/* extension: streaming decode (decode_append / stream_reset of the host class) */
+Q3T_API void q3t_dec_stream_reset(q3t_dec * d);
+Q3T_API int64_t q3t_dec_decode_append(q3t_dec * d, const int32_t * codes, int32_t n_new_frames, float * samples_out, int64_t cap);
 Q3T_API const char * q3t_dec_get_error(q3t_dec * d);
 Q3T_API q3t_ctx * q3t_dec_engine(q3t_dec * d);
 

@@ -90,6 +90,7 @@ def lib() -> C.CDLL:
         "q3t_dec_new": (vp, []), "q3t_dec_delete": (None, [vp]), "q3t_dec_load_model": (C.c_int, [vp, cp]),
         "q3t_dec_unload_model": (None, [vp]), "q3t_dec_decode": (C.c_int64, [vp, _i32p, C.c_int32, _f32p, C.c_int64]),
         "q3t_dec_get_error": (cp, [vp]), "q3t_dec_engine": (vp, [vp]),
+        "q3t_dec_stream_reset": (None, [vp]), "q3t_dec_decode_append": (C.c_int64, [vp, _i32p, C.c_int32, _f32p, C.c_int64]),
         "q3t_build_prompt": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32, _f32p, _i32p, _f32p, _i32p, _f32p]),
         "q3t_project_text": (C.c_int, [vp, _i32p, C.c_int32, _f32p]),
         "q3t_stage_prompt": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32]),
@@ -407,6 +408,20 @@ class AudioTokenizerDecoder:
         cap = max(int(self.L.q3t_vocoder_n_samples(T)), 0) + 16
         out = np.zeros(cap, np.float32)
         n = self.L.q3t_dec_decode(self.h, _ip(codes), T, _fp(out), cap)
+        if n < 0:
+            return None
+        return out[:n].copy()
+
+    # streaming extension: the concatenation of decode_append() results equals decode() of all the frames
+    def stream_reset(self):
+        self.L.q3t_dec_stream_reset(self.h)
+
+    def decode_append(self, codes):
+        codes = np.ascontiguousarray(codes, np.int32)
+        T = codes.shape[0]
+        cap = 1920 * T + 16
+        out = np.zeros(cap, np.float32)
+        n = self.L.q3t_dec_decode_append(self.h, _ip(codes), T, _fp(out), cap)
         if n < 0:
             return None
         return out[:n].copy()

@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 
 using namespace q3t;
 
@@ -933,16 +934,33 @@ extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * 
     if ((rc = rope_table(ctx, std::max(n_ctx, 16), &rope))) return rc;
     BatchSeqBuf buf[Q3T_MAX_BATCH];
     DevModel views[Q3T_MAX_BATCH];
+    // wall-clock split of the call (Q3T_BATCH_TRACE=1 prints it): setup, prompt + prefill, frames, copy-out
+    const bool trace = getenv("Q3T_BATCH_TRACE") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto ms_since = [&](std::chrono::steady_clock::time_point t0) { return std::chrono::duration<double, std::milli>(now() - t0).count(); };
+    double w_setup = 0, w_prefill = 0, w_frames = 0, w_out = 0;
+    const auto t_call = now();
+    GenState * hst = nullptr;                                        // pinned: pageable D2H copies stall now and then
+    if (cudaMallocHost(&hst, Q3T_MAX_BATCH * sizeof(GenState)) != cudaSuccess) { cudaFree(rope); return set_err(ctx, Q3T_ERR_CUDA, "cudaMallocHost failed"); }
     const size_t per = (size_t) L * NKV * n_ctx * HD;
     float ms_frames = 0.f, ms_prefill = 0.f;
-    auto fail = [&](int code) { for (auto & b : buf) b.release(); cudaFree(rope); ctx->hm = saved; return code; };
+    auto fail = [&](int code) {
+        const auto t0 = now();
+        for (auto & b : buf) b.release();
+        cudaFree(rope); cudaFreeHost(hst); ctx->hm = saved;
+        if (trace) fprintf(stderr, "[q3t_generate_batch] %d utterances: setup %.1f ms, prompt+prefill %.1f ms, frames %.1f ms, copy-out %.1f ms, release %.1f ms, total %.1f ms\n",
+                           n_seq, w_setup, w_prefill, w_frames, w_out, ms_since(t0), ms_since(t_call));
+        return code;
+    };
 
     for (int w0 = 0; w0 < n_seq && !rc; w0 += Q3T_MAX_BATCH) {
         const int nb = std::min(Q3T_MAX_BATCH, n_seq - w0);
         cudaEventRecord(ctx->ev[0], ctx->stream);
+        auto t_w = now();
         for (int q = 0; q < nb && !rc; ++q) {
             BatchSeqBuf & b = buf[q];
             if (!b.pk) {
+                const auto t_a = now();
                 bool ok = cudaMalloc(&b.pk, PKT_TOTAL * sizeof(Pkt)) == cudaSuccess && cudaMalloc(&b.hidden, H * 4) == cudaSuccess &&
                           cudaMalloc(&b.logits, 3072 * 4) == cudaSuccess && cudaMalloc(&b.seen, 4096) == cudaSuccess &&
                           cudaMalloc(&b.st, sizeof(GenState)) == cudaSuccess && cudaMalloc(&b.codes, (size_t) max_len * NCB * 4) == cudaSuccess &&
@@ -950,6 +968,7 @@ extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * 
                           cudaMalloc(&b.ck, (size_t) L2 * NKV * 16 * HD * 2) == cudaSuccess && cudaMalloc(&b.cv, (size_t) L2 * NKV * 16 * HD * 2) == cudaSuccess &&
                           cudaMalloc(&b.kf, (size_t) L2 * 2 * NKV * HD * 4) == cudaSuccess && cudaMalloc(&b.vf, (size_t) L2 * 2 * NKV * HD * 4) == cudaSuccess;
                 if (!ok) return fail(set_err(ctx, Q3T_ERR_CUDA, "cudaMalloc failed (batch buffers)"));
+                w_setup += ms_since(t_a);
             }
             const int i = w0 + q;
             if ((rc = q3t_stage_prompt(ctx, text_tokens[i], n_tokens[i], speaker_embd ? speaker_embd[i] : nullptr, language_id))) break;
@@ -988,7 +1007,8 @@ extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * 
         v.push_back(make_pass(0, XM_TALKER_NEXT, 0, -1, 0, 0, L, 1));
         if ((rc = upload_passes(ctx, v))) break;
         // frames: every launch advances all live sequences by one frame; poll `done` every 32 launches
-        std::vector<GenState> hst(nb);
+        if (trace) cudaStreamSynchronize(ctx->stream);
+        w_prefill += ms_since(t_w); t_w = now();
         int launched = 0;
         bool all_done = false;
         while (launched < max_len && !all_done && !rc) {
@@ -1006,6 +1026,7 @@ extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * 
         }
         if (rc) break;
         cudaEventRecord(ctx->ev[2], ctx->stream);
+        w_frames += ms_since(t_w); t_w = now();
         for (int q = 0; q < nb; ++q) {
             const int nf = hst[q].frame;
             n_frames_out[w0 + q] = nf;
@@ -1016,6 +1037,7 @@ extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * 
         float ms = 0.f;
         cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ms_prefill += ms;
         cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); ms_frames += ms;
+        w_out += ms_since(t_w);
     }
     ctx->timing.prefill_ms = ms_prefill; ctx->timing.frames_ms = ms_frames;
     return fail(rc);
@@ -1035,7 +1057,7 @@ extern "C" int q3t_run_staged(q3t_ctx * ctx, int32_t max_len, float repetition_p
         if (!ctx->voc_ready) return set_err(ctx, Q3T_ERR_STATE, "vocoder not loaded");
         cudaEventRecord(ctx->ev[2], ctx->stream);
         float * smp = nullptr;
-        const int64_t ns = vocoder_run(ctx, ctx->d_codes, nf, &smp);
+        const int64_t ns = vocoder_run(ctx, ctx->d_codes, nf, &smp, 0);
         if (ns < 0) return (int) ns;
         cudaEventRecord(ctx->ev[3], ctx->stream);
         CK(cudaStreamSynchronize(ctx->stream));

@@ -200,5 +200,5 @@ int  prompt_build(q3t_ctx * ctx, const int32_t * tokens_dev, int n_tokens, const
 int  prompt_project(q3t_ctx * ctx, const int32_t * tokens_dev, int n_tokens, float * out_dev);
 int  vocoder_finalize(q3t_ctx * ctx);
 void vocoder_free(q3t_ctx * ctx);
-int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int n_frames, float ** samples_dev);
+int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int n_frames, float ** samples_dev, int t_from);
 }

@@ -811,6 +811,7 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
         if (c + 1 < nck) { cbar(); ring_release(s, rg, (rows + 7) >> 3); }
         else { s0_last = s0; rows_last = rows; }             // the last slice also holds the leftover rows
     }
+    PROF(55);
     if (np > 0) {
         if (warp < 8) {
             if (pos < np && ((pos & 31) >> 2) == warp) {     // the new token is the last step of its chain
@@ -849,6 +850,7 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
         }
         pk_store(att + t, (float) sumf, ep_out);
     }
+    PROF(56);
     if (nck > 0) { cbar(); ring_release(s, rg, (rows_last + 7) >> 3); }
     if (writer && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }   // publish the appended K/V rows (see above)
 }

@@ -105,30 +105,47 @@ __device__ __forceinline__ float2 vgemm_load_res(const VGemm & p, size_t m, int 
     }
     return r;
 }
+// EPI selects a compile-time specialisation of the fused epilogue (the generic one tests ~10 run-time flags
+// per row, and the hot launches are instruction-issue bound):
+//   VEPI_GENERIC     every combination, flags read from VGemm
+//   VEPI_BIAS_SNAKE  out16 = F16(snake(acc + bias))                              (k7 conv of a residual unit)
+//   VEPI_RES_SNAKE   x = acc + bias + res; [out32 = x;] out16 = F16(snake(x))    (1x1 conv of a residual unit)
+//   VEPI_O32_SNAKE   x = acc + bias; out32 = x; out16 = F16(snake(x))            (ConvTranspose)
+// the specialised kinds require even N / leading dimensions (checked by voc_gemm).
+enum { VEPI_GENERIC = 0, VEPI_BIAS_SNAKE = 1, VEPI_RES_SNAKE = 2, VEPI_O32_SNAKE = 3 };
+
+template <int EPI>
 __device__ __forceinline__ void vgemm_epilogue_cols(const VGemm & p, size_t m, int n, float v0, float v1, bool ok1, const VEpiCols & c, float2 rr) {
-    if (p.swiglu) {
+    constexpr bool G = EPI == VEPI_GENERIC;
+    if (G && p.swiglu) {
         p.out16[m * p.ld16 + (n >> 1)] = __float2half_rn(silu_f(v0) * v1);
         return;
     }
+    const bool has_bias = G ? p.bias != nullptr : true;
+    const bool has_gamma = G ? p.gamma != nullptr : false;
+    const bool has_res = G ? p.res != nullptr : EPI == VEPI_RES_SNAKE;
+    const bool has_o32 = G ? p.out32 != nullptr : (EPI == VEPI_BIAS_SNAKE ? false : EPI == VEPI_O32_SNAKE ? true : p.out32 != nullptr);
+    const bool has_o16 = G ? p.out16 != nullptr : true;
+    const int  act = G ? p.act : VACT_SNAKE;
     float x[2] = {v0, v1};
     const float r[2] = {rr.x, rr.y};
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
-        if (p.bias)  x[e] += c.bias[e];
-        if (p.gamma) x[e] *= c.gamma[e];
-        if (p.res)   x[e] += r[e];
+        if (has_bias)  x[e] += c.bias[e];
+        if (has_gamma) x[e] *= c.gamma[e];
+        if (has_res)   x[e] += r[e];
     }
-    if (p.out32) {
-        if (ok1 && ((p.ld32 & 1) == 0)) *reinterpret_cast<float2 *>(p.out32 + m * p.ld32 + n) = make_float2(x[0], x[1]);
+    if (has_o32) {
+        if (!G || (ok1 && ((p.ld32 & 1) == 0))) *reinterpret_cast<float2 *>(p.out32 + m * p.ld32 + n) = make_float2(x[0], x[1]);
         else { p.out32[m * p.ld32 + n] = x[0]; if (ok1) p.out32[m * p.ld32 + n + 1] = x[1]; }
     }
-    if (p.out16) {
+    if (has_o16) {
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-            if (p.act == VACT_SNAKE) x[e] = snake_fast(x[e], c.ea[e], c.eb[e]);
-            else if (p.act == VACT_GELU) x[e] = gelu_f16_table(x[e]);
+            if (act == VACT_SNAKE) x[e] = snake_fast(x[e], c.ea[e], c.eb[e]);
+            else if (act == VACT_GELU) x[e] = gelu_f16_table(x[e]);
         }
-        if (ok1 && ((p.ld16 & 1) == 0)) *reinterpret_cast<__half2 *>(p.out16 + m * p.ld16 + n) = __floats2half2_rn(x[0], x[1]);
+        if (!G || (ok1 && ((p.ld16 & 1) == 0))) *reinterpret_cast<__half2 *>(p.out16 + m * p.ld16 + n) = __floats2half2_rn(x[0], x[1]);
         else { p.out16[m * p.ld16 + n] = __float2half_rn(x[0]); if (ok1) p.out16[m * p.ld16 + n + 1] = __float2half_rn(x[1]); }
     }
 }
@@ -218,6 +235,7 @@ __device__ __forceinline__ void vu_cp16(uint32_t dst, const void * src, bool ok)
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(n) : "memory");
 }
 
+template <int EPI>
 __global__ void __launch_bounds__(VU_THREADS)
 vgemm_umma(const VGemm p, const int BN) {
     extern __shared__ __align__(1024) unsigned char vu_sm[];
@@ -253,23 +271,29 @@ vgemm_umma(const VGemm p, const int BN) {
     // instruction descriptor (kind::f16): D = F32 [4,6) = 1, A = B = F16, both K-major, N >> 3 [17,23), M >> 4 [24,29)
     const uint32_t idesc = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (VU_BM >> 4) << 24);
 
+    // per-thread loader state, fixed for the whole K loop: the thread owns 16-byte chunk (row r, k-chunk kc) of
+    // two A rows (r, r + 64) and of up to two W rows; only the tap's row offset and the k origin change per step
+    const int l_r = tid >> 2, l_kc = tid & 3;
+    const uint32_t l_soff = (uint32_t) ((l_r >> 3) * VU_SBO + l_kc * VU_LBO + (l_r & 7) * 16);   // rows r and r + 64: + 8 * SBO
+    const long l_arow0 = m0 + l_r;                                                              // A row before the tap offset
+    const bool l_m_ok0 = l_arow0 < p.M, l_m_ok1 = l_arow0 + 64 < p.M;
+    const __half * l_a = p.A + l_kc * 8;
+    const bool l_w_ok0 = l_r < BN && n0 + l_r < p.N, l_w_ok1 = l_r + 64 < BN && n0 + l_r + 64 < p.N;
+    const __half * l_w0 = p.W + (size_t) (l_w_ok0 ? n0 + l_r : 0) * Ktot + l_kc * 8;
+    const __half * l_w1 = p.W + (size_t) (l_w_ok1 ? n0 + l_r + 64 : 0) * Ktot + l_kc * 8;
+    const bool l_w_has0 = l_r < BN, l_w_has1 = l_r + 64 < BN;
+
     auto load_step = [&](int step) {
         const int stage = step % VU_STAGES;
         const int tap = step / kpt, k0 = (step - tap * kpt) * VU_BK;
-        const uint32_t a_dst = vu_smem(smA + stage * VU_A_STAGE), b_dst = vu_smem(smB + stage * b_stage);
-        // A: 128 rows x 4 chunks; thread -> (row = idx / 4, chunk = idx % 4)
-#pragma unroll
-        for (int it = 0; it < (VU_BM * 4) / VU_THREADS; ++it) {
-            const int idx = tid + it * VU_THREADS, r = idx >> 2, kc = idx & 3;
-            const long arow = m0 + r + p.tap_off[tap];
-            const bool ok = arow >= 0 && arow < p.a_rows && m0 + r < p.M;
-            vu_cp16(a_dst + (r >> 3) * VU_SBO + kc * VU_LBO + (r & 7) * 16, p.A + (size_t) (ok ? arow : 0) * p.lda + k0 + kc * 8, ok);
-        }
-        for (int idx = tid; idx < BN * 4; idx += VU_THREADS) {
-            const int r = idx >> 2, kc = idx & 3;
-            const bool ok = n0 + r < p.N;
-            vu_cp16(b_dst + (r >> 3) * VU_SBO + kc * VU_LBO + (r & 7) * 16, p.W + (size_t) (ok ? n0 + r : 0) * Ktot + (size_t) tap * p.Kc + k0 + kc * 8, ok);
-        }
+        const uint32_t a_dst = vu_smem(smA + stage * VU_A_STAGE) + l_soff, b_dst = vu_smem(smB + stage * b_stage) + l_soff;
+        const long ar0 = l_arow0 + p.tap_off[tap], ar1 = ar0 + 64;
+        const bool ok0 = l_m_ok0 && ar0 >= 0 && ar0 < p.a_rows, ok1 = l_m_ok1 && ar1 >= 0 && ar1 < p.a_rows;
+        vu_cp16(a_dst, l_a + (size_t) (ok0 ? ar0 : 0) * p.lda + k0, ok0);
+        vu_cp16(a_dst + 8 * VU_SBO, l_a + (size_t) (ok1 ? ar1 : 0) * p.lda + k0, ok1);
+        // W: column tap * Kc + k0 = step * BK (the taps are contiguous in a W row)
+        if (l_w_has0) vu_cp16(b_dst, l_w0 + (size_t) step * VU_BK, l_w_ok0);
+        if (l_w_has1) vu_cp16(b_dst + 8 * VU_SBO, l_w1 + (size_t) step * VU_BK, l_w_ok1);
     };
 
     // prologue: S - 1 steps in flight
@@ -355,7 +379,8 @@ vgemm_umma(const VGemm p, const int BN) {
 #pragma unroll
                     for (int u = 0; u < U; ++u) {
                         const size_t m = (size_t) m0 + rb + u * rpp;
-                        rr[u] = (rb + u * rpp < VU_BM && m < (size_t) p.M) ? vgemm_load_res(p, m, n, ok1) : make_float2(0.0f, 0.0f);
+                        rr[u] = ((EPI == VEPI_GENERIC || EPI == VEPI_RES_SNAKE) && rb + u * rpp < VU_BM && m < (size_t) p.M)
+                              ? vgemm_load_res(p, m, n, ok1) : make_float2(0.0f, 0.0f);
                     }
 #pragma unroll
                     for (int u = 0; u < U; ++u) {
@@ -363,7 +388,7 @@ vgemm_umma(const VGemm p, const int BN) {
                         const size_t m = (size_t) m0 + r;
                         if (r < VU_BM && m < (size_t) p.M) {
                             const float2 v = *reinterpret_cast<const float2 *>(stg + (size_t) r * sld + 2 * pr);
-                            vgemm_epilogue_cols(p, m, n, v.x, v.y, ok1, ec, rr[u]);
+                            vgemm_epilogue_cols<EPI>(p, m, n, v.x, v.y, ok1, ec, rr[u]);
                         }
                     }
                 }
@@ -385,10 +410,25 @@ inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
         int BN = p.N >= 128 ? 128 : ((p.N + 15) / 16) * 16;
         for (int c = 128; c >= 64; c -= 16) if (p.N % c == 0) { BN = c; break; }
         const int smem = std::max(VU_STAGES * (VU_A_STAGE + vu_b_stage(BN)), VU_BM * (BN + 4) * 4);
+        const int smem_max = std::max(VU_STAGES * (VU_A_STAGE + vu_b_stage(128)), VU_BM * (128 + 4) * 4);
         static bool attr = false;
-        if (!attr) { cudaFuncSetAttribute(vgemm_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(VU_STAGES * (VU_A_STAGE + vu_b_stage(128)), VU_BM * (128 + 4) * 4)); attr = true; }
+        if (!attr) {
+            cudaFuncSetAttribute(vgemm_umma<VEPI_GENERIC>,    cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+            cudaFuncSetAttribute(vgemm_umma<VEPI_BIAS_SNAKE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+            cudaFuncSetAttribute(vgemm_umma<VEPI_RES_SNAKE>,  cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+            cudaFuncSetAttribute(vgemm_umma<VEPI_O32_SNAKE>,  cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+            attr = true;
+        }
         dim3 grid((unsigned) ((p.M + VU_BM - 1) / VU_BM), (unsigned) ((p.N + BN - 1) / BN));
-        vgemm_umma<<<grid, VU_THREADS, smem, ctx->stream>>>(p, BN);
+        const bool snake16 = p.bias && !p.gamma && !p.swiglu && p.out16 && p.act == VACT_SNAKE && (p.ld16 & 1) == 0;
+        if (snake16 && !p.res && !p.out32)
+            vgemm_umma<VEPI_BIAS_SNAKE><<<grid, VU_THREADS, smem, ctx->stream>>>(p, BN);
+        else if (snake16 && p.res && (p.ldres & 1) == 0 && (!p.out32 || (p.ld32 & 1) == 0))
+            vgemm_umma<VEPI_RES_SNAKE><<<grid, VU_THREADS, smem, ctx->stream>>>(p, BN);
+        else if (snake16 && !p.res && p.out32 && (p.ld32 & 1) == 0)
+            vgemm_umma<VEPI_O32_SNAKE><<<grid, VU_THREADS, smem, ctx->stream>>>(p, BN);
+        else
+            vgemm_umma<VEPI_GENERIC><<<grid, VU_THREADS, smem, ctx->stream>>>(p, BN);
         return;
     }
     dim3 grid((unsigned) ((p.M + VG_BM - 1) / VG_BM), (unsigned) ((p.N + VG_BN - 1) / VG_BN));

@@ -539,7 +539,11 @@ static size_t arena_need(int T) {
     return b + (1 << 20);
 }
 
-int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int T, float ** samples_dev) {
+// t_from > 0 (streaming, q3t_vocoder_decode_from): the RVQ / pre-conv / pre-transformer stages run on all T
+// frames (full causal attention has no finite window), the convolutional stack only on latent frames
+// [t_from, T); every conv is causal, so local sample j of the slice is global sample j + 1920 * t_from and is
+// exact once j is past the stack's left context (< 10 frames, VOC_STREAM_CONTEXT).
+int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int T, float ** samples_dev, int t_from) {
     q3t_vocoder * v = ctx->voc;
     if (!v || !ctx->voc_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
     if (T <= 0) return set_err(ctx, Q3T_ERR_ARG, "n_frames must be > 0");
@@ -554,7 +558,8 @@ int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int T, float ** sa
         if ((rc = cuda_check(ctx, cudaMalloc(&v->arena, need_b), "cudaMalloc vocoder scratch"))) return rc;
         v->arena_bytes = need_b;
     }
-    const int64_t n_out = 1920LL * T - 555;
+    if (t_from < 0 || t_from >= T) return set_err(ctx, Q3T_ERR_ARG, "internal: bad stream origin");
+    const int64_t n_out = 1920LL * (T - t_from) - 555;
     if (ctx->samples_cap < n_out) {
         cudaStreamSynchronize(st);
         if (ctx->d_samples) cudaFree(ctx->d_samples);
@@ -630,7 +635,8 @@ int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int T, float ** sa
     dump("tfm_out16", cur16, (size_t) T * LATENT * 2);
 
     // ---- two ConvNeXt-style x2 upsample blocks
-    int L = T;
+    cur16 += (size_t) t_from * LATENT;
+    int L = T - t_from;
     for (int i = 0; i < 2; ++i) {
         const VUpsample & u = v->up[i];
         const int L2 = 2 * L;
@@ -716,11 +722,52 @@ extern "C" int64_t q3t_vocoder_decode(q3t_ctx * ctx, const int32_t * codes, int3
     if (rc) return rc;
     cudaEventRecord(ctx->ev[2], ctx->stream);
     float * smp = nullptr;
-    const int64_t n = vocoder_run(ctx, v->codes_dev, n_frames, &smp);
+    const int64_t n = vocoder_run(ctx, v->codes_dev, n_frames, &smp, 0);
     if (n < 0) return n;
     cudaEventRecord(ctx->ev[3], ctx->stream);
     if (samples_out) {
         rc = cuda_check(ctx, cudaMemcpyAsync(samples_out, smp, (size_t) std::min<int64_t>(n, cap) * 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H samples");
+        if (rc) return rc;
+    }
+    rc = cuda_check(ctx, cudaStreamSynchronize(ctx->stream), "vocoder sync");
+    if (rc) return rc;
+    float ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]); ctx->timing.vocoder_ms = ms;
+    return n;
+}
+
+// Streaming decode: `codes` holds all n_frames frames received so far, of which the first n_done were already
+// decoded by earlier calls; returns the samples that became final: global samples [n(n_done), n(n_frames)) with
+// n(T) = 1920 T - 555 (n(0) = 0).  The waveform is identical to decode() of the whole utterance (causal stack).
+constexpr int VOC_STREAM_CONTEXT = 16;      // latent frames of left context re-run per chunk (the stack needs < 10)
+extern "C" int64_t q3t_vocoder_decode_from(q3t_ctx * ctx, const int32_t * codes, int32_t n_frames, int32_t n_done,
+                                           float * samples_out, int64_t cap) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->voc_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (!codes || n_frames <= 0) return set_err(ctx, Q3T_ERR_ARG, "codes is null or n_frames <= 0");
+    if (n_done < 0 || n_done >= n_frames) return set_err(ctx, Q3T_ERR_ARG, "n_done must be in [0, n_frames)");
+    cudaSetDevice(ctx->device);
+    q3t_vocoder * v = ctx->voc;
+    if (v->codes_cap < n_frames * 16) {
+        cudaStreamSynchronize(ctx->stream);
+        if (v->codes_dev) cudaFree(v->codes_dev);
+        v->codes_dev = nullptr; v->codes_cap = 0;
+        int rc = cuda_check(ctx, cudaMalloc(&v->codes_dev, (size_t) (n_frames + 64) * 16 * 4), "cudaMalloc codes");
+        if (rc) return rc;
+        v->codes_cap = (n_frames + 64) * 16;
+    }
+    int rc = cuda_check(ctx, cudaMemcpyAsync(v->codes_dev, codes, (size_t) n_frames * 16 * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D codes");
+    if (rc) return rc;
+    const int t_from = std::max(0, n_done - VOC_STREAM_CONTEXT);
+    cudaEventRecord(ctx->ev[2], ctx->stream);
+    float * smp = nullptr;
+    const int64_t n_loc = vocoder_run(ctx, v->codes_dev, n_frames, &smp, t_from);
+    if (n_loc < 0) return n_loc;
+    cudaEventRecord(ctx->ev[3], ctx->stream);
+    const int64_t g0 = n_done > 0 ? 1920LL * n_done - 555 : 0;          // first global sample not yet emitted
+    const int64_t skip = g0 - 1920LL * t_from;
+    const int64_t n = n_loc - skip;
+    if (samples_out) {
+        rc = cuda_check(ctx, cudaMemcpyAsync(samples_out, smp + skip, (size_t) std::min<int64_t>(n, cap) * 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H samples");
         if (rc) return rc;
     }
     rc = cuda_check(ctx, cudaStreamSynchronize(ctx->stream), "vocoder sync");

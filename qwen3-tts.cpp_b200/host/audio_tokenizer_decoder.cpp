@@ -11,6 +11,7 @@ AudioTokenizerDecoder::AudioTokenizerDecoder() = default;
 AudioTokenizerDecoder::~AudioTokenizerDecoder() { unload_model(); }
 
 void AudioTokenizerDecoder::unload_model() {
+    stream_reset();
     if (engine_) {
         q3t_unload(engine_, 2);
         release_preferred_backend(engine_, "AudioTokenizerDecoder");
@@ -62,6 +63,24 @@ bool AudioTokenizerDecoder::decode(const int32_t * codes, int32_t n_frames, std:
     const int64_t got = q3t_vocoder_decode(engine_, codes, n_frames, samples.data(), (int64_t) samples.size());
     if (got < 0) { error_msg_ = q3t_last_error(engine_); samples.clear(); return false; }
     samples.resize((size_t) got);
+    return true;
+}
+
+bool AudioTokenizerDecoder::decode_append(const int32_t * codes, int32_t n_new_frames, std::vector<float> & new_samples) {
+    if (!loaded_) { error_msg_ = "Model not loaded"; return false; }
+    if (!codes || n_new_frames <= 0) { error_msg_ = "codes is null or n_frames <= 0"; return false; }
+    stream_codes_.insert(stream_codes_.end(), codes, codes + (size_t) n_new_frames * config_.n_codebooks);
+    const int32_t total = stream_done_ + n_new_frames;
+    const int64_t n = q3t_vocoder_n_samples(total) - q3t_vocoder_n_samples(stream_done_);
+    new_samples.resize((size_t) std::max<int64_t>(n, 0));
+    const int64_t got = q3t_vocoder_decode_from(engine_, stream_codes_.data(), total, stream_done_, new_samples.data(), (int64_t) new_samples.size());
+    if (got < 0) {
+        error_msg_ = q3t_last_error(engine_); new_samples.clear();
+        stream_codes_.resize((size_t) stream_done_ * config_.n_codebooks);      // the chunk was not consumed
+        return false;
+    }
+    new_samples.resize((size_t) got);
+    stream_done_ = total;
     return true;
 }
 

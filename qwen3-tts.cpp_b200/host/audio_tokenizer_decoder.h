@@ -40,13 +40,20 @@ public:
     const audio_decoder_config & get_config() const { return config_; }
     const std::string & get_error() const { return error_msg_; }
 
-    q3t_ctx * engine() const { return engine_; }      // extension
+    // ---- extensions (not in the reference) --------------------------------------------------
+    // streaming: append n_new_frames frames of codes to the running utterance and receive the samples that
+    // became final; the concatenation over the calls equals decode() of all frames (the decoder is causal)
+    void stream_reset() { stream_codes_.clear(); stream_done_ = 0; }
+    bool decode_append(const int32_t * codes, int32_t n_new_frames, std::vector<float> & new_samples);
+    q3t_ctx * engine() const { return engine_; }
 
 private:
     audio_decoder_config config_;
     q3t_ctx * engine_ = nullptr;
     bool loaded_ = false;
     std::string error_msg_;
+    std::vector<int32_t> stream_codes_;
+    int32_t stream_done_ = 0;
 };
 
 } // namespace qwen3_tts

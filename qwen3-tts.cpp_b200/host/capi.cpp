@@ -155,6 +155,14 @@ Q3T_API int64_t q3t_dec_decode(q3t_dec * d, const int32_t * codes, int32_t n_fra
     if (samples_out) memcpy(samples_out, s.data(), (size_t) (n < cap ? n : cap) * sizeof(float));
     return n;
 }
+Q3T_API void q3t_dec_stream_reset(q3t_dec * d) { if (d) d->d.stream_reset(); }
+Q3T_API int64_t q3t_dec_decode_append(q3t_dec * d, const int32_t * codes, int32_t n_new_frames, float * samples_out, int64_t cap) {
+    if (!d) return -1;
+    std::vector<float> o;
+    if (!d->d.decode_append(codes, n_new_frames, o)) return -1;
+    if (samples_out) memcpy(samples_out, o.data(), std::min<size_t>(o.size(), (size_t) std::max<int64_t>(cap, 0)) * sizeof(float));
+    return (int64_t) o.size();
+}
 Q3T_API const char * q3t_dec_get_error(q3t_dec * d) { return d ? d->d.get_error().c_str() : "null object"; }
 Q3T_API q3t_ctx * q3t_dec_engine(q3t_dec * d) { return d ? d->d.engine() : nullptr; }
 

@@ -75,3 +75,28 @@ def test_decode_vs_live_reference(dec, T):
     assert got is not None and got.shape == want.shape
     s = snr_db(want, got)
     assert s >= SNR_MIN_DB and s >= SNR_EXPECT_DB, f"T={T}: SNR {s:.1f} dB"
+
+
+@pytest.mark.parametrize("chunks", [[1, 1, 1, 5, 24], [7, 40, 3, 30], [80]])
+def test_streaming_decode_equals_whole_decode(dec, chunks):
+    """decode_append: every layer of the decoder is causal, so chunked decoding with the
+    pre-transformer run over all frames so far and the conv stack over the new frames + 16 frames of left
+    context returns, chunk by chunk, exactly the waveform of one decode() over all frames."""
+    T = sum(chunks)
+    codes = np.random.default_rng(11).integers(0, 2048, size=(T, 16), dtype=np.int32)
+    whole = dec.decode(codes)
+    assert whole is not None, dec.get_error()
+    dec.stream_reset()
+    parts, t = [], 0
+    for c in chunks:
+        w = dec.decode_append(codes[t:t + c])
+        assert w is not None, dec.get_error()
+        t += c
+        parts.append(w)
+        assert sum(len(p) for p in parts) == 1920 * t - 555
+    got = np.concatenate(parts)
+    assert got.shape == whole.shape
+    assert np.array_equal(got, whole)
+    dec.stream_reset()
+    assert len(dec.decode_append(codes[:2])) == 1920 * 2 - 555
+    dec.stream_reset()
