@@ -680,8 +680,21 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
 #pragma unroll
         for (int i = 0; i < 4; ++i) q[i] = s.qr[lane + 32 * i];
         float mx = -CUDART_INF_F;
+        // the new token's row comes from shared memory; it goes to the warp that the next history row would go to
+        // and is done first, so the whole score phase needs one CTA barrier after its last slice
+        const int n_last = nck > 0 ? pos - (nck - 1) * KV_CH : 0;
+        if (warp == n_last % NCW) {
+            float a = __fmaf_rn(__half2float(s.knew_h[lane]), q[0], 0.0f);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 32]), q[1], a);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 64]), q[2], a);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 96]), q[3], a);
+            const float sv = __fmul_rn(reduce32_lanes(a), kq_scale);
+            mx = fmaxf(mx, sv);
+            if (lane == 0) s.sc[pos] = sv;
+        }
         for (int c = 0; c < nck; ++c) {
             const int s0 = ring_acquire(m, s, rg, wd_);
+            PROF(59);
             const int rows = min(KV_CH, pos - c * KV_CH);
 #pragma unroll 2
             for (int r = warp; r < rows; r += NCW) {
@@ -694,21 +707,12 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
                 mx = fmaxf(mx, sv);
                 if (lane == 0) s.sc[c * KV_CH + r] = sv;
             }
+            if (c + 1 == nck && lane == 0) s.fred[warp] = mx;
             cbar();
             ring_release(s, rg, (rows + 7) >> 3);
         }
-        if (warp == NCW - 1) {                               // the new token's row comes from shared memory
-            float a = __fmaf_rn(__half2float(s.knew_h[lane]), q[0], 0.0f);
-            a = __fmaf_rn(__half2float(s.knew_h[lane + 32]), q[1], a);
-            a = __fmaf_rn(__half2float(s.knew_h[lane + 64]), q[2], a);
-            a = __fmaf_rn(__half2float(s.knew_h[lane + 96]), q[3], a);
-            const float sv = __fmul_rn(reduce32_lanes(a), kq_scale);
-            mx = fmaxf(mx, sv);
-            if (lane == 0) s.sc[pos] = sv;
-        }
-        if (lane == 0) s.fred[warp] = mx;
+        if (nck == 0) { if (lane == 0) s.fred[warp] = mx; cbar(); }
     }
-    cbar();
     PROF(53);
     float M = s.fred[0];
 #pragma unroll
@@ -791,7 +795,7 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     for (int c = 0; c < nck; ++c) {
         const int s0 = ring_acquire(m, s, rg, wd_);
         const int rows = min(KV_CH, pos - c * KV_CH);
-        if (warp < 8) {
+        if (warp < 8 && c * KV_CH < np) {                    // short rows (np == 0) have no 32-lane part at all
 #pragma unroll
             for (int gq = 0; gq < KV_CH / 32; ++gq) {
 #pragma unroll
@@ -843,11 +847,24 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
             sumf = (double) __fadd_rn(__fadd_rn(t0, t1), __fadd_rn(t2, t3));
         }
         const int c_last = nck - 1;
-        for (int tt = np; tt < n_kv; ++tt) {
-            const __half vv = tt == pos ? s.vnew_h[t]
-                            : *reinterpret_cast<const __half *>(kv_row(s, s0_last, tt - c_last * KV_CH) + t * 2);
-            sumf += (double) __fmul_rn(__half2float(vv), __half2float(s.ph[tt]));
+        PROF(57);
+        // four positions per round, branch-free: the loads and products are independent, only the double additions
+        // keep the reference's order.  Positions past the row read a clamped index and add +0.0 (sumf is never
+        // -0.0, so that is an exact no-op); the new token's row is selected by pointer, not by a branch.
+        for (int tt = np; tt < n_kv; tt += 4) {
+            double pd[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int u = tt + j, uc = min(u, n_kv - 1);
+                const __half * hist = reinterpret_cast<const __half *>(kv_row(s, s0_last, uc - c_last * KV_CH)) + t;
+                const __half * src = uc == pos ? s.vnew_h + t : hist;
+                const float pr = __fmul_rn(__half2float(*src), __half2float(s.ph[uc]));
+                pd[j] = u < n_kv ? (double) pr : 0.0;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) sumf += pd[j];
         }
+        PROF(58);
         pk_store(att + t, (float) sumf, ep_out);
     }
     PROF(56);
