@@ -266,7 +266,7 @@ class TTSTransformer:
     def predict_codes(self, hidden, prev_codes=None):
         hidden = np.ascontiguousarray(hidden, np.float32)
         prev = None if prev_codes is None else np.ascontiguousarray(prev_codes, np.int32)
-        out = np.zeros((15, self.cfg.code_pred_vocab_size), np.float32)
+        out = np.zeros((15, self.cfg.code_pred_vocab_size if self.cfg is not None else 2048), np.float32)
         if not self.L.q3t_tts_predict_codes(self.h, _fp(hidden), _ip(prev), _fp(out)):
             return None
         return out

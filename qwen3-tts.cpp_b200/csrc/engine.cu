@@ -116,6 +116,7 @@ extern "C" void q3t_ctx_destroy(q3t_ctx * ctx) {
     ctx->raw.clear();
     for (auto & ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     if (ctx->h_done) cudaFreeHost(ctx->h_done);
+    if (ctx->h_states) cudaFreeHost(ctx->h_states);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -940,14 +941,17 @@ extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * 
     auto ms_since = [&](std::chrono::steady_clock::time_point t0) { return std::chrono::duration<double, std::milli>(now() - t0).count(); };
     double w_setup = 0, w_prefill = 0, w_frames = 0, w_out = 0;
     const auto t_call = now();
-    GenState * hst = nullptr;                                        // pinned: pageable D2H copies stall now and then
-    if (cudaMallocHost(&hst, Q3T_MAX_BATCH * sizeof(GenState)) != cudaSuccess) { cudaFree(rope); return set_err(ctx, Q3T_ERR_CUDA, "cudaMallocHost failed"); }
+    // pinned once per context: page-locking per call stalls for 100s of ms now and then
+    if (!ctx->h_states && cudaMallocHost(&ctx->h_states, Q3T_MAX_BATCH * sizeof(GenState)) != cudaSuccess) {
+        cudaFree(rope); return set_err(ctx, Q3T_ERR_CUDA, "cudaMallocHost failed");
+    }
+    GenState * hst = static_cast<GenState *>(ctx->h_states);
     const size_t per = (size_t) L * NKV * n_ctx * HD;
     float ms_frames = 0.f, ms_prefill = 0.f;
     auto fail = [&](int code) {
         const auto t0 = now();
         for (auto & b : buf) b.release();
-        cudaFree(rope); cudaFreeHost(hst); ctx->hm = saved;
+        cudaFree(rope); ctx->hm = saved;
         if (trace) fprintf(stderr, "[q3t_generate_batch] %d utterances: setup %.1f ms, prompt+prefill %.1f ms, frames %.1f ms, copy-out %.1f ms, release %.1f ms, total %.1f ms\n",
                            n_seq, w_setup, w_prefill, w_frames, w_out, ms_since(t0), ms_since(t_call));
         return code;

@@ -183,6 +183,7 @@ struct q3t_ctx {
 
     q3t_timing timing{};
     int * h_done = nullptr;           // pinned flag pair polled by the generate loop
+    void * h_states = nullptr;        // pinned GenState[Q3T_MAX_BATCH] read back by the batched generate loop
     unsigned long long * d_prof = nullptr; unsigned int * d_prof_n = nullptr; int prof_cap = 0;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
 };

@@ -67,6 +67,13 @@ def test_fails_loudly_without_gpu(q3t, tiny_models):
     assert d.get_error() == "Model not loaded"
     assert t.generate(np.arange(8, dtype=np.int32), None, 4) is None
     assert t.get_error() == "Model not loaded"
+    # the extensions fail the same way (no model, no device): streaming decode, legacy predict_codes, batching
+    d.stream_reset()
+    assert d.decode_append(np.zeros((2, 16), np.int32)) is None
+    assert d.get_error() == "Model not loaded"
+    assert t.predict_codes(np.zeros(1024, np.float32), None) is None
+    assert t.get_error() == "Model not loaded"
+    assert t.generate_batch([(np.arange(8, dtype=np.int32), None)], 4) is None
 
 
 def test_gguf_loader_matches_python_reader(q3t, tiny_models):
