@@ -727,25 +727,29 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
             const bool live = lane < n_kv;
             const bool simd = lane < n8 * 8;
             const float x = live ? __fsub_rn(s.sc[lane], M) : 0.0f;
-            float e = 0.0f;
-            if (live) e = simd ? v_expf(x) : tail_expf(x);
+            // straight-line code (this warp is the critical path of the layer): the SIMD exp is evaluated by every
+            // lane, the libm tail only when the row has one (a warp-uniform test); all sums below are selects,
+            // adding +0.0 to a non-negative double is exact
+            float e = live && simd ? v_expf(x) : 0.0f;
+            if (n8 * 8 < n_kv) {
+                const float et = tail_expf(x);
+                e = live && !simd ? et : e;
+            }
             // chunk sums in the oracle's order: ((e4+e0)+(e6+e2)) + ((e5+e1)+(e7+e3)) per 8 lanes
             float c = simd || !live ? e : 0.0f;              // masked lanes of a SIMD chunk add +0
             c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 4));
             c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 2));
             c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 1));
+            float cs[4], ev[7];
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch) cs[ch] = __shfl_sync(0xffffffffu, c, ch * 8);
+#pragma unroll
+            for (int i = 0; i < 7; ++i) ev[i] = __shfl_sync(0xffffffffu, e, (n8 * 8 + i) & 31);
             double S = 0.0;
 #pragma unroll
-            for (int ch = 0; ch < 4; ++ch) {
-                const float cs = __shfl_sync(0xffffffffu, c, ch * 8);
-                if (ch < n8v) S += (double) cs;
-            }
+            for (int ch = 0; ch < 4; ++ch) S += ch < n8v ? (double) cs[ch] : 0.0;
 #pragma unroll
-            for (int i = 0; i < 7; ++i) {                    // scalar tail, in order
-                const int tt = n8 * 8 + i;
-                const float ev = __shfl_sync(0xffffffffu, e, tt & 31);
-                if (tt < n_kv) S += (double) ev;
-            }
+            for (int i = 0; i < 7; ++i) S += n8 * 8 + i < n_kv ? (double) ev[i] : 0.0;      // scalar tail, in order
             const float inv = (float) (1.0 / S);
             if (live) s.ph[lane] = __float2half_rn(__fmul_rn(e, inv));
         }
