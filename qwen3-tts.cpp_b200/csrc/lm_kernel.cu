@@ -565,6 +565,39 @@ struct AttnRegs {          // per-lane parameters fetched ahead of use (warps 0 
 
 __device__ __forceinline__ uint2 ld_cg_u2(const void * p) { return __ldcg(reinterpret_cast<const uint2 *>(p)); }
 
+// ---- reduce32_lanes() of N accumulators at once ("transposed" butterfly): at every level a lane keeps one
+// half of its values and sends the other half to its partner, so the pair sums a[l] + a[l ^ mask] are formed
+// once instead of twice and N values cost N - 1 + (5 - log2 N) shuffles instead of 5 N.  The pairing per
+// level (xor 16, 8, 4, 1, 2) and therefore every rounding is the one of reduce32_lanes / GGML_F32x8_REDUCE.
+// Returns the finished sum of accumulator `idx` (set on return); every accumulator ends in 32 / N lanes.
+template <int N>
+__device__ __forceinline__ float reduce32_transposed(float (&v)[N], int lane, int & idx) {
+    constexpr int masks[5] = {16, 8, 4, 1, 2};
+    idx = 0;
+    int c = N;
+#pragma unroll
+    for (int lv = 0; lv < 5; ++lv) {
+        const int mask = masks[lv];
+        if (c > 1) {
+            const int h = c >> 1;
+            const bool up = (lane & mask) != 0;
+#pragma unroll
+            for (int k = 0; k < N / 2; ++k) {
+                if (k < h) {
+                    const float send = up ? v[k] : v[k + h];
+                    const float keep = up ? v[k + h] : v[k];
+                    v[k] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, mask));
+                }
+            }
+            if (up) idx += h;
+            c = h;
+        } else {
+            v[0] = __fadd_rn(v[0], __shfl_xor_sync(0xffffffffu, v[0], mask));
+        }
+    }
+    return v[0];
+}
+
 // address of history row r (0..KV_CH) of a K/V slice that starts at ring slot s0
 template <class SM>
 __device__ __forceinline__ const unsigned char * kv_row(const SM & s, int s0, int r) {
@@ -696,18 +729,31 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
             const int s0 = ring_acquire(m, s, rg, wd_);
             PROF(59);
             const int rows = min(KV_CH, pos - c * KV_CH);
-#pragma unroll 2
-            for (int r = warp; r < rows; r += NCW) {
-                const uint2 kk = *reinterpret_cast<const uint2 *>(kv_row(s, s0, r) + lane * 8);
-                const float2 f01 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.x));
-                const float2 f23 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.y));
-                float a = __fmaf_rn(f01.x, q[0], 0.0f);
-                a = __fmaf_rn(f01.y, q[1], a); a = __fmaf_rn(f23.x, q[2], a); a = __fmaf_rn(f23.y, q[3], a);
-                const float sv = __fmul_rn(reduce32_lanes(a), kq_scale);
-                mx = fmaxf(mx, sv);
-                if (lane == 0) s.sc[c * KV_CH + r] = sv;
+            // four rows per warp step: the 32-lane folds of the four dot products share their shuffles
+            // (reduce32_transposed: 6 shuffles instead of 20, same pairing and rounding per value)
+            for (int r0 = warp * 4; r0 < rows; r0 += NCW * 4) {
+                float a[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int r = min(r0 + i, rows - 1);
+                    const uint2 kk = *reinterpret_cast<const uint2 *>(kv_row(s, s0, r) + lane * 8);
+                    const float2 f01 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.x));
+                    const float2 f23 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.y));
+                    a[i] = __fmaf_rn(f01.x, q[0], 0.0f);
+                    a[i] = __fmaf_rn(f01.y, q[1], a[i]); a[i] = __fmaf_rn(f23.x, q[2], a[i]); a[i] = __fmaf_rn(f23.y, q[3], a[i]);
+                }
+                int idx;
+                const float sv = __fmul_rn(reduce32_transposed<4>(a, lane, idx), kq_scale);
+                if (r0 + idx < rows) {
+                    mx = fmaxf(mx, sv);
+                    s.sc[c * KV_CH + r0 + idx] = sv;         // the 8 lanes that hold row idx store the same value
+                }
             }
-            if (c + 1 == nck && lane == 0) s.fred[warp] = mx;
+            if (c + 1 == nck) {
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                if (lane == 0) s.fred[warp] = mx;
+            }
             cbar();
             ring_release(s, rg, (rows + 7) >> 3);
         }
