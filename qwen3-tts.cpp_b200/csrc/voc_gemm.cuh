@@ -215,13 +215,26 @@ vgemm_simt(const VGemm p) {
 //   offset(row, k16B) = (row / 8) * SBO + k16B * LBO + (row % 8) * 16      (core matrix = 8 rows x 16 bytes)
 // and consumed by tcgen05.mma.kind::f16 (F16 x F16 -> F32) issued by one thread.  The A tile of tap t is the
 // activation matrix read at row offset tap_off[t]; rows outside [0, a_rows) are zero-filled by cp.async
-// (= the causal left padding of the reference), so no im2col buffer exists.  4-stage ring: the loads of step
-// i + 3 are in flight while the MMAs of step i run; tcgen05.commit on a per-stage mbarrier frees the stage.
+// (= the causal left padding of the reference), so no im2col buffer exists.
+// Warp-specialised 4-stage ring with no CTA barrier in the K loop: warps 0-7 are loaders (cp.async, three steps
+// in flight; when a step of the warp has landed: cp.async.wait_group, fence.proxy.async, one arrive per warp on
+// the stage's `full` mbarrier), lane 0 of warp 8 waits on `full`, issues the step's MMAs and hands the stage back
+// through tcgen05.commit on its `empty` mbarrier, which the loaders wait on before they overwrite it.
 // Epilogue: tcgen05.ld (each warp owns its 32 TMEM lanes = 32 output rows), fused bias / layer-scale /
 // residual / snake / gelu / swiglu as in vgemm_epilogue_pair.
-constexpr int VU_BM = 128, VU_BK = 32, VU_STAGES = 4, VU_THREADS = 256;
+constexpr int VU_BM = 128, VU_BK = 32, VU_STAGES = 4, VU_THREADS = 256;      // VU_THREADS: loader / epilogue threads
+constexpr int VU_LAUNCH = VU_THREADS + 32;                                   // + the MMA warp
+constexpr int VU_AHEAD = VU_STAGES - 1;                                      // steps a loader keeps in flight
 constexpr int VU_LBO = 128, VU_SBO = (VU_BK / 8) * 128;            // bytes: 4 k-chunks of 16 B per 8-row group
-constexpr int VU_A_STAGE = VU_BM * VU_BK * 2;                       // 8 KB
+constexpr int VU_A_STAGE = VU_BM * VU_BK * 2;                       // 8 KB: A tile of one tap
+// A operand ring.  Its layout keeps the rows of a k-chunk contiguous: offset(row, k16B) = k16B * LBO_A + row * 16
+// (SBO = 128, LBO_A = rows * 16), so the tile "shifted down by d rows" is the same bytes with the descriptor start
+// address advanced by 16 d.  A k-block of a multi-tap conv is therefore loaded ONCE for rows
+// [m0 + min(tap_off), m0 + 127 + max(tap_off)] and every tap's MMA reads it at its own row shift (7x less A
+// traffic for the k7 convs, whose L2 -> SM operand stream is what bounds the 128 x 128 tile).  Taps too far apart
+// (span > VU_SPAN_MAX) and 1-tap GEMMs load a 128-row tile per step as before.
+constexpr int VU_SPAN_MAX = 64, VU_RA_SHARED = VU_BM + VU_SPAN_MAX;  // 192 rows
+constexpr int VU_A_RING = 3 * VU_RA_SHARED * VU_BK * 2;             // 36 KB: 3 shared stages (or 4 per-step stages of 8 KB)
 __host__ __device__ constexpr int vu_b_stage(int bn) { return bn * VU_BK * 2; }
 
 __device__ __forceinline__ uint32_t vu_smem(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
@@ -230,29 +243,39 @@ __device__ __forceinline__ uint64_t vu_desc(uint32_t saddr) {
     // version 1 [46,48), layout type SWIZZLE_NONE [61,64)
     return (uint64_t) ((saddr & 0x3FFFFu) >> 4) | ((uint64_t) (VU_LBO >> 4) << 16) | ((uint64_t) (VU_SBO >> 4) << 32) | (1ull << 46);
 }
+__device__ __forceinline__ uint64_t vu_desc2(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t) ((saddr & 0x3FFFFu) >> 4) | ((uint64_t) (lbo >> 4) << 16) | ((uint64_t) (sbo >> 4) << 32) | (1ull << 46);
+}
 __device__ __forceinline__ void vu_cp16(uint32_t dst, const void * src, bool ok) {
     const int n = ok ? 16 : 0;                                      // src-size 0: the 16 bytes are zero-filled
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(n) : "memory");
 }
 
+__device__ __forceinline__ void vu_mbar_wait(unsigned long long * bar, uint32_t parity) {
+    asm volatile("{ .reg .pred q; W_%=: mbarrier.try_wait.parity.shared::cta.b64 q, [%0], %1; @q bra D_%=; bra W_%=; D_%=: }"
+                 :: "r"(vu_smem(bar)), "r"(parity) : "memory");
+}
+
 template <int EPI>
-__global__ void __launch_bounds__(VU_THREADS)
+__global__ void __launch_bounds__(VU_LAUNCH)
 vgemm_umma(const VGemm p, const int BN) {
     extern __shared__ __align__(1024) unsigned char vu_sm[];
-    __shared__ unsigned long long mbar[VU_STAGES];
+    __shared__ unsigned long long mbar_full[VU_STAGES], mbar_empty[VU_STAGES];
     __shared__ unsigned long long mbar_done;
     __shared__ uint32_t tmem_base_s;
     const int tid = threadIdx.x, warp = tid >> 5;
     const long m0 = (long) blockIdx.x * VU_BM;
     const int n0 = blockIdx.y * BN;
     const int b_stage = vu_b_stage(BN);
-    unsigned char * smA = vu_sm;                                    // [stage][128 x 32 halves]
-    unsigned char * smB = vu_sm + VU_STAGES * VU_A_STAGE;           // [stage][BN x 32 halves]
+    unsigned char * smA = vu_sm;                                    // A ring (see VU_A_RING)
+    unsigned char * smB = vu_sm + VU_A_RING;                        // [stage][BN x 32 halves]
     const int tmem_cols = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
 
     if (tid == 0) {
-        for (int i = 0; i < VU_STAGES; ++i)
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(vu_smem(&mbar[i])));
+        for (int i = 0; i < VU_STAGES; ++i) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(vu_smem(&mbar_full[i])), "n"(VU_THREADS / 32));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(vu_smem(&mbar_empty[i])));
+        }
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(vu_smem(&mbar_done)));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -265,18 +288,24 @@ vgemm_umma(const VGemm p, const int BN) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = tmem_base_s;
 
-    const int kpt = p.Kc / VU_BK;                                    // k steps per tap
-    const int n_steps = p.ntaps * kpt;
+    // step = kb * ntaps + tap (k-block major): the taps of a k-block share one A stage when their offsets are close
+    const int n_steps = p.ntaps * (p.Kc / VU_BK);
     const int Ktot = p.ntaps * p.Kc;
+    int min_off = p.tap_off[0], max_off = p.tap_off[0];
+    for (int i = 1; i < p.ntaps; ++i) { min_off = min(min_off, p.tap_off[i]); max_off = max(max_off, p.tap_off[i]); }
+    const bool share = p.ntaps > 1 && max_off - min_off <= VU_SPAN_MAX;
+    const int ra = share ? VU_RA_SHARED : VU_BM;                     // rows of an A stage
+    const uint32_t lbo_a = (uint32_t) ra * 16, a_stage_b = (uint32_t) ra * VU_BK * 2;
+    const int n_a_stages = share ? 3 : VU_STAGES;
+    const int ra_used = share ? VU_BM + (max_off - min_off) : VU_BM;
     // instruction descriptor (kind::f16): D = F32 [4,6) = 1, A = B = F16, both K-major, N >> 3 [17,23), M >> 4 [24,29)
     const uint32_t idesc = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (VU_BM >> 4) << 24);
 
     // per-thread loader state, fixed for the whole K loop: the thread owns 16-byte chunk (row r, k-chunk kc) of
-    // two A rows (r, r + 64) and of up to two W rows; only the tap's row offset and the k origin change per step
+    // A rows r, r + 64 (, r + 128) and of up to two W rows; only the row origin and the k origin change per step
     const int l_r = tid >> 2, l_kc = tid & 3;
-    const uint32_t l_soff = (uint32_t) ((l_r >> 3) * VU_SBO + l_kc * VU_LBO + (l_r & 7) * 16);   // rows r and r + 64: + 8 * SBO
-    const long l_arow0 = m0 + l_r;                                                              // A row before the tap offset
-    const bool l_m_ok0 = l_arow0 < p.M, l_m_ok1 = l_arow0 + 64 < p.M;
+    const uint32_t l_soff = (uint32_t) ((l_r >> 3) * VU_SBO + l_kc * VU_LBO + (l_r & 7) * 16);   // B: rows r and r + 64: + 8 * SBO
+    const uint32_t l_aoff = (uint32_t) l_kc * lbo_a + (uint32_t) l_r * 16;                        // A: rows r + 64 i: + 1024 i
     const __half * l_a = p.A + l_kc * 8;
     const bool l_w_ok0 = l_r < BN && n0 + l_r < p.N, l_w_ok1 = l_r + 64 < BN && n0 + l_r + 64 < p.N;
     const __half * l_w0 = p.W + (size_t) (l_w_ok0 ? n0 + l_r : 0) * Ktot + l_kc * 8;
@@ -285,63 +314,72 @@ vgemm_umma(const VGemm p, const int BN) {
 
     auto load_step = [&](int step) {
         const int stage = step % VU_STAGES;
-        const int tap = step / kpt, k0 = (step - tap * kpt) * VU_BK;
-        const uint32_t a_dst = vu_smem(smA + stage * VU_A_STAGE) + l_soff, b_dst = vu_smem(smB + stage * b_stage) + l_soff;
-        const long ar0 = l_arow0 + p.tap_off[tap], ar1 = ar0 + 64;
-        const bool ok0 = l_m_ok0 && ar0 >= 0 && ar0 < p.a_rows, ok1 = l_m_ok1 && ar1 >= 0 && ar1 < p.a_rows;
-        vu_cp16(a_dst, l_a + (size_t) (ok0 ? ar0 : 0) * p.lda + k0, ok0);
-        vu_cp16(a_dst + 8 * VU_SBO, l_a + (size_t) (ok1 ? ar1 : 0) * p.lda + k0, ok1);
-        // W: column tap * Kc + k0 = step * BK (the taps are contiguous in a W row)
-        if (l_w_has0) vu_cp16(b_dst, l_w0 + (size_t) step * VU_BK, l_w_ok0);
-        if (l_w_has1) vu_cp16(b_dst + 8 * VU_SBO, l_w1 + (size_t) step * VU_BK, l_w_ok1);
+        const int kb = step / p.ntaps, tap = step - kb * p.ntaps, k0 = kb * VU_BK;
+        if (!share || tap == 0) {
+            const int ast = (share ? kb : step) % n_a_stages;
+            const uint32_t a_dst = vu_smem(smA) + (uint32_t) ast * a_stage_b + l_aoff;
+            const long ar = m0 + l_r + (share ? min_off : p.tap_off[tap]);
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                if (l_r + 64 * i < ra_used) {
+                    const long a = ar + 64 * i;
+                    const bool ok = a >= 0 && a < p.a_rows;
+                    vu_cp16(a_dst + 1024 * i, l_a + (size_t) (ok ? a : 0) * p.lda + k0, ok);
+                }
+            }
+        }
+        const uint32_t b_dst = vu_smem(smB + stage * b_stage) + l_soff;
+        const size_t wcol = (size_t) tap * p.Kc + k0;
+        if (l_w_has0) vu_cp16(b_dst, l_w0 + wcol, l_w_ok0);
+        if (l_w_has1) vu_cp16(b_dst + 8 * VU_SBO, l_w1 + wcol, l_w_ok1);
     };
 
-    // prologue: S - 1 steps in flight
-    for (int s = 0; s < VU_STAGES - 1; ++s) {
-        if (s < n_steps) load_step(s);
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    }
-    for (int step = 0; step < n_steps; ++step) {
-        const int stage = step % VU_STAGES;
-        asm volatile("cp.async.wait_group %0;" :: "n"(VU_STAGES - 2) : "memory");      // this thread's part of `step` landed
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                  // generic-proxy writes -> async proxy (UMMA)
-        __syncthreads();
-        if (tid == 0) {
+    if (warp < VU_THREADS / 32) {
+        // ---- loaders: iteration `it` issues the loads of step `it` and publishes step it - (VU_AHEAD - 1)
+        for (int it = 0; it < n_steps + VU_AHEAD - 1; ++it) {
+            if (it < n_steps) {
+                if (it >= VU_STAGES) vu_mbar_wait(&mbar_empty[it % VU_STAGES], (uint32_t) ((it / VU_STAGES) - 1) & 1u);
+                load_step(it);
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");                          // possibly empty: keeps the group count = it + 1
+            const int ready = it - (VU_AHEAD - 1);
+            if (ready >= 0) {
+                asm volatile("cp.async.wait_group %0;" :: "n"(VU_AHEAD - 1) : "memory");  // this thread's part of step `ready` landed
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");              // generic-proxy writes -> async proxy (UMMA)
+                __syncwarp();
+                if ((tid & 31) == 0)
+                    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(vu_smem(&mbar_full[ready % VU_STAGES])) : "memory");
+            }
+        }
+    } else if (tid == VU_THREADS) {
+        // ---- MMA issuer
+        for (int step = 0; step < n_steps; ++step) {
+            const int stage = step % VU_STAGES;
+            vu_mbar_wait(&mbar_full[stage], (uint32_t) (step / VU_STAGES) & 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t a_base = vu_smem(smA + stage * VU_A_STAGE), b_base = vu_smem(smB + stage * b_stage);
+            const int kb = step / p.ntaps, tap = step - kb * p.ntaps;
+            const uint32_t a_base = vu_smem(smA) + (uint32_t) ((share ? kb : step) % n_a_stages) * a_stage_b
+                                  + (share ? (uint32_t) (p.tap_off[tap] - min_off) * 16u : 0u);
+            const uint32_t b_base = vu_smem(smB + stage * b_stage);
 #pragma unroll
             for (int kk = 0; kk < VU_BK / 16; ++kk) {
-                const uint64_t ad = vu_desc(a_base + kk * 2 * VU_LBO), bd = vu_desc(b_base + kk * 2 * VU_LBO);
+                const uint64_t ad = vu_desc2(a_base + kk * 2 * lbo_a, lbo_a, 128u), bd = vu_desc(b_base + kk * 2 * VU_LBO);
                 const uint32_t accum = (step > 0 || kk > 0) ? 1u : 0u;
                 asm volatile("{ .reg .pred q; setp.ne.b32 q, %4, 0; tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, q; }"
                              :: "r"(tmem_d), "l"(ad), "l"(bd), "r"(idesc), "r"(accum) : "memory");
             }
             // frees this stage when the MMAs above (and all earlier ones) have read their operands
-            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(vu_smem(&mbar[stage])) : "memory");
-            if (step == n_steps - 1)
-                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(vu_smem(&mbar_done)) : "memory");
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(vu_smem(&mbar_empty[stage])) : "memory");
         }
-        // refill the stage used by step - 1 with step + S - 1 once its MMAs are done
-        const int nxt = step + VU_STAGES - 1;
-        if (nxt < n_steps) {
-            if (step >= 1) {
-                const int ps = (step - 1) % VU_STAGES;
-                const uint32_t parity = ((step - 1) / VU_STAGES) & 1;
-                asm volatile("{ .reg .pred q; W_%=: mbarrier.try_wait.parity.shared::cta.b64 q, [%0], %1; @q bra D_%=; bra W_%=; D_%=: }"
-                             :: "r"(vu_smem(&mbar[ps])), "r"(parity) : "memory");
-            }
-            load_step(nxt);
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(vu_smem(&mbar_done)) : "memory");
     }
     // ---- epilogue: TMEM -> registers (thread = output row) -> shared memory (padded rows) -> coalesced fused
     //      epilogue (consecutive threads = consecutive column pairs; per-column parameters live in registers)
-    asm volatile("{ .reg .pred q; W_%=: mbarrier.try_wait.parity.shared::cta.b64 q, [%0], 0; @q bra D_%=; bra W_%=; D_%=: }"
-                 :: "r"(vu_smem(&mbar_done)) : "memory");
+    vu_mbar_wait(&mbar_done, 0u);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     float * stg = reinterpret_cast<float *>(vu_sm);                   // the operand ring is idle now
     const int sld = BN + 4;                                           // row stride (floats): 16-byte aligned, conflict-free float4 rows
-    {
+    if (warp < VU_THREADS / 32) {
         // a warp may touch TMEM lanes 32 * (warp % 4) .. + 31 only: warps w and w + 4 share a lane quadrant and
         // take alternate 16-column chunks
         const int quad = warp & 3, lane = tid & 31;
@@ -409,8 +447,8 @@ inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
         // widest tile <= 128 columns that divides N (no half-empty last tile), else 128 / N rounded up to 16
         int BN = p.N >= 128 ? 128 : ((p.N + 15) / 16) * 16;
         for (int c = 128; c >= 64; c -= 16) if (p.N % c == 0) { BN = c; break; }
-        const int smem = std::max(VU_STAGES * (VU_A_STAGE + vu_b_stage(BN)), VU_BM * (BN + 4) * 4);
-        const int smem_max = std::max(VU_STAGES * (VU_A_STAGE + vu_b_stage(128)), VU_BM * (128 + 4) * 4);
+        const int smem = std::max(VU_A_RING + VU_STAGES * vu_b_stage(BN), VU_BM * (BN + 4) * 4);
+        const int smem_max = std::max(VU_A_RING + VU_STAGES * vu_b_stage(128), VU_BM * (128 + 4) * 4);
         static bool attr = false;
         if (!attr) {
             cudaFuncSetAttribute(vgemm_umma<VEPI_GENERIC>,    cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
@@ -422,13 +460,13 @@ inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
         dim3 grid((unsigned) ((p.M + VU_BM - 1) / VU_BM), (unsigned) ((p.N + BN - 1) / BN));
         const bool snake16 = p.bias && !p.gamma && !p.swiglu && p.out16 && p.act == VACT_SNAKE && (p.ld16 & 1) == 0;
         if (snake16 && !p.res && !p.out32)
-            vgemm_umma<VEPI_BIAS_SNAKE><<<grid, VU_THREADS, smem, ctx->stream>>>(p, BN);
+            vgemm_umma<VEPI_BIAS_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN);
         else if (snake16 && p.res && (p.ldres & 1) == 0 && (!p.out32 || (p.ld32 & 1) == 0))
-            vgemm_umma<VEPI_RES_SNAKE><<<grid, VU_THREADS, smem, ctx->stream>>>(p, BN);
+            vgemm_umma<VEPI_RES_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN);
         else if (snake16 && !p.res && p.out32 && (p.ld32 & 1) == 0)
-            vgemm_umma<VEPI_O32_SNAKE><<<grid, VU_THREADS, smem, ctx->stream>>>(p, BN);
+            vgemm_umma<VEPI_O32_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN);
         else
-            vgemm_umma<VEPI_GENERIC><<<grid, VU_THREADS, smem, ctx->stream>>>(p, BN);
+            vgemm_umma<VEPI_GENERIC><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN);
         return;
     }
     dim3 grid((unsigned) ((p.M + VG_BM - 1) / VG_BM), (unsigned) ((p.N + VG_BN - 1) / VG_BN));

@@ -1,0 +1,4 @@
+set -x
+timeout 120 tools/microbench/bin/umma_test > gpurun_out/umma_test.txt 2>&1; echo "umma rc=$?"; cat gpurun_out/umma_test.txt
+timeout 600 python -m pytest tests/test_vocoder_gpu.py -m gpu -q -x 2>&1 | tail -3
+timeout 120 python tests/dev_voc_only.py 2>&1 | tail -3

@@ -115,6 +115,10 @@ int main() {
     ok &= run_case(&ctx, 777, 768, 768, 7, o7, 777, true, false);
     ok &= run_case(&ctx, 2559, 768, 1536, 2, o2, 2560, false, false);
     ok &= run_case(&ctx, 5000, 192, 192, 7, o7d, 5000, true, false);
+    const int o7e[7] = {-54, -45, -36, -27, -18, -9, 0}, ofar[2] = {-80, 0}, o3[3] = {-2, -1, 0};
+    ok &= run_case(&ctx, 3000, 384, 384, 7, o7e, 3000, true, false);     // dilation 9: 182-row shared A stage
+    ok &= run_case(&ctx, 1000, 128, 64, 2, ofar, 1000, true, false);      // taps too far apart: per-step A tiles
+    ok &= run_case(&ctx, 130, 512, 1024, 3, o3, 130, false, false);
     ok &= run_epi_case(&ctx, 1000, 96, 96);
     ok &= run_epi_case(&ctx, 598485, 96, 96);
     ok &= run_epi_case(&ctx, 199500, 192, 192);
