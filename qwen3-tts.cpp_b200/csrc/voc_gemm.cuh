@@ -233,8 +233,14 @@ constexpr int VU_A_STAGE = VU_BM * VU_BK * 2;                       // 8 KB: A t
 // [m0 + min(tap_off), m0 + 127 + max(tap_off)] and every tap's MMA reads it at its own row shift (7x less A
 // traffic for the k7 convs, whose L2 -> SM operand stream is what bounds the 128 x 128 tile).  Taps too far apart
 // (span > VU_SPAN_MAX) and 1-tap GEMMs load a 128-row tile per step as before.
-constexpr int VU_SPAN_MAX = 64, VU_RA_SHARED = VU_BM + VU_SPAN_MAX;  // 192 rows
-constexpr int VU_A_RING = 3 * VU_RA_SHARED * VU_BK * 2;             // 36 KB: 3 shared stages (or 4 per-step stages of 8 KB)
+// MT = 2: the CTA owns two M tiles (256 rows, two accumulators in TMEM): every B stage feeds two MMAs, which
+// halves the W traffic per flop; used when the grid still fills the GPU.
+constexpr int VU_SPAN_MAX = 64;
+__host__ __device__ constexpr int vu_ra_shared(int mt) { return VU_BM * mt + VU_SPAN_MAX; }            // 192 / 320 rows
+__host__ __device__ constexpr int vu_a_ring(int mt) {                                                  // 36 KB / 64 KB
+    return 3 * vu_ra_shared(mt) * VU_BK * 2 > VU_STAGES * VU_BM * mt * VU_BK * 2 ? 3 * vu_ra_shared(mt) * VU_BK * 2
+                                                                                  : VU_STAGES * VU_BM * mt * VU_BK * 2;
+}
 __host__ __device__ constexpr int vu_b_stage(int bn) { return bn * VU_BK * 2; }
 
 __device__ __forceinline__ uint32_t vu_smem(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
@@ -258,18 +264,18 @@ __device__ __forceinline__ void vu_mbar_wait(unsigned long long * bar, uint32_t 
 
 template <int EPI>
 __global__ void __launch_bounds__(VU_LAUNCH)
-vgemm_umma(const VGemm p, const int BN) {
+vgemm_umma(const VGemm p, const int BN, const int MT) {
     extern __shared__ __align__(1024) unsigned char vu_sm[];
     __shared__ unsigned long long mbar_full[VU_STAGES], mbar_empty[VU_STAGES];
     __shared__ unsigned long long mbar_done;
     __shared__ uint32_t tmem_base_s;
     const int tid = threadIdx.x, warp = tid >> 5;
-    const long m0 = (long) blockIdx.x * VU_BM;
+    const long m0 = (long) blockIdx.x * VU_BM * MT;
     const int n0 = blockIdx.y * BN;
     const int b_stage = vu_b_stage(BN);
     unsigned char * smA = vu_sm;                                    // A ring (see VU_A_RING)
-    unsigned char * smB = vu_sm + VU_A_RING;                        // [stage][BN x 32 halves]
-    const int tmem_cols = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+    unsigned char * smB = vu_sm + vu_a_ring(MT);                    // [stage][BN x 32 halves]
+    const int tmem_cols = BN * MT <= 32 ? 32 : BN * MT <= 64 ? 64 : BN * MT <= 128 ? 128 : 256;   // tile j: columns j * BN ..
 
     if (tid == 0) {
         for (int i = 0; i < VU_STAGES; ++i) {
@@ -294,15 +300,15 @@ vgemm_umma(const VGemm p, const int BN) {
     int min_off = p.tap_off[0], max_off = p.tap_off[0];
     for (int i = 1; i < p.ntaps; ++i) { min_off = min(min_off, p.tap_off[i]); max_off = max(max_off, p.tap_off[i]); }
     const bool share = p.ntaps > 1 && max_off - min_off <= VU_SPAN_MAX;
-    const int ra = share ? VU_RA_SHARED : VU_BM;                     // rows of an A stage
+    const int ra = share ? vu_ra_shared(MT) : VU_BM * MT;            // rows of an A stage
     const uint32_t lbo_a = (uint32_t) ra * 16, a_stage_b = (uint32_t) ra * VU_BK * 2;
     const int n_a_stages = share ? 3 : VU_STAGES;
-    const int ra_used = share ? VU_BM + (max_off - min_off) : VU_BM;
+    const int ra_used = VU_BM * MT + (share ? max_off - min_off : 0);
     // instruction descriptor (kind::f16): D = F32 [4,6) = 1, A = B = F16, both K-major, N >> 3 [17,23), M >> 4 [24,29)
     const uint32_t idesc = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (VU_BM >> 4) << 24);
 
     // per-thread loader state, fixed for the whole K loop: the thread owns 16-byte chunk (row r, k-chunk kc) of
-    // A rows r, r + 64 (, r + 128) and of up to two W rows; only the row origin and the k origin change per step
+    // A rows r + 64 i (i < 5) and of up to two W rows; only the row origin and the k origin change per step
     const int l_r = tid >> 2, l_kc = tid & 3;
     const uint32_t l_soff = (uint32_t) ((l_r >> 3) * VU_SBO + l_kc * VU_LBO + (l_r & 7) * 16);   // B: rows r and r + 64: + 8 * SBO
     const uint32_t l_aoff = (uint32_t) l_kc * lbo_a + (uint32_t) l_r * 16;                        // A: rows r + 64 i: + 1024 i
@@ -320,7 +326,7 @@ vgemm_umma(const VGemm p, const int BN) {
             const uint32_t a_dst = vu_smem(smA) + (uint32_t) ast * a_stage_b + l_aoff;
             const long ar = m0 + l_r + (share ? min_off : p.tap_off[tap]);
 #pragma unroll
-            for (int i = 0; i < 3; ++i) {
+            for (int i = 0; i < 5; ++i) {
                 if (l_r + 64 * i < ra_used) {
                     const long a = ar + 64 * i;
                     const bool ok = a >= 0 && a < p.a_rows;
@@ -367,6 +373,11 @@ vgemm_umma(const VGemm p, const int BN) {
                 const uint32_t accum = (step > 0 || kk > 0) ? 1u : 0u;
                 asm volatile("{ .reg .pred q; setp.ne.b32 q, %4, 0; tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, q; }"
                              :: "r"(tmem_d), "l"(ad), "l"(bd), "r"(idesc), "r"(accum) : "memory");
+                if (MT == 2) {                                   // second M tile: A rows + 128, accumulator columns + BN
+                    const uint64_t ad1 = vu_desc2(a_base + kk * 2 * lbo_a + VU_BM * 16, lbo_a, 128u);
+                    asm volatile("{ .reg .pred q; setp.ne.b32 q, %4, 0; tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, q; }"
+                                 :: "r"(tmem_d + (uint32_t) BN), "l"(ad1), "l"(bd), "r"(idesc), "r"(accum) : "memory");
+                }
             }
             // frees this stage when the MMAs above (and all earlier ones) have read their operands
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(vu_smem(&mbar_empty[stage])) : "memory");
@@ -379,6 +390,10 @@ vgemm_umma(const VGemm p, const int BN) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     float * stg = reinterpret_cast<float *>(vu_sm);                   // the operand ring is idle now
     const int sld = BN + 4;                                           // row stride (floats): 16-byte aligned, conflict-free float4 rows
+    for (int mt = 0; mt < MT; ++mt) {
+    const long m0t = m0 + (long) mt * VU_BM;
+    if (m0t >= p.M) break;                                            // uniform over the CTA
+    if (mt > 0) __syncthreads();                                      // the staging buffer is being read by the previous tile's stores
     if (warp < VU_THREADS / 32) {
         // a warp may touch TMEM lanes 32 * (warp % 4) .. + 31 only: warps w and w + 4 share a lane quadrant and
         // take alternate 16-column chunks
@@ -386,7 +401,7 @@ vgemm_umma(const VGemm p, const int BN) {
         const int row = quad * 32 + lane;
         for (int c0 = (warp >> 2) * 16; c0 < BN; c0 += 32) {
             uint32_t v[16];
-            const uint32_t taddr = tmem_d + ((uint32_t) (quad * 32) << 16) + (uint32_t) c0;
+            const uint32_t taddr = tmem_d + ((uint32_t) (quad * 32) << 16) + (uint32_t) (mt * BN + c0);
             asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
                          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
                            "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
@@ -416,14 +431,14 @@ vgemm_umma(const VGemm p, const int BN) {
                     float2 rr[U];
 #pragma unroll
                     for (int u = 0; u < U; ++u) {
-                        const size_t m = (size_t) m0 + rb + u * rpp;
+                        const size_t m = (size_t) m0t + rb + u * rpp;
                         rr[u] = ((EPI == VEPI_GENERIC || EPI == VEPI_RES_SNAKE) && rb + u * rpp < VU_BM && m < (size_t) p.M)
                               ? vgemm_load_res(p, m, n, ok1) : make_float2(0.0f, 0.0f);
                     }
 #pragma unroll
                     for (int u = 0; u < U; ++u) {
                         const int r = rb + u * rpp;
-                        const size_t m = (size_t) m0 + r;
+                        const size_t m = (size_t) m0t + r;
                         if (r < VU_BM && m < (size_t) p.M) {
                             const float2 v = *reinterpret_cast<const float2 *>(stg + (size_t) r * sld + 2 * pr);
                             vgemm_epilogue_cols<EPI>(p, m, n, v.x, v.y, ok1, ec, rr[u]);
@@ -433,6 +448,8 @@ vgemm_umma(const VGemm p, const int BN) {
             }
         }
     }
+    }   // M tiles
+    __syncthreads();                                                  // every warp is done with TMEM
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_d), "r"(tmem_cols) : "memory");
 }
 
@@ -447,8 +464,13 @@ inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
         // widest tile <= 128 columns that divides N (no half-empty last tile), else 128 / N rounded up to 16
         int BN = p.N >= 128 ? 128 : ((p.N + 15) / 16) * 16;
         for (int c = 128; c >= 64; c -= 16) if (p.N % c == 0) { BN = c; break; }
-        const int smem = std::max(VU_A_RING + VU_STAGES * vu_b_stage(BN), VU_BM * (BN + 4) * 4);
-        const int smem_max = std::max(VU_A_RING + VU_STAGES * vu_b_stage(128), VU_BM * (128 + 4) * 4);
+        // two M tiles per CTA when the grid still gives every SM its two resident CTAs
+        const long tiles256 = (long) ((p.M + 2 * VU_BM - 1) / (2 * VU_BM)) * ((p.N + BN - 1) / BN);
+        static int mt_env = -1;
+        if (mt_env < 0) { const char * e = getenv("Q3T_VOC_MT"); mt_env = e ? atoi(e) : 0; }
+        const int MT = mt_env ? mt_env : (tiles256 >= 2 * 148 && p.ntaps * p.Kc >= 1024 ? 2 : 1);   // short K: the epilogue dominates, keep 3 CTAs per SM
+        const int smem = std::max(vu_a_ring(MT) + VU_STAGES * vu_b_stage(BN), VU_BM * (BN + 4) * 4);
+        const int smem_max = std::max(vu_a_ring(2) + VU_STAGES * vu_b_stage(128), VU_BM * (128 + 4) * 4);
         static bool attr = false;
         if (!attr) {
             cudaFuncSetAttribute(vgemm_umma<VEPI_GENERIC>,    cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
@@ -457,16 +479,16 @@ inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
             cudaFuncSetAttribute(vgemm_umma<VEPI_O32_SNAKE>,  cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
             attr = true;
         }
-        dim3 grid((unsigned) ((p.M + VU_BM - 1) / VU_BM), (unsigned) ((p.N + BN - 1) / BN));
+        dim3 grid((unsigned) ((p.M + VU_BM * MT - 1) / (VU_BM * MT)), (unsigned) ((p.N + BN - 1) / BN));
         const bool snake16 = p.bias && !p.gamma && !p.swiglu && p.out16 && p.act == VACT_SNAKE && (p.ld16 & 1) == 0;
         if (snake16 && !p.res && !p.out32)
-            vgemm_umma<VEPI_BIAS_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN);
+            vgemm_umma<VEPI_BIAS_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT);
         else if (snake16 && p.res && (p.ldres & 1) == 0 && (!p.out32 || (p.ld32 & 1) == 0))
-            vgemm_umma<VEPI_RES_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN);
+            vgemm_umma<VEPI_RES_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT);
         else if (snake16 && !p.res && p.out32 && (p.ld32 & 1) == 0)
-            vgemm_umma<VEPI_O32_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN);
+            vgemm_umma<VEPI_O32_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT);
         else
-            vgemm_umma<VEPI_GENERIC><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN);
+            vgemm_umma<VEPI_GENERIC><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT);
         return;
     }
     dim3 grid((unsigned) ((p.M + VG_BM - 1) / VG_BM), (unsigned) ((p.N + VG_BN - 1) / VG_BN));

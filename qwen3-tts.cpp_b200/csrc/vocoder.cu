@@ -194,58 +194,91 @@ __global__ void k_rope_qk(float * __restrict__ qkv, const float * __restrict__ r
     }
 }
 
-// causal attention, F32 (the vocoder's K/Q/V never pass through F16: :450-470), one warp per
-// (query, head): scores over keys 0..t in chunks of 32 lanes, two-pass soft-max, P.V; out F16
-// (operand of the o-projection).
-__global__ void k_attention(const float * __restrict__ qkv, __half * __restrict__ out, int T) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int t = blockIdx.x * 4 + warp, h = blockIdx.y;
-    __shared__ float qs[4][THD];
-    __shared__ float ps[4][32];
-    if (t < T) { qs[warp][lane] = qkv[(size_t) t * 3072 + h * THD + lane]; qs[warp][lane + 32] = qkv[(size_t) t * 3072 + h * THD + lane + 32]; }
-    __syncwarp();
-    if (t >= T) return;
-    const float scale = 0.125f;                       // 1/sqrt(64)
+// causal attention, F32 (the vocoder's K/Q/V never pass through F16: :450-470); out F16 (operand of the
+// o-projection).
+constexpr int VA_QW = 4, VA_QB = 4 * VA_QW;          // queries per warp / per block (4 warps)
+__global__ void __launch_bounds__(128)
+k_attention(const float * __restrict__ qkv, __half * __restrict__ out, int T) {
+    // Causal soft-max attention of 16 consecutive queries of one head.  K/V tiles of 32 positions are staged in
+    // shared memory once per block (K transposed: lane = key position in the score loop), a warp carries four
+    // queries through the tile (running max / sum, F32), lane = output dims (lane, lane + 32) in the P.V loop.
+    // Tiles start at absolute multiples of 32 and masked keys contribute exact zeros, so a query's result does
+    // not depend on how many rows the call has (streaming decode == whole decode, bit for bit).
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, h = blockIdx.y;
+    const int tq0 = blockIdx.x * VA_QB + warp * VA_QW;
+    __shared__ float Ks[THD * 33];
+    __shared__ __align__(16) float Vs[32 * THD];
+    __shared__ float qs[4][VA_QW][THD];
+#pragma unroll
+    for (int qi = 0; qi < VA_QW; ++qi) {
+        const int t = tq0 + qi;
+        qs[warp][qi][lane]      = t < T ? qkv[(size_t) t * 3072 + h * THD + lane] * 0.125f : 0.f;        // 1/sqrt(64), exact
+        qs[warp][qi][lane + 32] = t < T ? qkv[(size_t) t * 3072 + h * THD + lane + 32] * 0.125f : 0.f;
+    }
     const float * kb = qkv + LATENT + h * THD;
     const float * vb = qkv + 2 * LATENT + h * THD;
-    float mx = -INFINITY;
-    for (int j0 = 0; j0 <= t; j0 += 32) {
-        const int j = j0 + lane;
-        if (j <= t) {
-            const float4 * kr = reinterpret_cast<const float4 *>(kb + (size_t) j * 3072);
-            float acc = 0.f;
+    float m[VA_QW], l[VA_QW], o0[VA_QW], o1[VA_QW];
 #pragma unroll
-            for (int d = 0; d < 16; ++d) { const float4 k4 = kr[d]; acc += k4.x * qs[warp][4 * d] + k4.y * qs[warp][4 * d + 1] + k4.z * qs[warp][4 * d + 2] + k4.w * qs[warp][4 * d + 3]; }
-            mx = fmaxf(mx, acc * scale);
+    for (int qi = 0; qi < VA_QW; ++qi) { m[qi] = -INFINITY; l[qi] = 0.f; o0[qi] = 0.f; o1[qi] = 0.f; }
+    const int t_last = min(T - 1, (int) blockIdx.x * VA_QB + VA_QB - 1);
+    const int ntiles = t_last / 32 + 1;
+    for (int tile = 0; tile < ntiles; ++tile) {
+        const int j0 = tile * 32;
+        __syncthreads();                                         // the previous tile has been consumed
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int idx = threadIdx.x + 128 * i, row = idx >> 4, c4 = idx & 15;
+            float4 k4 = make_float4(0.f, 0.f, 0.f, 0.f), v4 = k4;
+            if (j0 + row < T) {
+                k4 = reinterpret_cast<const float4 *>(kb + (size_t) (j0 + row) * 3072)[c4];
+                v4 = reinterpret_cast<const float4 *>(vb + (size_t) (j0 + row) * 3072)[c4];
+            }
+            Ks[(4 * c4) * 33 + row] = k4.x; Ks[(4 * c4 + 1) * 33 + row] = k4.y; Ks[(4 * c4 + 2) * 33 + row] = k4.z; Ks[(4 * c4 + 3) * 33 + row] = k4.w;
+            reinterpret_cast<float4 *>(Vs + row * THD)[c4] = v4;
+        }
+        __syncthreads();
+        if (j0 > tq0 + VA_QW - 1 || tq0 >= T) continue;          // warp-uniform: nothing visible to this warp's queries
+        float sc[VA_QW];
+#pragma unroll
+        for (int qi = 0; qi < VA_QW; ++qi) sc[qi] = 0.f;
+#pragma unroll 16
+        for (int d = 0; d < THD; ++d) {
+            const float kd = Ks[d * 33 + lane];
+#pragma unroll
+            for (int qi = 0; qi < VA_QW; ++qi) sc[qi] = fmaf(kd, qs[warp][qi][d], sc[qi]);
+        }
+        float pq[VA_QW];
+#pragma unroll
+        for (int qi = 0; qi < VA_QW; ++qi) {
+            const int t = tq0 + qi;
+            const bool valid = j0 + lane <= t && t < T;
+            const float sv = valid ? sc[qi] : -INFINITY;
+            const float mn = fmaxf(m[qi], warp_max(sv));
+            float p = 0.f, corr = 1.f;
+            if (mn != -INFINITY) { p = valid ? expf(sv - mn) : 0.f; corr = expf(m[qi] - mn); }
+            l[qi] = l[qi] * corr + warp_sum(p);
+            o0[qi] *= corr; o1[qi] *= corr;
+            m[qi] = mn; pq[qi] = p;
+        }
+        const int nj = min(32, tq0 + VA_QW - j0);                // keys beyond the warp's last query have p = 0
+        for (int j = 0; j < nj; ++j) {
+            const float v0 = Vs[j * THD + lane], v1 = Vs[j * THD + lane + 32];
+#pragma unroll
+            for (int qi = 0; qi < VA_QW; ++qi) {
+                const float pj = __shfl_sync(0xffffffffu, pq[qi], j);
+                o0[qi] = fmaf(pj, v0, o0[qi]); o1[qi] = fmaf(pj, v1, o1[qi]);
+            }
         }
     }
-    mx = warp_max(mx);
-    float o0 = 0.f, o1 = 0.f; double sum = 0.0;
-    for (int j0 = 0; j0 <= t; j0 += 32) {
-        const int j = j0 + lane;
-        float p = 0.f;
-        if (j <= t) {
-            const float4 * kr = reinterpret_cast<const float4 *>(kb + (size_t) j * 3072);
-            float acc = 0.f;
 #pragma unroll
-            for (int d = 0; d < 16; ++d) { const float4 k4 = kr[d]; acc += k4.x * qs[warp][4 * d] + k4.y * qs[warp][4 * d + 1] + k4.z * qs[warp][4 * d + 2] + k4.w * qs[warp][4 * d + 3]; }
-            p = expf(acc * scale - mx);
+    for (int qi = 0; qi < VA_QW; ++qi) {
+        const int t = tq0 + qi;
+        if (t < T) {
+            const float inv = 1.0f / l[qi];
+            out[(size_t) t * LATENT + h * THD + lane]      = __float2half_rn(o0[qi] * inv);
+            out[(size_t) t * LATENT + h * THD + lane + 32] = __float2half_rn(o1[qi] * inv);
         }
-        sum += (double) p;
-        ps[warp][lane] = p;
-        __syncwarp();
-        const int nj = min(32, t + 1 - j0);
-        for (int jj = 0; jj < nj; ++jj) {
-            const float pj = ps[warp][jj];
-            const float * vr = vb + (size_t) (j0 + jj) * 3072;
-            o0 += pj * vr[lane]; o1 += pj * vr[lane + 32];
-        }
-        __syncwarp();
     }
-    sum = warp_sum_d(sum);
-    const float inv = (float) (1.0 / sum);
-    out[(size_t) t * LATENT + h * THD + lane] = __float2half_rn(o0 * inv);
-    out[(size_t) t * LATENT + h * THD + lane + 32] = __float2half_rn(o1 * inv);
 }
 
 // depthwise causal conv k7 (+bias) on F16-rounded input, LayerNorm over the 1024 channels
@@ -618,7 +651,7 @@ int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int T, float ** sa
         { VGemm p{}; p.A = n16; p.lda = TH; p.a_rows = T; p.M = T; p.ntaps = 1; p.Kc = TH; p.W = y.wqkv; p.N = 3 * LATENT; p.pmod = 3 * LATENT;
           p.out32 = qkv; p.ld32 = 3 * LATENT; voc_gemm(ctx, p); ++nl; }
         k_rope_qk<<<T, 256, 0, st>>>(qkv, v->rope, T); ++nl;
-        k_attention<<<dim3((T + 3) / 4, TNH), 128, 0, st>>>(qkv, att16, T); ++nl;
+        k_attention<<<dim3((T + VA_QB - 1) / VA_QB, TNH), 128, 0, st>>>(qkv, att16, T); ++nl;
         { VGemm p{}; p.A = att16; p.lda = LATENT; p.a_rows = T; p.M = T; p.ntaps = 1; p.Kc = LATENT; p.W = y.wo; p.N = TH; p.pmod = TH;
           p.gamma = y.attn_scale; p.res = x32; p.ldres = TH; p.out32 = x32; p.ld32 = TH; voc_gemm(ctx, p); ++nl; }
         k_rmsnorm512<<<(T + 7) / 8, 256, 0, st>>>(x32, y.ffn_norm, n16, T, T_EPS); ++nl;
