@@ -221,10 +221,11 @@ def run_ours(args, rank, world, local_rank):
         return run_sharded_workload(args, rank, world, local_rank, t, d, have_voc, dist, sync_all, m)
 
     def step_resident():
-        return t.run_staged(frames, repetition_penalty=1.05, temperature=0.0, top_k=0, seed=0, with_vocoder=have_voc)
+        return t.run_staged(frames, repetition_penalty=1.05, temperature=args.temperature, top_k=args.top_k, seed=args.seed,
+                            with_vocoder=have_voc)
 
     def step_e2e():
-        codes = t.generate(tokens, spk, frames, repetition_penalty=1.05, temperature=0.0, top_k=0)
+        codes = t.generate(tokens, spk, frames, repetition_penalty=1.05, temperature=args.temperature, top_k=args.top_k)
         if codes is None:
             raise SystemExit("generate: " + t.get_error())
         wav = d.decode(codes) if have_voc else np.zeros(n_samples(len(codes)), np.float32)
@@ -290,7 +291,9 @@ def run_ours(args, rank, world, local_rank):
             "vs_baseline": None, "dtype": "f16" if args.wtype == "f16" else "q8_0 weights, int8 x int8 / f32 accumulate",
             "data": "synthetic (seeded random-init GGUF of the real 0.6B shapes; no checkpoint offline)",
             "config": {"workload": f"0.6B {args.wtype.upper()} voice-clone-style prompt ('Hello, world!' + 1024-d speaker vector), "
-                                   f"greedy, {frames} frames + vocoder, batch 1 per GPU, one utterance per rank per step",
+                                   + ("greedy" if args.temperature <= 0 else f"sampled (temp {args.temperature}, top-k {args.top_k}, "
+                                      f"rep-penalty 1.05, seed {args.seed})")
+                                   + f", {frames} frames + vocoder, batch 1 per GPU, one utterance per rank per step",
                        "frames": nf, "samples": ns, "batch_per_gpu": 1, "vocoder": bool(have_voc),
                        "l2": "weights streamed per frame (3.3 GB) exceed the 126 MB L2; no explicit flush",
                        "parallelism": f"request-parallel x{world} (no collective)"},
@@ -425,6 +428,9 @@ def main():
     ap.add_argument("--frames", type=int, default=320)
     ap.add_argument("--ref-frames", type=int, default=96, help="frames per bounded CPU sample")
     ap.add_argument("--wtype", default="f16", choices=["f16", "q8_0"])
+    ap.add_argument("--temperature", type=float, default=0.0, help="0 = greedy (configs 1/2/4/5); config 3 uses 0.9")
+    ap.add_argument("--top-k", type=int, default=0, help="config 3 uses 50")
+    ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-vocoder", action="store_true", help="debug only: codes without the waveform (not a valid bench value)")
     ap.add_argument("--no-batch", action="store_true", help="config 4 through the batch-1 engine, one utterance at a time")
