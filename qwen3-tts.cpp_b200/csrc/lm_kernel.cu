@@ -1006,10 +1006,25 @@ __device__ __noinline__ int select_sample(const DevModel & m, Smem & s, unsigned
                 }
             }
             cbar();
-            if (t == 0) {
-                int acc = 0, d = 255;
-                for (; d > 0; --d) { if (acc + hist[d] >= k_rem) break; acc += hist[d]; }
-                hist[256] = d; hist[257] = k_rem - acc;
+            if (warp == 0) {
+                // highest bin d whose count, added to the bins above it, reaches k_rem (a serial scan of the 256
+                // bins by one thread cost ~7 k cycles per pass): lane i owns bins 8i..8i+7, suffix sums by shuffles
+                int c[8], lsum = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { c[j] = hist[lane * 8 + j]; lsum += c[j]; }
+                int inc = lsum;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_down_sync(0xffffffffu, inc, o); if (lane + o < 32) inc += v; }
+                const int above = inc - lsum;                 // entries in the bins above this lane's
+                if (above < k_rem && inc >= k_rem) {          // exactly one lane (the group holds >= k_rem entries)
+                    int acc = above, d = lane * 8;
+                    bool found = false;
+#pragma unroll
+                    for (int j = 7; j >= 0; --j) {
+                        if (!found) { if (acc + c[j] >= k_rem) { d = lane * 8 + j; found = true; } else acc += c[j]; }
+                    }
+                    hist[256] = d; hist[257] = k_rem - acc;
+                }
             }
             cbar();
             prefix |= ((unsigned int) hist[256]) << shift;

@@ -466,9 +466,12 @@ inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
         for (int c = 128; c >= 64; c -= 16) if (p.N % c == 0) { BN = c; break; }
         // two M tiles per CTA when the grid still gives every SM its two resident CTAs
         const long tiles256 = (long) ((p.M + 2 * VU_BM - 1) / (2 * VU_BM)) * ((p.N + BN - 1) / BN);
-        static int mt_env = -1;
-        if (mt_env < 0) { const char * e = getenv("Q3T_VOC_MT"); mt_env = e ? atoi(e) : 0; }
-        const int MT = mt_env ? mt_env : (tiles256 >= 2 * 148 && p.ntaps * p.Kc >= 1024 ? 2 : 1);   // short K: the epilogue dominates, keep 3 CTAs per SM
+        static int mt_env = -1, mt_k = 1024;
+        if (mt_env < 0) {
+            const char * e = getenv("Q3T_VOC_MT"); mt_env = e ? atoi(e) : 0;
+            if ((e = getenv("Q3T_VOC_MT_K"))) mt_k = atoi(e);
+        }
+        const int MT = mt_env ? mt_env : (tiles256 >= 2 * 148 && p.ntaps * p.Kc >= mt_k ? 2 : 1);   // short K: the epilogue dominates, keep 3 CTAs per SM
         const int smem = std::max(vu_a_ring(MT) + VU_STAGES * vu_b_stage(BN), VU_BM * (BN + 4) * 4);
         const int smem_max = std::max(vu_a_ring(2) + VU_STAGES * vu_b_stage(128), VU_BM * (128 + 4) * 4);
         static bool attr = false;

@@ -204,6 +204,15 @@ def test_sampler_semantics(tts_tiny):
     logits = p._linear("code_pred.lm_head.0.weight", hh[1], 2048, 1024)[0]
     top50 = set(np.argsort(-logits)[:50].tolist())
     assert seen <= top50
+    # the k-th-largest threshold of the radix select, for small k: the first code stays inside the top-k set and
+    # reaches more than one member of it
+    for k in (2, 3, 7):
+        topk = set(np.argsort(-logits)[:k].tolist())
+        got = set()
+        for s in range(40):
+            t.set_seed(5000 + 97 * k + s)
+            got.add(int(t.predict_codes_autoregressive(h, cb0, 2.0, k)[0]))
+        assert got <= topk and len(got) > 1, (k, got, topk)
 
 
 @pytest.mark.skipif(not os.path.exists(os.path.join(os.path.dirname(GOLDEN), "..", "oracle", "_ref", "libq3t_ref.so")),
