@@ -11,7 +11,7 @@ frames = int(sys.argv[1]) if len(sys.argv) > 1 else 40
 print("POLL_D0", os.environ.get("Q3T_POLL_D0"))
 m = pkg()
 t = m.TTSTransformer()
-assert t.load_model(models("full", "f16")[0]), t.get_error()
+assert t.load_model(models("full", os.environ.get("Q3T_WTYPE", "f16"))[0]), t.get_error()
 rng = np.random.default_rng(2024)
 spk = (rng.standard_normal(1024) * 0.05).astype(np.float32)
 nbatch = int(sys.argv[2]) if len(sys.argv) > 2 else 0

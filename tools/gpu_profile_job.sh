@@ -1,7 +1,10 @@
+# Round-end measurement job (run with: gpurun --timeout 2400 -- "bash tools/gpu_profile_job.sh"): GPU tests, the bench lines
+# of configs 2/3/5, the tcgen05 tap-GEMM check, the ncu launch list and the full captures that profiles/ summarises.
 set -x
 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log; tail -4 gpurun_out/pytest_gpu.log
 python bench.py --steps 3 --warmup 3 > gpurun_out/bench_r1g.json 2> gpurun_out/bench_r1g.err; echo "bench rc=$?"; cat gpurun_out/bench_r1g.json
 python bench.py --steps 2 --warmup 3 --wtype q8_0 --no-cpu-baseline > gpurun_out/bench_r1g_q8.json 2> gpurun_out/bench_r1g_q8.err; echo "bench q8 rc=$?"
+python bench.py --steps 2 --warmup 3 --wtype q8_0 --temperature 0.9 --top-k 50 --seed 7 --no-cpu-baseline > gpurun_out/bench_r1g_config3.json 2> gpurun_out/bench_r1g_config3.err; echo "bench config3 rc=$?"
 python bench.py --steps 1 --warmup 3 --frames 4096 --no-cpu-baseline > gpurun_out/bench_r1g_long.json 2> gpurun_out/bench_r1g_long.err; echo "bench long rc=$?"
 timeout 120 tools/microbench/bin/umma_test > gpurun_out/umma_test.txt 2>&1; echo "umma rc=$?"
 python bench.py --steps 1 --warmup 1 --frames 24 --no-cpu-baseline > gpurun_out/plain.log 2>&1 && \
