@@ -323,6 +323,12 @@ __device__ __forceinline__ float fhfma_hi(unsigned w, unsigned x, float acc) {
     asm("{.reg .b16 wl, wh, xl, xh; mov.b32 {wl, wh}, %1; mov.b32 {xl, xh}, %2; fma.rn.f32.f16 %0, wh, xh, %0;}" : "+f"(acc) : "r"(w), "r"(x));
     return acc;
 }
+// 16-byte shared-memory load that keeps its place in program order
+__device__ __forceinline__ uint4 lds_v4(const unsigned char * p) {
+    uint4 v;
+    asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
+    return v;
+}
 __device__ __forceinline__ unsigned u4_get(const uint4 & v, int e) { return e == 0 ? v.x : e == 1 ? v.y : e == 2 ? v.z : v.w; }
 
 // Rows of chain-major F16 weights in the shared-memory ring (slice starting at slot s0, K/1024 slots
@@ -355,14 +361,37 @@ __device__ __forceinline__ void gemv_ring(Smem & s, int s0, int n_rows) {
             const int r = rb + i < n_rows ? rb + i : rb;
             sb[i] = s0 + r * SPR;
         }
+        // ffn_down (XF32, one row = one FMA chain per warp): ptxas issues each 16-byte weight load right before its
+        // use and the chain eats the full shared-memory latency 12 times per row; volatile loads keep their program
+        // order, two k-chunks ahead of the arithmetic
+        uint4 wq[XF32 ? 2 : 1][R];
+        if (XF32) {
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int i = 0; i < R; ++i) {
+                    int slot = sb[i] + (a >> 2);
+                    if (slot >= NSLOT) slot -= NSLOT;
+                    wq[a][i] = lds_v4(s.ring + (size_t) slot * SLOT_B + (a & 3) * 512 + lane * 16);
+                }
+        }
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
             uint4 wv[R];
 #pragma unroll
             for (int i = 0; i < R; ++i) {
-                int slot = sb[i] + (u >> 2);
-                if (slot >= NSLOT) slot -= NSLOT;
-                wv[i] = *reinterpret_cast<const uint4 *>(s.ring + (size_t) slot * SLOT_B + (u & 3) * 512 + lane * 16);
+                if (XF32) {
+                    wv[i] = wq[u & 1][i];
+                    if (u + 2 < NU) {
+                        int slot = sb[i] + ((u + 2) >> 2);
+                        if (slot >= NSLOT) slot -= NSLOT;
+                        wq[u & 1][i] = lds_v4(s.ring + (size_t) slot * SLOT_B + ((u + 2) & 3) * 512 + lane * 16);
+                    }
+                } else {
+                    int slot = sb[i] + (u >> 2);
+                    if (slot >= NSLOT) slot -= NSLOT;
+                    wv[i] = *reinterpret_cast<const uint4 *>(s.ring + (size_t) slot * SLOT_B + (u & 3) * 512 + lane * 16);
+                }
             }
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
