@@ -117,7 +117,7 @@ def run_reference(args, rank, world):
     from oracle import reflib
     from util import models
     if not reflib.available():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libq3t_ref.so was not built"}))
+        emit_json(({"impl": "reference", "unavailable": "oracle/_ref/libq3t_ref.so was not built"}))
         return
     cores = os.cpu_count() or 1
     reflib.RefLib.get().set_threads(cores)
@@ -141,7 +141,7 @@ def run_reference(args, rank, world):
     audio_s = len(wav) / 24000.0 * args.steps
     v = audio_s / dt
     sample = f"{sample_frames} greedy frames (generate) + vocoder over them per step, ggml-CPU AVX2 build, {cores} threads"
-    print(json.dumps({
+    emit_json(({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f16" if args.wtype == "f16" else "q8_0", "data": "synthetic",
@@ -319,7 +319,7 @@ def run_ours(args, rank, world, local_rank):
             cb = cpu_baseline(args)
             if cb:
                 out["cpu_baseline"] = cb
-        print(json.dumps(out))
+        emit_json((out))
     if dist:
         dist.barrier()
         dist.destroy_process_group()
@@ -403,7 +403,7 @@ def run_sharded_workload(args, rank, world, local_rank, t, d, have_voc, dist, sy
         audio_s = sum(v[1] for v in merged.values()) / 24000.0
         h2d = sum(u.tokens.nbytes + u.spk.nbytes for u in utts)
         d2h = sum(v[0] * 16 * 4 + v[1] * 4 for v in merged.values())
-        print(json.dumps({
+        emit_json(({
             "metric": METRIC, "value": audio_s / step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": 1, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f16", "data": "synthetic (seeded random-init GGUF of the real 0.6B shapes)",
@@ -417,6 +417,15 @@ def run_sharded_workload(args, rank, world, local_rank, t, d, have_voc, dist, sy
     if dist:
         dist.barrier()
         dist.destroy_process_group()
+
+
+_JSON_FD = None
+
+
+def emit_json(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    sys.stdout.flush()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, line)
 
 
 def main():
@@ -438,6 +447,12 @@ def main():
                     help="config 4: this many independent utterances (8-64 byte texts) per step, dealt i mod G to the ranks; "
                          "0 = the default config-2 workload (one utterance per rank per step)")
     args = ap.parse_args()
+    # stdout carries exactly ONE line, the JSON: libraries that write to file descriptor 1 (the NCCL version banner at
+    # communicator creation, compiler chatter) are sent to stderr, and the JSON goes to the saved descriptor
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
