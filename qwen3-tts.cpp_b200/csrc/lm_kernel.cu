@@ -783,8 +783,10 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
                 for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
                 if (lane == 0) s.fred[warp] = mx;
             }
+            PROF(72);
             cbar();
             ring_release(s, rg, (rows + 7) >> 3);
+            PROF(73);
         }
         if (nck == 0) { if (lane == 0) s.fred[warp] = mx; cbar(); }
     }
