@@ -1191,12 +1191,15 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
 
         // ---- phase A: RMSNorm + fused QKV mat-vec
         PROF(1);
+        // the slice wait comes BEFORE the packet poll in every phase: the slice was requested thousands of cycles
+        // ago, and what the mbarrier wait costs (~350 cycles even when the phase has completed) then overlaps the
+        // flight time of the packets instead of sitting between the last packet and the first FMA
+        int s0 = ring_acquire(m, s, rg, w);
         if (l > 0) { poll_vec<H>(m, m.x_x, ep, s.xres, w); cbar(); }
         token(s);
         PROF(2);
         rmsnorm_to_xh<Q8>(s, ga, m.eps, nullptr, nullptr);
         PROF(3);
-        int s0 = ring_acquire(m, s, rg, w);
         PROF(4);
         if (Q8) gemv_q8<1024>(s, s0, nA); else gemv_ring<1024, 3, false>(s, s0, nA);
         PROF(40);
@@ -1217,6 +1220,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
             const int mine = t < NP ? (NP - 1 - t) / NCT + 1 : 0;
             float2 f[PER];
             spin_cycles(m.poll_d0);
+            s0 = ring_acquire(m, s, rg, w);
             pk_poll2_n<PER>(m, m.x_att + 2 * t, NCT, mine, e_att, f, w);
 #pragma unroll
             for (int j = 0; j < PER; ++j)
@@ -1229,7 +1233,6 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         if (Q8) quant_q8<NH * HD>(s);
         token(s);
         PROF(7);
-        s0 = ring_acquire(m, s, rg, w);
         PROF(8);
         if (Q8) gemv_q8<2048>(s, s0, nO); else gemv_ring<2048, 1, false>(s, s0, nO);
         cbar();
@@ -1238,13 +1241,13 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(9);
 
         // ---- phase D: RMSNorm + gate/up mat-vec + SwiGLU
+        s0 = ring_acquire(m, s, rg, w);
         poll_vec<H>(m, m.x_x1, e_x1, s.xres, w);
         cbar();
         token(s);
         PROF(10);
         rmsnorm_to_xh<Q8>(s, gf, m.eps, nullptr, nullptr);
         PROF(11);
-        s0 = ring_acquire(m, s, rg, w);
         PROF(12);
         if (Q8) gemv_q8<1024>(s, s0, 2 * nP); else gemv_ring<1024, 4, false>(s, s0, 2 * nP);
         cbar();
@@ -1257,11 +1260,11 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(13);
 
         // ---- phase E: ffn_down on F32 activations (weights exact in F32) + residual
+        s0 = ring_acquire(m, s, rg, w);
         poll_vec<FFN>(m, m.x_m, e_m, s.xf, w);
         cbar();
         token(s);
         PROF(14);
-        s0 = ring_acquire(m, s, rg, w);
         PROF(15);
         if (Q8) gemv_q8_f32<3072>(s, s0, nD); else gemv_ring<3072, 1, true>(s, s0, nD);
         cbar();
