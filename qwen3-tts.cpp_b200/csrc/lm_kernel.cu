@@ -654,6 +654,8 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     const int nck = f32attn ? 0 : (pos + KV_CH - 1) / KV_CH; // history slices (K, then V) the producer streams
 
     PROF(50);
+    // the first K slice was requested long ago: take its mbarrier wait now, while q/k/v are still in flight
+    const int s0_first = nck > 0 ? ring_acquire(m, s, rg, wd_) : 0;
     // ---- prologue: q, k, v of the new token (warps 0, 1, 2)
     if (warp < 3) {
         const Pkt * src = m.x_qkv + (warp == 0 ? h * HD : warp == 1 ? NH * HD + g * HD : (NH + NKV) * HD + g * HD);
@@ -755,7 +757,7 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
             if (lane == 0) s.sc[pos] = sv;
         }
         for (int c = 0; c < nck; ++c) {
-            const int s0 = ring_acquire(m, s, rg, wd_);
+            const int s0 = c == 0 ? s0_first : ring_acquire(m, s, rg, wd_);
             PROF(59);
             const int rows = min(KV_CH, pos - c * KV_CH);
             // four rows per warp step: the 32-lane folds of the four dot products share their shuffles
