@@ -343,12 +343,11 @@ __device__ __forceinline__ void gemv_ring(Smem & s, int s0, int n_rows) {
     constexpr int SPR = K / 1024, NU = K / 256, NJ = K / 32;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp * R >= n_rows) return;
-    float    xr[XF32 ? NJ : 1];
+    // XF32: the activation is read from shared memory step by step (conflict-free, addresses known up front);
+    // holding all K/32 = 96 values in registers left ptxas no room to issue the weight loads ahead of their use
+    const float * xr = s.xf + lane;
     unsigned xp[XF32 ? 1 : NJ / 2];
-    if (XF32) {
-#pragma unroll
-        for (int j = 0; j < NJ; ++j) xr[j] = s.xf[32 * j + lane];
-    } else {
+    if (!XF32) {
 #pragma unroll
         for (int m2 = 0; m2 < NJ / 2; ++m2) xp[m2] = s.xh[m2 * 32 + lane];
     }
@@ -400,8 +399,8 @@ __device__ __forceinline__ void gemv_ring(Smem & s, int s0, int n_rows) {
                     const unsigned w2 = u4_get(wv[i], e);
                     if (XF32) {
                         const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&w2));
-                        acc[i] = __fmaf_rn(f.x, xr[8 * u + 2 * e], acc[i]);
-                        acc[i] = __fmaf_rn(f.y, xr[8 * u + 2 * e + 1], acc[i]);
+                        acc[i] = __fmaf_rn(f.x, xr[32 * (8 * u + 2 * e)], acc[i]);
+                        acc[i] = __fmaf_rn(f.y, xr[32 * (8 * u + 2 * e + 1)], acc[i]);
                     } else {
                         acc[i] = fhfma_lo(w2, xp[4 * u + e], acc[i]);
                         acc[i] = fhfma_hi(w2, xp[4 * u + e], acc[i]);
