@@ -129,6 +129,19 @@ Q3T_API int  q3t_build_prompt(q3t_ctx * ctx, const int32_t * text_tokens, int32_
                               float * trailing_out, int32_t * trailing_len, float * pad_out);
 /* project_text_tokens (src/tts_transformer.cpp:917-982): out f32[n_tokens*H] */
 Q3T_API int  q3t_project_text(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_tokens, float * out);
+/* No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * computation and bit-identical result as q3t_project_text, but it allocates NOTHING: tokens and output
+ * are DEVICE pointers (int32[n_tokens], f32[n_tokens*H]) supplied by the caller, and the intermediates
+ * live in a file-scope `static __device__` array of the library (1.14 MiB, held by every GPU that loads
+ * the library until exit; its device address is resolved once per device with cudaGetSymbolAddress).
+ * Limit: n_tokens <= q3t_project_text_static_max_tokens() (64) and text_embd_dim <= 2048; larger sizes
+ * fail with Q3T_ERR_ARG.  Token ids are range-checked on the device (Q3T_ERR_ARG, the bad row is zero).
+ * All calls on one GPU share the array, which keeps the previous call's contents (everything that is read
+ * is rewritten first, the error flag is cleared per call): calls that overlap on the GPU RACE - serialise
+ * them.  The call is synchronous (returns after the work on the engine stream has finished). */
+Q3T_API int  q3t_project_text_static_dev(q3t_ctx * ctx, const int32_t * text_tokens_dev, int32_t n_tokens, float * out_dev);
+Q3T_API int  q3t_project_text_static_max_tokens(void);
 /* lookup_embedding_rows on talker.codec_embd (src/tts_transformer.cpp:793-915) */
 Q3T_API int  q3t_codec_embed(q3t_ctx * ctx, const int32_t * ids, int32_t n, float * out);
 

@@ -93,6 +93,8 @@ def lib() -> C.CDLL:
         "q3t_dec_stream_reset": (None, [vp]), "q3t_dec_decode_append": (C.c_int64, [vp, _i32p, C.c_int32, _f32p, C.c_int64]),
         "q3t_build_prompt": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32, _f32p, _i32p, _f32p, _i32p, _f32p]),
         "q3t_project_text": (C.c_int, [vp, _i32p, C.c_int32, _f32p]),
+        "q3t_project_text_static_dev": (C.c_int, [vp, vp, C.c_int32, vp]),
+        "q3t_project_text_static_max_tokens": (C.c_int, []),
         "q3t_stage_prompt": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32]),
         "q3t_run_staged": (C.c_int, [vp, C.c_int32, C.c_float, C.c_float, C.c_int32, C.c_uint64, C.c_int32, _i32p, _i64p]),
         "q3t_fetch_codes": (C.c_int, [vp, _i32p, C.c_int32]), "q3t_fetch_samples": (C.c_int64, [vp, _f32p, C.c_int64]),

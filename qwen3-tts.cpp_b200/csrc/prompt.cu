@@ -247,4 +247,117 @@ int prompt_build(q3t_ctx * ctx, const int32_t * tokens_dev, int n_tokens, const 
     return rc;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// q3t_project_text_static_dev: the text projection above for callers that cannot allocate (CUDA graph
+// capture, tight serving loops).  No counterpart in the reference.
+// The intermediates live in ONE file-scope device array instead of cudaMalloc'd buffers:
+// every GPU that loads the library holds STATIC_SCRATCH_BYTES (1.14 MiB) until exit, all calls on a
+// device share it (it keeps the last call's contents), so calls that overlap on the GPU race.
+constexpr int    STATIC_MAX_TOKENS = 64;                 // rows per call
+constexpr int    STATIC_MAX_K      = 2048;               // text_embd_dim of the 0.6B model
+constexpr size_t SCR_XH   = 0;                                                      // half  [64][2048] gathered rows
+constexpr size_t SCR_HH   = SCR_XH + (size_t) STATIC_MAX_TOKENS * STATIC_MAX_K * 2; // half  [64][2048] silu(fc1)
+constexpr size_t SCR_HF   = SCR_HH + (size_t) STATIC_MAX_TOKENS * STATIC_MAX_K * 2; // float [64][2048] silu(fc1), Q8_0 path
+constexpr size_t SCR_XQ   = SCR_HF + (size_t) STATIC_MAX_TOKENS * STATIC_MAX_K * 4; // int8  [64][2048] quantised rows
+constexpr size_t SCR_XD   = SCR_XQ + (size_t) STATIC_MAX_TOKENS * STATIC_MAX_K;     // float [64][64]   block scales
+constexpr size_t SCR_FLAG = SCR_XD + (size_t) STATIC_MAX_TOKENS * (STATIC_MAX_K / 32) * 4;  // int: bad-token flag
+constexpr size_t STATIC_SCRATCH_BYTES = SCR_FLAG + 256;
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+// In host code `g_static_scratch` is only a handle: the device address is asked for once per device
+// (cudaGetSymbolAddress with that device current) and kept here.
+constexpr int STATIC_MAX_DEVICES = 64;
+static unsigned char * g_static_scratch_ptr[STATIC_MAX_DEVICES] = {};
+
+static int static_scratch_for(q3t_ctx * ctx, unsigned char ** out) {
+    if (ctx->device < 0 || ctx->device >= STATIC_MAX_DEVICES) return set_err(ctx, Q3T_ERR_ARG, "device index out of range for the static scratch");
+    int rc = cuda_check(ctx, cudaSetDevice(ctx->device), "cudaSetDevice");
+    if (rc) return rc;
+    if (!g_static_scratch_ptr[ctx->device]) {
+        void * p = nullptr;
+        rc = cuda_check(ctx, cudaGetSymbolAddress(&p, g_static_scratch), "cudaGetSymbolAddress(g_static_scratch)");
+        if (rc) return rc;
+        if (!p) return set_err(ctx, Q3T_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address");
+        g_static_scratch_ptr[ctx->device] = (unsigned char *) p;
+    }
+    *out = g_static_scratch_ptr[ctx->device];
+    return Q3T_OK;
+}
+
+// gather with a range test (the ids are device memory, the host cannot validate them): a bad id gives a
+// zero row and raises the flag
+__global__ void gather_rows_h_checked(const __half * __restrict__ table, const int * __restrict__ ids, int K, int vocab,
+                                      __half * __restrict__ out, int * __restrict__ flag) {
+    const int r = blockIdx.x;
+    const int id = ids[r];
+    uint4 * dst = reinterpret_cast<uint4 *>(out + (size_t) r * K);
+    if (id < 0 || id >= vocab) {
+        if (threadIdx.x == 0) atomicOr(flag, 1);
+        for (int i = threadIdx.x; i < K / 8; i += blockDim.x) dst[i] = make_uint4(0u, 0u, 0u, 0u);
+        return;
+    }
+    const uint4 * src = reinterpret_cast<const uint4 *>(table + (size_t) id * K);
+    for (int i = threadIdx.x; i < K / 8; i += blockDim.x) dst[i] = src[i];
+}
+
 } // namespace q3t
+
+extern "C" int q3t_project_text_static_max_tokens(void) { return q3t::STATIC_MAX_TOKENS; }
+
+extern "C" int q3t_project_text_static_dev(q3t_ctx * ctx, const int32_t * text_tokens_dev, int32_t n_tokens, float * out_dev) {
+    using namespace q3t;
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (n_tokens <= 0) return Q3T_OK;
+    if (!text_tokens_dev || !out_dev) return set_err(ctx, Q3T_ERR_ARG, "text_tokens is null");
+    if (n_tokens > STATIC_MAX_TOKENS)
+        return set_err(ctx, Q3T_ERR_ARG, "q3t_project_text_static_dev: n_tokens exceeds the static scratch (max 64 tokens per call)");
+    const q3t_tts_config & c = ctx->cfg;
+    const int K = c.text_embd_dim, T = n_tokens;
+    if (K > STATIC_MAX_K || K % 32 != 0)
+        return set_err(ctx, Q3T_ERR_ARG, "q3t_project_text_static_dev: text_embd_dim exceeds the static scratch (max 2048)");
+    auto get = [&](const char * n) -> const q3t_host_tensor * {
+        auto it = ctx->raw.find(n);
+        return it == ctx->raw.end() ? nullptr : &it->second;
+    };
+    const q3t_host_tensor * emb = get("talker.text_embd.weight");
+    const q3t_host_tensor * w1 = get("talker.text_proj.fc1.weight"), * b1 = get("talker.text_proj.fc1.bias");
+    const q3t_host_tensor * w2 = get("talker.text_proj.fc2.weight"), * b2 = get("talker.text_proj.fc2.bias");
+    if (!emb || !w1 || !b1 || !w2 || !b2) return set_err(ctx, Q3T_ERR_FORMAT, "missing text embedding / projection tensors");
+    const bool q8 = w1->type == Q3T_TYPE_Q8_0;
+    if (emb->type != Q3T_TYPE_F16 || (w1->type != Q3T_TYPE_F16 && !q8) || w2->type != w1->type)
+        return set_err(ctx, Q3T_ERR_FORMAT, "text projection: text_embd must be F16, fc1/fc2 both F16 or both Q8_0");
+    if (emb->ne[0] != K || w1->ne[0] != K || w1->ne[1] != K || w2->ne[0] != K || w2->ne[1] != H)
+        return set_err(ctx, Q3T_ERR_FORMAT, "unexpected text projection shapes");
+
+    unsigned char * scr = nullptr;
+    int rc = static_scratch_for(ctx, &scr);          // device address of g_static_scratch on ctx->device
+    if (rc) return rc;
+    __half * xh = (__half *) (scr + SCR_XH), * hh = (__half *) (scr + SCR_HH);
+    float * hf = (float *) (scr + SCR_HF), * xd = (float *) (scr + SCR_XD);
+    signed char * xq = (signed char *) (scr + SCR_XQ);
+    int * flag = (int *) (scr + SCR_FLAG);
+    // the array keeps the previous call's contents; every buffer is fully overwritten for the T rows in
+    // use before it is read, only the flag has to start at zero
+    rc = cuda_check(ctx, cudaMemsetAsync(flag, 0, sizeof(int), ctx->stream), "cudaMemsetAsync");
+    if (rc) return rc;
+    gather_rows_h_checked<<<T, 128, 0, ctx->stream>>>((const __half *) emb->dev, text_tokens_dev, K, (int) emb->ne[1], xh, flag);
+    if (!q8) {
+        proj_rows<1><<<(K + 7) / 8, 256, 0, ctx->stream>>>((const __half *) w1->dev, xh, (const float *) b1->dev, K, K, T, nullptr, hh);
+        proj_rows<0><<<(H + 7) / 8, 256, 0, ctx->stream>>>((const __half *) w2->dev, hh, (const float *) b2->dev, H, K, T, out_dev, nullptr);
+        ctx->timing.kernel_launches += 3;
+    } else {
+        quant_rows_q8<__half><<<T, 256, 0, ctx->stream>>>(xh, K, xq, xd);
+        proj_rows_q8<1><<<(K + 7) / 8, 256, 0, ctx->stream>>>((const unsigned char *) w1->dev, xq, xd, (const float *) b1->dev, K, K, T, hf);
+        quant_rows_q8<float><<<T, 256, 0, ctx->stream>>>(hf, K, xq, xd);
+        proj_rows_q8<0><<<(H + 7) / 8, 256, 0, ctx->stream>>>((const unsigned char *) w2->dev, xq, xd, (const float *) b2->dev, H, K, T, out_dev);
+        ctx->timing.kernel_launches += 5;
+    }
+    rc = cuda_check(ctx, cudaGetLastError(), "text projection launch");
+    int bad = 0;
+    if (!rc) rc = cuda_check(ctx, cudaMemcpyAsync(&bad, flag, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream), "D2H");
+    if (!rc) rc = cuda_check(ctx, cudaStreamSynchronize(ctx->stream), "cudaStreamSynchronize");
+    if (!rc && bad) rc = set_err(ctx, Q3T_ERR_ARG, "Embedding token ID out of range");
+    return rc;
+}
