@@ -117,6 +117,15 @@ Q3T_API int  q3t_talker_step(q3t_ctx * ctx, const float * embd, int32_t n_past,
  * (the reference's rng_ is unseedable, src/tts_transformer.h:336). */
 Q3T_API int  q3t_codepred_frame(q3t_ctx * ctx, const float * hidden, int32_t cb0,
                                 float temperature, int32_t top_k, uint64_t seed, int32_t * codes15_out);
+/* The token selection of sample_or_argmax / the cb0 post-processing in isolation (src/tts_transformer.cpp:2349-2387,
+ * :2664-2722): n_draws tokens drawn from ONE logit vector f32[vocab] (vocab <= 3072) by the very device routine the
+ * decode kernels run after a head: temperature, top-k threshold (k-th largest, ties kept, `<` test), soft-max with a
+ * double-precision sum, inverse-CDF draw number d of stream `seed`.  process != 0 first applies the codebook-0 rules:
+ * ids >= codec_vocab-1024 except EOS set to -inf, HF repetition penalty over the ids in seen_ids.  Exists so the
+ * distribution can be tested against the reference's; temperature must be > 0. */
+Q3T_API int  q3t_sample_logits(q3t_ctx * ctx, const float * logits, int32_t vocab, int32_t process,
+                               const int32_t * seen_ids, int32_t n_seen, float repetition_penalty,
+                               float temperature, int32_t top_k, uint64_t seed, int32_t n_draws, int32_t * tokens_out);
 /* predict_codes, the legacy parallel-heads formulation (src/tts_transformer.cpp:2130-2180,
  * graph :1413-1532): logits_out f32[15*code_pred_vocab]. prev_codes may be NULL. */
 Q3T_API int  q3t_codepred_parallel(q3t_ctx * ctx, const float * hidden, const int32_t * prev_codes,

@@ -85,16 +85,34 @@ def gen_legacy(out):
     print("wrote", out)
 
 
+def gen_long(out, n_frames=4096):
+    """BASELINE.json config 5 on the full-size F16 model: the reference's greedy codes for every one of the
+    4096 frames (n_ctx 4114), same tokens / speaker vector as full_f16.npz.  ~51 ms per frame at 16 threads;
+    stored as int16 (codes < 3072)."""
+    tts, _ = models("full", "f16")
+    ref = reflib.RefTTS(tts)
+    spk, _ = golden_inputs()
+    codes = ref.generate(HELLO_FULL, spk, n_frames, rep_penalty=1.05, temperature=0.0)
+    ref.close()
+    assert codes.max() < 32768 and codes.min() >= 0
+    np.savez_compressed(out, tokens=HELLO_FULL, spk=spk, codes=codes.astype(np.int16))
+    print("wrote", out, codes.shape)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--full", action="store_true", help="also write the full-size (28-layer) goldens")
     ap.add_argument("--threads", type=int, default=8)
     ap.add_argument("--only-legacy", action="store_true", help="write only legacy_predict_codes.npz")
+    ap.add_argument("--long", action="store_true", help="write only long_f16.npz (4096 greedy frames of the full F16 model)")
     a = ap.parse_args()
     if not reflib.available():
         sys.exit("oracle/_ref/libq3t_ref.so missing: make -f oracle/Makefile.ref")
     reflib.RefLib.get().set_threads(a.threads)
     os.makedirs(GOLDEN, exist_ok=True)
+    if a.long:
+        gen_long(os.path.join(GOLDEN, "long_f16.npz"))
+        return
     if a.only_legacy:
         gen_legacy(os.path.join(GOLDEN, "legacy_predict_codes.npz"))
         return

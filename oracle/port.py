@@ -265,3 +265,32 @@ class PortTTS:
             logits, _ = self.step(e.astype(np.float32), n_past)
             n_past += 1
         return np.asarray(frames, np.int32).reshape(-1, 16)
+
+
+# ---------------------------------------------------------------------------------------------------
+# Sampling (src/tts_transformer.cpp:2349-2387 `sample_or_argmax`, and the codebook-0 variant with its
+# post-processing :2664-2722).  The reference draws with std::discrete_distribution over an unseedable
+# std::mt19937 (src/tts_transformer.h:336), so the oracle is the PROBABILITY VECTOR the reference hands to
+# discrete_distribution, computed with the reference's own arithmetic: in-place float division by the
+# temperature, k-th largest value as threshold with a `<` test (ties at the threshold all survive), float
+# expf(l - max), double-precision sum, (float)(e / sum).
+def sample_probs(logits, temperature, top_k, process=False, seen=(), rep_penalty=1.0, suppress_start=2048, eos_id=2150):
+    l = np.array(logits, np.float32, copy=True)
+    if process:                                       # :2666-2683 (codebook 0 only)
+        for i in range(suppress_start, len(l)):
+            if i != eos_id:
+                l[i] = -np.inf
+        if rep_penalty != 1.0:
+            rp = np.float32(rep_penalty)
+            for tok in sorted(set(int(t) for t in seen)):
+                if 0 <= tok < len(l):
+                    l[tok] = l[tok] / rp if l[tok] > 0 else l[tok] * rp
+    l = (l / np.float32(temperature)).astype(np.float32)
+    if 0 < top_k < len(l):
+        thr = np.sort(l)[::-1][top_k - 1]             # partial_sort ... scored[top_k - 1].first
+        l[l < thr] = -np.inf
+    mx = l.max()
+    with np.errstate(over="ignore", under="ignore"):
+        e = np.exp((l - mx).astype(np.float32)).astype(np.float32)      # expf per element (float result)
+    total = float(np.sum(e.astype(np.float64)))
+    return (e.astype(np.float64) / total).astype(np.float32), l

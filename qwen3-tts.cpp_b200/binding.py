@@ -93,6 +93,7 @@ def lib() -> C.CDLL:
         "q3t_dec_stream_reset": (None, [vp]), "q3t_dec_decode_append": (C.c_int64, [vp, _i32p, C.c_int32, _f32p, C.c_int64]),
         "q3t_build_prompt": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32, _f32p, _i32p, _f32p, _i32p, _f32p]),
         "q3t_project_text": (C.c_int, [vp, _i32p, C.c_int32, _f32p]),
+        "q3t_sample_logits": (C.c_int, [vp, _f32p, C.c_int32, C.c_int32, _i32p, C.c_int32, C.c_float, C.c_float, C.c_int32, C.c_uint64, C.c_int32, _i32p]),
         "q3t_project_text_static_dev": (C.c_int, [vp, vp, C.c_int32, vp]),
         "q3t_project_text_static_max_tokens": (C.c_int, []),
         "q3t_stage_prompt": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32]),
@@ -367,6 +368,17 @@ class TTSTransformer:
         if n < 0:
             raise Q3TError("profile_read failed")
         return (buf[:n] >> np.uint64(8)).astype(np.int64), (buf[:n] & np.uint64(0xff)).astype(np.int64)
+
+    def sample_logits(self, logits, n_draws, temperature, top_k, seed=0, process=False, seen=None, repetition_penalty=1.0):
+        """n_draws tokens from one logit vector through the device sampler (q3t_sample_logits)."""
+        logits = np.ascontiguousarray(logits, np.float32)
+        seen = np.zeros(0, np.int32) if seen is None else np.ascontiguousarray(seen, np.int32)
+        out = np.zeros(n_draws, np.int32)
+        rc = self.L.q3t_sample_logits(self.engine(), _fp(logits), len(logits), 1 if process else 0, _ip(seen), len(seen),
+                                      repetition_penalty, temperature, top_k, seed, n_draws, _ip(out))
+        if rc != 0:
+            raise Q3TError(self.L.q3t_last_error(self.engine()).decode())
+        return out
 
     def timing(self):
         t = Timing()

@@ -648,6 +648,34 @@ extern "C" int q3t_codepred_frame(q3t_ctx * ctx, const float * hidden, int32_t c
     return Q3T_OK;
 }
 
+// ------------------------------------------------------------------------------ sampler in isolation
+extern "C" int q3t_sample_logits(q3t_ctx * ctx, const float * logits, int32_t vocab, int32_t process,
+                                 const int32_t * seen_ids, int32_t n_seen, float repetition_penalty,
+                                 float temperature, int32_t top_k, uint64_t seed, int32_t n_draws, int32_t * tokens_out) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (!logits || !tokens_out || vocab <= 0 || vocab > 3072 || n_draws <= 0) return set_err(ctx, Q3T_ERR_ARG, "q3t_sample_logits: bad argument");
+    if (!(temperature > 0.0f)) return set_err(ctx, Q3T_ERR_ARG, "q3t_sample_logits: temperature must be > 0 (greedy selection is a decode-kernel path)");
+    if (n_seen > 0 && !seen_ids) return set_err(ctx, Q3T_ERR_ARG, "q3t_sample_logits: seen_ids is null");
+    cudaSetDevice(ctx->device);
+    std::vector<Pkt> pk((size_t) vocab);
+    for (int i = 0; i < vocab; ++i) { pk[i].v = logits[i]; pk[i].e = 1u; }
+    std::vector<unsigned char> seen(4096, 0);
+    for (int i = 0; i < n_seen; ++i) if (seen_ids[i] >= 0 && seen_ids[i] < 4096) seen[seen_ids[i]] = 1;
+    Pkt * d_pk = nullptr; unsigned char * d_seen = nullptr; int * d_out = nullptr;
+    int rc = cuda_check(ctx, cudaMalloc(&d_pk, pk.size() * sizeof(Pkt)), "cudaMalloc");
+    if (!rc) rc = cuda_check(ctx, cudaMalloc(&d_seen, seen.size()), "cudaMalloc");
+    if (!rc) rc = cuda_check(ctx, cudaMalloc(&d_out, (size_t) n_draws * 4), "cudaMalloc");
+    if (!rc) rc = cuda_check(ctx, cudaMemcpyAsync(d_pk, pk.data(), pk.size() * sizeof(Pkt), cudaMemcpyHostToDevice, ctx->stream), "H2D");
+    if (!rc) rc = cuda_check(ctx, cudaMemcpyAsync(d_seen, seen.data(), seen.size(), cudaMemcpyHostToDevice, ctx->stream), "H2D");
+    if (!rc) rc = lm_sample_logits(ctx, d_pk, d_seen, vocab, process, repetition_penalty, temperature, top_k, seed, 0ull, n_draws, d_out);
+    if (!rc) rc = cuda_check(ctx, cudaMemcpyAsync(tokens_out, d_out, (size_t) n_draws * 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H");
+    if (!rc) rc = cuda_check(ctx, cudaStreamSynchronize(ctx->stream), "sample_logits_kernel");
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_pk); cudaFree(d_seen); cudaFree(d_out);
+    return rc;
+}
+
 // ------------------------------------------------------------------------------ legacy predict_codes
 // src/tts_transformer.cpp:2130-2180 + build_code_pred_graph :1413-1532: ONE token through the five
 // code-predictor layers without RoPE or KV cache, then all 15 heads on the un-normed layer output.

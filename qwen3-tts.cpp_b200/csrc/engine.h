@@ -194,6 +194,9 @@ int  set_err(q3t_ctx * ctx, int code, const std::string & msg);
 int  cuda_check(q3t_ctx * ctx, cudaError_t e, const char * what);
 int  lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int frame_mode);
 int  lm_max_grid(q3t_ctx * ctx);
+int  lm_sample_logits(q3t_ctx * ctx, const Pkt * logits_pk_dev, const unsigned char * seen_dev, int vocab, int process,
+                      float rep_penalty, float temperature, int top_k, unsigned long long seed, unsigned long long draw0,
+                      int n_draws, int * out_dev);
 int  lm_launch_batch(q3t_ctx * ctx, const DevModel * seqs, int nb, const PassDesc * passes_dev, int n_passes);
 int  prompt_build(q3t_ctx * ctx, const int32_t * tokens_dev, int n_tokens, const float * spk_dev,
                   int language_id, float * prefill_dev, int * prefill_len, float * trailing_dev,

@@ -1536,6 +1536,43 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
 
 #include "lm_batch.inc"
 
+// --------------------------------------------------------------------------- sampler in isolation
+// Test hook ("distribution test of the sampler in isolation"): draws n tokens from ONE logit
+// vector through select_sample, i.e. exactly the code the decode kernels run after a head
+// (src/tts_transformer.cpp:2349-2387 for the code predictor, :2664-2722 with suppress / repetition penalty
+// for codebook 0).  The logits arrive as epoch-1 packets in a private buffer; CTA b takes draws b, b + grid, ...
+__global__ void __launch_bounds__(LM_THREADS, 1)
+sample_logits_kernel(const __grid_constant__ DevModel m, int vocab, int process, int suppress_start, int eos_id, float rep_penalty,
+                     float temperature, int top_k, unsigned long long seed, unsigned long long draw0, int n_draws, int * __restrict__ out) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem & s = *reinterpret_cast<Smem *>(smem_raw);
+    if (threadIdx.x >= NCT) return;
+    Watch w; w.t0 = clock64(); w.dead = false; w.err = &m.st->error;
+    for (int d = blockIdx.x; d < n_draws; d += gridDim.x) {
+        const int tok = select_sample(m, s, 1u, w, vocab, process != 0, suppress_start, eos_id, rep_penalty, temperature, top_k,
+                                      seed, draw0 + (unsigned long long) d);
+        if (threadIdx.x == 0) out[d] = tok;
+    }
+}
+
+int lm_sample_logits(q3t_ctx * ctx, const Pkt * logits_pk_dev, const unsigned char * seen_dev, int vocab, int process,
+                     float rep_penalty, float temperature, int top_k, unsigned long long seed, unsigned long long draw0,
+                     int n_draws, int * out_dev) {
+    if (lm_max_grid(ctx) <= 0) return set_err(ctx, Q3T_ERR_CUDA, "cannot configure the decode kernels on this device");
+    cudaError_t e = cudaFuncSetAttribute(sample_logits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(Smem));
+    if (e != cudaSuccess) return cuda_check(ctx, e, "cudaFuncSetAttribute");
+    DevModel m = ctx->hm;
+    m.x_logit = const_cast<Pkt *>(logits_pk_dev);
+    m.seen = const_cast<unsigned char *>(seen_dev);
+    m.poll_d0 = 0; m.poll_d1 = 0;
+    const int grid = n_draws < 128 ? n_draws : 128;
+    sample_logits_kernel<<<grid, LM_THREADS, sizeof(Smem), ctx->stream>>>(m, vocab, process, ctx->cfg.codec_vocab_size - 1024, ctx->cfg.codec_eos_id,
+                                                                         rep_penalty, temperature, top_k, seed, draw0, n_draws, out_dev);
+    ctx->timing.kernel_launches++;
+    return cuda_check(ctx, cudaGetLastError(), "sample_logits_kernel launch");
+}
+
+
 // --------------------------------------------------------------------------- host launch
 int lm_max_grid(q3t_ctx * ctx) {
     static bool attr_set = false;

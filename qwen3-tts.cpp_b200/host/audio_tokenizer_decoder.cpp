@@ -1,11 +1,16 @@
 #include "audio_tokenizer_decoder.h"
-#include "gguf_loader.h"
+#include "b200_gguf_loader.h"
 
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
 
 namespace qwen3_tts {
+
+using b200::GGUFLoader;
+using b200::init_preferred_backend;
+using b200::release_preferred_backend;
+using b200::load_tensor_data_from_file;
 
 AudioTokenizerDecoder::AudioTokenizerDecoder() = default;
 AudioTokenizerDecoder::~AudioTokenizerDecoder() { unload_model(); }

@@ -26,7 +26,7 @@ struct audio_decoder_config {                 // src/audio_tokenizer_decoder.h:1
     float rope_theta = 10000.0f;
 };
 
-class AudioTokenizerDecoder {
+class Q3T_API AudioTokenizerDecoder {
 public:
     AudioTokenizerDecoder();
     ~AudioTokenizerDecoder();

@@ -1,10 +1,11 @@
-#include "gguf_loader.h"
+#include "b200_gguf_loader.h"
 
 #include <cstdlib>
 #include <cstring>
 #include <vector>
 
 namespace qwen3_tts {
+namespace b200 {
 
 namespace {
 // The reference shares one ggml backend between all components of a process
@@ -148,4 +149,5 @@ bool load_tensor_data_from_file(const GGUFLoader & loader, q3t_ctx * engine, con
     return true;
 }
 
+} // namespace b200
 } // namespace qwen3_tts

@@ -1,16 +1,23 @@
-// qwen3_tts::GGUFLoader and the backend helpers with the reference's names and meaning
-// (src/gguf_loader.h:16-81), on top of our own GGUF reader and the q3t engine instead of ggml.
+// GGUF loader and engine-context helpers of the B200 host classes: the role of the reference's
+// GGUFLoader / init_preferred_backend / load_tensor_data_from_file (src/gguf_loader.h:16-81), same method
+// names and meaning, on top of our own GGUF reader and the q3t engine instead of ggml.
+//
+// They live in namespace qwen3_tts::b200 (and in files of their own name) on purpose: the reference's
+// pipeline keeps using ITS src/gguf_loader.h for the text tokenizer and the speaker encoder
+// (src/qwen3_tts.cpp:138-151 needs loader.get_ctx(), a ggml handle), so both loaders are linked into one
+// program and must not collide.
 #pragma once
 
 #include "../../include/q3t.h"
-#include "gguf_reader.h"
+#include "b200_gguf_reader.h"
 
 #include <cstdint>
 #include <string>
 
 namespace qwen3_tts {
+namespace b200 {
 
-class GGUFLoader {
+class Q3T_API GGUFLoader {
 public:
     GGUFLoader();
     ~GGUFLoader();
@@ -41,7 +48,7 @@ protected:
 
 // Upload every tensor whose name starts with one of `prefixes` to the engine
 // (role of load_tensor_data_from_file, src/gguf_loader.cpp:154-227).
-bool load_tensor_data_from_file(const GGUFLoader & loader, q3t_ctx * engine,
+Q3T_API bool load_tensor_data_from_file(const GGUFLoader & loader, q3t_ctx * engine,
                                 const char * const * prefixes, int n_prefixes,
                                 std::string & error_msg, int64_t * n_uploaded = nullptr);
 
@@ -49,7 +56,8 @@ bool load_tensor_data_from_file(const GGUFLoader & loader, q3t_ctx * engine,
 // (src/gguf_loader.cpp:10-82); one context serves one transformer and one vocoder, further
 // instances of the same component get their own context.  The CUDA device is taken from QWEN3_TTS_DEVICE (default 0);
 // there is no IGPU/ACCEL/CPU fallback chain: without a B200 this returns nullptr.
-q3t_ctx * init_preferred_backend(const char * component_name, std::string * error_msg);
-void release_preferred_backend(q3t_ctx * backend, const char * component_name = nullptr);
+Q3T_API q3t_ctx * init_preferred_backend(const char * component_name, std::string * error_msg);
+Q3T_API void release_preferred_backend(q3t_ctx * backend, const char * component_name = nullptr);
 
+} // namespace b200
 } // namespace qwen3_tts

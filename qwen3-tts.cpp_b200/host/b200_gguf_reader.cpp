@@ -1,4 +1,4 @@
-#include "gguf_reader.h"
+#include "b200_gguf_reader.h"
 
 #include <cstring>
 #include <fcntl.h>
@@ -7,6 +7,7 @@
 #include <unistd.h>
 
 namespace qwen3_tts {
+namespace b200 {
 
 namespace {
 
@@ -179,4 +180,5 @@ int64_t GGUFFile::find_tensor(const std::string & name) const {
     return it == by_name_.end() ? -1 : (int64_t) it->second;
 }
 
+} // namespace b200
 } // namespace qwen3_tts

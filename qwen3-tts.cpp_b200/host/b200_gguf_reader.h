@@ -10,6 +10,7 @@
 #include <vector>
 
 namespace qwen3_tts {
+namespace b200 {
 
 enum gguf_value_type : uint32_t {
     GGUF_T_U8 = 0, GGUF_T_I8, GGUF_T_U16, GGUF_T_I16, GGUF_T_U32, GGUF_T_I32, GGUF_T_F32, GGUF_T_BOOL,
@@ -64,4 +65,5 @@ private:
     std::map<std::string, size_t> by_name_;
 };
 
+} // namespace b200
 } // namespace qwen3_tts

@@ -2,13 +2,14 @@
 // of the reference's TTSTransformer / AudioTokenizerDecoder / GGUFLoader would call.
 #include "../../include/q3t.h"
 #include "audio_tokenizer_decoder.h"
-#include "gguf_loader.h"
+#include "b200_gguf_loader.h"
 #include "tts_transformer.h"
 
 #include <cstring>
 #include <vector>
 
 using namespace qwen3_tts;
+using qwen3_tts::b200::GGUFLoader;
 
 struct q3t_gguf { GGUFLoader l; std::string err; };
 struct q3t_tts  { TTSTransformer t; };

@@ -1,5 +1,5 @@
 #include "tts_transformer.h"
-#include "gguf_loader.h"
+#include "b200_gguf_loader.h"
 
 #include <algorithm>
 #include <chrono>
@@ -8,6 +8,11 @@
 #include <initializer_list>
 
 namespace qwen3_tts {
+
+using b200::GGUFLoader;
+using b200::init_preferred_backend;
+using b200::release_preferred_backend;
+using b200::load_tensor_data_from_file;
 
 TTSTransformer::TTSTransformer() = default;
 

@@ -52,9 +52,9 @@ struct tts_transformer_config {
     int32_t english_language_id = 2050;
 };
 
-class GGUFLoader;
+namespace b200 { class GGUFLoader; }
 
-class TTSTransformer {
+class Q3T_API TTSTransformer {
 public:
     TTSTransformer();
     ~TTSTransformer();
@@ -113,12 +113,12 @@ public:
                         const std::vector<const float *> & speaker_embd, int32_t max_len,
                         std::vector<std::vector<int32_t>> & outputs,
                         int32_t language_id = 2050, float repetition_penalty = 1.05f);
-    void set_seed(uint64_t seed) { seed_ = seed; }        // the reference's rng_ cannot be seeded
+    void set_seed(uint64_t seed) { seed_ = seed; draws_ = 0; }   // the reference's rng_ cannot be seeded; re-seeding restarts the stream
     q3t_ctx * engine() const { return engine_; }
     const tts_timing & last_timing() const { return timing_; }
 
 private:
-    bool parse_config(const GGUFLoader & loader);
+    bool parse_config(const b200::GGUFLoader & loader);
     bool fail(int rc);
 
     tts_transformer_config config_;

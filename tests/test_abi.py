@@ -77,7 +77,7 @@ def test_fails_loudly_without_gpu(q3t, tiny_models):
 
 
 def test_gguf_loader_matches_python_reader(q3t, tiny_models):
-    """Own GGUF v3 reader (host/gguf_reader.cpp) vs the `gguf` python package on the same file."""
+    """Own GGUF v3 reader (host/b200_gguf_reader.cpp) vs the `gguf` python package on the same file."""
     import gguf
     for path in tiny_models:
         g = q3t.GGUFLoader()

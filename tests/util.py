@@ -28,9 +28,9 @@ def pkg():
     return m
 
 
-def models(preset="tiny", wtype="f16"):
+def models(preset="tiny", wtype="f16", **kw):
     from tools.make_random_gguf import ensure_models
-    return ensure_models(MODEL_DIR, preset=preset, wtype=wtype)
+    return ensure_models(MODEL_DIR, preset=preset, wtype=wtype, **kw)
 
 
 # "Hello, world!" with the synthetic byte-level vocabulary, remapped into

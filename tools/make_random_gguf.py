@@ -56,13 +56,38 @@ def _add(writer, name, data, qtype):
         writer.add_tensor(name, data.astype(np.float16), raw_dtype=gguf.GGMLQuantizationType.F16)
 
 
+def gpt2_byte_chars() -> list[str]:
+    """bytes_to_unicode of GPT-2 in vocabulary order: printable bytes first, the other 68 as chr(256 + n)."""
+    bs = list(range(ord("!"), ord("~") + 1)) + list(range(0xA1, 0xAC + 1)) + list(range(0xAE, 0xFF + 1))
+    out = [chr(b) for b in bs]
+    n = 0
+    for b in range(256):
+        if b not in bs:
+            out.append(chr(256 + n))
+            n += 1
+    return out
+
+
+def synthetic_vocab(n: int) -> list[str]:
+    toks = gpt2_byte_chars() + [f"[unused{i}]" for i in range(256, n)]
+    toks[77091] = "assistant"
+    toks[151643] = "<|endoftext|>"
+    toks[151644] = "<|im_start|>"
+    toks[151645] = "<|im_end|>"
+    return toks
+
+
 def write_tts_gguf(path: str, preset: str = "full", seed: int = 1234, wtype: str = "f16",
-                   w_std: float = 0.02) -> dict:
+                   w_std: float = 0.02, eos_scale: float = 1.0) -> dict:
     """Talker + code predictor file (reference name: qwen3-tts-0.6b-f16.gguf).
 
     wtype "q8_0" quantises exactly the tensors the reference converter quantises
     (attn q/k/v/o, ffn gate/up/down, text_proj fc1/fc2); embeddings and heads stay F16
     (scripts/convert_tts_to_gguf.py:244-270).
+
+    eos_scale != 1 multiplies the EOS row (id 2150) of talker.codec_head: with plain random weights EOS is
+    practically never the arg-max; scaled by ~2-3 it wins at some frame a few dozen frames in, which is what
+    the early-stop tests need (every other tensor is byte-identical to the unscaled file).
     """
     p = PRESETS[preset]
     rng = _Rng(seed)
@@ -90,6 +115,16 @@ def write_tts_gguf(path: str, preset: str = "full", seed: int = 1234, wtype: str
     w.add_uint32(f"{arch}.tts_eos_token_id", p["tts_eos"])
     w.add_uint32(f"{arch}.tts_pad_token_id", p["tts_pad"])
 
+    if p["text_vocab"] >= 151646:
+        # synthetic byte-level vocabulary for the reference's TextTokenizer (src/text_tokenizer.cpp:80-165), so the
+        # unmodified qwen3-tts-cli can run on this file: the 256 GPT-2 byte tokens at ids 0..255 in
+        # GPT-2 order ('!' = 0, 'Ġ' = 220, 'Ċ' = 198), "assistant" = 77091, <|im_start|> = 151644, <|im_end|> = 151645,
+        # no merges -> text encodes byte by byte ("Hello, world!" -> HELLO_FULL of tests/util.py)
+        w.add_token_list(synthetic_vocab(p["text_vocab"]))
+        w.add_uint32("tokenizer.ggml.bos_token_id", 151644)
+        w.add_uint32("tokenizer.ggml.eos_token_id", 151645)
+        w.add_uint32("tokenizer.ggml.padding_token_id", 151643)
+
     q = wtype  # quantisable class
     f = "f16"  # always-F16 class
 
@@ -99,7 +134,10 @@ def write_tts_gguf(path: str, preset: str = "full", seed: int = 1234, wtype: str
     _add(w, "talker.text_proj.fc2.weight", rng.normal((H, TEXT_DIM), w_std), q)
     _add(w, "talker.text_proj.fc2.bias", rng.normal((H,), 0.01), f)
     _add(w, "talker.codec_embd.weight", rng.normal((CODEC_VOCAB, H), w_std), f)
-    _add(w, "talker.codec_head.weight", rng.normal((CODEC_VOCAB, H), w_std), f)
+    head = rng.normal((CODEC_VOCAB, H), w_std)
+    if eos_scale != 1.0:
+        head[2150] *= np.float32(eos_scale)
+    _add(w, "talker.codec_head.weight", head, f)
     _add(w, "talker.output_norm.weight", 1.0 + rng.normal((H,), 0.02), f)
 
     def layer(prefix):
@@ -132,13 +170,16 @@ def write_tts_gguf(path: str, preset: str = "full", seed: int = 1234, wtype: str
     return dict(preset=preset, seed=seed, wtype=wtype, **p)
 
 
-def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain: float = 0.06) -> dict:
+def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain: float = 0.06, usage: bool = False) -> dict:
     """Vocoder file (reference name: qwen3-tts-tokenizer-f16.gguf), `tok_dec.*` tensors only.
 
     Conv / linear weights ~ N(0, gain^2 / fan_in); snake alpha/beta ~ N(0, 0.1^2) (log-scale
     parameters, reference src/audio_tokenizer_decoder.cpp:383-397); layer scales 0.01-ish;
     codebooks N(0,1).  `out_gain` scales the final 96->1 conv so the pre-tanh RMS stays well
     inside the linear range of tanh (otherwise an SNR test is meaningless).
+
+    usage=True appends the `*.usage` tensors of older converters (src/audio_tokenizer_decoder.cpp:40-73,141,189:
+    codebook rows are divided by max(usage, 1e-5) at load); they come last so every other tensor keeps its values.
     """
     rng = _Rng(seed)
     arch = "qwen3-tts-tokenizer"
@@ -218,6 +259,11 @@ def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain:
     _add(w, "tok_dec.dec.5.snake.beta", rng.normal((96,), 0.1), f)
     _add(w, "tok_dec.dec.6.conv.weight", fan((1, 96, 7), 96 * 7, g=out_gain), f)
     _add(w, "tok_dec.dec.6.conv.bias", rng.normal((1,), 0.01), f)
+    if usage:
+        for name in ["tok_dec.vq_first.0.usage"] + [f"tok_dec.vq_rest.{i}.usage" for i in range(15)]:
+            u = np.abs(rng.normal((2048,), 0.5)) + np.float32(0.5)
+            u[::97] = np.float32(1e-7)                      # below the epsilon: clamped to 1e-5 by the loader
+            _add(w, name, u, f)
 
     w.write_header_to_file(path=path)
     w.write_kv_data_to_file()
@@ -227,24 +273,26 @@ def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain:
 
 
 def ensure_models(model_dir: str, preset: str = "tiny", wtype: str = "f16", seed: int = 1234,
-                  voc_seed: int = 4321, verbose: bool = False) -> tuple[str, str]:
+                  voc_seed: int = 4321, verbose: bool = False, eos_scale: float = 1.0,
+                  usage: bool = False) -> tuple[str, str]:
     """Create (if missing) the two GGUFs under model_dir; returns (tts_path, vocoder_path).
 
     File names follow the reference pipeline (src/qwen3_tts.cpp:118-119) with a preset /
     weight-type infix so several variants can sit side by side in one cache directory.
     """
     os.makedirs(model_dir, exist_ok=True)
-    tts = os.path.join(model_dir, f"qwen3-tts-0.6b-{preset}-{wtype}-s{seed}.gguf")
-    voc = os.path.join(model_dir, f"qwen3-tts-tokenizer-f16-s{voc_seed}.gguf")
+    eos = "" if eos_scale == 1.0 else f"-eos{eos_scale:g}"
+    tts = os.path.join(model_dir, f"qwen3-tts-0.6b-{preset}-{wtype}-s{seed}{eos}.gguf")
+    voc = os.path.join(model_dir, f"qwen3-tts-tokenizer-f16-s{voc_seed}{'-usage' if usage else ''}.gguf")
     if not os.path.exists(tts):
         if verbose:
             print(f"[make_random_gguf] writing {tts}", file=sys.stderr)
-        write_tts_gguf(tts + ".tmp", preset=preset, seed=seed, wtype=wtype)
+        write_tts_gguf(tts + ".tmp", preset=preset, seed=seed, wtype=wtype, eos_scale=eos_scale)
         os.replace(tts + ".tmp", tts)
     if not os.path.exists(voc):
         if verbose:
             print(f"[make_random_gguf] writing {voc}", file=sys.stderr)
-        write_vocoder_gguf(voc + ".tmp", seed=voc_seed)
+        write_vocoder_gguf(voc + ".tmp", seed=voc_seed, usage=usage)
         os.replace(voc + ".tmp", voc)
     return tts, voc
 
