@@ -44,6 +44,7 @@ constexpr int KV_CH      = 128;                        // K/V history rows per r
 constexpr int SLOT_Q8    = 1088;                       // Q8_0 record of 1024 weights: 1024 int8 + 32 F16 block scales
 constexpr int NMB        = 8;                          // mbarriers cycling over the slices in flight
 constexpr int ATT_MAX_KV = LM_ATT_MAX_KV;              // positions the attention phase can hold
+constexpr int ATT_FAST_KV = 16;                        // rows up to this width take the register-fed short path (no K/V ring slices)
 
 struct __align__(128) Smem {
     static constexpr int NSLOTS = NSLOT;
@@ -626,6 +627,40 @@ __device__ __forceinline__ float reduce32_transposed(float (&v)[N], int lane, in
     return v[0];
 }
 
+// soft-max of a row of at most 32 entries by ONE warp (ggml_vec_soft_max_f32: 8 lanes at a time, libm tail;
+// vec.cpp:548-617): lane i holds score i; returns exp(score - M) / sum for the lane (0 for lanes >= n_kv).
+// n8 = chunks of the reference row width that take the SIMD exp, n8v = those holding unmasked positions.
+__device__ __forceinline__ float softmax_row32(float score, float M, int lane, int n_kv, int n8, int n8v) {
+    const bool live = lane < n_kv;
+    const bool simd = lane < n8 * 8;
+    const float x = live ? __fsub_rn(score, M) : 0.0f;
+    // straight-line code (this warp is the critical path of the layer): the SIMD exp is evaluated by every
+    // lane, the libm tail only when the row has one (a warp-uniform test); all sums below are selects,
+    // adding +0.0 to a non-negative double is exact
+    float e = live && simd ? v_expf(x) : 0.0f;
+    if (n8 * 8 < n_kv) {
+        const float et = tail_expf(x);
+        e = live && !simd ? et : e;
+    }
+    // chunk sums in the oracle's order: ((e4+e0)+(e6+e2)) + ((e5+e1)+(e7+e3)) per 8 lanes
+    float c = simd || !live ? e : 0.0f;              // masked lanes of a SIMD chunk add +0
+    c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 4));
+    c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 2));
+    c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 1));
+    float cs[4], ev[7];
+#pragma unroll
+    for (int ch = 0; ch < 4; ++ch) cs[ch] = __shfl_sync(0xffffffffu, c, ch * 8);
+#pragma unroll
+    for (int i = 0; i < 7; ++i) ev[i] = __shfl_sync(0xffffffffu, e, (n8 * 8 + i) & 31);
+    double S = 0.0;
+#pragma unroll
+    for (int ch = 0; ch < 4; ++ch) S += ch < n8v ? (double) cs[ch] : 0.0;
+#pragma unroll
+    for (int i = 0; i < 7; ++i) S += n8 * 8 + i < n_kv ? (double) ev[i] : 0.0;      // scalar tail, in order
+    const float inv = (float) (1.0 / S);
+    return __fmul_rn(e, inv);
+}
+
 // address of history row r (0..KV_CH) of a K/V slice that starts at ring slot s0
 template <class SM>
 __device__ __forceinline__ const unsigned char * kv_row(const SM & s, int s0, int r) {
@@ -650,11 +685,42 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     const size_t kv_head_base = ((size_t) (l * NKV + g) * W.n_ctx) * HD;
     Pkt * att = m.x_att + h * HD;
     const int np = min(wd & ~31, n_kv);                      // positions in the 32-lane part of the P.V dot
-    const int nck = f32attn ? 0 : (pos + KV_CH - 1) / KV_CH; // history slices (K, then V) the producer streams
+    // rows of at most ATT_FAST_KV entries (every code-predictor step, the first talker frames): the K/V history is a
+    // few KB, so it is fetched straight from L2 into registers while q/k/v are still in flight instead of being
+    // streamed through the ring: no slice waits, no ring hand-over, two CTA barriers (same arithmetic, same order)
+    const bool fast = !f32attn && wd <= ATT_FAST_KV;
+    const int nck = (f32attn || fast) ? 0 : (pos + KV_CH - 1) / KV_CH; // history slices (K, then V) the producer streams
 
     PROF(50);
     // the first K slice was requested long ago: take its mbarrier wait now, while q/k/v are still in flight
     const int s0_first = nck > 0 ? ring_acquire(m, s, rg, wd_) : 0;
+    // fast path: history rows warp, warp + 11 of K (this lane's chain: 4 halves) and, in warps 4..7, column
+    // d = t - 128 of V for all history rows (packed two positions per register); f32attn: row 0 of the F32 shadow
+    uint2 kpre[2] = {make_uint2(0u, 0u), make_uint2(0u, 0u)};
+    unsigned vpre[ATT_FAST_KV / 2];
+    float kf0[4] = {0.f, 0.f, 0.f, 0.f}, vf0[4] = {0.f, 0.f, 0.f, 0.f};
+    if (fast) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int r = warp + j * NCW;
+            if (r < pos) kpre[j] = __ldcg(reinterpret_cast<const uint2 *>(W.kcache + kv_head_base + (size_t) r * HD) + lane);
+        }
+        if (warp >= 4 && warp < 8) {
+            const unsigned short * vcol = reinterpret_cast<const unsigned short *>(W.vcache + kv_head_base) + (t - 128);
+#pragma unroll
+            for (int j = 0; j < ATT_FAST_KV / 2; ++j) {
+                const unsigned lo = 2 * j     < pos ? (unsigned) __ldcg(vcol + (size_t) (2 * j) * HD)     : 0u;
+                const unsigned hi = 2 * j + 1 < pos ? (unsigned) __ldcg(vcol + (size_t) (2 * j + 1) * HD) : 0u;
+                vpre[j] = lo | (hi << 16);
+            }
+        }
+    } else if (f32attn && pos == 1 && warp == 0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            kf0[i] = ld_act(W.kf32 + ((size_t) (l * 2) * NKV + g) * HD + lane + 32 * i);
+            vf0[i] = ld_act(W.vf32 + ((size_t) (l * 2) * NKV + g) * HD + lane + 32 * i);
+        }
+    }
     // ---- prologue: q, k, v of the new token (warps 0, 1, 2)
     if (warp < 3) {
         const Pkt * src = m.x_qkv + (warp == 0 ? h * HD : warp == 1 ? NH * HD + g * HD : (NH + NKV) * HD + g * HD);
@@ -704,11 +770,10 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
             float mx = -CUDART_INF_F;
             const int n = pos + 1 < 2 ? pos + 1 : 2;
             for (int tt = 0; tt < n; ++tt) {
-                const float * krow = W.kf32 + ((size_t) (l * 2 + tt) * NKV + g) * HD;
                 float acc = 0.0f;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const float kv = (tt == pos) ? s.knew_f[lane + 32 * i] : ld_act(krow + lane + 32 * i);
+                    const float kv = (tt == pos) ? s.knew_f[lane + 32 * i] : kf0[i];       // tt < pos only for pos == 1: row 0
                     acc = __fmaf_rn(kv, s.qf[lane + 32 * i], acc);
                 }
                 sc_t[tt] = __fmul_rn(reduce32_lanes(acc), kq_scale);
@@ -719,11 +784,10 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
             const float inv = (float) (1.0 / sum);
             float o[4] = {0.f, 0.f, 0.f, 0.f};
             for (int tt = 0; tt < n; ++tt) {
-                const float * vrow = W.vf32 + ((size_t) (l * 2 + tt) * NKV + g) * HD;
                 const float p = __fmul_rn(sc_t[tt], inv);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const float vv = (tt == pos) ? s.vnew_f[lane + 32 * i] : ld_act(vrow + lane + 32 * i);
+                    const float vv = (tt == pos) ? s.vnew_f[lane + 32 * i] : vf0[i];
                     o[i] = __fmaf_rn(vv, p, o[i]);
                 }
             }
@@ -732,6 +796,63 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
         }
         // the K/V rows appended above are read by other CTAs one pass later: publish them before this
         // CTA's next packets (off the critical path: after the attention output has left)
+        if (writer && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }
+        return;
+    }
+
+    if (fast) {
+        // ---- scores from registers: warp w has rows w and w + 11, the warp the next row would go to takes the new token
+        float q[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) q[i] = s.qr[lane + 32 * i];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int r = warp + j * NCW;
+            if (r < pos) {
+                const float2 f01 = __half22float2(*reinterpret_cast<const __half2 *>(&kpre[j].x));
+                const float2 f23 = __half22float2(*reinterpret_cast<const __half2 *>(&kpre[j].y));
+                float a = __fmaf_rn(f01.x, q[0], 0.0f);
+                a = __fmaf_rn(f01.y, q[1], a); a = __fmaf_rn(f23.x, q[2], a); a = __fmaf_rn(f23.y, q[3], a);
+                const float sv = __fmul_rn(reduce32_lanes(a), kq_scale);
+                if (lane == 0) s.sc[r] = sv;
+            }
+        }
+        if (warp == pos % NCW) {
+            float a = __fmaf_rn(__half2float(s.knew_h[lane]), q[0], 0.0f);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 32]), q[1], a);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 64]), q[2], a);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 96]), q[3], a);
+            const float sv = __fmul_rn(reduce32_lanes(a), kq_scale);
+            if (lane == 0) s.sc[pos] = sv;
+        }
+        PROF(72);
+        cbar();
+        PROF(53);
+        // ---- soft-max + P.V in warps 4..7 (each evaluates the 16-entry soft-max itself: no barrier in between);
+        //      wd < 32, so every position is a double-precision leftover of ggml_vec_dot_f16 (vec.cpp:381-384)
+        if (warp >= 4 && warp < 8) {
+            const float sv = lane < n_kv ? s.sc[lane] : -CUDART_INF_F;
+            float M = sv;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+            const float pv = softmax_row32(sv, M, lane, n_kv, wd >> 3, min(wd >> 3, (n_kv + 7) >> 3));
+            const unsigned ph = (unsigned) __half_as_ushort(__float2half_rn(pv));
+            PROF(54);
+            const int d = t - 128;
+            const float vnew = __half2float(s.vnew_h[d]);
+            double sumf = 0.0;
+#pragma unroll
+            for (int tt = 0; tt < ATT_FAST_KV; ++tt) {
+                const float p  = __half2float(__ushort_as_half((unsigned short) __shfl_sync(0xffffffffu, ph, tt)));
+                const unsigned vw = vpre[tt >> 1];
+                const float vh = __half2float(__ushort_as_half((unsigned short) ((tt & 1) ? (vw >> 16) : (vw & 0xffffu))));
+                const float pr = __fmul_rn(tt == pos ? vnew : vh, p);
+                sumf += tt < n_kv ? (double) pr : 0.0;
+            }
+            PROF(58);
+            pk_store(att + d, (float) sumf, ep_out);
+        }
+        PROF(56);
         if (writer && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }
         return;
     }
@@ -802,34 +923,8 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     if (wd <= 32) {
         // short rows (the code predictor, early talker steps): one warp, no block-level reductions
         if (warp == 0) {
-            const bool live = lane < n_kv;
-            const bool simd = lane < n8 * 8;
-            const float x = live ? __fsub_rn(s.sc[lane], M) : 0.0f;
-            // straight-line code (this warp is the critical path of the layer): the SIMD exp is evaluated by every
-            // lane, the libm tail only when the row has one (a warp-uniform test); all sums below are selects,
-            // adding +0.0 to a non-negative double is exact
-            float e = live && simd ? v_expf(x) : 0.0f;
-            if (n8 * 8 < n_kv) {
-                const float et = tail_expf(x);
-                e = live && !simd ? et : e;
-            }
-            // chunk sums in the oracle's order: ((e4+e0)+(e6+e2)) + ((e5+e1)+(e7+e3)) per 8 lanes
-            float c = simd || !live ? e : 0.0f;              // masked lanes of a SIMD chunk add +0
-            c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 4));
-            c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 2));
-            c = __fadd_rn(c, __shfl_xor_sync(0xffffffffu, c, 1));
-            float cs[4], ev[7];
-#pragma unroll
-            for (int ch = 0; ch < 4; ++ch) cs[ch] = __shfl_sync(0xffffffffu, c, ch * 8);
-#pragma unroll
-            for (int i = 0; i < 7; ++i) ev[i] = __shfl_sync(0xffffffffu, e, (n8 * 8 + i) & 31);
-            double S = 0.0;
-#pragma unroll
-            for (int ch = 0; ch < 4; ++ch) S += ch < n8v ? (double) cs[ch] : 0.0;
-#pragma unroll
-            for (int i = 0; i < 7; ++i) S += n8 * 8 + i < n_kv ? (double) ev[i] : 0.0;      // scalar tail, in order
-            const float inv = (float) (1.0 / S);
-            if (live) s.ph[lane] = __float2half_rn(__fmul_rn(e, inv));
+            const float pv = softmax_row32(lane < n_kv ? s.sc[lane] : 0.0f, M, lane, n_kv, n8, n8v);
+            if (lane < n_kv) s.ph[lane] = __float2half_rn(pv);
         }
     } else {
         double ds = 0.0;
@@ -1346,7 +1441,8 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
         const int pos = passes[ip].pos >= 0 ? passes[ip].pos : n_past;
         if (passes[ip].stack == 0 && passes[ip].pos < 0) ++n_past;
         // attention CTAs: the K then V history of the head (rows 0..pos-1) follows the QKV slice, KV_CH rows per slice
-        const int n_kvs = (attn_cta && !passes[ip].f32attn) ? (pos + KV_CH - 1) / KV_CH : 0;
+        const bool fast = max(passes[ip].width, pos + 1) <= ATT_FAST_KV;        // same test as attention_head
+        const int n_kvs = (attn_cta && !passes[ip].f32attn && !fast) ? (pos + KV_CH - 1) / KV_CH : 0;
         for (int l = 0; l < n_layers && !aborted; ++l) {
             for (int k = 0; k < 4 + 2 * n_kvs; ++k) {
                 const void * src; int n_slots, slot_bytes = W.wtype == Q3T_TYPE_Q8_0 ? SLOT_Q8 : SLOT_B, tail = SLOT_B;
