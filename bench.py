@@ -105,9 +105,26 @@ class ClockSampler:
 
 def workload(frames):
     from util import HELLO_FULL
-    rng = np.random.default_rng(2024)
-    spk = (rng.standard_normal(1024) * 0.05).astype(np.float32)     # stands in for the ECAPA x-vector (config 2)
+    spk_path = os.path.join(ROOT, "tests", "golden", "speaker_xvector.npz")
+    if os.path.exists(spk_path):
+        # config 2: the x-vector the reference's own ECAPA encoder gives for examples/readme_clone_input.wav with the
+        # random-init spk_enc.* weights (golden G7, oracle/gen_golden.py --speaker)
+        spk = np.load(spk_path)["embedding"].astype(np.float32)
+    else:
+        rng = np.random.default_rng(2024)
+        spk = (rng.standard_normal(1024) * 0.05).astype(np.float32)
     return HELLO_FULL, spk, frames
+
+
+def config_block(args, frames):
+    """The `config` object: identical in both arms (same workload, same frames)."""
+    decoding = "greedy" if args.temperature <= 0 else f"sampled (temp {args.temperature}, top-k {args.top_k}, rep-penalty 1.05)"
+    return {"workload": f"0.6B {args.wtype.upper()} voice clone ('Hello, world!' + 1024-d speaker x-vector), {decoding}, {frames} frames "
+                        f"(12.5 Hz, 16 codebooks) + vocoder over them = one utterance per step; this repo: batch 1 per GPU, one utterance "
+                        f"per rank per step; reference arm: the same utterance on the host CPU (unmodified reference, ggml-CPU AVX2 build, "
+                        f"all host threads, ONE CPU process regardless of --gpus)",
+            "frames": frames, "samples": n_samples(frames), "batch_per_gpu": 1, "vocoder": True,
+            "l2": "weights streamed per frame (3.3 GB) exceed the 126 MB L2; no explicit flush"}
 
 
 # ------------------------------------------------------------------------------ reference arm
@@ -123,30 +140,33 @@ def run_reference(args, rank, world):
     reflib.RefLib.get().set_threads(cores)
     tts_path, voc_path = models("full", args.wtype)
     tokens, spk, _ = workload(args.frames)
-    sample_frames = args.ref_frames
+    sample_frames = args.ref_frames if args.ref_frames > 0 else args.frames
     ref = reflib.RefTTS(tts_path)
     dec = reflib.RefDecoder(voc_path)
 
-    def step():
-        codes = ref.generate(tokens, spk, sample_frames, temperature=0.0)
+    def step(n=sample_frames):
+        codes = ref.generate(tokens, spk, n, temperature=args.temperature, top_k=args.top_k)
         wav = dec.decode(codes)
         return codes, wav
 
+    # warm-up steps touch every weight page and spin the thread pool up; on the CPU that needs a few frames, not a
+    # whole 25 s utterance (the timed steps below are the full workload)
     for _ in range(args.warmup):
-        step()
+        step(min(sample_frames, 8))
     t0 = time.perf_counter()
     for _ in range(args.steps):
         codes, wav = step()
     dt = time.perf_counter() - t0
     audio_s = len(wav) / 24000.0 * args.steps
     v = audio_s / dt
-    sample = f"{sample_frames} greedy frames (generate) + vocoder over them per step, ggml-CPU AVX2 build, {cores} threads"
+    sample = (f"{sample_frames} frames (generate) + vocoder over them per step = the whole workload of `config`, unmodified reference "
+              f"(oracle/_ref, ggml-CPU, AVX2+FMA+F16C build, not -march=native), {cores} threads, one CPU process regardless of --gpus; "
+              f"warm-up steps are 8-frame runs")
     emit_json(({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f16" if args.wtype == "f16" else "q8_0", "data": "synthetic",
-        "config": {"workload": f"0.6B {args.wtype.upper()} voice-clone-style prompt ('Hello, world!' + 1024-d speaker vector), greedy, "
-                               f"bounded sample of {sample_frames} frames per step on the host CPU", "frames": sample_frames},
+        "config": config_block(args, sample_frames),
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -165,7 +185,7 @@ def cpu_baseline(args):
         reflib.RefLib.get().set_threads(cores)
         tts_path, voc_path = models("full", args.wtype)
         tokens, spk, _ = workload(args.frames)
-        n = args.ref_frames
+        n = args.ref_frames if args.ref_frames > 0 else min(args.frames, 96)      # bounded sample (~10 s of CPU work)
         ref = reflib.RefTTS(tts_path)
         dec = reflib.RefDecoder(voc_path)
         ref.generate(tokens, spk, 2, temperature=0.0)                 # warm the page cache / threadpool
@@ -278,6 +298,9 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
     step_s, e2e_s = float(times[0]), float(times[1])
 
+    # ---- BASELINE.json config 4 at this N: 64 utterances, strong scaling, batched engine (every rank takes part)
+    c4 = None if args.no_batch else config4_line(args, rank, world, t, d, have_voc, dist, sync_all)
+
     if rank == 0:
         peak, peak_kind = measured_peaks()
         avg_kv = 10 + frames / 2.0
@@ -290,13 +313,8 @@ def run_ours(args, rank, world, local_rank):
             "warmup": max(args.warmup, 3), "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f16" if args.wtype == "f16" else "q8_0 weights, int8 x int8 / f32 accumulate",
             "data": "synthetic (seeded random-init GGUF of the real 0.6B shapes; no checkpoint offline)",
-            "config": {"workload": f"0.6B {args.wtype.upper()} voice-clone-style prompt ('Hello, world!' + 1024-d speaker vector), "
-                                   + ("greedy" if args.temperature <= 0 else f"sampled (temp {args.temperature}, top-k {args.top_k}, "
-                                      f"rep-penalty 1.05, seed {args.seed})")
-                                   + f", {frames} frames + vocoder, batch 1 per GPU, one utterance per rank per step",
-                       "frames": nf, "samples": ns, "batch_per_gpu": 1, "vocoder": bool(have_voc),
-                       "l2": "weights streamed per frame (3.3 GB) exceed the 126 MB L2; no explicit flush",
-                       "parallelism": f"request-parallel x{world} (no collective)"},
+            "config": config_block(args, frames),
+            "parallelism": f"request-parallel x{world} (no collective)",
             "device_ms_per_step": {"prefill": prefill_ms / args.steps, "frames": frames_ms / args.steps,
                                    "vocoder": voc_ms / args.steps, "events_total": dev_ms / args.steps},
             "e2e": {"value": world * audio_s / e2e_s, "unit": UNIT,
@@ -313,8 +331,10 @@ def run_ours(args, rank, world, local_rank):
             "realtime_factor_per_gpu": audio_s / step_s,
             "clocks": clocks,
         }
-        if world == 1 and not args.no_batch:
-            out["batch64"] = batch64_line(args, t, d, have_voc)
+        if c4 is not None:
+            out["config4"] = c4
+            if world == 1:
+                out["batch64"] = c4                      # BASELINE.json's "batch 64" metric point = config 4 on one GPU
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_baseline(args)
             if cb:
@@ -325,23 +345,27 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
-def batch64_line(args, t, d, have_voc):
-    """BASELINE.json's second metric point: audio-s per wall-s with 64 concurrent utterances on this GPU
-    (config 4 on one GPU): generate_batch advances 8 sequences in lock-step per launch (lm_batch_kernel),
-    the vocoder then decodes each utterance.  Host buffers in, host buffers out, wall clock."""
+def config4_line(args, rank, world, t, d, have_voc, dist, sync_all):
+    """BASELINE.json config 4 / the "batch 64" metric point: 64 utterances (8-64 byte texts, seed 4), greedy, `--frames`
+    frames each + vocoder, strong scaling: utterance i -> rank i mod N, every rank pushes its share through the batched
+    engine (generate_batch: 8 sequences in lock-step per launch), then decodes each utterance.  Host buffers in and out;
+    one timed step bracketed by barrier + synchronize, max over ranks.  Returned on rank 0 (None elsewhere)."""
     import importlib
     import torch
     disp = importlib.import_module("q3t_b200.dispatch")
-    utts = disp.make_workload(64, seed=4, max_len=args.frames)
-    pairs = [(u.tokens, u.spk) for u in utts]
-    if t.generate_batch(pairs[:8], 8) is None:                      # warm-up (instantiation, buffers)
-        return {"error": t.get_error()}
-    torch.cuda.synchronize()
+    n_utt = 64
+    utts = disp.make_workload(n_utt, seed=4, max_len=args.frames)
+    mine = [utts[i] for i in disp.my_share(utts, rank, world)]
+    pairs = [(u.tokens, u.spk) for u in mine]
+    if pairs and t.generate_batch(pairs[:min(8, len(pairs))], 8) is None:          # warm-up (instantiation, buffers)
+        raise SystemExit("generate_batch: " + t.get_error())
+    sync_all()
     w0 = time.perf_counter()
-    codes = t.generate_batch(pairs, args.frames, repetition_penalty=1.05)
+    codes = t.generate_batch(pairs, args.frames, repetition_penalty=1.05) if pairs else []
     if codes is None:
-        return {"error": t.get_error()}
+        raise SystemExit("generate_batch: " + t.get_error())
     tm = t.timing()
+    torch.cuda.synchronize()
     w1 = time.perf_counter()
     ns = 0
     for c in codes:
@@ -349,11 +373,37 @@ def batch64_line(args, t, d, have_voc):
         ns += len(wav)
     torch.cuda.synchronize()
     w2 = time.perf_counter()
+    sync_all()
+    w3 = time.perf_counter()
     nf = sum(len(c) for c in codes)
-    return {"utterances": 64, "frames_each": args.frames, "sequences_per_launch": 8, "value": ns / 24000.0 / (w2 - w0), "unit": UNIT,
-            "generate_s": w1 - w0, "vocoder_s": w2 - w1, "ms_per_batched_frame": tm.frames_ms / max(nf / 8.0, 1.0),
-            "codes_only_audio_s_per_s": nf / FRAME_RATE / (w1 - w0),
-            "workload": "config 4 on one GPU: 64 utterances (8-64 byte texts, seed 4), greedy, host buffers in/out"}
+    groups = (len(pairs) + 7) // 8
+    stats = torch.tensor([w3 - w0, w1 - w0, w2 - w1, tm.prefill_ms * 1e-3, tm.frames_ms * 1e-3], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([float(ns), float(nf)], dtype=torch.float64, device="cuda")
+    if dist:
+        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    if rank != 0:
+        return None
+    step_s, gen_s, voc_s, prefill_s, frames_s = [float(x) for x in stats]
+    ns_all, nf_all = float(tot[0]), float(tot[1])
+    per_gpu = (n_utt + world - 1) // world
+    # bytes one batched frame launch streams: the frame's weights once for all sequences + every sequence's KV history
+    frame_bytes = CODEPRED_FRAME_BYTES[args.wtype] + TALKER_STEP_BYTES[args.wtype] + 8 * KV_BYTES_PER_POS * (10 + args.frames / 2.0 + 1)
+    ms_frame = frames_s * 1e3 / max(groups * args.frames, 1)
+    peak, _ = measured_peaks()
+    return {"utterances": n_utt, "frames_each": args.frames, "n_gpus": world, "utterances_per_gpu": per_gpu, "sequences_per_launch": 8,
+            "value": ns_all / 24000.0 / step_s, "unit": UNIT, "scaling": "strong", "ms_per_step": step_s * 1e3,
+            "phases_s_max_over_ranks": {"prompt_prefill": prefill_s, "frames": frames_s, "generate_wall": gen_s, "vocoder": voc_s},
+            "ms_per_batched_frame": ms_frame, "codes_only_audio_s_per_s": nf_all / FRAME_RATE / gen_s,
+            "roofline": {"kernel": "lm_batch_kernel<8> (one launch = one frame of 8 sequences)", "bound": "hbm",
+                         "algorithmic_bytes_per_launch": int(frame_bytes), "achieved": frame_bytes / (ms_frame * 1e-3) / 1e9,
+                         "peak": peak, "unit": "GB/s", "frac": frame_bytes / (ms_frame * 1e-3) / 1e9 / peak,
+                         "note": "weights are read once per launch for 8 sequences, so HBM is not the binding resource here: the launch is "
+                                 "bound by the FMA pipe (8 x the batch-1 FMAs) and the L2-bandwidth-bound packet exchanges (DESIGN.md 4.1b)"},
+            "limiter": (f"{per_gpu} utterances per GPU = {(per_gpu + 7) // 8} lock-step group(s) of <= 8: frames of a group cost ~fixed latency + "
+                        f"0.145 ms per sequence, prompts/prefills ({prefill_s:.2f} s) and vocoder decodes ({voc_s:.2f} s) run one utterance at a "
+                        f"time and do not shrink below one group's share"),
+            "workload": "config 4: 64 utterances (8-64 byte texts, seed 4), greedy, host buffers in/out, utterance i -> rank i mod N"}
 
 
 def run_sharded_workload(args, rank, world, local_rank, t, d, have_voc, dist, sync_all, m):
@@ -435,7 +485,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=320)
-    ap.add_argument("--ref-frames", type=int, default=96, help="frames per bounded CPU sample")
+    ap.add_argument("--ref-frames", type=int, default=0, help="frames per step of the CPU arms; 0 = --frames (the same workload)")
     ap.add_argument("--wtype", default="f16", choices=["f16", "q8_0"])
     ap.add_argument("--temperature", type=float, default=0.0, help="0 = greedy (configs 1/2/4/5); config 3 uses 0.9")
     ap.add_argument("--top-k", type=int, default=0, help="config 3 uses 50")

@@ -99,17 +99,34 @@ def gen_long(out, n_frames=4096):
     print("wrote", out, codes.shape)
 
 
+def gen_vocoder_long(out, T=1024, n_win=32, win=2048):
+    """Reference waveform for T = 1024 frames; only n_win windows of `win` samples are kept (the whole waveform is
+    7.9 MB): enough to pin the multi-tile attention and the large-grid GEMM paths at a length the short goldens miss."""
+    _, voc = models("tiny", "f16")
+    dec = reflib.RefDecoder(voc)
+    codes = np.random.default_rng(1024).integers(0, 2048, size=(T, 16), dtype=np.int32)
+    wav = dec.decode(codes)
+    dec.close()
+    offsets = np.linspace(0, len(wav) - win, n_win).astype(np.int64)
+    np.savez_compressed(out, codes=codes.astype(np.int16), offsets=offsets, win=np.stack([wav[o:o + win] for o in offsets]).astype(np.float32))
+    print("wrote", out, wav.shape, "rms", float(np.sqrt((wav ** 2).mean())))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--full", action="store_true", help="also write the full-size (28-layer) goldens")
     ap.add_argument("--threads", type=int, default=8)
     ap.add_argument("--only-legacy", action="store_true", help="write only legacy_predict_codes.npz")
     ap.add_argument("--long", action="store_true", help="write only long_f16.npz (4096 greedy frames of the full F16 model)")
+    ap.add_argument("--vocoder-long", action="store_true", help="write only vocoder_long_f16.npz (T = 1024 reference windows)")
     a = ap.parse_args()
     if not reflib.available():
         sys.exit("oracle/_ref/libq3t_ref.so missing: make -f oracle/Makefile.ref")
     reflib.RefLib.get().set_threads(a.threads)
     os.makedirs(GOLDEN, exist_ok=True)
+    if a.vocoder_long:
+        gen_vocoder_long(os.path.join(GOLDEN, "vocoder_long_f16.npz"))
+        return
     if a.long:
         gen_long(os.path.join(GOLDEN, "long_f16.npz"))
         return

@@ -140,6 +140,22 @@ int ref_tts_generate(void * h, const int32_t * tokens, int32_t n_tokens, const f
     return (int) (out.size() / t->get_config().n_codebooks);
 }
 
+// legacy wrappers (src/tts_transformer.cpp:1963-1991, 2110-2120)
+int ref_tts_forward_text(void * h, const int32_t * tokens, int32_t n_tokens, const float * spk, int32_t n_past, float * hidden_out) {
+    auto * t = (TTSTransformer *) h;
+    std::vector<float> hid;
+    if (!t->forward_text(tokens, n_tokens, spk, n_past, hid)) { g_err = t->get_error(); return -1; }
+    memcpy(hidden_out, hid.data(), hid.size() * sizeof(float));
+    return (int) hid.size();
+}
+int ref_tts_forward_codec(void * h, int32_t codec_token, int32_t n_past, float * logits_out) {
+    auto * t = (TTSTransformer *) h;
+    std::vector<float> logits;
+    if (!t->forward_codec(codec_token, n_past, logits)) { g_err = t->get_error(); return -1; }
+    memcpy(logits_out, logits.data(), logits.size() * sizeof(float));
+    return (int) logits.size();
+}
+
 // ---------------- AudioTokenizerDecoder ----------------
 void * ref_dec_load(const char * path) {
     auto * d = new AudioTokenizerDecoder();

@@ -50,6 +50,8 @@ class RefLib:
         L.ref_tts_predict_codes.argtypes = [C.c_void_p, _f32p, _i32p, _f32p]
         L.ref_tts_generate.argtypes = [C.c_void_p, _i32p, C.c_int32, _f32p, C.c_int32, _i32p,
                                        C.c_int32, C.c_float, C.c_float, C.c_int32]
+        L.ref_tts_forward_text.argtypes = [C.c_void_p, _i32p, C.c_int32, _f32p, C.c_int32, _f32p]
+        L.ref_tts_forward_codec.argtypes = [C.c_void_p, C.c_int32, C.c_int32, _f32p]
         L.ref_dec_load.restype = C.c_void_p
         L.ref_dec_load.argtypes = [C.c_char_p]
         L.ref_dec_free.argtypes = [C.c_void_p]
@@ -140,6 +142,20 @@ class RefTTS:
         if self.lib.L.ref_tts_predict_codes(self.h, _fp(hidden), _ip(prev), _fp(out)) < 0:
             raise RuntimeError(self.lib.err())
         return out
+
+    def forward_text(self, tokens, spk, n_past=0):
+        tokens = np.ascontiguousarray(tokens, np.int32)
+        spk = None if spk is None else np.ascontiguousarray(spk, np.float32)
+        hid = np.zeros((len(tokens), self.H), np.float32)
+        if self.lib.L.ref_tts_forward_text(self.h, _ip(tokens), len(tokens), _fp(spk), n_past, _fp(hid)) < 0:
+            raise RuntimeError(self.lib.err())
+        return hid
+
+    def forward_codec(self, token, n_past):
+        logits = np.zeros(self.V, np.float32)
+        if self.lib.L.ref_tts_forward_codec(self.h, int(token), n_past, _fp(logits)) < 0:
+            raise RuntimeError(self.lib.err())
+        return logits
 
     def generate(self, tokens, spk, max_len, language_id=2050, rep_penalty=1.05, temperature=0.0, top_k=0):
         tokens = np.ascontiguousarray(tokens, np.int32)

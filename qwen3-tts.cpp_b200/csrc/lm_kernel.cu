@@ -1671,7 +1671,9 @@ int lm_sample_logits(q3t_ctx * ctx, const Pkt * logits_pk_dev, const unsigned ch
 
 // --------------------------------------------------------------------------- host launch
 int lm_max_grid(q3t_ctx * ctx) {
-    static bool attr_set = false;
+    // function attributes are per device: one flag per device, not per process (a process may hold contexts on several GPUs)
+    static bool attr_set_dev[64] = {};
+    bool & attr_set = attr_set_dev[ctx->device & 63];
     const size_t smem = sizeof(Smem);
     if (!attr_set) {
         if (cudaFuncSetAttribute(lm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem) != cudaSuccess) return -1;
@@ -1707,7 +1709,8 @@ int lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int fram
 // batched frame launch: nb sequences (views in `seqs`), instantiation = smallest NB >= nb
 template <int NB>
 static cudaError_t launch_batch_t(q3t_ctx * ctx, const BatchModel & bm, const PassDesc * passes_dev, int n_passes) {
-    static bool attr_set = false;
+    static bool attr_set_dev[64] = {};                         // per device, see lm_max_grid
+    bool & attr_set = attr_set_dev[ctx->device & 63];
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(lm_batch_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(BSmem<NB>));
         if (e != cudaSuccess) return e;

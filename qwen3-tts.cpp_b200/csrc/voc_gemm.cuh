@@ -474,7 +474,8 @@ inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
         const int MT = mt_env ? mt_env : (tiles256 >= 2 * 148 && p.ntaps * p.Kc >= mt_k ? 2 : 1);   // short K: the epilogue dominates, keep 3 CTAs per SM
         const int smem = std::max(vu_a_ring(MT) + VU_STAGES * vu_b_stage(BN), VU_BM * (BN + 4) * 4);
         const int smem_max = std::max(vu_a_ring(2) + VU_STAGES * vu_b_stage(128), VU_BM * (128 + 4) * 4);
-        static bool attr = false;
+        static bool attr_dev[64] = {};                     // function attributes are per device
+        bool & attr = attr_dev[ctx->device & 63];
         if (!attr) {
             cudaFuncSetAttribute(vgemm_umma<VEPI_GENERIC>,    cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
             cudaFuncSetAttribute(vgemm_umma<VEPI_BIAS_SNAKE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);

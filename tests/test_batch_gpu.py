@@ -45,6 +45,49 @@ def test_batched_codes_equal_single_sequence_codes(tts, n, frames):
         assert len(neq) == 0, f"utterance {i}: first mismatch at frame/codebook {neq[0]}"
 
 
+def test_config4_job_64_utterances_320_frames_equals_generate(tts):
+    """The job bench.py times for config 4 (64 utterances x 320 frames through the batched engine): every code of
+    every utterance equals generate() for it alone -- and generate() at 320 frames is compared with the live
+    reference in tests/test_parity_gpu.py."""
+    utts = _utterances(64, seed=4)
+    got = tts.generate_batch(utts, 320)
+    assert got is not None, tts.get_error()
+    assert len(got) == 64
+    for i, (toks, spk) in enumerate(utts):
+        want = tts.generate(toks, spk, 320, temperature=0.0)
+        assert want is not None, tts.get_error()
+        assert got[i].shape == want.shape == (320, 16), f"utterance {i}"
+        neq = np.argwhere(got[i] != want)
+        assert len(neq) == 0, f"utterance {i}: first mismatch at frame/codebook {neq[0]}"
+
+
+def test_batched_early_stop_two_waves(q3t):
+    """EOS inside the batched engine: 11 utterances of the EOS-scaled model = one wave of 8 + one of 3
+    re-using the buffers; sequences stop at different frames (finished ones keep flowing with frozen outputs),
+    frame counts and codes equal generate() alone (itself pinned to the reference in test_parity_gpu)."""
+    from test_parity_gpu import EOS_LIKE
+    from util import HELLO_TINY
+    t = q3t.TTSTransformer()
+    assert t.load_model(models("tiny", "f16", eos_like=EOS_LIKE)[0]), t.get_error()
+    utts = []
+    for i in range(11):
+        rng = np.random.default_rng(100 + i)
+        toks = HELLO_TINY.copy(); toks[3:11] = rng.integers(32, 120, size=8)
+        utts.append((toks, (rng.standard_normal(1024) * 0.05).astype(np.float32)))
+    got = t.generate_batch(utts, 64)
+    assert got is not None, t.get_error()
+    stops = []
+    for i, (toks, spk) in enumerate(utts):
+        want = t.generate(toks, spk, 64, temperature=0.0)
+        assert got[i].shape == want.shape, f"utterance {i}: {got[i].shape[0]} frames vs {want.shape[0]}"
+        assert np.array_equal(got[i], want), f"utterance {i}"
+        stops.append(want.shape[0])
+    assert len(set(stops)) > 2 and any(n < 64 for n in stops), stops
+    again = t.generate_batch(utts[:3], 64)                      # the engine is reusable after early stops
+    assert all(np.array_equal(again[i], got[i]) for i in range(3))
+    t.close()
+
+
 def test_batch_errors(tts):
     assert tts.generate_batch([(HELLO_FULL[:3], None)], 8) is None
     assert tts.get_error() == "Need at least 4 text tokens for generation"

@@ -18,6 +18,7 @@ from util import GOLDEN, HELLO_FULL, HELLO_TINY, models
 pytestmark = pytest.mark.gpu
 
 LOGIT_TOL = 1e-2      # BASELINE.json north_star: logits within 1e-2 max-abs
+EOS_LIKE = 752        # the early-stop models' EOS row copies this token's row x 1.02 (tools/make_random_gguf.py)
 
 
 def _gold(name):
@@ -119,7 +120,7 @@ def test_generate_is_prefix_stable_and_repeatable(tts_full):
     assert np.array_equal(a[:64], g["codes"])
     b = tts_full.generate(g["tokens"], g["spk"], 400, temperature=0.0)
     assert np.array_equal(a, b)
-    assert a[:, 0].max() < 2048 or (a[:, 0] == 2150).any() is False      # suppressed ids never emitted
+    assert a[:, 0].max() < 2048 and not (a[:, 0] == 2150).any()          # suppressed ids / EOS never emitted
     assert a[:, 1:].max() < 2048 and a.min() >= 0
 
 
@@ -235,7 +236,7 @@ def test_generate_320_frames_identical_to_live_reference(tts_full):
 
 @pytest.mark.skipif(not os.path.exists(os.path.join(os.path.dirname(GOLDEN), "..", "oracle", "_ref", "libq3t_ref.so")),
                     reason="oracle/_ref not shipped")
-def test_generate_q8_0_160_frames_identical_to_live_reference(tts_full_q8):
+def test_generate_q8_0_320_frames_identical_to_live_reference(tts_full_q8):
     """Q8_0 layer weights (config 3's model): int8 x int8 block dots, activations re-quantised per
     mat-vec, ffn_down on de-quantised weights — greedy codes identical to the reference's ggml-CPU run."""
     from oracle import reflib
@@ -243,9 +244,9 @@ def test_generate_q8_0_160_frames_identical_to_live_reference(tts_full_q8):
     ref = reflib.RefTTS(models("full", "q8_0")[0])
     rng = np.random.default_rng(4)
     spk = (rng.standard_normal(1024) * 0.05).astype(np.float32)
-    want = ref.generate(HELLO_FULL, spk, 160, temperature=0.0)
+    want = ref.generate(HELLO_FULL, spk, 320, temperature=0.0)
     ref.close()
-    got = tts_full_q8.generate(HELLO_FULL, spk, 160, temperature=0.0)
+    got = tts_full_q8.generate(HELLO_FULL, spk, 320, temperature=0.0)
     assert got is not None and got.shape == want.shape
     neq = np.argwhere(got != want)
     assert len(neq) == 0, f"first mismatch at frame/codebook {neq[0]}"
@@ -281,3 +282,102 @@ def test_legacy_predict_codes_vs_golden_and_oracle(wtype, request):
     gg = _gold(f"full_{wtype}.npz")
     codes = tf.generate(gg["tokens"], gg["spk"], 4, temperature=0.0)
     assert np.array_equal(codes, gg["codes"][:4])
+
+
+HAVE_REF = os.path.exists(os.path.join(os.path.dirname(GOLDEN), "..", "oracle", "_ref", "libq3t_ref.so"))
+
+
+@pytest.mark.skipif(not HAVE_REF, reason="oracle/_ref not shipped")
+@pytest.mark.parametrize("wtype", ["f16", "q8_0"])
+def test_legacy_wrappers_forward_text_and_forward_codec_vs_live_reference(wtype, request):
+    """forward_text = project_text_tokens (+ speaker vector on every row) -> forward_prefill,
+    forward_codec = codec_embd row -> forward_step (src/tts_transformer.cpp:1963-1991, 2110-2120); forward and
+    forward_with_audio are forward_text without a speaker (:2853-2866).  Bit-exact against the reference."""
+    from oracle import reflib
+    t = _fixture_for(request, "tiny", wtype)
+    reflib.RefLib.get().set_threads(min(16, os.cpu_count() or 4))
+    ref = reflib.RefTTS(models("tiny", wtype)[0])
+    g = _gold(f"tiny_{wtype}.npz")
+    toks = g["tokens"][:12]
+    for spk in (g["spk"], None):
+        ref.init_kv(64)
+        assert t.init_kv_cache(64)
+        want = ref.forward_text(toks, spk)
+        got = t.forward_text(toks, spk)
+        assert got is not None, t.get_error()
+        assert np.array_equal(got, want)
+        for tok, n_past in ((7, 12), (2049, 13), (1500, 14)):
+            a = ref.forward_codec(tok, n_past)
+            b = t.forward_codec(tok, n_past)
+            assert b is not None, t.get_error()
+            assert np.array_equal(a, b), (tok, n_past)
+    assert t.forward_codec(5000, 15) is None and "out of range" in t.get_error()
+    ref.close()
+
+
+@pytest.mark.skipif(not HAVE_REF, reason="oracle/_ref not shipped")
+@pytest.mark.parametrize("wtype", ["f16", "q8_0"])
+def test_eos_early_stop_identical_to_live_reference(q3t, wtype):
+    """the EOS path.  tools/make_random_gguf.py eos_like makes the EOS row a louder copy of a token greedy
+    decoding emits, so generation stops a few to a few dozen frames in; frame count and every code must equal the reference's
+    (src/tts_transformer.cpp:2724-2729: EOS stops BEFORE a frame is emitted), for several utterances that stop at
+    different frames, and the engine must be reusable afterwards (producer drain of in-flight bulk copies)."""
+    from oracle import reflib
+    tts = models("tiny", wtype, eos_like=EOS_LIKE)[0]
+    reflib.RefLib.get().set_threads(min(16, os.cpu_count() or 4))
+    ref = reflib.RefTTS(tts)
+    t = q3t.TTSTransformer()
+    assert t.load_model(tts), t.get_error()
+    stops = []
+    for i in range(8):
+        rng = np.random.default_rng(100 + i)
+        toks = HELLO_TINY.copy(); toks[3:11] = rng.integers(32, 120, size=8)
+        spk = (rng.standard_normal(1024) * 0.05).astype(np.float32)
+        want = ref.generate(toks, spk, 64, temperature=0.0)
+        got = t.generate(toks, spk, 64, temperature=0.0)
+        assert got is not None, t.get_error()
+        assert got.shape == want.shape, f"utterance {i}: {got.shape[0]} frames, reference {want.shape[0]}"
+        assert np.array_equal(got, want)
+        stops.append(want.shape[0])
+    assert any(0 < n < 64 for n in stops), f"no utterance stopped early: {stops} (re-tune EOS_LIKE)"
+    assert len(set(stops)) > 1
+    ref.close()
+    t.close()
+
+
+def test_two_devices_in_one_process(q3t):
+    """kernel attributes (dynamic shared memory > 48 KB) are per device; a process that holds engines on
+    two GPUs (QWEN3_TTS_DEVICE is read at every load_model) must be able to launch on both."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    g = _gold("tiny_f16.npz")
+    tts, voc = models("tiny", "f16")
+    outs, waves = [], []
+    old = os.environ.get("QWEN3_TTS_DEVICE")
+    try:
+        objs = []
+        for dev in (0, 1):
+            os.environ["QWEN3_TTS_DEVICE"] = str(dev)
+            t = q3t.TTSTransformer(); d = q3t.AudioTokenizerDecoder()
+            assert t.load_model(tts), t.get_error()
+            assert d.load_model(voc), d.get_error()
+            objs.append((t, d))
+        for t, d in objs:                                   # first launches on device 1 come after device 0's
+            c = t.generate(g["tokens"], g["spk"], 16, temperature=0.0)
+            assert c is not None, t.get_error()
+            outs.append(c)
+            w = d.decode(c)
+            assert w is not None, d.get_error()
+            waves.append(w)
+        b = objs[1][0].generate_batch([(g["tokens"], g["spk"])] * 3, 8)
+        assert b is not None and np.array_equal(b[0], g["codes"][:8])
+        for t, d in objs:
+            t.close(); d.close()
+    finally:
+        if old is None:
+            os.environ.pop("QWEN3_TTS_DEVICE", None)
+        else:
+            os.environ["QWEN3_TTS_DEVICE"] = old
+    assert np.array_equal(outs[0], g["codes"]) and np.array_equal(outs[1], g["codes"])
+    assert np.array_equal(waves[0], waves[1])

@@ -62,8 +62,10 @@ def test_error_behaviour(q3t, dec):
 
 @pytest.mark.skipif(not os.path.exists(os.path.join(os.path.dirname(GOLDEN), "..", "oracle", "_ref", "libq3t_ref.so")),
                     reason="oracle/_ref not shipped")
-@pytest.mark.parametrize("T", [2, 33])
+@pytest.mark.parametrize("T", [2, 33, 320])
 def test_decode_vs_live_reference(dec, T):
+    # T = 320 is the length bench.py times: the MT = 2 two-accumulator tap-GEMM (taken only when the grid is large) and
+    # the pre-transformer attention across ten 32-position tiles are compared with the reference, not with themselves
     from oracle import reflib
     reflib.RefLib.get().set_threads(min(16, os.cpu_count() or 4))
     ref = reflib.RefDecoder(models("tiny", "f16")[1])
@@ -100,3 +102,44 @@ def test_streaming_decode_equals_whole_decode(dec, chunks):
     dec.stream_reset()
     assert len(dec.decode_append(codes[:2])) == 1920 * 2 - 555
     dec.stream_reset()
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(os.path.dirname(GOLDEN), "..", "oracle", "_ref", "libq3t_ref.so")),
+                    reason="oracle/_ref not shipped")
+def test_usage_normalised_codebooks_vs_live_reference(q3t):
+    """normalize_codebooks (src/audio_tokenizer_decoder.cpp:40-73): files of older converters carry `*.usage`
+    tensors and un-normalised codebooks; rows are divided by max(usage, 1e-5) and re-rounded to F16 at load."""
+    from oracle import reflib
+    voc = models("tiny", "f16", usage=True)[1]
+    reflib.RefLib.get().set_threads(min(16, os.cpu_count() or 4))
+    ref = reflib.RefDecoder(voc)
+    codes = np.random.default_rng(5).integers(0, 2048, size=(6, 16), dtype=np.int32)
+    codes[0, :] = 97 * np.arange(16)                          # entries whose usage is below the epsilon (clamped)
+    want = ref.decode(codes)
+    ref.close()
+    d = q3t.AudioTokenizerDecoder()
+    assert d.load_model(voc), d.get_error()
+    got = d.decode(codes)
+    d.close()
+    assert got is not None and got.shape == want.shape
+    assert np.isfinite(want).all() and np.isfinite(got).all()
+    s = snr_db(want, got)
+    assert s >= SNR_MIN_DB and s >= SNR_EXPECT_DB, f"SNR {s:.1f} dB"
+    plain = np.load(os.path.join(GOLDEN, "vocoder_f16.npz"))     # and it does change the waveform
+    assert not np.array_equal(got[:1000], plain["wav"][:1000])
+
+
+def test_long_decode_matches_committed_reference_windows(dec):
+    """T = 1024 against the reference's waveform (tests/golden/vocoder_long_f16.npz: 32 windows of 2048 samples
+    spread over the 1 965 525 samples, written by oracle/gen_golden.py --vocoder-long)."""
+    path = os.path.join(GOLDEN, "vocoder_long_f16.npz")
+    if not os.path.exists(path):
+        pytest.skip("vocoder_long_f16.npz not generated")
+    g = np.load(path)
+    wav = dec.decode(g["codes"])
+    assert wav is not None and wav.shape == (1920 * g["codes"].shape[0] - 555,)
+    got = np.stack([wav[o:o + g["win"].shape[1]] for o in g["offsets"]])
+    s = snr_db(g["win"].reshape(-1), got.reshape(-1))
+    assert s >= SNR_MIN_DB and s >= SNR_EXPECT_DB, f"SNR {s:.1f} dB"
+    worst = min(snr_db(g["win"][i], got[i]) for i in range(len(g["offsets"])))
+    assert worst >= SNR_MIN_DB, f"worst window {worst:.1f} dB"

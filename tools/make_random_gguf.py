@@ -78,16 +78,18 @@ def synthetic_vocab(n: int) -> list[str]:
 
 
 def write_tts_gguf(path: str, preset: str = "full", seed: int = 1234, wtype: str = "f16",
-                   w_std: float = 0.02, eos_scale: float = 1.0) -> dict:
+                   w_std: float = 0.02, eos_like: int = -1) -> dict:
     """Talker + code predictor file (reference name: qwen3-tts-0.6b-f16.gguf).
 
     wtype "q8_0" quantises exactly the tensors the reference converter quantises
     (attn q/k/v/o, ffn gate/up/down, text_proj fc1/fc2); embeddings and heads stay F16
     (scripts/convert_tts_to_gguf.py:244-270).
 
-    eos_scale != 1 multiplies the EOS row (id 2150) of talker.codec_head: with plain random weights EOS is
-    practically never the arg-max; scaled by ~2-3 it wins at some frame a few dozen frames in, which is what
-    the early-stop tests need (every other tensor is byte-identical to the unscaled file).
+    eos_like >= 0 makes the EOS row (id 2150) of talker.codec_head 1.02 x the row of token `eos_like`: with plain
+    random weights the EOS logit is persistently negative (the hidden state of a random model has a dominant
+    direction) and never wins; as a slightly louder copy of a token that greedy decoding does emit, EOS wins at
+    the first frame where that token would have been chosen, a few to a few dozen frames in and at a different
+    frame per utterance -- what the early-stop tests need (every other tensor is byte-identical to the plain file).
     """
     p = PRESETS[preset]
     rng = _Rng(seed)
@@ -135,8 +137,8 @@ def write_tts_gguf(path: str, preset: str = "full", seed: int = 1234, wtype: str
     _add(w, "talker.text_proj.fc2.bias", rng.normal((H,), 0.01), f)
     _add(w, "talker.codec_embd.weight", rng.normal((CODEC_VOCAB, H), w_std), f)
     head = rng.normal((CODEC_VOCAB, H), w_std)
-    if eos_scale != 1.0:
-        head[2150] *= np.float32(eos_scale)
+    if eos_like >= 0:
+        head[2150] = head[eos_like] * np.float32(1.02)
     _add(w, "talker.codec_head.weight", head, f)
     _add(w, "talker.output_norm.weight", 1.0 + rng.normal((H,), 0.02), f)
 
@@ -195,11 +197,17 @@ def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain:
 
     _add(w, "tok_dec.vq_first.input_proj.weight", fan((256, 512, 1), 512), f)
     _add(w, "tok_dec.vq_first.output_proj.weight", fan((512, 256, 1), 256 * 16), f)
-    _add(w, "tok_dec.vq_first.0.codebook", rng.normal((2048, 256), 1.0), f)
+    def codebook():
+        cb = rng.normal((2048, 256), 1.0)
+        if usage:
+            cb[::97] *= np.float32(1e-3)          # rows whose usage is below the loader's epsilon: x 1e5 must stay finite in F16
+        return cb
+
+    _add(w, "tok_dec.vq_first.0.codebook", codebook(), f)
     _add(w, "tok_dec.vq_rest.input_proj.weight", fan((256, 512, 1), 512), f)
     _add(w, "tok_dec.vq_rest.output_proj.weight", fan((512, 256, 1), 256 * 16), f)
     for i in range(15):
-        _add(w, f"tok_dec.vq_rest.{i}.codebook", rng.normal((2048, 256), 1.0), f)
+        _add(w, f"tok_dec.vq_rest.{i}.codebook", codebook(), f)
     _add(w, "tok_dec.pre_conv.weight", fan((1024, 512, 3), 512 * 3), f)
     _add(w, "tok_dec.pre_conv.bias", rng.normal((1024,), 0.01), f)
     _add(w, "tok_dec.pre_tfm.input_proj.weight", fan((512, 1024), 1024), f)
@@ -273,7 +281,7 @@ def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain:
 
 
 def ensure_models(model_dir: str, preset: str = "tiny", wtype: str = "f16", seed: int = 1234,
-                  voc_seed: int = 4321, verbose: bool = False, eos_scale: float = 1.0,
+                  voc_seed: int = 4321, verbose: bool = False, eos_like: int = -1,
                   usage: bool = False) -> tuple[str, str]:
     """Create (if missing) the two GGUFs under model_dir; returns (tts_path, vocoder_path).
 
@@ -281,13 +289,13 @@ def ensure_models(model_dir: str, preset: str = "tiny", wtype: str = "f16", seed
     weight-type infix so several variants can sit side by side in one cache directory.
     """
     os.makedirs(model_dir, exist_ok=True)
-    eos = "" if eos_scale == 1.0 else f"-eos{eos_scale:g}"
+    eos = "" if eos_like < 0 else f"-eoslike{eos_like}"
     tts = os.path.join(model_dir, f"qwen3-tts-0.6b-{preset}-{wtype}-s{seed}{eos}.gguf")
     voc = os.path.join(model_dir, f"qwen3-tts-tokenizer-f16-s{voc_seed}{'-usage' if usage else ''}.gguf")
     if not os.path.exists(tts):
         if verbose:
             print(f"[make_random_gguf] writing {tts}", file=sys.stderr)
-        write_tts_gguf(tts + ".tmp", preset=preset, seed=seed, wtype=wtype, eos_scale=eos_scale)
+        write_tts_gguf(tts + ".tmp", preset=preset, seed=seed, wtype=wtype, eos_like=eos_like)
         os.replace(tts + ".tmp", tts)
     if not os.path.exists(voc):
         if verbose:
