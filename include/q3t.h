@@ -162,6 +162,15 @@ Q3T_API int  q3t_generate(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_
                           float repetition_penalty, float temperature, int32_t top_k, uint64_t seed,
                           int32_t * codes_out, int32_t * n_frames_out);
 
+/* Streaming form of q3t_generate (extension; the reference pipeline hands codes to the vocoder only
+ * when the utterance is complete, src/qwen3_tts.cpp:345-396).  begin: prompt + prefill; next: up to max_frames more frames,
+ * codes_out int32[max_frames*n_codebooks] receives the new frames (*n_new_out of them), *done_out = 1 after EOS / max_len.
+ * The concatenation over the calls equals what q3t_generate returns for the same arguments, for any chunking. */
+Q3T_API int  q3t_stream_begin(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd,
+                              int32_t max_len, int32_t language_id, float repetition_penalty, float temperature,
+                              int32_t top_k, uint64_t seed);
+Q3T_API int  q3t_stream_next(q3t_ctx * ctx, int32_t max_frames, int32_t * codes_out, int32_t * n_new_out, int32_t * done_out);
+
 /* Batched generate (extension; SURVEY.md §8b "batched variants take n_seq + per-seq arrays"): n_seq
  * independent utterances, greedy, same semantics per utterance as q3t_generate with temperature 0
  * (src/tts_transformer.cpp:2577-2851).  Sequences advance in lock-step, up to 8 per kernel launch;
@@ -268,6 +277,38 @@ Q3T_API void q3t_dec_stream_reset(q3t_dec * d);
 Q3T_API int64_t q3t_dec_decode_append(q3t_dec * d, const int32_t * codes, int32_t n_new_frames, float * samples_out, int64_t cap);
 Q3T_API const char * q3t_dec_get_error(q3t_dec * d);
 Q3T_API q3t_ctx * q3t_dec_engine(q3t_dec * d);
+
+/* ------------------------------------------- streaming / batched front door (extensions)
+ * The reference pipeline synthesises one utterance at a time and decodes after the last frame
+ * (Qwen3TTS::synthesize_internal, src/qwen3_tts.cpp:278-442).  C view of host/b200_pipeline.h. */
+typedef struct q3t_stream_stats {
+    double  t_first_audio_ms;     /* call -> first chunk of samples available */
+    double  t_total_ms;
+    int32_t n_frames, n_chunks;
+    int64_t n_samples;
+} q3t_stream_stats;
+typedef struct q3t_batch_stats {
+    double  t_generate_ms, t_decode_ms, t_total_ms;
+    int64_t n_frames, n_samples;
+} q3t_batch_stats;
+/* generate() in chunks (TTSTransformer::generate_begin / generate_next); 1 = ok, 0 = failed (q3t_tts_get_error) */
+Q3T_API int  q3t_tts_generate_begin(q3t_tts * t, const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd,
+                                    int32_t max_len, int32_t language_id, float repetition_penalty, float temperature, int32_t top_k);
+Q3T_API int  q3t_tts_generate_next(q3t_tts * t, int32_t max_frames, int32_t * codes_out, int32_t * n_new_out, int32_t * done_out);
+/* text tokens -> waveform with the vocoder fed chunk by chunk (first_chunk_frames, then chunk_frames frames at a time);
+ * the samples equal decode(generate(...)); returns the sample count or -1 (q3t_pipe_get_error). */
+Q3T_API int64_t q3t_pipe_synthesize_stream(q3t_tts * t, q3t_dec * d, const int32_t * text_tokens, int32_t n_tokens,
+                                           const float * speaker_embd, int32_t max_len, int32_t language_id,
+                                           float repetition_penalty, float temperature, int32_t top_k,
+                                           int32_t first_chunk_frames, int32_t chunk_frames,
+                                           float * samples_out, int64_t cap, q3t_stream_stats * stats_out);
+/* n utterances through the batched engine (greedy) + one decode each; samples_out[i] has room for caps[i] floats;
+ * 1 = ok, 0 = failed (q3t_pipe_get_error). */
+Q3T_API int  q3t_pipe_synthesize_batch(q3t_tts * t, q3t_dec * d, int32_t n, const int32_t * const * text_tokens, const int32_t * n_tokens,
+                                       const float * const * speaker_embd, int32_t max_len, int32_t language_id,
+                                       float repetition_penalty, float * const * samples_out, const int64_t * caps,
+                                       int64_t * n_samples_out, q3t_batch_stats * stats_out);
+Q3T_API const char * q3t_pipe_get_error(void);
 
 #ifdef __cplusplus
 }

@@ -47,6 +47,16 @@ class TTSConfig(C.Structure):
                                           "codec_think_bos_id", "codec_think_eos_id", "english_language_id")]
 
 
+class StreamStats(C.Structure):
+    _fields_ = [("t_first_audio_ms", C.c_double), ("t_total_ms", C.c_double), ("n_frames", C.c_int32), ("n_chunks", C.c_int32),
+                ("n_samples", C.c_int64)]
+
+
+class BatchStats(C.Structure):
+    _fields_ = [("t_generate_ms", C.c_double), ("t_decode_ms", C.c_double), ("t_total_ms", C.c_double), ("n_frames", C.c_int64),
+                ("n_samples", C.c_int64)]
+
+
 class Timing(C.Structure):
     _fields_ = [("prefill_ms", C.c_double), ("frames_ms", C.c_double), ("vocoder_ms", C.c_double),
                 ("n_frames", C.c_int32), ("kernel_launches", C.c_int64)]
@@ -93,6 +103,15 @@ def lib() -> C.CDLL:
         "q3t_dec_stream_reset": (None, [vp]), "q3t_dec_decode_append": (C.c_int64, [vp, _i32p, C.c_int32, _f32p, C.c_int64]),
         "q3t_build_prompt": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32, _f32p, _i32p, _f32p, _i32p, _f32p]),
         "q3t_project_text": (C.c_int, [vp, _i32p, C.c_int32, _f32p]),
+        "q3t_stream_begin": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_int32, C.c_uint64]),
+        "q3t_stream_next": (C.c_int, [vp, C.c_int32, _i32p, _i32p, _i32p]),
+        "q3t_tts_generate_begin": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_int32]),
+        "q3t_tts_generate_next": (C.c_int, [vp, C.c_int32, _i32p, _i32p, _i32p]),
+        "q3t_pipe_synthesize_stream": (C.c_int64, [vp, vp, _i32p, C.c_int32, _f32p, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_int32,
+                                                   C.c_int32, C.c_int32, _f32p, C.c_int64, C.POINTER(StreamStats)]),
+        "q3t_pipe_synthesize_batch": (C.c_int, [vp, vp, C.c_int32, C.POINTER(_i32p), _i32p, C.POINTER(_f32p), C.c_int32, C.c_int32, C.c_float,
+                                                C.POINTER(_f32p), _i64p, _i64p, C.POINTER(BatchStats)]),
+        "q3t_pipe_get_error": (cp, []),
         "q3t_sample_logits": (C.c_int, [vp, _f32p, C.c_int32, C.c_int32, _i32p, C.c_int32, C.c_float, C.c_float, C.c_int32, C.c_uint64, C.c_int32, _i32p]),
         "q3t_project_text_static_dev": (C.c_int, [vp, vp, C.c_int32, vp]),
         "q3t_project_text_static_max_tokens": (C.c_int, []),
@@ -292,6 +311,23 @@ class TTSTransformer:
             return None
         return out[:nf.value].copy()
 
+    def generate_stream(self, tokens, spk, max_len, chunk, language_id=2050, repetition_penalty=1.05, temperature=0.9, top_k=50):
+        """generate() in chunks of `chunk` frames (generate_begin / generate_next): yields int32[n, 16] arrays."""
+        tokens = np.ascontiguousarray(tokens, np.int32)
+        spk = None if spk is None else np.ascontiguousarray(spk, np.float32)
+        if not self.L.q3t_tts_generate_begin(self.h, _ip(tokens), len(tokens), _fp(spk), max_len, language_id,
+                                             repetition_penalty, temperature, top_k):
+            raise Q3TError(self.get_error())
+        done = max_len <= 0
+        while not done:
+            buf = np.zeros((chunk, 16), np.int32)
+            n, d = C.c_int32(0), C.c_int32(1)
+            if not self.L.q3t_tts_generate_next(self.h, chunk, _ip(buf), C.byref(n), C.byref(d)):
+                raise Q3TError(self.get_error())
+            done = bool(d.value)
+            if n.value:
+                yield buf[:n.value].copy()
+
     def generate_batch(self, utterances, max_len, language_id=2050, repetition_penalty=1.05):
         """utterances: list of (tokens int32[], speaker f32[1024] or None); greedy; returns a list of code arrays."""
         n = len(utterances)
@@ -439,3 +475,39 @@ class AudioTokenizerDecoder:
         if n < 0:
             return None
         return out[:n].copy()
+
+
+def synthesize_stream(tts: TTSTransformer, dec: AudioTokenizerDecoder, tokens, spk, max_len, first_chunk=8, chunk=32,
+                      language_id=2050, repetition_penalty=1.05, temperature=0.0, top_k=0):
+    """Streaming front door (host/b200_pipeline.h): returns (waveform, StreamStats)."""
+    tokens = np.ascontiguousarray(tokens, np.int32)
+    spk = None if spk is None else np.ascontiguousarray(spk, np.float32)
+    cap = 1920 * max(max_len, 1) + 16
+    out = np.zeros(cap, np.float32)
+    st = StreamStats()
+    n = lib().q3t_pipe_synthesize_stream(tts.h, dec.h, _ip(tokens), len(tokens), _fp(spk), max_len, language_id, repetition_penalty,
+                                         temperature, top_k, first_chunk, chunk, _fp(out), cap, C.byref(st))
+    if n < 0:
+        raise Q3TError(lib().q3t_pipe_get_error().decode())
+    return out[:n].copy(), st
+
+
+def synthesize_batch(tts: TTSTransformer, dec: AudioTokenizerDecoder, utterances, max_len, language_id=2050, repetition_penalty=1.05):
+    """Batched front door: utterances = [(tokens, spk or None)], greedy; returns ([waveform], BatchStats)."""
+    n = len(utterances)
+    toks = [np.ascontiguousarray(u[0], np.int32) for u in utterances]
+    spks = [None if u[1] is None else np.ascontiguousarray(u[1], np.float32) for u in utterances]
+    cap = 1920 * max(max_len, 1) + 16
+    outs = [np.zeros(cap, np.float32) for _ in range(n)]
+    tp = (_i32p * n)(*[_ip(t) for t in toks])
+    sp = (_f32p * n)(*[_fp(x) if x is not None else C.cast(None, _f32p) for x in spks])
+    op = (_f32p * n)(*[_fp(o) for o in outs])
+    nt = np.array([len(t) for t in toks], np.int32)
+    caps = np.full(n, cap, np.int64)
+    ns = np.zeros(n, np.int64)
+    st = BatchStats()
+    ok = lib().q3t_pipe_synthesize_batch(tts.h, dec.h, n, tp, _ip(nt), sp, max_len, language_id, repetition_penalty, op,
+                                         caps.ctypes.data_as(_i64p), ns.ctypes.data_as(_i64p), C.byref(st))
+    if not ok:
+        raise Q3TError(lib().q3t_pipe_get_error().decode())
+    return [outs[i][:ns[i]].copy() for i in range(n)], st

@@ -910,6 +910,72 @@ extern "C" int q3t_generate(q3t_ctx * ctx, const int32_t * text_tokens, int32_t 
     return Q3T_OK;
 }
 
+// ------------------------------------------------------------------------------ streaming generate
+// The generate loop of src/tts_transformer.cpp:2577-2851 cut into chunks of frames (the reference
+// pipeline only hands codes to the vocoder when the whole utterance is done, src/qwen3_tts.cpp:345-396).  begin = prompt
+// staging + prefill + frame program; next = up to max_frames more frame launches, returns the codes of the new frames.
+// The codes are those of q3t_generate with the same arguments (same launches, same state), chunk size has no effect.
+extern "C" int q3t_stream_begin(q3t_ctx * ctx, const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd,
+                                int32_t max_len, int32_t language_id, float repetition_penalty, float temperature,
+                                int32_t top_k, uint64_t seed) {
+    if (!ctx) return Q3T_ERR_ARG;
+    ctx->stream_max_len = 0; ctx->stream_launched = 0; ctx->stream_fetched = 0; ctx->stream_done = 1;
+    if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (!text_tokens) return set_err(ctx, Q3T_ERR_ARG, "text_tokens is null");
+    if (n_tokens < 4) return set_err(ctx, Q3T_ERR_ARG, "Need at least 4 text tokens for generation");
+    if (max_len <= 0) return Q3T_OK;
+    int rc = q3t_stage_prompt(ctx, text_tokens, n_tokens, speaker_embd, language_id);
+    if (rc) return rc;
+    const q3t_tts_config & c = ctx->cfg;
+    const int M = ctx->staged_prefill_len;
+    const int required_ctx = M + max_len + 8;
+    if (ctx->n_ctx < required_ctx || ctx->n_ctx > std::max(required_ctx * 2, 512))
+        if ((rc = q3t_kv_init(ctx, required_ctx))) return rc;
+    if ((rc = ensure_buf_i(ctx, &ctx->d_codes, &ctx->codes_cap, max_len * NCB))) return rc;
+    ctx->hm.codes_out = ctx->d_codes;
+    GenState st = default_state(ctx);
+    st.max_len = max_len; st.n_past = M; st.trailing_len = ctx->staged_trailing_len;
+    st.rep_penalty = repetition_penalty; st.temperature = temperature; st.top_k = top_k; st.seed = seed;
+    if ((rc = reset_state(ctx, st, true))) return rc;
+    if ((rc = run_talker_rows(ctx, ctx->d_prefill, M, 0, false, 1, nullptr))) return rc;
+    std::vector<PassDesc> v;
+    append_codepred(ctx, v, XM_HIDDEN, nullptr);
+    v.push_back(make_pass(0, XM_TALKER_NEXT, 0, -1, 0, 0, c.n_layers, 1));
+    if ((rc = upload_passes(ctx, v))) return rc;
+    ctx->stream_n_passes = (int) v.size();
+    ctx->stream_max_len = max_len; ctx->stream_done = 0;
+    return Q3T_OK;
+}
+
+extern "C" int q3t_stream_next(q3t_ctx * ctx, int32_t max_frames, int32_t * codes_out, int32_t * n_new_out, int32_t * done_out) {
+    if (!ctx || !n_new_out || !done_out) return Q3T_ERR_ARG;
+    *n_new_out = 0; *done_out = 1;
+    if (ctx->stream_done || ctx->stream_max_len <= 0) return Q3T_OK;
+    if (max_frames <= 0) return set_err(ctx, Q3T_ERR_ARG, "max_frames must be > 0");
+    cudaSetDevice(ctx->device);
+    const int n = std::min(max_frames, ctx->stream_max_len - ctx->stream_launched);
+    int rc = Q3T_OK;
+    for (int i = 0; i < n && !rc; ++i) rc = lm_launch(ctx, ctx->d_passes, ctx->stream_n_passes, 1);
+    if (rc) return rc;
+    ctx->stream_launched += n;
+    GenState out;
+    CK(cudaMemcpyAsync(&out, ctx->hm.st, sizeof(GenState), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (out.error) return set_err(ctx, Q3T_ERR_DEVICE, "device watchdog: a grid barrier timed out inside lm_kernel");
+    const int n_new = out.frame - ctx->stream_fetched;
+    if (n_new > 0 && codes_out) {
+        CK(cudaMemcpyAsync(codes_out, ctx->d_codes + (size_t) ctx->stream_fetched * NCB, (size_t) n_new * NCB * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->stream_fetched = out.frame;
+    ctx->last_n_frames = out.frame;
+    ctx->timing.n_frames = out.frame;
+    ctx->stream_done = (out.done || ctx->stream_launched >= ctx->stream_max_len) ? 1 : 0;
+    *n_new_out = n_new > 0 ? n_new : 0;
+    *done_out = ctx->stream_done;
+    return Q3T_OK;
+}
+
 // ------------------------------------------------------------------------------ batched generate
 // n_seq independent utterances, greedy, in waves of Q3T_MAX_BATCH sequences that advance in lock-step
 // through lm_batch_kernel (lm_batch.inc).  Each sequence gets its own packet block, KV caches, state,

@@ -180,6 +180,8 @@ struct q3t_ctx {
     q3t_vocoder * voc = nullptr;
     float * d_samples = nullptr; int64_t samples_cap = 0; int64_t last_n_samples = 0;
     int last_n_frames = 0;
+    // streaming generate (q3t_stream_begin / q3t_stream_next)
+    int stream_max_len = 0, stream_launched = 0, stream_fetched = 0, stream_done = 1, stream_n_passes = 0;
 
     q3t_timing timing{};
     int * h_done = nullptr;           // pinned flag pair polled by the generate loop

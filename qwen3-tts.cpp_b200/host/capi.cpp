@@ -3,6 +3,7 @@
 #include "../../include/q3t.h"
 #include "audio_tokenizer_decoder.h"
 #include "b200_gguf_loader.h"
+#include "b200_pipeline.h"
 #include "tts_transformer.h"
 
 #include <cstring>
@@ -165,6 +166,67 @@ Q3T_API int64_t q3t_dec_decode_append(q3t_dec * d, const int32_t * codes, int32_
     return (int64_t) o.size();
 }
 Q3T_API const char * q3t_dec_get_error(q3t_dec * d) { return d ? d->d.get_error().c_str() : "null object"; }
+
+// ---------------------------------------------------------------- streaming / batched front door (b200_pipeline.h)
+Q3T_API int q3t_tts_generate_begin(q3t_tts * t, const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd, int32_t max_len,
+                                   int32_t language_id, float repetition_penalty, float temperature, int32_t top_k) {
+    return t && t->t.generate_begin(text_tokens, n_tokens, speaker_embd, max_len, language_id, repetition_penalty, temperature, top_k) ? 1 : 0;
+}
+Q3T_API int q3t_tts_generate_next(q3t_tts * t, int32_t max_frames, int32_t * codes_out, int32_t * n_new_out, int32_t * done_out) {
+    if (!t || !n_new_out || !done_out) return 0;
+    std::vector<int32_t> c; bool done = true;
+    if (!t->t.generate_next(max_frames, c, done)) return 0;
+    if (codes_out && !c.empty()) memcpy(codes_out, c.data(), c.size() * sizeof(int32_t));
+    *n_new_out = (int32_t) (c.size() / (size_t) t->t.get_config().n_codebooks);
+    *done_out = done ? 1 : 0;
+    return 1;
+}
+static std::string g_pipe_err;
+Q3T_API const char * q3t_pipe_get_error(void) { return g_pipe_err.c_str(); }
+Q3T_API int64_t q3t_pipe_synthesize_stream(q3t_tts * t, q3t_dec * d, const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd,
+                                           int32_t max_len, int32_t language_id, float repetition_penalty, float temperature, int32_t top_k,
+                                           int32_t first_chunk_frames, int32_t chunk_frames, float * samples_out, int64_t cap,
+                                           q3t_stream_stats * stats_out) {
+    if (!t || !d) { g_pipe_err = "null object"; return -1; }
+    b200::synth_params p;
+    p.max_audio_tokens = max_len; p.language_id = language_id; p.repetition_penalty = repetition_penalty; p.temperature = temperature; p.top_k = top_k;
+    int64_t n = 0;
+    b200::stream_stats st;
+    auto sink = [&](const float * s, size_t k) {
+        if (samples_out && n < cap) memcpy(samples_out + n, s, (size_t) std::min<int64_t>((int64_t) k, cap - n) * sizeof(float));
+        n += (int64_t) k;
+    };
+    if (!b200::synthesize_stream(t->t, d->d, text_tokens, n_tokens, speaker_embd, p, first_chunk_frames, chunk_frames, sink, &st, g_pipe_err)) return -1;
+    if (stats_out) {
+        stats_out->t_first_audio_ms = st.t_first_audio_ms; stats_out->t_total_ms = st.t_total_ms;
+        stats_out->n_frames = st.n_frames; stats_out->n_chunks = st.n_chunks; stats_out->n_samples = st.n_samples;
+    }
+    return n;
+}
+Q3T_API int q3t_pipe_synthesize_batch(q3t_tts * t, q3t_dec * d, int32_t n, const int32_t * const * text_tokens, const int32_t * n_tokens,
+                                      const float * const * speaker_embd, int32_t max_len, int32_t language_id, float repetition_penalty,
+                                      float * const * samples_out, const int64_t * caps, int64_t * n_samples_out, q3t_batch_stats * stats_out) {
+    if (!t || !d || n <= 0 || !text_tokens || !n_tokens || !n_samples_out) { g_pipe_err = "bad argument"; return 0; }
+    b200::synth_params p;
+    p.max_audio_tokens = max_len; p.language_id = language_id; p.repetition_penalty = repetition_penalty; p.temperature = 0.0f; p.top_k = 0;
+    std::vector<const int32_t *> tt(text_tokens, text_tokens + n);
+    std::vector<int32_t> nt(n_tokens, n_tokens + n);
+    std::vector<const float *> sp;
+    if (speaker_embd) sp.assign(speaker_embd, speaker_embd + n);
+    std::vector<std::vector<float>> audio;
+    b200::batch_stats st;
+    if (!b200::synthesize_batch(t->t, d->d, tt, nt, sp, p, audio, &st, g_pipe_err)) return 0;
+    for (int i = 0; i < n; ++i) {
+        n_samples_out[i] = (int64_t) audio[i].size();
+        if (samples_out && samples_out[i] && caps)
+            memcpy(samples_out[i], audio[i].data(), (size_t) std::min<int64_t>((int64_t) audio[i].size(), caps[i]) * sizeof(float));
+    }
+    if (stats_out) {
+        stats_out->t_generate_ms = st.t_generate_ms; stats_out->t_decode_ms = st.t_decode_ms; stats_out->t_total_ms = st.t_total_ms;
+        stats_out->n_frames = st.n_frames; stats_out->n_samples = st.n_samples;
+    }
+    return 1;
+}
 Q3T_API q3t_ctx * q3t_dec_engine(q3t_dec * d) { return d ? d->d.engine() : nullptr; }
 
 } // extern "C"

@@ -229,6 +229,25 @@ bool TTSTransformer::generate(const int32_t * text_tokens, int32_t n_tokens, con
     return true;
 }
 
+bool TTSTransformer::generate_begin(const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd, int32_t max_len,
+                                    int32_t language_id, float repetition_penalty, float temperature, int32_t top_k) {
+    if (!loaded_) { error_msg_ = "Model not loaded"; return false; }
+    if (!text_tokens) { error_msg_ = "text_tokens is null"; return false; }
+    if (n_tokens < 4) { error_msg_ = "Need at least 4 text tokens for generation"; return false; }
+    return !fail(q3t_stream_begin(engine_, text_tokens, n_tokens, speaker_embd, max_len, language_id, repetition_penalty,
+                                  temperature, top_k, seed_ + 0x9E3779B97F4A7C15ULL * (++draws_)));
+}
+
+bool TTSTransformer::generate_next(int32_t max_frames, std::vector<int32_t> & new_codes, bool & done) {
+    if (!loaded_) { error_msg_ = "Model not loaded"; return false; }
+    new_codes.resize((size_t) std::max(max_frames, 0) * config_.n_codebooks);
+    int32_t n_new = 0, d = 1;
+    if (fail(q3t_stream_next(engine_, max_frames, new_codes.data(), &n_new, &d))) { new_codes.clear(); return false; }
+    new_codes.resize((size_t) n_new * config_.n_codebooks);
+    done = d != 0;
+    return true;
+}
+
 bool TTSTransformer::generate_batch(const std::vector<const int32_t *> & text_tokens, const std::vector<int32_t> & n_tokens,
                                     const std::vector<const float *> & speaker_embd, int32_t max_len,
                                     std::vector<std::vector<int32_t>> & outputs, int32_t language_id, float repetition_penalty) {

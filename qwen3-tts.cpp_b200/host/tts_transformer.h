@@ -113,6 +113,11 @@ public:
                         const std::vector<const float *> & speaker_embd, int32_t max_len,
                         std::vector<std::vector<int32_t>> & outputs,
                         int32_t language_id = 2050, float repetition_penalty = 1.05f);
+    // streaming generate: begin = prompt + prefill, next = up to max_frames more frames appended to `new_codes`;
+    // the concatenation equals generate() with the same arguments
+    bool generate_begin(const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd, int32_t max_len,
+                        int32_t language_id = 2050, float repetition_penalty = 1.05f, float temperature = 0.9f, int32_t top_k = 50);
+    bool generate_next(int32_t max_frames, std::vector<int32_t> & new_codes, bool & done);
     void set_seed(uint64_t seed) { seed_ = seed; draws_ = 0; }   // the reference's rng_ cannot be seeded; re-seeding restarts the stream
     q3t_ctx * engine() const { return engine_; }
     const tts_timing & last_timing() const { return timing_; }
