@@ -52,7 +52,7 @@ typedef enum q3t_status {
 } q3t_status;
 
 /* ggml type ids as stored in GGUF (ggml/include/ggml.h:390-398) */
-enum { Q3T_TYPE_F32 = 0, Q3T_TYPE_F16 = 1, Q3T_TYPE_Q8_0 = 8 };
+enum { Q3T_TYPE_F32 = 0, Q3T_TYPE_F16 = 1, Q3T_TYPE_Q8_0 = 8, Q3T_TYPE_Q4_K = 12 };
 
 typedef struct q3t_ctx q3t_ctx;
 
@@ -93,7 +93,9 @@ Q3T_API int  q3t_set_tts_config(q3t_ctx * ctx, const q3t_tts_config * cfg);
 /* replaces ggml_backend_tensor_set per tensor in load_tensor_data
  * (src/tts_transformer.cpp:648-677) and load_tensor_data_from_file
  * (src/gguf_loader.cpp:154-227).  `name` is the GGUF tensor name, `type` a Q3T_TYPE_*,
- * `ne` the ggml shape (ne[0] fastest).  Unknown names are ignored (returns 1). */
+ * `ne` the ggml shape (ne[0] fastest).  Unknown names are ignored (returns 1).  F16 everywhere and Q8_0 talker /
+ * code-predictor matrices are consumed natively (bit-exact paths); F32 and Q4_K matrices and Q8_0 vocoder matrices
+ * (the other outputs of the reference's converters) are converted to F16 on the host here. */
 Q3T_API int  q3t_upload_tensor(q3t_ctx * ctx, const char * name, int32_t type,
                                const int64_t ne[4], const void * data, size_t nbytes);
 /* private device repack after the last upload (fused QKV / gate-up planes, Q8_0 split into

@@ -149,9 +149,53 @@ static size_t type_row_bytes(int32_t type, int64_t ne0) {
     switch (type) {
         case Q3T_TYPE_F32:  return (size_t) ne0 * 4;
         case Q3T_TYPE_F16:  return (size_t) ne0 * 2;
-        case Q3T_TYPE_Q8_0: return (size_t) (ne0 / 32) * 34;
+        case Q3T_TYPE_Q8_0: return (ne0 % 32) ? 0 : (size_t) (ne0 / 32) * 34;
+        case Q3T_TYPE_Q4_K: return (ne0 % 256) ? 0 : (size_t) (ne0 / 256) * 144;
         default: return 0;
     }
+}
+
+// ---- GGUF variants that the kernels do not consume natively are converted to F16 on the host at
+// load: F32 matrices (`convert_*_to_gguf.py --type f32`), Q4_K talker / code-predictor matrices
+// (scripts/convert_tts_to_gguf.py:306-317) and Q8_0 vocoder matrices (scripts/convert_tokenizer_to_gguf.py:286-297).
+// The reference multiplies these types with other activation roundings (F32 x F32, Q4_K x Q8_K, Q8_0 x Q8_0), so such
+// files are supported within the logit / SNR tolerance, not bit for bit; F16 files and Q8_0 talker files keep the
+// bit-exact native paths.
+static inline float half_bits_to_float(uint16_t h) { __half v; memcpy(&v, &h, 2); return __half2float(v); }
+
+// block_q4_K (ggml/src/ggml-common.h: 256 weights = {half d, half dmin, u8 scales[12] (8 x 6-bit scale + 8 x 6-bit min),
+// u8 qs[128]}); value = d * scale * q - dmin * min per sub-block of 32
+static void dequant_q4_k_row(const uint8_t * src, int64_t n, float * dst) {
+    for (int64_t b = 0; b < n / 256; ++b, src += 144, dst += 256) {
+        uint16_t dh, mh;
+        memcpy(&dh, src, 2); memcpy(&mh, src + 2, 2);
+        const float d = half_bits_to_float(dh), dmin = half_bits_to_float(mh);
+        const uint8_t * sc = src + 4, * q = src + 16;
+        for (int j = 0; j < 8; ++j) {
+            int scale, mn;
+            if (j < 4) { scale = sc[j] & 63; mn = sc[j + 4] & 63; }
+            else       { scale = (sc[j + 4] & 0xF) | ((sc[j - 4] >> 6) << 4); mn = (sc[j + 4] >> 4) | ((sc[j] >> 6) << 4); }
+            const float dl = d * (float) scale, ml = dmin * (float) mn;
+            const uint8_t * qq = q + 32 * (j >> 1);
+            for (int l = 0; l < 32; ++l) dst[32 * j + l] = dl * (float) ((j & 1) ? (qq[l] >> 4) : (qq[l] & 0xF)) - ml;
+        }
+    }
+}
+static void dequant_q8_0_row(const uint8_t * src, int64_t n, float * dst) {
+    for (int64_t b = 0; b < n / 32; ++b, src += 34, dst += 32) {
+        uint16_t dh; memcpy(&dh, src, 2);
+        const float d = half_bits_to_float(dh);
+        for (int l = 0; l < 32; ++l) dst[l] = (float) (int8_t) src[2 + l] * d;
+    }
+}
+
+// does this tensor have to become F16 before the engine can use it?
+static bool wants_f16_conversion(const char * name, int32_t type, const int64_t ne[4]) {
+    const bool matrix = ne[1] * ne[2] * ne[3] > 1;            // 1-D tensors (norms, biases, snake parameters) stay F32
+    if (!matrix) return false;
+    if (type == Q3T_TYPE_F32 || type == Q3T_TYPE_Q4_K) return true;
+    if (type == Q3T_TYPE_Q8_0 && !strncmp(name, "tok_dec.", 8)) return true;   // the tensor-core vocoder consumes F16 operands
+    return false;
 }
 
 extern "C" int q3t_upload_tensor(q3t_ctx * ctx, const char * name, int32_t type, const int64_t ne[4],
@@ -160,18 +204,38 @@ extern "C" int q3t_upload_tensor(q3t_ctx * ctx, const char * name, int32_t type,
     cudaSetDevice(ctx->device);
     const bool mine = !strncmp(name, "talker.", 7) || !strncmp(name, "code_pred.", 10) || !strncmp(name, "tok_dec.", 8);
     if (!mine) return 1;       // spk_enc.*, tok_enc.* ...: not on this path (src/tts_transformer.cpp:375-377)
+    for (int i = 0; i < 4; ++i) if (ne[i] <= 0 || ne[i] > (int64_t) 1 << 40) return set_err(ctx, Q3T_ERR_FORMAT, std::string("bad shape for ") + name);
     const size_t rb = type_row_bytes(type, ne[0]);
     if (rb == 0) return set_err(ctx, Q3T_ERR_FORMAT, std::string("unsupported tensor type for ") + name);
-    if (type == Q3T_TYPE_Q8_0 && (ne[0] % 32) != 0) return set_err(ctx, Q3T_ERR_FORMAT, std::string("Q8_0 row not a multiple of 32: ") + name);
-    const size_t expect = rb * (size_t) (ne[1] * ne[2] * ne[3]);
+    const size_t rows = (size_t) (ne[1] * ne[2] * ne[3]);
+    const size_t expect = rb * rows;
     if (expect != nbytes) return set_err(ctx, Q3T_ERR_FORMAT, std::string("size mismatch for ") + name);
     auto it = ctx->raw.find(name);
     if (it != ctx->raw.end()) { cudaFree(it->second.dev); ctx->raw.erase(it); }
     q3t_host_tensor t{};
-    t.type = type; t.nbytes = nbytes;
+    t.type = type; t.src_type = type; t.nbytes = nbytes;
     for (int i = 0; i < 4; ++i) t.ne[i] = ne[i];
+    std::vector<__half> conv;
+    if (wants_f16_conversion(name, type, ne)) {
+        conv.resize((size_t) ne[0] * rows);
+        std::vector<float> rowf((size_t) ne[0]);
+        for (size_t r = 0; r < rows; ++r) {
+            const uint8_t * src = static_cast<const uint8_t *>(data) + r * rb;
+            const float * f = rowf.data();
+            if (type == Q3T_TYPE_F32) f = reinterpret_cast<const float *>(src);
+            else if (type == Q3T_TYPE_Q4_K) dequant_q4_k_row(src, ne[0], rowf.data());
+            else dequant_q8_0_row(src, ne[0], rowf.data());
+            __half * o = conv.data() + r * (size_t) ne[0];
+            for (int64_t k = 0; k < ne[0]; ++k) o[k] = __float2half_rn(f[k]);
+        }
+        data = conv.data();
+        nbytes = conv.size() * sizeof(__half);
+        t.type = Q3T_TYPE_F16; t.nbytes = nbytes;
+        ctx->converted_tensors++;
+    }
     CK(cudaMalloc(&t.dev, std::max<size_t>(nbytes, 16)));
     cudaError_t e = cudaMemcpyAsync(t.dev, data, nbytes, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess && !conv.empty()) e = cudaStreamSynchronize(ctx->stream);       // the staging vector dies with this call
     if (e != cudaSuccess) { cudaFree(t.dev); return cuda_check(ctx, e, "tensor upload"); }
     ctx->raw[name] = t;
     return Q3T_OK;

@@ -135,6 +135,7 @@ constexpr int LM_ATT_MAX_KV = 4608;  // KV positions the attention phase support
 
 struct q3t_host_tensor {
     int32_t type;
+    int32_t src_type;    // dtype in the GGUF file (differs from `type` when the matrix was converted to F16 at load)
     int64_t ne[4];
     void * dev;          // raw upload in GGUF layout
     size_t nbytes;
@@ -154,6 +155,7 @@ struct q3t_ctx {
 
     std::map<std::string, q3t_host_tensor> raw;     // uploaded tensors by GGUF name
     bool tts_ready = false;
+    int converted_tensors = 0;                      // tensors converted to F16 at load (F32 / Q4_K / Q8_0-vocoder files)
     bool voc_ready = false;
 
     // talker / code predictor

@@ -62,7 +62,9 @@ __device__ __forceinline__ float silu_f(float g) { return g / (1.0f + expf(-g));
 __device__ __forceinline__ void vgemm_epilogue_pair(const VGemm & p, size_t m, int n, float v0, float v1, bool ok1) {
     // two adjacent columns n, n+1 of row m (n even)
     if (p.swiglu) {
-        p.out16[m * p.ld16 + (n >> 1)] = __float2half_rn(silu_f(v0) * v1);
+        const float sv = silu_f(v0) * v1;
+        p.out16[m * p.ld16 + (n >> 1)] = __float2half_rn(sv);
+        if (p.out32) p.out32[m * p.ld32 + (n >> 1)] = sv;          // un-rounded copy (Q8_0 files: the next mat-mul quantises it)
         return;
     }
     float v[2] = {v0, v1};
@@ -118,7 +120,9 @@ template <int EPI>
 __device__ __forceinline__ void vgemm_epilogue_cols(const VGemm & p, size_t m, int n, float v0, float v1, bool ok1, const VEpiCols & c, float2 rr) {
     constexpr bool G = EPI == VEPI_GENERIC;
     if (G && p.swiglu) {
-        p.out16[m * p.ld16 + (n >> 1)] = __float2half_rn(silu_f(v0) * v1);
+        const float sv = silu_f(v0) * v1;
+        p.out16[m * p.ld16 + (n >> 1)] = __float2half_rn(sv);
+        if (p.out32) p.out32[m * p.ld32 + (n >> 1)] = sv;          // un-rounded copy (Q8_0 files: the next mat-mul quantises it)
         return;
     }
     const bool has_bias = G ? p.bias != nullptr : true;

@@ -94,6 +94,9 @@ struct q3t_vocoder {
     VSnake dec5;
     const __half * dec6;               // [7*96]  k-major
     const float * dec6_b;
+    // Q8_0 matrices in the file (scripts/convert_tokenizer_to_gguf.py:286-297): the reference then quantises the ACTIVATIONS of
+    // those mat-muls to Q8_0 too; the F16 operand is passed through the same quantise / de-quantise before the GEMM
+    bool q8_in_proj = false, q8_tfm[TL] = {}, q8_out_proj = false, q8_pw[2] = {};
     float * rope = nullptr;            // [n_rope][64]: cos[32] | sin[32]
     int n_rope = 0;
     std::vector<void *> owned;         // repacked weights
@@ -145,6 +148,25 @@ __global__ void k_exp(const float * __restrict__ x, float * __restrict__ y, int 
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) y[i] = expf(sign * x[i]);
 }
+// Activation side of ggml's mul_mat with Q8_0 weights (AVX2 quantize_row_q8_0, arch/x86/quants.c:290-385): per block of 32,
+// d = F16(amax / 127), q = round-half-even(x * 127 / amax); the operand becomes q * d (one warp per block, in place)
+// src32 (optional): the un-rounded activations, which is what the reference quantises (rounding to F16 first would flip
+// a few percent of the quants by one step)
+__global__ void k_fake_quant_q8(__half * __restrict__ a, const float * __restrict__ src32, long n_blocks) {
+    const int lane = threadIdx.x & 31;
+    const long w0 = ((long) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((long) gridDim.x * blockDim.x) >> 5;
+    for (long b = w0; b < n_blocks; b += nw) {
+        const float v = src32 ? src32[b * 32 + lane] : __half2float(a[b * 32 + lane]);
+        float amax = fabsf(v);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        const float d  = __half2float(__float2half_rn(__fdiv_rn(amax, 127.0f)));
+        const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
+        const float q = rintf(__fmul_rn(v, id));
+        a[b * 32 + lane] = __float2half_rn(__fmul_rn(q, d));
+    }
+}
+
 // normalize_codebooks (src/audio_tokenizer_decoder.cpp:40-64): row / max(usage, 1e-5), re-rounded to F16
 __global__ void k_normalize_codebook(__half * cb, const float * __restrict__ usage, int rows, int dim) {
     const size_t n = (size_t) rows * dim;
@@ -167,7 +189,8 @@ __global__ void k_rvq_gather(const GatherArgs g, const int * __restrict__ codes,
 }
 
 // RMSNorm over 512 channels * gamma -> F16 (the next mat-mul's operand); one warp per row
-__global__ void k_rmsnorm512(const float * __restrict__ x, const float * __restrict__ gamma, __half * __restrict__ out, int T, float eps) {
+__global__ void k_rmsnorm512(const float * __restrict__ x, const float * __restrict__ gamma, __half * __restrict__ out, int T, float eps,
+                             float * __restrict__ o32 = nullptr) {
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (row >= T) return;
     const float * xr = x + (size_t) row * TH;
@@ -177,7 +200,11 @@ __global__ void k_rmsnorm512(const float * __restrict__ x, const float * __restr
     sq = warp_sum_d(sq);
     const float scale = 1.0f / sqrtf((float) (sq / TH) + eps);
 #pragma unroll
-    for (int i = 0; i < 16; ++i) out[(size_t) row * TH + lane + 32 * i] = __float2half_rn((v[i] * scale) * gamma[lane + 32 * i]);
+    for (int i = 0; i < 16; ++i) {
+        const float y = (v[i] * scale) * gamma[lane + 32 * i];
+        out[(size_t) row * TH + lane + 32 * i] = __float2half_rn(y);
+        if (o32) o32[(size_t) row * TH + lane + 32 * i] = y;
+    }
 }
 
 // NEOX RoPE on q and k (heads of 64, pairs (i, i+32)), in place on the F32 qkv buffer [T][3072]
@@ -198,7 +225,7 @@ __global__ void k_rope_qk(float * __restrict__ qkv, const float * __restrict__ r
 // o-projection).
 constexpr int VA_QW = 4, VA_QB = 4 * VA_QW;          // queries per warp / per block (4 warps)
 __global__ void __launch_bounds__(128)
-k_attention(const float * __restrict__ qkv, __half * __restrict__ out, int T) {
+k_attention(const float * __restrict__ qkv, __half * __restrict__ out, int T, float * __restrict__ o32 = nullptr) {
     // Causal soft-max attention of 16 consecutive queries of one head.  K/V tiles of 32 positions are staged in
     // shared memory once per block (K transposed: lane = key position in the score loop), a warp carries four
     // queries through the tile (running max / sum, F32), lane = output dims (lane, lane + 32) in the P.V loop.
@@ -277,6 +304,7 @@ k_attention(const float * __restrict__ qkv, __half * __restrict__ out, int T) {
             const float inv = 1.0f / l[qi];
             out[(size_t) t * LATENT + h * THD + lane]      = __float2half_rn(o0[qi] * inv);
             out[(size_t) t * LATENT + h * THD + lane + 32] = __float2half_rn(o1[qi] * inv);
+            if (o32) { o32[(size_t) t * LATENT + h * THD + lane] = o0[qi] * inv; o32[(size_t) t * LATENT + h * THD + lane + 32] = o1[qi] * inv; }
         }
     }
 }
@@ -286,7 +314,7 @@ k_attention(const float * __restrict__ qkv, __half * __restrict__ out, int T) {
 // (apply_upsample_block, :509-529).  One block per time step, 256 threads x 4 channels.
 __global__ void __launch_bounds__(256)
 k_dwconv_ln(const float * __restrict__ x /* [L][1024] F32 */, const __half * __restrict__ w /* [1024][7] */, const float * __restrict__ b,
-            const float * __restrict__ ln_w, const float * __restrict__ ln_b, __half * __restrict__ out, int L) {
+            const float * __restrict__ ln_w, const float * __restrict__ ln_b, __half * __restrict__ out, int L, float * __restrict__ o32 = nullptr) {
     const int t = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     __shared__ float red[8];
     float v[4];
@@ -323,7 +351,9 @@ k_dwconv_ln(const float * __restrict__ x /* [L][1024] F32 */, const __half * __r
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int c = tid + 256 * i;
-        out[(size_t) t * LATENT + c] = __float2half_rn((v[i] * scale) * ln_w[c] + ln_b[c]);
+        const float y = (v[i] * scale) * ln_w[c] + ln_b[c];
+        out[(size_t) t * LATENT + c] = __float2half_rn(y);
+        if (o32) o32[(size_t) t * LATENT + c] = y;
     }
 }
 
@@ -452,6 +482,9 @@ int vocoder_finalize(q3t_ctx * ctx) {
     v->pre_conv_b = L.f(P + "pre_conv.bias", LATENT);
     v->in_proj = L.h(P + "pre_tfm.input_proj.weight", (int64_t) TH * LATENT);
     v->in_proj_b = L.f(P + "pre_tfm.input_proj.bias", TH);
+    auto was_q8 = [&](const std::string & name) { const q3t_host_tensor * t = vfind(ctx, name); return t && t->src_type == Q3T_TYPE_Q8_0; };
+    v->q8_in_proj = was_q8(P + "pre_tfm.input_proj.weight");
+    v->q8_out_proj = was_q8(P + "pre_tfm.output_proj.weight");
     for (int l = 0; l < TL && !L.rc; ++l) {
         const std::string b = P + "pre_tfm.blk." + std::to_string(l) + ".";
         VTfmLayer & y = v->tfm[l];
@@ -470,6 +503,7 @@ int vocoder_finalize(q3t_ctx * ctx) {
         k_copy_rows_h<<<256, 256, 0, st>>>(g, wgu, TFFN, TH, 2, 0, TH, 0);
         k_copy_rows_h<<<256, 256, 0, st>>>(u, wgu, TFFN, TH, 2, 1, TH, 0);
         y.wqkv = wqkv; y.wgu = wgu;
+        v->q8_tfm[l] = was_q8(b + "attn_q.weight");
     }
     v->tfm_norm = L.f(P + "pre_tfm.norm.weight", TH);
     v->out_proj = L.h(P + "pre_tfm.output_proj.weight", (int64_t) LATENT * TH);
@@ -489,6 +523,7 @@ int vocoder_finalize(q3t_ctx * ctx) {
         u.pw1 = L.h(b + "pwconv1.weight", (int64_t) 4 * LATENT * LATENT); u.pw1_b = L.f(b + "pwconv1.bias", 4 * LATENT);
         u.pw2 = L.h(b + "pwconv2.weight", (int64_t) 4 * LATENT * LATENT); u.pw2_b = L.f(b + "pwconv2.bias", LATENT);
         u.gamma = L.f(b + "gamma", LATENT);
+        v->q8_pw[i] = was_q8(b + "pwconv1.weight");
     }
     v->dec0 = L.conv(P + "dec.0.conv.weight", DEC_DIM, LATENT, 7);
     v->dec0_b = L.f(P + "dec.0.conv.bias", DEC_DIM);
@@ -567,6 +602,7 @@ static size_t arena_need(int T) {
     b += t * (4096 * 2 + 512 * 2 + 1024 * 2 + 512 * 4 + 512 * 2 + 3072 * 4 + 1024 * 2 + 1024 * 2 + 1024 * 2);
     b += 4 * t * (1024 * 4 + 1024 * 2 + 4096 * 2 + 1024 * 2) * 2;
     b += 4 * t * 1536 * 2;
+    b += 4 * t * 1024 * 4;                                     // f32s (Q8_0 files)
     size_t L = 4 * t; int C = 1536; const int rates[4] = {8, 5, 4, 3};
     for (int i = 0; i < 4; ++i) { L = L * rates[i]; C /= 2; b += L * C * (4 + 4 + 2 + 2); }
     return b + (1 << 20);
@@ -613,6 +649,13 @@ int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int T, float ** sa
         if (FILE * f = fopen(path.c_str(), "wb")) { fwrite(h.data(), 1, bytes, f); fclose(f); }
     };
 
+    const bool any_q8 = v->q8_in_proj || v->q8_out_proj || v->q8_pw[0] || v->q8_pw[1] || v->q8_tfm[0];
+    float * f32s = any_q8 ? A.take<float>((size_t) 4 * T * LATENT) : nullptr;      // un-rounded copy of the operand being quantised
+    auto fq = [&](bool on, __half * a, const float * src32, size_t n_elem) {       // Q8_0 files: the reference's activation quantisation
+        if (!on) return;
+        const long nb = (long) (n_elem / 32);
+        k_fake_quant_q8<<<(unsigned) std::min<long>((nb + 7) / 8, 148 * 8), 256, 0, st>>>(a, src32, nb); ++nl;
+    };
     // ---- RVQ lookup + projections as one K = 16*256 GEMM -> F16 latent [T][512]
     __half * a_rvq = A.take<__half>((size_t) T * 16 * VQ_DIM);
     __half * lat16 = A.take<__half>((size_t) T * VQ_OUT);
@@ -630,11 +673,13 @@ int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int T, float ** sa
         VGemm p{}; p.A = lat16; p.lda = VQ_OUT; p.a_rows = T; p.M = T; p.ntaps = 3; p.Kc = VQ_OUT;
         p.tap_off[0] = -2; p.tap_off[1] = -1; p.tap_off[2] = 0;
         p.W = v->pre_conv; p.N = LATENT; p.bias = v->pre_conv_b; p.pmod = LATENT; p.out16 = pc16; p.ld16 = LATENT;
+        if (v->q8_in_proj) { p.out32 = f32s; p.ld32 = LATENT; }
         voc_gemm(ctx, p); ++nl;
         dump("pc16", pc16, (size_t) T * LATENT * 2);
     }
     // ---- transformer input projection -> F32 residual stream [T][512]
     float * x32 = A.take<float>((size_t) T * TH);
+    fq(v->q8_in_proj, pc16, f32s, (size_t) T * LATENT);
     {
         VGemm p{}; p.A = pc16; p.lda = LATENT; p.a_rows = T; p.M = T; p.ntaps = 1; p.Kc = LATENT;
         p.W = v->in_proj; p.N = TH; p.bias = v->in_proj_b; p.pmod = TH; p.out32 = x32; p.ld32 = TH;
@@ -647,21 +692,26 @@ int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int T, float ** sa
     __half * h16 = A.take<__half>((size_t) T * TFFN);
     for (int l = 0; l < TL; ++l) {
         const VTfmLayer & y = v->tfm[l];
-        k_rmsnorm512<<<(T + 7) / 8, 256, 0, st>>>(x32, y.attn_norm, n16, T, T_EPS); ++nl;
+        k_rmsnorm512<<<(T + 7) / 8, 256, 0, st>>>(x32, y.attn_norm, n16, T, T_EPS, v->q8_tfm[l] ? f32s : nullptr); ++nl;
+        fq(v->q8_tfm[l], n16, f32s, (size_t) T * TH);
         { VGemm p{}; p.A = n16; p.lda = TH; p.a_rows = T; p.M = T; p.ntaps = 1; p.Kc = TH; p.W = y.wqkv; p.N = 3 * LATENT; p.pmod = 3 * LATENT;
           p.out32 = qkv; p.ld32 = 3 * LATENT; voc_gemm(ctx, p); ++nl; }
         k_rope_qk<<<T, 256, 0, st>>>(qkv, v->rope, T); ++nl;
-        k_attention<<<dim3((T + VA_QB - 1) / VA_QB, TNH), 128, 0, st>>>(qkv, att16, T); ++nl;
+        k_attention<<<dim3((T + VA_QB - 1) / VA_QB, TNH), 128, 0, st>>>(qkv, att16, T, v->q8_tfm[l] ? f32s : nullptr); ++nl;
+        fq(v->q8_tfm[l], att16, f32s, (size_t) T * LATENT);
         { VGemm p{}; p.A = att16; p.lda = LATENT; p.a_rows = T; p.M = T; p.ntaps = 1; p.Kc = LATENT; p.W = y.wo; p.N = TH; p.pmod = TH;
           p.gamma = y.attn_scale; p.res = x32; p.ldres = TH; p.out32 = x32; p.ld32 = TH; voc_gemm(ctx, p); ++nl; }
-        k_rmsnorm512<<<(T + 7) / 8, 256, 0, st>>>(x32, y.ffn_norm, n16, T, T_EPS); ++nl;
+        k_rmsnorm512<<<(T + 7) / 8, 256, 0, st>>>(x32, y.ffn_norm, n16, T, T_EPS, v->q8_tfm[l] ? f32s : nullptr); ++nl;
+        fq(v->q8_tfm[l], n16, f32s, (size_t) T * TH);
         { VGemm p{}; p.A = n16; p.lda = TH; p.a_rows = T; p.M = T; p.ntaps = 1; p.Kc = TH; p.W = y.wgu; p.N = 2 * TFFN; p.pmod = 2 * TFFN;
-          p.swiglu = 1; p.out16 = h16; p.ld16 = TFFN; voc_gemm(ctx, p); ++nl; }
+          p.swiglu = 1; p.out16 = h16; p.ld16 = TFFN; if (v->q8_tfm[l]) { p.out32 = f32s; p.ld32 = TFFN; } voc_gemm(ctx, p); ++nl; }
+        fq(v->q8_tfm[l], h16, f32s, (size_t) T * TFFN);
         { VGemm p{}; p.A = h16; p.lda = TFFN; p.a_rows = T; p.M = T; p.ntaps = 1; p.Kc = TFFN; p.W = y.wdown; p.N = TH; p.pmod = TH;
           p.gamma = y.ffn_scale; p.res = x32; p.ldres = TH; p.out32 = x32; p.ld32 = TH; voc_gemm(ctx, p); ++nl; }
     }
     dump("tfm_x", x32, (size_t) T * TH * 4);
-    k_rmsnorm512<<<(T + 7) / 8, 256, 0, st>>>(x32, v->tfm_norm, n16, T, T_EPS); ++nl;
+    k_rmsnorm512<<<(T + 7) / 8, 256, 0, st>>>(x32, v->tfm_norm, n16, T, T_EPS, v->q8_out_proj ? f32s : nullptr); ++nl;
+    fq(v->q8_out_proj, n16, f32s, (size_t) T * TH);
     __half * cur16 = A.take<__half>((size_t) T * LATENT);
     { VGemm p{}; p.A = n16; p.lda = TH; p.a_rows = T; p.M = T; p.ntaps = 1; p.Kc = TH; p.W = v->out_proj; p.N = LATENT; p.pmod = LATENT;
       p.bias = v->out_proj_b; p.out16 = cur16; p.ld16 = LATENT; voc_gemm(ctx, p); ++nl; }
@@ -679,9 +729,11 @@ int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int T, float ** sa
         __half * y16 = A.take<__half>((size_t) L2 * LATENT);
         { VGemm p{}; p.A = cur16; p.lda = LATENT; p.a_rows = L; p.M = L; p.ntaps = 1; p.Kc = LATENT; p.W = u.convt; p.N = 2 * LATENT; p.pmod = LATENT;
           p.bias = u.convt_b; p.out32 = res32; p.ld32 = 2 * LATENT; voc_gemm(ctx, p); ++nl; }
-        k_dwconv_ln<<<L2, 256, 0, st>>>(res32, u.dw, u.dw_b, u.ln_w, u.ln_b, d16, L2); ++nl;
+        k_dwconv_ln<<<L2, 256, 0, st>>>(res32, u.dw, u.dw_b, u.ln_w, u.ln_b, d16, L2, v->q8_pw[i] ? f32s : nullptr); ++nl;
+        fq(v->q8_pw[i], d16, f32s, (size_t) L2 * LATENT);
         { VGemm p{}; p.A = d16; p.lda = LATENT; p.a_rows = L2; p.M = L2; p.ntaps = 1; p.Kc = LATENT; p.W = u.pw1; p.N = 4 * LATENT; p.pmod = 4 * LATENT;
           p.bias = u.pw1_b; p.act = VACT_GELU; p.out16 = g16; p.ld16 = 4 * LATENT; voc_gemm(ctx, p); ++nl; }
+        fq(v->q8_pw[i], g16, nullptr, (size_t) L2 * 4 * LATENT);      // GELU goes through the F16 table in the reference: g16 IS its operand
         { VGemm p{}; p.A = g16; p.lda = 4 * LATENT; p.a_rows = L2; p.M = L2; p.ntaps = 1; p.Kc = 4 * LATENT; p.W = u.pw2; p.N = LATENT; p.pmod = LATENT;
           p.bias = u.pw2_b; p.gamma = u.gamma; p.res = res32; p.ldres = LATENT; p.out16 = y16; p.ld16 = LATENT; voc_gemm(ctx, p); ++nl; }
         cur16 = y16; L = L2;

@@ -45,13 +45,34 @@ class _Rng:
         return a
 
 
+def _q4_k(data: np.ndarray) -> np.ndarray:
+    """Q4_K blocks from ggml's own quantiser (gguf-py has none: the reference's converter falls back to F16 with this
+    gguf version).  Uses ggml_quantize_chunk of the reference build under oracle/_ref -- test infrastructure only."""
+    import ctypes as C
+    so = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libq3t_ref.so")
+    L = C.CDLL(so)
+    L.ggml_quantize_chunk.restype = C.c_size_t
+    L.ggml_quantize_chunk.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]
+    rows, k = data.shape
+    assert k % 256 == 0
+    src = np.ascontiguousarray(data, np.float32)
+    dst = np.zeros((rows, k // 256 * 144), np.uint8)
+    n = L.ggml_quantize_chunk(12, src.ctypes.data, dst.ctypes.data, 0, rows, k, None)
+    assert n == dst.nbytes, (n, dst.nbytes)
+    return dst
+
+
 def _add(writer, name, data, qtype):
-    """1-D -> F32; >=2-D -> F16 or Q8_0 (quantised along the last numpy axis = ggml ne[0])."""
+    """1-D -> F32; >=2-D -> F16, F32, Q8_0 or Q4_K (quantised along the last numpy axis = ggml ne[0])."""
     if data.ndim <= 1:
         writer.add_tensor(name, data.astype(np.float32), raw_dtype=gguf.GGMLQuantizationType.F32)
     elif qtype == "q8_0":
         q = gguf.quants.quantize(data.astype(np.float32), gguf.GGMLQuantizationType.Q8_0)
         writer.add_tensor(name, q, raw_dtype=gguf.GGMLQuantizationType.Q8_0)
+    elif qtype == "q4_k":
+        writer.add_tensor(name, _q4_k(data.astype(np.float32)), raw_dtype=gguf.GGMLQuantizationType.Q4_K)
+    elif qtype == "f32":
+        writer.add_tensor(name, data.astype(np.float32), raw_dtype=gguf.GGMLQuantizationType.F32)
     else:
         writer.add_tensor(name, data.astype(np.float16), raw_dtype=gguf.GGMLQuantizationType.F16)
 
@@ -127,8 +148,8 @@ def write_tts_gguf(path: str, preset: str = "full", seed: int = 1234, wtype: str
         w.add_uint32("tokenizer.ggml.eos_token_id", 151645)
         w.add_uint32("tokenizer.ggml.padding_token_id", 151643)
 
-    q = wtype  # quantisable class
-    f = "f16"  # always-F16 class
+    q = wtype                                   # quantisable class (attn q/k/v/o, ffn gate/up/down, text_proj fc1/fc2)
+    f = "f32" if wtype == "f32" else "f16"      # the rest: F16, or F32 in `--type f32` files (scripts/convert_tts_to_gguf.py:289-291)
 
     _add(w, "talker.text_embd.weight", rng.normal((p["text_vocab"], TEXT_DIM), w_std), f)
     _add(w, "talker.text_proj.fc1.weight", rng.normal((TEXT_DIM, TEXT_DIM), w_std), q)
@@ -172,7 +193,8 @@ def write_tts_gguf(path: str, preset: str = "full", seed: int = 1234, wtype: str
     return dict(preset=preset, seed=seed, wtype=wtype, **p)
 
 
-def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain: float = 0.06, usage: bool = False) -> dict:
+def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain: float = 0.06, usage: bool = False,
+                       wtype: str = "f16") -> dict:
     """Vocoder file (reference name: qwen3-tts-tokenizer-f16.gguf), `tok_dec.*` tensors only.
 
     Conv / linear weights ~ N(0, gain^2 / fan_in); snake alpha/beta ~ N(0, 0.1^2) (log-scale
@@ -190,88 +212,107 @@ def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain:
     w.add_uint32(f"{arch}.num_codebooks", 16)
     w.add_uint32(f"{arch}.codebook_size", 2048)
     w.add_uint32(f"{arch}.sample_rate", 24000)
+
     f = "f16"
+    if wtype != "f16":
+        # what the reference's converter does for --type q8_0 / f32 (scripts/convert_tokenizer_to_gguf.py:277-297): 1-D stay F32;
+        # q8_0: codebook / norm / scale / alpha / beta names stay F16, everything else is handed to the Q8_0 quantiser, which
+        # only succeeds when the last axis is a multiple of 32 (the conv kernels' K = 1..16 fall back to F16)
+        real_add = _add
+
+        def _add_v(writer, name, data, _q):
+            if data.ndim <= 1:
+                return real_add(writer, name, data, "f16")
+            if wtype == "f32":
+                return real_add(writer, name, data, "f32")
+            keep = any(x in name for x in ["codebook", "_norm", "norm.", "scale", "alpha", "beta"])
+            if keep or data.shape[-1] % 32 != 0:
+                return real_add(writer, name, data, "f16")
+            return real_add(writer, name, data, "q8_0")
+        globals()["_add_voc"] = _add_v
+    else:
+        globals()["_add_voc"] = _add
 
     def fan(shape, fan_in, g=gain):
         return rng.normal(shape, g / np.sqrt(fan_in))
 
-    _add(w, "tok_dec.vq_first.input_proj.weight", fan((256, 512, 1), 512), f)
-    _add(w, "tok_dec.vq_first.output_proj.weight", fan((512, 256, 1), 256 * 16), f)
+    _add_voc(w, "tok_dec.vq_first.input_proj.weight", fan((256, 512, 1), 512), f)
+    _add_voc(w, "tok_dec.vq_first.output_proj.weight", fan((512, 256, 1), 256 * 16), f)
     def codebook():
         cb = rng.normal((2048, 256), 1.0)
         if usage:
             cb[::97] *= np.float32(1e-3)          # rows whose usage is below the loader's epsilon: x 1e5 must stay finite in F16
         return cb
 
-    _add(w, "tok_dec.vq_first.0.codebook", codebook(), f)
-    _add(w, "tok_dec.vq_rest.input_proj.weight", fan((256, 512, 1), 512), f)
-    _add(w, "tok_dec.vq_rest.output_proj.weight", fan((512, 256, 1), 256 * 16), f)
+    _add_voc(w, "tok_dec.vq_first.0.codebook", codebook(), f)
+    _add_voc(w, "tok_dec.vq_rest.input_proj.weight", fan((256, 512, 1), 512), f)
+    _add_voc(w, "tok_dec.vq_rest.output_proj.weight", fan((512, 256, 1), 256 * 16), f)
     for i in range(15):
-        _add(w, f"tok_dec.vq_rest.{i}.codebook", codebook(), f)
-    _add(w, "tok_dec.pre_conv.weight", fan((1024, 512, 3), 512 * 3), f)
-    _add(w, "tok_dec.pre_conv.bias", rng.normal((1024,), 0.01), f)
-    _add(w, "tok_dec.pre_tfm.input_proj.weight", fan((512, 1024), 1024), f)
-    _add(w, "tok_dec.pre_tfm.input_proj.bias", rng.normal((512,), 0.01), f)
+        _add_voc(w, f"tok_dec.vq_rest.{i}.codebook", codebook(), f)
+    _add_voc(w, "tok_dec.pre_conv.weight", fan((1024, 512, 3), 512 * 3), f)
+    _add_voc(w, "tok_dec.pre_conv.bias", rng.normal((1024,), 0.01), f)
+    _add_voc(w, "tok_dec.pre_tfm.input_proj.weight", fan((512, 1024), 1024), f)
+    _add_voc(w, "tok_dec.pre_tfm.input_proj.bias", rng.normal((512,), 0.01), f)
     for i in range(8):
         b = f"tok_dec.pre_tfm.blk.{i}"
-        _add(w, f"{b}.attn_norm.weight", 1.0 + rng.normal((512,), 0.02), f)
-        _add(w, f"{b}.attn_q.weight", fan((1024, 512), 512), f)
-        _add(w, f"{b}.attn_k.weight", fan((1024, 512), 512), f)
-        _add(w, f"{b}.attn_v.weight", fan((1024, 512), 512), f)
-        _add(w, f"{b}.attn_output.weight", fan((512, 1024), 1024), f)
-        _add(w, f"{b}.attn_scale", 0.01 + rng.normal((512,), 0.002), f)
-        _add(w, f"{b}.ffn_norm.weight", 1.0 + rng.normal((512,), 0.02), f)
-        _add(w, f"{b}.ffn_gate.weight", fan((1024, 512), 512), f)
-        _add(w, f"{b}.ffn_up.weight", fan((1024, 512), 512), f)
-        _add(w, f"{b}.ffn_down.weight", fan((512, 1024), 1024), f)
-        _add(w, f"{b}.ffn_scale", 0.01 + rng.normal((512,), 0.002), f)
-    _add(w, "tok_dec.pre_tfm.norm.weight", 1.0 + rng.normal((512,), 0.02), f)
-    _add(w, "tok_dec.pre_tfm.output_proj.weight", fan((1024, 512), 512), f)
-    _add(w, "tok_dec.pre_tfm.output_proj.bias", rng.normal((1024,), 0.01), f)
+        _add_voc(w, f"{b}.attn_norm.weight", 1.0 + rng.normal((512,), 0.02), f)
+        _add_voc(w, f"{b}.attn_q.weight", fan((1024, 512), 512), f)
+        _add_voc(w, f"{b}.attn_k.weight", fan((1024, 512), 512), f)
+        _add_voc(w, f"{b}.attn_v.weight", fan((1024, 512), 512), f)
+        _add_voc(w, f"{b}.attn_output.weight", fan((512, 1024), 1024), f)
+        _add_voc(w, f"{b}.attn_scale", 0.01 + rng.normal((512,), 0.002), f)
+        _add_voc(w, f"{b}.ffn_norm.weight", 1.0 + rng.normal((512,), 0.02), f)
+        _add_voc(w, f"{b}.ffn_gate.weight", fan((1024, 512), 512), f)
+        _add_voc(w, f"{b}.ffn_up.weight", fan((1024, 512), 512), f)
+        _add_voc(w, f"{b}.ffn_down.weight", fan((512, 1024), 1024), f)
+        _add_voc(w, f"{b}.ffn_scale", 0.01 + rng.normal((512,), 0.002), f)
+    _add_voc(w, "tok_dec.pre_tfm.norm.weight", 1.0 + rng.normal((512,), 0.02), f)
+    _add_voc(w, "tok_dec.pre_tfm.output_proj.weight", fan((1024, 512), 512), f)
+    _add_voc(w, "tok_dec.pre_tfm.output_proj.bias", rng.normal((1024,), 0.01), f)
     for i in range(2):
         b = f"tok_dec.upsample.{i}"
-        _add(w, f"{b}.conv.weight", fan((1024, 1024, 2), 1024), f)      # ConvT [Cin,Cout,K]
-        _add(w, f"{b}.conv.bias", rng.normal((1024,), 0.01), f)
-        _add(w, f"{b}.dwconv.weight", fan((1024, 1, 7), 7), f)
-        _add(w, f"{b}.dwconv.bias", rng.normal((1024,), 0.01), f)
-        _add(w, f"{b}.norm.weight", 1.0 + rng.normal((1024,), 0.02), f)
-        _add(w, f"{b}.norm.bias", rng.normal((1024,), 0.01), f)
-        _add(w, f"{b}.pwconv1.weight", fan((4096, 1024), 1024), f)
-        _add(w, f"{b}.pwconv1.bias", rng.normal((4096,), 0.01), f)
-        _add(w, f"{b}.pwconv2.weight", fan((1024, 4096), 4096), f)
-        _add(w, f"{b}.pwconv2.bias", rng.normal((1024,), 0.01), f)
-        _add(w, f"{b}.gamma", 0.1 + rng.normal((1024,), 0.01), f)
-    _add(w, "tok_dec.dec.0.conv.weight", fan((1536, 1024, 7), 1024 * 7), f)
-    _add(w, "tok_dec.dec.0.conv.bias", rng.normal((1536,), 0.01), f)
+        _add_voc(w, f"{b}.conv.weight", fan((1024, 1024, 2), 1024), f)      # ConvT [Cin,Cout,K]
+        _add_voc(w, f"{b}.conv.bias", rng.normal((1024,), 0.01), f)
+        _add_voc(w, f"{b}.dwconv.weight", fan((1024, 1, 7), 7), f)
+        _add_voc(w, f"{b}.dwconv.bias", rng.normal((1024,), 0.01), f)
+        _add_voc(w, f"{b}.norm.weight", 1.0 + rng.normal((1024,), 0.02), f)
+        _add_voc(w, f"{b}.norm.bias", rng.normal((1024,), 0.01), f)
+        _add_voc(w, f"{b}.pwconv1.weight", fan((4096, 1024), 1024), f)
+        _add_voc(w, f"{b}.pwconv1.bias", rng.normal((4096,), 0.01), f)
+        _add_voc(w, f"{b}.pwconv2.weight", fan((1024, 4096), 4096), f)
+        _add_voc(w, f"{b}.pwconv2.bias", rng.normal((1024,), 0.01), f)
+        _add_voc(w, f"{b}.gamma", 0.1 + rng.normal((1024,), 0.01), f)
+    _add_voc(w, "tok_dec.dec.0.conv.weight", fan((1536, 1024, 7), 1024 * 7), f)
+    _add_voc(w, "tok_dec.dec.0.conv.bias", rng.normal((1536,), 0.01), f)
     cin = 1536
     for bi, s in enumerate((8, 5, 4, 3), start=1):
         cout = cin // 2
         b = f"tok_dec.dec.{bi}"
-        _add(w, f"{b}.snake.alpha", rng.normal((cin,), 0.1), f)
-        _add(w, f"{b}.snake.beta", rng.normal((cin,), 0.1), f)
+        _add_voc(w, f"{b}.snake.alpha", rng.normal((cin,), 0.1), f)
+        _add_voc(w, f"{b}.snake.beta", rng.normal((cin,), 0.1), f)
         # each output sample sees K/s = 2 taps x Cin inputs
-        _add(w, f"{b}.conv_t.weight", fan((cin, cout, 2 * s), cin * 2), f)
-        _add(w, f"{b}.conv_t.bias", rng.normal((cout,), 0.01), f)
+        _add_voc(w, f"{b}.conv_t.weight", fan((cin, cout, 2 * s), cin * 2), f)
+        _add_voc(w, f"{b}.conv_t.bias", rng.normal((cout,), 0.01), f)
         for r in (2, 3, 4):
             rb = f"{b}.res.{r}"
-            _add(w, f"{rb}.act1.alpha", rng.normal((cout,), 0.1), f)
-            _add(w, f"{rb}.act1.beta", rng.normal((cout,), 0.1), f)
-            _add(w, f"{rb}.conv1.weight", fan((cout, cout, 7), cout * 7), f)
-            _add(w, f"{rb}.conv1.bias", rng.normal((cout,), 0.01), f)
-            _add(w, f"{rb}.act2.alpha", rng.normal((cout,), 0.1), f)
-            _add(w, f"{rb}.act2.beta", rng.normal((cout,), 0.1), f)
-            _add(w, f"{rb}.conv2.weight", fan((cout, cout, 1), cout, g=0.5 * gain), f)
-            _add(w, f"{rb}.conv2.bias", rng.normal((cout,), 0.01), f)
+            _add_voc(w, f"{rb}.act1.alpha", rng.normal((cout,), 0.1), f)
+            _add_voc(w, f"{rb}.act1.beta", rng.normal((cout,), 0.1), f)
+            _add_voc(w, f"{rb}.conv1.weight", fan((cout, cout, 7), cout * 7), f)
+            _add_voc(w, f"{rb}.conv1.bias", rng.normal((cout,), 0.01), f)
+            _add_voc(w, f"{rb}.act2.alpha", rng.normal((cout,), 0.1), f)
+            _add_voc(w, f"{rb}.act2.beta", rng.normal((cout,), 0.1), f)
+            _add_voc(w, f"{rb}.conv2.weight", fan((cout, cout, 1), cout, g=0.5 * gain), f)
+            _add_voc(w, f"{rb}.conv2.bias", rng.normal((cout,), 0.01), f)
         cin = cout
-    _add(w, "tok_dec.dec.5.snake.alpha", rng.normal((96,), 0.1), f)
-    _add(w, "tok_dec.dec.5.snake.beta", rng.normal((96,), 0.1), f)
-    _add(w, "tok_dec.dec.6.conv.weight", fan((1, 96, 7), 96 * 7, g=out_gain), f)
-    _add(w, "tok_dec.dec.6.conv.bias", rng.normal((1,), 0.01), f)
+    _add_voc(w, "tok_dec.dec.5.snake.alpha", rng.normal((96,), 0.1), f)
+    _add_voc(w, "tok_dec.dec.5.snake.beta", rng.normal((96,), 0.1), f)
+    _add_voc(w, "tok_dec.dec.6.conv.weight", fan((1, 96, 7), 96 * 7, g=out_gain), f)
+    _add_voc(w, "tok_dec.dec.6.conv.bias", rng.normal((1,), 0.01), f)
     if usage:
         for name in ["tok_dec.vq_first.0.usage"] + [f"tok_dec.vq_rest.{i}.usage" for i in range(15)]:
             u = np.abs(rng.normal((2048,), 0.5)) + np.float32(0.5)
             u[::97] = np.float32(1e-7)                      # below the epsilon: clamped to 1e-5 by the loader
-            _add(w, name, u, f)
+            _add_voc(w, name, u, f)
 
     w.write_header_to_file(path=path)
     w.write_kv_data_to_file()
@@ -282,7 +323,7 @@ def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain:
 
 def ensure_models(model_dir: str, preset: str = "tiny", wtype: str = "f16", seed: int = 1234,
                   voc_seed: int = 4321, verbose: bool = False, eos_like: int = -1,
-                  usage: bool = False) -> tuple[str, str]:
+                  usage: bool = False, voc_wtype: str = "f16") -> tuple[str, str]:
     """Create (if missing) the two GGUFs under model_dir; returns (tts_path, vocoder_path).
 
     File names follow the reference pipeline (src/qwen3_tts.cpp:118-119) with a preset /
@@ -291,7 +332,7 @@ def ensure_models(model_dir: str, preset: str = "tiny", wtype: str = "f16", seed
     os.makedirs(model_dir, exist_ok=True)
     eos = "" if eos_like < 0 else f"-eoslike{eos_like}"
     tts = os.path.join(model_dir, f"qwen3-tts-0.6b-{preset}-{wtype}-s{seed}{eos}.gguf")
-    voc = os.path.join(model_dir, f"qwen3-tts-tokenizer-f16-s{voc_seed}{'-usage' if usage else ''}.gguf")
+    voc = os.path.join(model_dir, f"qwen3-tts-tokenizer-{voc_wtype}-s{voc_seed}{'-usage' if usage else ''}.gguf")
     if not os.path.exists(tts):
         if verbose:
             print(f"[make_random_gguf] writing {tts}", file=sys.stderr)
@@ -300,7 +341,7 @@ def ensure_models(model_dir: str, preset: str = "tiny", wtype: str = "f16", seed
     if not os.path.exists(voc):
         if verbose:
             print(f"[make_random_gguf] writing {voc}", file=sys.stderr)
-        write_vocoder_gguf(voc + ".tmp", seed=voc_seed, usage=usage)
+        write_vocoder_gguf(voc + ".tmp", seed=voc_seed, usage=usage, wtype=voc_wtype)
         os.replace(voc + ".tmp", voc)
     return tts, voc
 
@@ -309,7 +350,7 @@ def main():
     ap = argparse.ArgumentParser(description=__doc__)
     ap.add_argument("--dir", required=True)
     ap.add_argument("--preset", default="tiny", choices=list(PRESETS))
-    ap.add_argument("--wtype", default="f16", choices=["f16", "q8_0"])
+    ap.add_argument("--wtype", default="f16", choices=["f16", "q8_0", "q4_k", "f32"])
     ap.add_argument("--seed", type=int, default=1234)
     a = ap.parse_args()
     print(*ensure_models(a.dir, a.preset, a.wtype, a.seed, verbose=True))
