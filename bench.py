@@ -302,6 +302,24 @@ def run_ours(args, rank, world, local_rank):
         except Exception as e:                                   # never takes the bench down
             first_audio = {"error": str(e)}
 
+    # ---- speaker encoder (config 2's x-vector; the reference needs ~27 s of CPU for a 30 s clip, OPTIMIZATION.md:30)
+    spk_enc = None
+    if rank == 0:
+        try:
+            enc = m.AudioTokenizerEncoder()
+            if enc.load_model(tts_path):
+                rng = np.random.default_rng(7)
+                clip = (0.1 * rng.standard_normal(24000 * 30)).astype(np.float32)
+                enc.encode(clip)
+                torch.cuda.synchronize(); s0 = time.perf_counter()
+                enc.encode(clip)
+                torch.cuda.synchronize()
+                spk_enc = {"clip_seconds": 30, "ms": (time.perf_counter() - s0) * 1e3, "what": "host samples in, 1024-d x-vector out: log-mel "
+                           "(DFT as an F32 GEMM with the reference's twiddles) + ECAPA-TDNN on the tap GEMM"}
+            enc.close()
+        except Exception as e:
+            spk_enc = {"error": str(e)}
+
     # ---- talker decode step alone (north-star: HBM GB/s of the batch-1 talker step)
     n_mid = t.cfg_prefill_len if hasattr(t, "cfg_prefill_len") else 10
     us_step = t.bench_talker_step(n_mid + frames // 2, 64)
@@ -343,6 +361,7 @@ def run_ours(args, rank, world, local_rank):
                             "frac": talker_bytes / (us_step * 1e-6) / 1e9 / peak, "n_kv": n_mid + frames // 2 + 1},
             "realtime_factor_per_gpu": audio_s / step_s,
             "first_audio": first_audio,
+            "speaker_encoder": spk_enc,
             "clocks": clocks,
         }
         if c4 is not None:

@@ -99,7 +99,8 @@ Q3T_API int  q3t_set_tts_config(q3t_ctx * ctx, const q3t_tts_config * cfg);
 Q3T_API int  q3t_upload_tensor(q3t_ctx * ctx, const char * name, int32_t type,
                                const int64_t ne[4], const void * data, size_t nbytes);
 /* private device repack after the last upload (fused QKV / gate-up planes, Q8_0 split into
- * quant + scale planes, RoPE tables).  `which`: 1 = talker+code predictor, 2 = vocoder. */
+ * quant + scale planes, RoPE tables).  `which`: 1 = talker+code predictor, 2 = vocoder, 3 = speaker encoder
+ * (q3t_unload takes the bit mask 1 | 2 | 4). */
 Q3T_API int  q3t_finalize_weights(q3t_ctx * ctx, int32_t which);
 Q3T_API int  q3t_unload(q3t_ctx * ctx, int32_t which);
 
@@ -197,6 +198,11 @@ Q3T_API int64_t q3t_vocoder_n_samples(int32_t n_frames);
 Q3T_API int64_t q3t_vocoder_decode_from(q3t_ctx * ctx, const int32_t * codes, int32_t n_frames, int32_t n_done,
                                         float * samples_out, int64_t cap);
 
+/* AudioTokenizerEncoder::encode (src/audio_tokenizer_encoder.cpp:703-760, mel front end :288-373, ECAPA-TDNN graph :445-701):
+ * samples f32[n_samples] at 24 kHz in [-1, 1] -> embedding_out f32[1024] (the x-vector of prefill row 7).  Needs the
+ * spk_enc.* tensors uploaded and q3t_finalize_weights(ctx, 3).  *n_frames_out (optional) = mel frames. */
+Q3T_API int  q3t_speaker_encode(q3t_ctx * ctx, const float * samples, int32_t n_samples, float * embedding_out, int32_t * n_frames_out);
+
 /* Device-resident variants used by bench.py `value` (inputs already in HBM):
  * run generate+decode for a prompt that was staged with q3t_stage_prompt, leave the
  * result on the device, report frames and samples. */
@@ -267,6 +273,13 @@ Q3T_API void q3t_tts_set_seed(q3t_tts * t, uint64_t seed);   /* extension: the r
 Q3T_API int  q3t_tts_get_config(q3t_tts * t, q3t_tts_config * out);
 Q3T_API const char * q3t_tts_get_error(q3t_tts * t);
 Q3T_API q3t_ctx * q3t_tts_engine(q3t_tts * t);                /* the engine context behind the object */
+
+typedef struct q3t_enc q3t_enc;                /* qwen3_tts::AudioTokenizerEncoder (src/audio_tokenizer_encoder.h:104-150) */
+Q3T_API q3t_enc * q3t_enc_new(void);
+Q3T_API void      q3t_enc_delete(q3t_enc * e);
+Q3T_API int  q3t_enc_load_model(q3t_enc * e, const char * model_path);                 /* the TTS GGUF (spk_enc.* tensors) */
+Q3T_API int  q3t_enc_encode(q3t_enc * e, const float * samples, int32_t n_samples, float * embedding_out /* f32[1024] */);
+Q3T_API const char * q3t_enc_get_error(q3t_enc * e);
 
 typedef struct q3t_dec q3t_dec;                /* qwen3_tts::AudioTokenizerDecoder */
 Q3T_API q3t_dec * q3t_dec_new(void);

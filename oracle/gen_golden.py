@@ -112,18 +112,52 @@ def gen_vocoder_long(out, T=1024, n_win=32, win=2048):
     print("wrote", out, wav.shape, "rms", float(np.sqrt((wav ** 2).mean())))
 
 
+def resample_linear(x, in_rate, out_rate):
+    """src/qwen3_tts.cpp:84-102 restated (double-precision position, float result)."""
+    ratio = float(in_rate) / float(out_rate)
+    n_out = int(float(len(x)) / ratio)
+    src = np.arange(n_out, dtype=np.float64) * ratio
+    i0 = src.astype(np.int64)
+    frac = src - i0
+    i1 = np.minimum(i0 + 1, len(x) - 1)
+    y = ((1.0 - frac) * x[i0].astype(np.float64) + frac * x[i1].astype(np.float64)).astype(np.float32)
+    y[i0 + 1 >= len(x)] = x[-1]
+    return y
+
+
+def gen_speaker(out, wav_path="/root/reference/examples/readme_clone_input.wav"):
+    """Golden G7 (SURVEY.md §8c): the x-vector the reference's own ECAPA encoder (AudioTokenizerEncoder::encode) gives for
+    examples/readme_clone_input.wav (16 kHz mono, 60 s, resampled to 24 kHz as the pipeline does) with the random-init
+    spk_enc.* weights of tools/make_random_gguf.py.  Only the 1024 floats are stored, not the recording."""
+    import wave
+    with wave.open(wav_path, "rb") as w:
+        assert w.getnchannels() == 1 and w.getsampwidth() == 2
+        rate = w.getframerate()
+        pcm = np.frombuffer(w.readframes(w.getnframes()), np.int16).astype(np.float32) / 32768.0
+    x = resample_linear(pcm, rate, 24000)
+    tts, _ = models("tiny", "f16")                       # both presets carry the same spk_enc.* tensors
+    emb = reflib.speaker_embed(tts, x)
+    assert emb.shape == (1024,) and np.isfinite(emb).all()
+    np.savez_compressed(out, embedding=emb.astype(np.float32), n_samples_24k=np.int64(len(x)), source="examples/readme_clone_input.wav")
+    print("wrote", out, "rms", float(np.sqrt((emb ** 2).mean())), "max", float(np.abs(emb).max()))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--full", action="store_true", help="also write the full-size (28-layer) goldens")
     ap.add_argument("--threads", type=int, default=8)
     ap.add_argument("--only-legacy", action="store_true", help="write only legacy_predict_codes.npz")
     ap.add_argument("--long", action="store_true", help="write only long_f16.npz (4096 greedy frames of the full F16 model)")
+    ap.add_argument("--speaker", action="store_true", help="write only speaker_xvector.npz (golden G7)")
     ap.add_argument("--vocoder-long", action="store_true", help="write only vocoder_long_f16.npz (T = 1024 reference windows)")
     a = ap.parse_args()
     if not reflib.available():
         sys.exit("oracle/_ref/libq3t_ref.so missing: make -f oracle/Makefile.ref")
     reflib.RefLib.get().set_threads(a.threads)
     os.makedirs(GOLDEN, exist_ok=True)
+    if a.speaker:
+        gen_speaker(os.path.join(GOLDEN, "speaker_xvector.npz"))
+        return
     if a.vocoder_long:
         gen_vocoder_long(os.path.join(GOLDEN, "vocoder_long_f16.npz"))
         return

@@ -103,6 +103,9 @@ def lib() -> C.CDLL:
         "q3t_dec_stream_reset": (None, [vp]), "q3t_dec_decode_append": (C.c_int64, [vp, _i32p, C.c_int32, _f32p, C.c_int64]),
         "q3t_build_prompt": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32, _f32p, _i32p, _f32p, _i32p, _f32p]),
         "q3t_project_text": (C.c_int, [vp, _i32p, C.c_int32, _f32p]),
+        "q3t_enc_new": (vp, []), "q3t_enc_delete": (None, [vp]), "q3t_enc_load_model": (C.c_int, [vp, cp]),
+        "q3t_enc_encode": (C.c_int, [vp, _f32p, C.c_int32, _f32p]), "q3t_enc_get_error": (cp, [vp]),
+        "q3t_speaker_encode": (C.c_int, [vp, _f32p, C.c_int32, _f32p, _i32p]),
         "q3t_stream_begin": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_int32, C.c_uint64]),
         "q3t_stream_next": (C.c_int, [vp, C.c_int32, _i32p, _i32p, _i32p]),
         "q3t_tts_generate_begin": (C.c_int, [vp, _i32p, C.c_int32, _f32p, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_int32]),
@@ -475,6 +478,38 @@ class AudioTokenizerDecoder:
         if n < 0:
             return None
         return out[:n].copy()
+
+
+class AudioTokenizerEncoder:
+    """qwen3_tts::AudioTokenizerEncoder (speaker x-vector; src/audio_tokenizer_encoder.h:104-150)."""
+
+    def __init__(self):
+        self.L = lib()
+        self.h = self.L.q3t_enc_new()
+
+    def close(self):
+        if self.h:
+            self.L.q3t_enc_delete(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def get_error(self) -> str:
+        return self.L.q3t_enc_get_error(self.h).decode()
+
+    def load_model(self, path: str) -> bool:
+        return bool(self.L.q3t_enc_load_model(self.h, path.encode()))
+
+    def encode(self, samples):
+        samples = np.ascontiguousarray(samples, np.float32)
+        out = np.zeros(1024, np.float32)
+        if not self.L.q3t_enc_encode(self.h, _fp(samples), len(samples), _fp(out)):
+            return None
+        return out
 
 
 def synthesize_stream(tts: TTSTransformer, dec: AudioTokenizerDecoder, tokens, spk, max_len, first_chunk=8, chunk=32,

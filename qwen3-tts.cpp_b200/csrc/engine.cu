@@ -106,12 +106,16 @@ extern "C" int q3t_unload(q3t_ctx * ctx, int32_t which) {
         free_raw(ctx, "tok_dec.");
         ctx->voc_ready = false;
     }
+    if (which & 4) {
+        spk_release(ctx);
+        free_raw(ctx, "spk_enc.");
+    }
     return Q3T_OK;
 }
 
 extern "C" void q3t_ctx_destroy(q3t_ctx * ctx) {
     if (!ctx) return;
-    q3t_unload(ctx, 3);
+    q3t_unload(ctx, 7);
     for (auto & kv : ctx->raw) cudaFree(kv.second.dev);
     ctx->raw.clear();
     for (auto & ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -202,8 +206,9 @@ extern "C" int q3t_upload_tensor(q3t_ctx * ctx, const char * name, int32_t type,
                                  const void * data, size_t nbytes) {
     if (!ctx || !name || !ne || !data) return Q3T_ERR_ARG;
     cudaSetDevice(ctx->device);
-    const bool mine = !strncmp(name, "talker.", 7) || !strncmp(name, "code_pred.", 10) || !strncmp(name, "tok_dec.", 8);
-    if (!mine) return 1;       // spk_enc.*, tok_enc.* ...: not on this path (src/tts_transformer.cpp:375-377)
+    const bool mine = !strncmp(name, "talker.", 7) || !strncmp(name, "code_pred.", 10) || !strncmp(name, "tok_dec.", 8) ||
+                      !strncmp(name, "spk_enc.", 8);
+    if (!mine) return 1;       // tok_enc.* ...: not on this path (src/tts_transformer.cpp:375-377)
     for (int i = 0; i < 4; ++i) if (ne[i] <= 0 || ne[i] > (int64_t) 1 << 40) return set_err(ctx, Q3T_ERR_FORMAT, std::string("bad shape for ") + name);
     const size_t rb = type_row_bytes(type, ne[0]);
     if (rb == 0) return set_err(ctx, Q3T_ERR_FORMAT, std::string("unsupported tensor type for ") + name);
@@ -501,7 +506,8 @@ extern "C" int q3t_finalize_weights(q3t_ctx * ctx, int32_t which) {
     cudaSetDevice(ctx->device);
     if (which == 1) return finalize_tts(ctx);
     if (which == 2) return vocoder_finalize(ctx);
-    return set_err(ctx, Q3T_ERR_ARG, "q3t_finalize_weights: which must be 1 (tts) or 2 (vocoder)");
+    if (which == 3) return spk_finalize(ctx);
+    return set_err(ctx, Q3T_ERR_ARG, "q3t_finalize_weights: which must be 1 (tts), 2 (vocoder) or 3 (speaker encoder)");
 }
 
 extern "C" int64_t q3t_weight_bytes(q3t_ctx * ctx, int32_t which) {
@@ -1038,6 +1044,26 @@ extern "C" int q3t_stream_next(q3t_ctx * ctx, int32_t max_frames, int32_t * code
     *n_new_out = n_new > 0 ? n_new : 0;
     *done_out = ctx->stream_done;
     return Q3T_OK;
+}
+
+// ------------------------------------------------------------------------------ speaker encoder
+extern "C" int q3t_speaker_encode(q3t_ctx * ctx, const float * samples, int32_t n_samples, float * embedding_out, int32_t * n_frames_out) {
+    if (!ctx) return Q3T_ERR_ARG;
+    if (!ctx->spk_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
+    if (!samples || !embedding_out || n_samples <= 0) return set_err(ctx, Q3T_ERR_ARG, "samples is null or n_samples <= 0");
+    cudaSetDevice(ctx->device);
+    float * d_in = nullptr, * d_out = nullptr;
+    int rc = cuda_check(ctx, cudaMalloc(&d_in, (size_t) n_samples * 4), "cudaMalloc");
+    if (!rc) rc = cuda_check(ctx, cudaMalloc(&d_out, 1024 * 4), "cudaMalloc");
+    if (!rc) rc = cuda_check(ctx, cudaMemcpyAsync(d_in, samples, (size_t) n_samples * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D");
+    int nf = 0;
+    if (!rc) rc = spk_run(ctx, d_in, n_samples, d_out, &nf);
+    if (!rc) rc = cuda_check(ctx, cudaMemcpyAsync(embedding_out, d_out, 1024 * 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H");
+    if (!rc) rc = cuda_check(ctx, cudaStreamSynchronize(ctx->stream), "speaker encoder");
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_in); cudaFree(d_out);
+    if (n_frames_out) *n_frames_out = nf;
+    return rc;
 }
 
 // ------------------------------------------------------------------------------ batched generate

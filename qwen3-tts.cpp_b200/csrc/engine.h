@@ -142,6 +142,7 @@ struct q3t_host_tensor {
 };
 
 struct q3t_vocoder;      // defined in vocoder.cu
+struct q3t_spk_encoder;  // defined in spk_encoder.inc (vocoder.cu)
 
 struct q3t_ctx {
     int device = 0;
@@ -180,6 +181,7 @@ struct q3t_ctx {
 
     // vocoder
     q3t_vocoder * voc = nullptr;
+    q3t_spk_encoder * spk = nullptr; bool spk_ready = false;   // speaker encoder (ECAPA x-vector)
     float * d_samples = nullptr; int64_t samples_cap = 0; int64_t last_n_samples = 0;
     int last_n_frames = 0;
     // streaming generate (q3t_stream_begin / q3t_stream_next)
@@ -207,6 +209,9 @@ int  prompt_build(q3t_ctx * ctx, const int32_t * tokens_dev, int n_tokens, const
                   int * trailing_len, float * pad_dev);
 int  prompt_project(q3t_ctx * ctx, const int32_t * tokens_dev, int n_tokens, float * out_dev);
 int  vocoder_finalize(q3t_ctx * ctx);
+int  spk_finalize(q3t_ctx * ctx);
+void spk_release(q3t_ctx * ctx);
+int  spk_run(q3t_ctx * ctx, const float * samples_dev, int n, float * out_dev, int * n_frames_out);
 void vocoder_free(q3t_ctx * ctx);
 int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int n_frames, float ** samples_dev, int t_from);
 }

@@ -9,6 +9,7 @@
 //
 //   v = acc (+ bias[n % pmod]) (* gamma[n % pmod]) (+ res[m][n])     -> out32 (optional)
 //   v = act(v): none | snake(ea, eb)[n % pmod] | gelu-through-F16    -> out16 = F16(v) (optional)
+//   act relu / relu+tanh (speaker encoder) are applied BEFORE out32: there the F32 stream is the activated one
 //   swiglu: columns (2i, 2i+1) = (gate_i, up_i) -> out16[m][i] = F16(silu(gate) * up)
 #pragma once
 
@@ -18,7 +19,7 @@
 
 namespace q3t {
 
-enum { VACT_NONE = 0, VACT_SNAKE = 1, VACT_GELU = 2 };
+enum { VACT_NONE = 0, VACT_SNAKE = 1, VACT_GELU = 2, VACT_RELU = 3, VACT_RELU_TANH = 4 };   // 3, 4: speaker encoder (spk_encoder.inc)
 
 struct VGemm {
     const __half * A; int lda; int a_rows;
@@ -76,6 +77,7 @@ __device__ __forceinline__ void vgemm_epilogue_pair(const VGemm & p, size_t m, i
         if (p.bias)  x += p.bias[pi];
         if (p.gamma) x *= p.gamma[pi];
         if (p.res)   x += p.res[m * p.ldres + nn];
+        if (p.act >= VACT_RELU) { x = fmaxf(x, 0.0f); if (p.act == VACT_RELU_TANH) x = tanhf(x); }
         if (p.out32) p.out32[m * p.ld32 + nn] = x;
         if (p.out16) {
             if (p.act == VACT_SNAKE) x = snake_f(x, p.ea[pi], p.eb[pi]);
@@ -138,6 +140,7 @@ __device__ __forceinline__ void vgemm_epilogue_cols(const VGemm & p, size_t m, i
         if (has_bias)  x[e] += c.bias[e];
         if (has_gamma) x[e] *= c.gamma[e];
         if (has_res)   x[e] += r[e];
+        if (G && act >= VACT_RELU) { x[e] = fmaxf(x[e], 0.0f); if (act == VACT_RELU_TANH) x[e] = tanhf(x[e]); }   // ReLU outputs are the F32 stream too
     }
     if (has_o32) {
         if (!G || (ok1 && ((p.ld32 & 1) == 0))) *reinterpret_cast<float2 *>(p.out32 + m * p.ld32 + n) = make_float2(x[0], x[1]);

@@ -871,3 +871,6 @@ extern "C" int64_t q3t_fetch_samples(q3t_ctx * ctx, float * samples_out, int64_t
     return rc ? rc : n;
 }
 
+#include "spk_encoder.inc"
+
+namespace q3t { void spk_release(q3t_ctx * ctx) { spk_free(ctx); } }

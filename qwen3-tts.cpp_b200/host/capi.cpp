@@ -2,6 +2,7 @@
 // of the reference's TTSTransformer / AudioTokenizerDecoder / GGUFLoader would call.
 #include "../../include/q3t.h"
 #include "audio_tokenizer_decoder.h"
+#include "audio_tokenizer_encoder.h"
 #include "b200_gguf_loader.h"
 #include "b200_pipeline.h"
 #include "tts_transformer.h"
@@ -15,6 +16,7 @@ using qwen3_tts::b200::GGUFLoader;
 struct q3t_gguf { GGUFLoader l; std::string err; };
 struct q3t_tts  { TTSTransformer t; };
 struct q3t_dec  { AudioTokenizerDecoder d; };
+struct q3t_enc  { AudioTokenizerEncoder e; };
 
 extern "C" {
 
@@ -166,6 +168,19 @@ Q3T_API int64_t q3t_dec_decode_append(q3t_dec * d, const int32_t * codes, int32_
     return (int64_t) o.size();
 }
 Q3T_API const char * q3t_dec_get_error(q3t_dec * d) { return d ? d->d.get_error().c_str() : "null object"; }
+
+// ---------------------------------------------------------------- AudioTokenizerEncoder
+Q3T_API q3t_enc * q3t_enc_new(void) { return new q3t_enc(); }
+Q3T_API void q3t_enc_delete(q3t_enc * e) { delete e; }
+Q3T_API int q3t_enc_load_model(q3t_enc * e, const char * model_path) { return e && model_path && e->e.load_model(model_path) ? 1 : 0; }
+Q3T_API int q3t_enc_encode(q3t_enc * e, const float * samples, int32_t n_samples, float * embedding_out) {
+    if (!e || !embedding_out) return 0;
+    std::vector<float> v;
+    if (!e->e.encode(samples, n_samples, v)) return 0;
+    memcpy(embedding_out, v.data(), v.size() * sizeof(float));
+    return 1;
+}
+Q3T_API const char * q3t_enc_get_error(q3t_enc * e) { return e ? e->e.get_error().c_str() : "null object"; }
 
 // ---------------------------------------------------------------- streaming / batched front door (b200_pipeline.h)
 Q3T_API int q3t_tts_generate_begin(q3t_tts * t, const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd, int32_t max_len,

@@ -148,3 +148,31 @@ def test_dropin_cli_equals_reference_cli_hello_world(tmp_path):
     a, b = _read_wav(tmp_path / "b200.wav"), _read_wav(tmp_path / "ref.wav")
     assert len(a) == len(b) == 1920 * 24 - 555
     assert snr_db(b, a) >= 30.0, snr_db(b, a)
+
+
+@gpu
+@need_bins
+def test_dropin_cli_voice_clone_runs_the_gpu_speaker_encoder(tmp_path):
+    """BASELINE.json config 2 through the reference's front door: `-r <wav>` -> load_audio_file / resample (reference
+    host code) -> AudioTokenizerEncoder::encode (the engine's GPU encoder) -> generate -> decode.  The two encoders agree
+    to ~6e-4 relative (tests/test_speaker_encoder_gpu.py); with random weights that can flip a greedy token, so the
+    waveforms are compared for length and reported, not asserted equal."""
+    from test_speaker_encoder_gpu import _clip
+    tts, voc = models("full", "f16")
+    mdir = tmp_path / "models"
+    mdir.mkdir()
+    os.symlink(tts, mdir / "qwen3-tts-0.6b-f16.gguf")
+    os.symlink(voc, mdir / "qwen3-tts-tokenizer-f16.gguf")
+    x = _clip(2.0, 21)
+    with wave.open(str(tmp_path / "voice.wav"), "wb") as w:
+        w.setnchannels(1); w.setsampwidth(2); w.setframerate(24000)
+        w.writeframes((x * 32767.0).astype(np.int16).tobytes())
+    args = ["-m", str(mdir), "-t", "Hello, world!", "-r", str(tmp_path / "voice.wav"), "--temperature", "0", "--max-tokens", "12"]
+    rc, out = _run([os.path.join(BIN, "qwen3-tts-cli")] + args + ["-o", str(tmp_path / "b200.wav")])
+    assert rc == 0, out[-3000:]
+    assert "AudioTokenizerEncoder backend: CUDA sm_100" in out, out[-3000:]
+    rc, out_ref = _run([os.path.join(BIN, "qwen3-tts-cli-ref")] + args + ["-o", str(tmp_path / "ref.wav")])
+    assert rc == 0, out_ref[-3000:]
+    a, b = _read_wav(tmp_path / "b200.wav"), _read_wav(tmp_path / "ref.wav")
+    assert len(a) == len(b) == 1920 * 12 - 555
+    print(f"[voice clone CLI] SNR of the drop-in waveform vs the reference CLI: {snr_db(b, a):.1f} dB")

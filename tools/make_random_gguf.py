@@ -186,11 +186,40 @@ def write_tts_gguf(path: str, preset: str = "full", seed: int = 1234, wtype: str
         _add(w, f"code_pred.lm_head.{cb}.weight", rng.normal((CP_VOCAB, H), w_std), f)
     _add(w, "code_pred.output_norm.weight", 1.0 + rng.normal((H,), 0.02), f)
 
+    add_speaker_encoder(w, seed)
+
     w.write_header_to_file(path=path)
     w.write_kv_data_to_file()
     w.write_tensors_to_file()
     w.close()
     return dict(preset=preset, seed=seed, wtype=wtype, **p)
+
+
+def add_speaker_encoder(w, seed: int) -> None:
+    """ECAPA-TDNN speaker encoder tensors (`spk_enc.*`, names and shapes of scripts/convert_tts_to_gguf.py:59-125 and
+    src/audio_tokenizer_encoder.cpp:172-246; conv weights are numpy [Cout, Cin, K] -> F16, biases F32).  They come from
+    a generator of their own (seed + 7919), after every other tensor, so the talker / code-predictor tensors keep their
+    values and both presets carry the same encoder."""
+    rng = _Rng(seed + 7919)
+    w.add_uint32("qwen3-tts.speaker_encoder.embedding_length", 1024)
+    w.add_uint32("qwen3-tts.speaker_encoder.sample_rate", 24000)
+
+    def conv(name, cout, cin, k, gain=1.0):
+        _add(w, f"spk_enc.{name}.weight", rng.normal((cout, cin, k), gain / np.sqrt(cin * k)), "f16")
+        _add(w, f"spk_enc.{name}.bias", rng.normal((cout,), 0.05), "f16")
+
+    conv("conv0", 512, 128, 5, gain=0.3)                 # log-mel inputs are O(5)
+    for b in (1, 2, 3):
+        conv(f"blk.{b}.tdnn1", 512, 512, 1, gain=1.4)
+        for r in range(7):
+            conv(f"blk.{b}.res2net.{r}", 64, 64, 3, gain=1.4)
+        conv(f"blk.{b}.tdnn2", 512, 512, 1, gain=1.4)
+        conv(f"blk.{b}.se.conv1", 128, 512, 1)
+        conv(f"blk.{b}.se.conv2", 512, 128, 1)
+    conv("mfa", 1536, 1536, 1, gain=1.4)
+    conv("asp.tdnn", 128, 4608, 1)
+    conv("asp.conv", 1536, 128, 1, gain=3.0)
+    conv("fc", 1024, 3072, 1, gain=0.2)
 
 
 def write_vocoder_gguf(path: str, seed: int = 4321, gain: float = 1.0, out_gain: float = 0.06, usage: bool = False,
