@@ -14,6 +14,7 @@
 #pragma once
 
 #include <algorithm>
+#include <cuda.h>           // CUtensorMap (types only: the encoder is fetched with cudaGetDriverEntryPoint, no -lcuda)
 #include "common.cuh"
 #include "engine.h"
 
@@ -269,9 +270,17 @@ __device__ __forceinline__ void vu_mbar_wait(unsigned long long * bar, uint32_t 
                  :: "r"(vu_smem(bar)), "r"(parity) : "memory");
 }
 
+// TMA tensor-map load of a [box rows][4 k-chunks][8 halves] tile (cp.async.bulk.tensor.3d, SASS UTMALDG): coordinates
+// {0, row, k / 8}; rows outside [0, rows) -- the causal left pad of a conv, the tail of the last tile -- arrive as zeros
+__device__ __forceinline__ void vu_tma_3d(uint32_t dst, const CUtensorMap * tm, int c1, int c2, unsigned long long * bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 :: "r"(dst), "l"(tm), "r"(0), "r"(c1), "r"(c2), "r"(vu_smem(bar)) : "memory");
+}
+
 template <int EPI>
 __global__ void __launch_bounds__(VU_LAUNCH)
-vgemm_umma(const VGemm p, const int BN, const int MT) {
+vgemm_umma(const VGemm p, const int BN, const int MT, const int use_tma, const int a_box_rows, const int a_box_kc,
+           const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW) {
     extern __shared__ __align__(1024) unsigned char vu_sm[];
     __shared__ unsigned long long mbar_full[VU_STAGES], mbar_empty[VU_STAGES];
     __shared__ unsigned long long mbar_done;
@@ -286,7 +295,8 @@ vgemm_umma(const VGemm p, const int BN, const int MT) {
 
     if (tid == 0) {
         for (int i = 0; i < VU_STAGES; ++i) {
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(vu_smem(&mbar_full[i])), "n"(VU_THREADS / 32));
+            // cp.async path: one arrival per loader warp; TMA path: the producer thread's arrive.expect_tx
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(vu_smem(&mbar_full[i])), "r"(use_tma ? 1 : VU_THREADS / 32));
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(vu_smem(&mbar_empty[i])));
         }
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(vu_smem(&mbar_done)));
@@ -310,6 +320,9 @@ vgemm_umma(const VGemm p, const int BN, const int MT) {
     const int ra = share ? vu_ra_shared(MT) : VU_BM * MT;            // rows of an A stage
     const uint32_t lbo_a = (uint32_t) ra * 16, a_stage_b = (uint32_t) ra * VU_BK * 2;
     const int n_a_stages = share ? 3 : VU_STAGES;
+    // W stage layout.  cp.async path: 8-row groups of 4 k-chunks (LBO 128, SBO 512).  TMA path: what a {8, BN, 4} box
+    // lands as, [k-chunk][row][8 halves] (LBO = BN * 16, SBO 128) -- the A ring's layout.
+    const uint32_t lbo_b = use_tma ? (uint32_t) BN * 16 : (uint32_t) VU_LBO, sbo_b = use_tma ? 128u : (uint32_t) VU_SBO;
     const int ra_used = VU_BM * MT + (share ? max_off - min_off : 0);
     // instruction descriptor (kind::f16): D = F32 [4,6) = 1, A = B = F16, both K-major, N >> 3 [17,23), M >> 4 [24,29)
     const uint32_t idesc = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (VU_BM >> 4) << 24);
@@ -347,7 +360,33 @@ vgemm_umma(const VGemm p, const int BN, const int MT) {
         if (l_w_has1) vu_cp16(b_dst + 8 * VU_SBO, l_w1 + wcol, l_w_ok1);
     };
 
-    if (warp < VU_THREADS / 32) {
+    if (use_tma && tid == 0) {
+        // ---- TMA producer: one thread walks the steps; a step's operands are 1..5 tensor-map copies of A (64 rows each, only when
+        //      the A stage changes) and one of W, all completing on the stage's `full` barrier
+        {
+            // an A stage is [4 k-chunks][ra rows][16 B]; the A box is {8 halves, a_box_rows rows, a_box_kc k-chunks}: the whole
+            // stage in one copy when ra <= 256 (box limit), else half stages one k-chunk at a time
+            const int row_parts = ra / a_box_rows, kc_parts = (VU_BK / 8) / a_box_kc;
+            const uint32_t a_bytes = (uint32_t) ra * VU_BK * 2;
+            for (int it = 0; it < n_steps; ++it) {
+                const int stage = it % VU_STAGES;
+                if (it >= VU_STAGES) vu_mbar_wait(&mbar_empty[stage], (uint32_t) ((it / VU_STAGES) - 1) & 1u);
+                const int kb = it / p.ntaps, tap = it - kb * p.ntaps, k0 = kb * VU_BK;
+                const bool load_a = !share || tap == 0;
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+                             :: "r"(vu_smem(&mbar_full[stage])), "r"((uint32_t) b_stage + (load_a ? a_bytes : 0u)) : "memory");
+                if (load_a) {
+                    const int ast = (share ? kb : it) % n_a_stages;
+                    const long ar = m0 + (share ? min_off : p.tap_off[tap]);
+                    for (int i = 0; i < row_parts; ++i)
+                        for (int kc = 0; kc < kc_parts; ++kc)
+                            vu_tma_3d(vu_smem(smA) + (uint32_t) ast * a_stage_b + (uint32_t) (kc * a_box_kc) * lbo_a + (uint32_t) i * a_box_rows * 16,
+                                      &tmA, (int) (ar + (long) i * a_box_rows), k0 / 8 + kc * a_box_kc, &mbar_full[stage]);
+                }
+                vu_tma_3d(vu_smem(smB + stage * b_stage), &tmW, n0, (tap * p.Kc + k0) / 8, &mbar_full[stage]);
+            }
+        }
+    } else if (!use_tma && warp < VU_THREADS / 32) {
         // ---- loaders: iteration `it` issues the loads of step `it` and publishes step it - (VU_AHEAD - 1)
         for (int it = 0; it < n_steps + VU_AHEAD - 1; ++it) {
             if (it < n_steps) {
@@ -376,7 +415,7 @@ vgemm_umma(const VGemm p, const int BN, const int MT) {
             const uint32_t b_base = vu_smem(smB + stage * b_stage);
 #pragma unroll
             for (int kk = 0; kk < VU_BK / 16; ++kk) {
-                const uint64_t ad = vu_desc2(a_base + kk * 2 * lbo_a, lbo_a, 128u), bd = vu_desc(b_base + kk * 2 * VU_LBO);
+                const uint64_t ad = vu_desc2(a_base + kk * 2 * lbo_a, lbo_a, 128u), bd = vu_desc2(b_base + kk * 2 * lbo_b, lbo_b, sbo_b);
                 const uint32_t accum = (step > 0 || kk > 0) ? 1u : 0u;
                 asm volatile("{ .reg .pred q; setp.ne.b32 q, %4, 0; tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, q; }"
                              :: "r"(tmem_d), "l"(ad), "l"(bd), "r"(idesc), "r"(accum) : "memory");
@@ -466,6 +505,34 @@ inline bool voc_use_umma() {
     return v != 0;
 }
 
+typedef CUresult (*vu_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+inline vu_encode_fn vu_encoder() {
+    static vu_encode_fn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void * p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (vu_encode_fn) p;
+    }
+    return fn;
+}
+// [rows][ld] F16 matrix (k contiguous) as the rank-3 tensor {8 halves, rows, K / 8}: a box {8, box_rows, box_kc} lands in shared
+// memory as [k-chunk][row][16 B] = the no-swizzle K-major core-matrix layout the UMMA descriptors describe (LBO = box_rows * 16, SBO 128)
+inline bool vu_make_map(CUtensorMap * tm, const __half * base, long rows, long K, long ld, int box_rows, int box_kc) {
+    vu_encode_fn enc = vu_encoder();
+    if (!enc || ((uintptr_t) base & 15) || (ld % 8) || (K % 8) || box_rows > 256 || rows <= 0) return false;
+    const cuuint64_t dims[3] = {8, (cuuint64_t) rows, (cuuint64_t) (K / 8)};
+    const cuuint64_t strides[2] = {(cuuint64_t) ld * 2, 16};
+    const cuuint32_t box[3] = {8, (cuuint32_t) box_rows, (cuuint32_t) box_kc};
+    const cuuint32_t es[3] = {1, 1, 1};
+    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<__half *>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
     if (voc_use_umma() && p.Kc % VU_BK == 0 && p.N >= 16 && p.N % 2 == 0 && p.lda % 8 == 0) {
         // widest tile <= 128 columns that divides N (no half-empty last tile), else 128 / N rounded up to 16
@@ -473,10 +540,11 @@ inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
         for (int c = 128; c >= 64; c -= 16) if (p.N % c == 0) { BN = c; break; }
         // two M tiles per CTA when the grid still gives every SM its two resident CTAs
         const long tiles256 = (long) ((p.M + 2 * VU_BM - 1) / (2 * VU_BM)) * ((p.N + BN - 1) / BN);
-        static int mt_env = -1, mt_k = 1024;
+        static int mt_env = -1, mt_k = 1024, tma_env = -1;
         if (mt_env < 0) {
             const char * e = getenv("Q3T_VOC_MT"); mt_env = e ? atoi(e) : 0;
             if ((e = getenv("Q3T_VOC_MT_K"))) mt_k = atoi(e);
+            e = getenv("Q3T_VOC_TMA"); tma_env = e ? atoi(e) : 1;      // 0: operands staged with cp.async (the round-1 path, kept for A/B runs)
         }
         const int MT = mt_env ? mt_env : (tiles256 >= 2 * 148 && p.ntaps * p.Kc >= mt_k ? 2 : 1);   // short K: the epilogue dominates, keep 3 CTAs per SM
         const int smem = std::max(vu_a_ring(MT) + VU_STAGES * vu_b_stage(BN), VU_BM * (BN + 4) * 4);
@@ -490,16 +558,26 @@ inline void voc_gemm(q3t_ctx * ctx, const VGemm & p) {
             cudaFuncSetAttribute(vgemm_umma<VEPI_O32_SNAKE>,  cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
             attr = true;
         }
+        // TMA tensor maps of both operands (the kernel's stage geometry decides the A box)
+        int min_off = p.tap_off[0], max_off = p.tap_off[0];
+        for (int i = 1; i < p.ntaps; ++i) { min_off = std::min(min_off, p.tap_off[i]); max_off = std::max(max_off, p.tap_off[i]); }
+        const bool share = p.ntaps > 1 && max_off - min_off <= VU_SPAN_MAX;
+        const int ra = share ? vu_ra_shared(MT) : VU_BM * MT;
+        const int a_box_rows = ra <= 256 ? ra : ra / 2, a_box_kc = ra <= 256 ? VU_BK / 8 : 1;
+        CUtensorMap tmA, tmW;
+        memset(&tmA, 0, sizeof(tmA)); memset(&tmW, 0, sizeof(tmW));
+        const int use_tma = tma_env && vu_make_map(&tmA, p.A, p.a_rows, p.Kc, p.lda, a_box_rows, a_box_kc) &&
+                            vu_make_map(&tmW, p.W, p.N, (long) p.ntaps * p.Kc, (long) p.ntaps * p.Kc, BN, VU_BK / 8) ? 1 : 0;
         dim3 grid((unsigned) ((p.M + VU_BM * MT - 1) / (VU_BM * MT)), (unsigned) ((p.N + BN - 1) / BN));
         const bool snake16 = p.bias && !p.gamma && !p.swiglu && p.out16 && p.act == VACT_SNAKE && (p.ld16 & 1) == 0;
         if (snake16 && !p.res && !p.out32)
-            vgemm_umma<VEPI_BIAS_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT);
+            vgemm_umma<VEPI_BIAS_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT, use_tma, a_box_rows, a_box_kc, tmA, tmW);
         else if (snake16 && p.res && (p.ldres & 1) == 0 && (!p.out32 || (p.ld32 & 1) == 0))
-            vgemm_umma<VEPI_RES_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT);
+            vgemm_umma<VEPI_RES_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT, use_tma, a_box_rows, a_box_kc, tmA, tmW);
         else if (snake16 && !p.res && p.out32 && (p.ld32 & 1) == 0)
-            vgemm_umma<VEPI_O32_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT);
+            vgemm_umma<VEPI_O32_SNAKE><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT, use_tma, a_box_rows, a_box_kc, tmA, tmW);
         else
-            vgemm_umma<VEPI_GENERIC><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT);
+            vgemm_umma<VEPI_GENERIC><<<grid, VU_LAUNCH, smem, ctx->stream>>>(p, BN, MT, use_tma, a_box_rows, a_box_kc, tmA, tmW);
         return;
     }
     dim3 grid((unsigned) ((p.M + VG_BM - 1) / VG_BM), (unsigned) ((p.N + VG_BN - 1) / VG_BN));
