@@ -119,6 +119,8 @@ extern "C" void q3t_ctx_destroy(q3t_ctx * ctx) {
     for (auto & kv : ctx->raw) cudaFree(kv.second.dev);
     ctx->raw.clear();
     for (auto & ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    if (ctx->d_prof) cudaFree(ctx->d_prof);
+    if (ctx->d_prof_n) cudaFree(ctx->d_prof_n);
     if (ctx->h_done) cudaFreeHost(ctx->h_done);
     if (ctx->h_states) cudaFreeHost(ctx->h_states);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -658,12 +660,13 @@ extern "C" int q3t_talker_prefill(q3t_ctx * ctx, const float * embd, int32_t n_t
     if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
     if (!embd) return set_err(ctx, Q3T_ERR_ARG, "prefill_embd is null");
     if (n_tokens <= 0) return set_err(ctx, Q3T_ERR_ARG, "n_tokens must be > 0");
+    if (n_past < 0) return set_err(ctx, Q3T_ERR_ARG, "n_past must be >= 0");
     cudaSetDevice(ctx->device);
     int rc = ensure_ctx(ctx, n_past + n_tokens, n_past + n_tokens + 16);
     if (rc) return rc;
     float * d_in = nullptr, * d_hid = nullptr;
     CK(cudaMalloc(&d_in, (size_t) n_tokens * H * 4));
-    CK(cudaMalloc(&d_hid, (size_t) n_tokens * H * 4));
+    if ((rc = cuda_check(ctx, cudaMalloc(&d_hid, (size_t) n_tokens * H * 4), "cudaMalloc"))) { cudaFree(d_in); return rc; }
     rc = cuda_check(ctx, cudaMemcpyAsync(d_in, embd, (size_t) n_tokens * H * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D");
     if (!rc) rc = reset_state(ctx, default_state(ctx), false);
     if (!rc) rc = run_talker_rows(ctx, d_in, n_tokens, n_past, true, 0, d_hid);
@@ -679,6 +682,7 @@ extern "C" int q3t_talker_step(q3t_ctx * ctx, const float * embd, int32_t n_past
     if (!ctx) return Q3T_ERR_ARG;
     if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
     if (!embd) return set_err(ctx, Q3T_ERR_ARG, "step_embd is null");
+    if (n_past < 0) return set_err(ctx, Q3T_ERR_ARG, "n_past must be >= 0");
     cudaSetDevice(ctx->device);
     int rc = ensure_ctx(ctx, n_past + 1, n_past + 1 + 16);
     if (rc) return rc;
@@ -1258,6 +1262,8 @@ extern "C" int q3t_run_staged(q3t_ctx * ctx, int32_t max_len, float repetition_p
 
 extern "C" int q3t_fetch_codes(q3t_ctx * ctx, int32_t * codes_out, int32_t n_frames) {
     if (!ctx || !codes_out) return Q3T_ERR_ARG;
+    if (n_frames < 0) return set_err(ctx, Q3T_ERR_ARG, "n_frames must be >= 0");
+    if (n_frames == 0) return Q3T_OK;
     if (n_frames > ctx->last_n_frames) return set_err(ctx, Q3T_ERR_ARG, "more frames requested than generated");
     CK(cudaMemcpyAsync(codes_out, ctx->d_codes, (size_t) n_frames * NCB * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
@@ -1282,6 +1288,7 @@ extern "C" int q3t_profile_arm(q3t_ctx * ctx, int32_t cta, int32_t cap) {
 // copies the records (clock64 << 8 | tag) of the selected CTA for the LAST launch out; returns the count
 extern "C" int q3t_profile_read(q3t_ctx * ctx, uint64_t * out, int32_t cap) {
     if (!ctx || !ctx->d_prof) return Q3T_ERR_STATE;
+    if (!out || cap < 0) return Q3T_ERR_ARG;
     CK(cudaStreamSynchronize(ctx->stream));
     const int cta = ctx->hm.prof_cta;
     unsigned n = 0;

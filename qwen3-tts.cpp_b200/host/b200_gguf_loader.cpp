@@ -118,6 +118,8 @@ int32_t GGUFLoader::get_u32(const char * key, int32_t default_val) const {
     const gguf_kv * kv = file_.find(key);
     if (!kv || kv->type == GGUF_T_STRING || kv->type == GGUF_T_ARRAY) return default_val;
     if (kv->type == GGUF_T_F32 || kv->type == GGUF_T_F64) return (int32_t) kv->f;
+    const int64_t v = (int64_t) kv->u;                       // 64-bit keys that do not fit are treated as absent,
+    if (v < INT32_MIN || v > (int64_t) UINT32_MAX) return default_val;   // not silently truncated
     return (int32_t) kv->u;
 }
 float GGUFLoader::get_f32(const char * key, float default_val) const {

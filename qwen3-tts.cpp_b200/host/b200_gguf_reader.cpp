@@ -88,8 +88,16 @@ size_t GGUFFile::type_nbytes(uint32_t type, const int64_t ne[4]) {
         case 30: bsz = 2; break;              // BF16
         default: return 0;
     }
+    // every extent must be positive and the product must fit: a hostile header must not be able to wrap the
+    // byte count past the bounds check in open() (0 = "unknown / invalid", which open() rejects)
+    for (int d = 0; d < 4; ++d) if (ne[d] <= 0) return 0;
     if (ne[0] % blck != 0) return 0;
-    return (size_t) (ne[0] / blck) * bsz * (size_t) (ne[1] * ne[2] * ne[3]);
+    unsigned __int128 n = (unsigned __int128) (uint64_t) (ne[0] / blck) * bsz;
+    for (int d = 1; d < 4; ++d) {
+        n *= (uint64_t) ne[d];
+        if (n > (unsigned __int128) 1 << 62) return 0;
+    }
+    return (size_t) n;
 }
 
 GGUFFile::~GGUFFile() { close(); }
@@ -98,6 +106,7 @@ void GGUFFile::close() {
     if (map_) { munmap((void *) map_, size_); map_ = nullptr; }
     if (fd_ >= 0) { ::close(fd_); fd_ = -1; }
     size_ = 0; kv_.clear(); tensors_.clear(); by_name_.clear(); data_offset_ = 0;
+    alignment_ = 32; version_ = 0;
 }
 
 bool GGUFFile::open(const std::string & path, std::string & err, bool keep_string_arrays) {
@@ -137,7 +146,7 @@ bool GGUFFile::open(const std::string & path, std::string & err, bool keep_strin
                 }
             } else {
                 const size_t es = scalar_size(kv.arr_type);
-                if (es == 0) { c.ok = false; break; }
+                if (es == 0 || kv.arr_n > (uint64_t) (c.end - c.p) / es) { c.ok = false; break; }
                 c.skip(es * kv.arr_n);
             }
         } else if (!read_scalar(c, kv.type, kv)) {
@@ -146,7 +155,13 @@ bool GGUFFile::open(const std::string & path, std::string & err, bool keep_strin
         kv_[key] = std::move(kv);
     }
     if (!c.ok) { err = "Failed to open GGUF file: " + path + " (corrupt metadata)"; close(); return false; }
-    if (const gguf_kv * a = find("general.alignment")) if (a->u > 0) alignment_ = (uint32_t) a->u;
+    if (const gguf_kv * a = find("general.alignment")) {
+        // ggml accepts only powers of two here; anything else (or > 1 MiB) is a corrupt file
+        if (a->u == 0 || a->u > (1u << 20) || (a->u & (a->u - 1)) != 0) {
+            err = "Failed to open GGUF file: " + path + " (bad general.alignment)"; close(); return false;
+        }
+        alignment_ = (uint32_t) a->u;
+    }
 
     tensors_.reserve((size_t) n_tensors);
     for (uint64_t i = 0; i < n_tensors && c.ok; ++i) {
@@ -158,14 +173,20 @@ bool GGUFFile::open(const std::string & path, std::string & err, bool keep_strin
         ti.type = c.get<uint32_t>();
         ti.offset = c.get<uint64_t>();
         ti.nbytes = type_nbytes(ti.type, ti.ne);
+        if (c.ok && ti.nbytes == 0) {
+            err = "Failed to open GGUF file: " + path + " (bad type or shape: " + ti.name + ")"; close(); return false;
+        }
         by_name_[ti.name] = tensors_.size();
         tensors_.push_back(std::move(ti));
     }
     if (!c.ok) { err = "Failed to open GGUF file: " + path + " (corrupt tensor directory)"; close(); return false; }
     const size_t pos = (size_t) (c.p - map_);
     data_offset_ = (pos + alignment_ - 1) / alignment_ * alignment_;
+    if (data_offset_ > size_) { err = "Failed to open GGUF file: " + path + " (truncated before tensor data)"; close(); return false; }
+    const size_t data_size = size_ - data_offset_;
     for (const auto & t : tensors_) {
-        if (data_offset_ + t.offset + t.nbytes > size_) { err = "Failed to open GGUF file: " + path + " (tensor data out of bounds: " + t.name + ")"; close(); return false; }
+        // subtraction form: no sum of attacker-controlled 64-bit values that could wrap
+        if (t.offset > data_size || t.nbytes > data_size - t.offset) { err = "Failed to open GGUF file: " + path + " (tensor data out of bounds: " + t.name + ")"; close(); return false; }
     }
     return true;
 }

@@ -113,6 +113,82 @@ def test_gguf_loader_rejects_garbage(q3t, tmp_path):
     assert g.open(str(trunc)) is False
 
 
+def _gguf_bytes(tensors, kvs=(), pad_data=64, alignment=None):
+    """Hand-assembled GGUF v3 file: tensors = [(name, ne, type, offset)], kvs = [(key, type, payload bytes)]."""
+    import struct
+    def s(x): return struct.pack("<Q", len(x)) + x.encode()
+    kvs = list(kvs)
+    if alignment is not None:
+        kvs.append(("general.alignment", 4, struct.pack("<I", alignment)))
+    out = b"GGUF" + struct.pack("<IQQ", 3, len(tensors), len(kvs))
+    for key, typ, payload in kvs:
+        out += s(key) + struct.pack("<I", typ) + payload
+    for name, ne, typ, off in tensors:
+        out += s(name) + struct.pack("<I", len(ne)) + b"".join(struct.pack("<Q", n & (2**64 - 1)) for n in ne)
+        out += struct.pack("<IQ", typ, off & (2**64 - 1))
+    a = alignment if alignment else 32
+    out += b"\0" * ((-len(out)) % a)
+    return out + b"\x11" * pad_data
+
+
+def test_gguf_loader_rejects_overflowing_headers(q3t, tmp_path):
+    """bounds checks must not be defeatable by 64-bit wrap-around (the reference's ggml parser rejects
+    such files, ggml/src/gguf.cpp gguf_init_from_file_impl); every file here is refused at open(), none crashes."""
+    import struct
+    g = q3t.GGUFLoader()
+    ok = tmp_path / "ok.gguf"
+    ok.write_bytes(_gguf_bytes([("a", [8, 2], 0, 0)]))
+    assert g.open(str(ok)), g.get_error()
+    assert g.get_n_tensors() == 1 and g.get_tensor_size(0) == 64
+    cases = {
+        "offset_wraps":   _gguf_bytes([("a", [8, 2], 0, 2**64 - 32)]),            # data_offset + offset wraps to a small value
+        "offset_past":    _gguf_bytes([("a", [8, 2], 0, 32)]),                     # 32 + 64 > 64 bytes of data
+        "ne_product":     _gguf_bytes([("a", [2**32, 2**32], 0, 0)]),              # element count wraps to 0
+        "ne_product3":    _gguf_bytes([("a", [2**21, 2**21, 2**21, 2], 1, 0)]),    # 2^64 halves
+        "ne_negative":    _gguf_bytes([("a", [-8, 2], 0, 0)]),
+        "ne_zero":        _gguf_bytes([("a", [0, 2], 0, 0)]),
+        "blck_misfit":    _gguf_bytes([("a", [33, 2], 8, 0)]),                     # Q8_0 row not a multiple of 32
+        "unknown_type":   _gguf_bytes([("a", [8, 2], 99, 0)]),
+        "too_many_dims":  _gguf_bytes([("a", [2, 2, 2, 2, 2], 0, 0)]),
+        "array_wraps":    _gguf_bytes([("a", [8, 2], 0, 0)], kvs=[("k", 9, struct.pack("<IQ", 10, 2**61 + 1))]),  # u64[] * 8 wraps
+        "array_long":     _gguf_bytes([("a", [8, 2], 0, 0)], kvs=[("k", 9, struct.pack("<IQ", 4, 2**40))]),
+        "string_long":    _gguf_bytes([("a", [8, 2], 0, 0)], kvs=[("k", 8, struct.pack("<Q", 2**63))]),
+        "bad_kv_type":    _gguf_bytes([("a", [8, 2], 0, 0)], kvs=[("k", 77, b"\0" * 8)]),
+        "alignment_zero": _gguf_bytes([("a", [8, 2], 0, 0)], alignment=0),
+        "alignment_odd":  _gguf_bytes([("a", [8, 2], 0, 0)], alignment=48),
+        "alignment_huge": _gguf_bytes([("a", [8, 2], 0, 0)], alignment=2**31),
+        "counts_huge":    b"GGUF" + struct.pack("<IQQ", 3, 2**60, 2**60),
+    }
+    good = _gguf_bytes([("a", [8, 2], 0, 0)])
+    for cut in (5, 12, 23, 24, 30, len(good) - 65, len(good) - 1):                 # truncations of a good file
+        cases[f"trunc_{cut}"] = good[:cut]
+    for name, blob in cases.items():
+        f = tmp_path / f"{name}.gguf"
+        f.write_bytes(blob)
+        assert g.open(str(f)) is False, name
+        assert g.get_error(), name
+        assert g.get_n_tensors() == 0, name
+
+
+def test_gguf_loader_alignment_is_per_file(q3t, tmp_path):
+    """close()/re-open must not carry general.alignment from the previous file over."""
+    g = q3t.GGUFLoader()
+    a = tmp_path / "a64.gguf"; a.write_bytes(_gguf_bytes([("a", [8, 2], 0, 0)], alignment=256))
+    b = tmp_path / "b.gguf";   b.write_bytes(_gguf_bytes([("a", [8, 2], 0, 0)]))
+    assert g.open(str(a)), g.get_error()
+    assert g.get_data_offset() % 256 == 0
+    off_a = g.get_data_offset()
+    assert g.open(str(b)), g.get_error()
+    assert g.get_data_offset() % 32 == 0 and g.get_data_offset() < off_a
+    big = tmp_path / "big.gguf"
+    import struct
+    big.write_bytes(_gguf_bytes([("a", [8, 2], 0, 0)], kvs=[("qwen3-tts.block_count", 10, struct.pack("<Q", 2**40 + 5)),
+                                                              ("small", 10, struct.pack("<Q", 28))]))
+    assert g.open(str(big)), g.get_error()
+    assert g.get_u32("qwen3-tts.block_count", -7) == -7          # does not fit 32 bits: default, not 5
+    assert g.get_u32("small", -7) == 28
+
+
 def test_q8_0_model_metadata(q3t):
     from util import models
     tts, _ = models("tiny", "q8_0")
