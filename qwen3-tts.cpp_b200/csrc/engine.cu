@@ -295,7 +295,8 @@ static int chain_pack_inplace(q3t_ctx * ctx, __half * w, size_t rows, int K) {
 // 1024 weights: [1024 int8][32 F16 block scales] = 1088 B, K/1024 records per row, rows at
 // dst_row0 + r * dst_row_step (fused q|k|v planes, gate/up interleave).
 //   mode 0 (int8 dot, lm_kernel.cu gemv_q8):      value e of block b -> (b/4)*128 + (e/4)*16 + (b%4)*4 + e%4
-//   mode 1 (F32 chain, lm_kernel.cu gemv_q8_f32): value e of block b -> (b/8)*256 + e*8 + b%8
+//   mode 1 (F32 chain, lm_kernel.cu gemv_q8_f32): value e of block b -> (b/8)*256 + e*8 + b%8, stored as q + 128
+//           (biased: the kernel turns the byte into a float with one byte-permute instead of an int->float conversion)
 __global__ void k_q8_pack(const unsigned char * __restrict__ raw, unsigned char * __restrict__ dst, size_t n_rows, int K,
                           size_t dst_row0, int dst_row_step, int mode) {
     const int nb = K / 32;
@@ -309,7 +310,7 @@ __global__ void k_q8_pack(const unsigned char * __restrict__ raw, unsigned char 
         for (int e = 0; e < 32; ++e) {
             const int off = mode == 0 ? (bl >> 2) * 128 + (e >> 2) * 16 + (bl & 3) * 4 + (e & 3)
                                       : (bl >> 3) * 256 + e * 8 + (bl & 7);
-            rec[off] = src[2 + e];
+            rec[off] = mode == 0 ? src[2 + e] : (unsigned char) (src[2 + e] ^ 0x80u);
         }
     }
 }
@@ -484,6 +485,11 @@ static int finalize_tts(q3t_ctx * ctx) {
     if ((rc = dev_alloc(ctx, &pk, PKT_TOTAL, true))) return rc;
     m.x_qkv = pk; m.x_att = m.x_qkv + QKV_N; m.x_x1 = m.x_att + NH * HD; m.x_m = m.x_x1 + H; m.x_x = m.x_m + FFN;
     m.x_logit = m.x_x + H; m.x_cand = m.x_logit + 3072;
+    if ((rc = dev_alloc(ctx, &m.x_sc, (size_t) NH * LM_ATT_MAX_KV, true))) return rc;
+    {   // rows longer than this are scored by 8 CTAs per head (0 = never); Q3T_WIDE_MIN overrides for experiments
+        const char * e = getenv("Q3T_WIDE_MIN");
+        m.wide_min = e ? atoi(e) : 48;
+    }
     if ((rc = dev_alloc(ctx, &m.hidden, H, true))) return rc;
     if ((rc = dev_alloc(ctx, &m.logits, 3072, true))) return rc;
     if ((rc = dev_alloc(ctx, &m.seen, 4096, true))) return rc;
@@ -534,15 +540,17 @@ extern "C" int q3t_kv_init(q3t_ctx * ctx, int32_t n_ctx) {
     const size_t per = (size_t) L * NKV * n_ctx * HD;                    // halves per K (or V)
     const int n_rope = std::max(n_ctx, 16);
     const size_t rope_bytes = (size_t) n_rope * HD * sizeof(float);
-    const size_t total = per * 2 * sizeof(__half) + rope_bytes;
+    // K | V | V again, dealt in 16-dim slices for the wide attention path (lm_kernel.cu attention_wide) | RoPE table
+    const size_t total = per * 3 * sizeof(__half) + rope_bytes;
     CK(cudaMalloc(&ctx->kv_alloc, total));
-    CK(cudaMemsetAsync(ctx->kv_alloc, 0, per * 2 * sizeof(__half), ctx->stream));
+    CK(cudaMemsetAsync(ctx->kv_alloc, 0, per * 3 * sizeof(__half), ctx->stream));
     DevModel & m = ctx->hm;
     m.talker.kcache = (__half *) ctx->kv_alloc;
     m.talker.vcache = m.talker.kcache + per;
+    m.talker.vslice = m.talker.vcache + per;
     m.talker.kf32 = nullptr; m.talker.vf32 = nullptr;
     m.talker.n_ctx = n_ctx;
-    float * rope_dev = (float *) (m.talker.vcache + per);
+    float * rope_dev = (float *) (m.talker.vslice + per);
     std::vector<float> tab((size_t) n_rope * HD);
     const float theta_scale = powf(ctx->cfg.rope_theta, -2.0f / (float) HD);
     for (int p = 0; p < n_rope; ++p) {
@@ -569,6 +577,7 @@ static int reset_state(q3t_ctx * ctx, const GenState & init, bool clear_seen) {
     st.ep_base = 0; st.pending_ep = 0;
     st.error = 0;
     CK(cudaMemsetAsync(m.x_qkv, 0, PKT_TOTAL * sizeof(Pkt), ctx->stream));     // epoch 0 = never written
+    if (m.talker.vslice && m.x_sc) CK(cudaMemsetAsync(m.x_sc, 0, (size_t) NH * LM_ATT_MAX_KV * sizeof(Pkt), ctx->stream));
     if (clear_seen) CK(cudaMemsetAsync(m.seen, 0, 4096, ctx->stream));
     CK(cudaMemcpyAsync(m.st, &st, sizeof(GenState), cudaMemcpyHostToDevice, ctx->stream));
     return Q3T_OK;
@@ -642,7 +651,9 @@ static int run_talker_rows(q3t_ctx * ctx, const float * embd_dev, int n_tokens, 
             const bool last = r == n_tokens - 1;
             PassDesc p = make_pass(0, XM_BUF, 0, n_past + r, 0, (all_heads || last) ? 0 : -1, L, last ? process : 0);
             p.xsrc = embd_dev + (size_t) r * H;
-            p.width = n_past + n_tokens;               // the reference scores the whole prefill block per row
+            // the reference scores the whole prefill block per row; a single token's row is just its n_kv entries
+            // (width 0: the form the frame program uses, which may take the wide attention path on long rows)
+            p.width = n_tokens == 1 ? 0 : n_past + n_tokens;
             if (hidden_all_dev && (all_heads || last)) p.hidden_dst = hidden_all_dev + (size_t) r * H;
             v.push_back(p);
         }
@@ -1177,6 +1188,7 @@ extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * 
             m.x_logit = m.x_x + H; m.x_cand = m.x_logit + 3072;
             m.hidden = b.hidden; m.logits = b.logits; m.seen = b.seen; m.st = b.st; m.codes_out = b.codes;
             m.trailing = b.trailing; m.pad_embed = ctx->d_pad;
+            m.talker.vslice = nullptr;                              // the batched kernel keeps one CTA per (sequence, head)
             m.talker.kcache = b.kv; m.talker.vcache = b.kv + per; m.talker.kf32 = nullptr; m.talker.vf32 = nullptr; m.talker.n_ctx = n_ctx;
             m.cp.kcache = b.ck; m.cp.vcache = b.cv; m.cp.kf32 = b.kf; m.cp.vf32 = b.vf; m.cp.n_ctx = 16;
             m.rope = rope; m.n_rope_pos = std::max(n_ctx, 16);

@@ -36,6 +36,7 @@ struct StackW {
     const float * out_norm;    // [1024]
     __half * kcache;           // [L][8][n_ctx][128]
     __half * vcache;
+    __half * vslice;           // [L][8][8][n_ctx][16]  the V history again, dealt in 16-dim slices (wide attention; talker only)
     float  * kf32;             // [L][2][8][128]  F32 shadow of positions 0,1 (code-pred prefill numerics)
     float  * vf32;
     int n_ctx;
@@ -110,6 +111,8 @@ struct DevModel {
     Pkt * x_x;                       // [1024] layer output                        (E -> next A / head)
     Pkt * x_logit;                   // [3072] raw head logits                     (head -> select)
     Pkt * x_cand;                    // [2*grid] per-CTA arg-max candidate {value, index}
+    Pkt * x_sc;                      // [16][LM_ATT_MAX_KV] attention scores of a head (wide attention: members -> members)
+    int wide_min;                    // rows longer than this take the wide attention path (0 = never)
     float * hidden;                  // [1024]
     float * logits;                  // [3072]
     unsigned char * seen;            // [3072] repetition-penalty set

@@ -44,6 +44,9 @@ constexpr int KV_CH      = 128;                        // K/V history rows per r
 constexpr int SLOT_Q8    = 1088;                       // Q8_0 record of 1024 weights: 1024 int8 + 32 F16 block scales
 constexpr int NMB        = 8;                          // mbarriers cycling over the slices in flight
 constexpr int ATT_MAX_KV = LM_ATT_MAX_KV;              // positions the attention phase can hold
+constexpr int WIDE_G     = 8;                          // wide attention: CTAs per head,
+constexpr int VS_D       = HD / WIDE_G;                // dims per member (16 halves = 32 bytes per position),
+constexpr int VS_CH      = 512;                        // positions per V slice (16 KB = 8 ring slots)
 constexpr int ATT_FAST_KV = 16;                        // rows up to this width take the register-fed short path (no K/V ring slices)
 
 struct __align__(128) Smem {
@@ -330,6 +333,11 @@ __device__ __forceinline__ uint4 lds_v4(const unsigned char * p) {
     asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
     return v;
 }
+__device__ __forceinline__ uint2 lds_v2(const unsigned char * p) {
+    uint2 v;
+    asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(smem_u32(p)));
+    return v;
+}
 __device__ __forceinline__ unsigned u4_get(const uint4 & v, int e) { return e == 0 ? v.x : e == 1 ? v.y : e == 2 ? v.z : v.w; }
 
 // Rows of chain-major F16 weights in the shared-memory ring (slice starting at slot s0, K/1024 slots
@@ -423,20 +431,49 @@ __device__ __forceinline__ void gemv_ring(Smem & s, int s0, int n_rows) {
 // s.xf[0..K) -> s.xq (int8) + s.xd (scale as float).  Layout of s.xq per 1024 values: group c of 4
 // blocks is 128 bytes, lane l (0..7) owns bytes [c*128 + l*16, +16) = its 4 values (4l..4l+3) of each
 // of the 4 blocks -- the operand order of one dp4a per block in gemv_q8.  Ends with a cbar().
+// N blocks of one warp at once (b0, b0 + NCW, ...; lane `lane` holds value `lane` of each): the N max-reductions
+// are independent, so their shuffle latencies overlap, and the two IEEE divisions of block i (d = amax / 127,
+// id = 127 / amax) are evaluated by lane i alone and broadcast -- one pair of division sequences per warp instead
+// of N (this sits on the layer's critical path twice)
+template <int N>
+__device__ __forceinline__ void q8_blocks(Smem & s, int b0, int n_blocks, int lane, const float (&v)[N]) {
+    float amax[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) amax[i] = fabsf(v[i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+        for (int i = 0; i < N; ++i) amax[i] = fmaxf(amax[i], __shfl_xor_sync(0xffffffffu, amax[i], o));
+    float am = amax[0];
+#pragma unroll
+    for (int i = 1; i < N; ++i) am = lane == i ? amax[i] : am;
+    const float d_l  = __half2float(__float2half_rn(__fdiv_rn(am, 127.0f)));
+    const float id_l = am != 0.0f ? __fdiv_rn(127.0f, am) : 0.0f;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const int b = b0 + i * NCW;
+        const float id = __shfl_sync(0xffffffffu, id_l, i);
+        const int q = __float2int_rn(__fmul_rn(v[i], id));
+        const int bl = b & 31;
+        if (b < n_blocks) {
+            s.xq[(b >> 5) * 1024 + (bl >> 2) * 128 + (lane >> 2) * 16 + (bl & 3) * 4 + (lane & 3)] = (signed char) q;
+            if (lane == i) s.xd[b] = d_l;
+        }
+    }
+}
 template <int K>
 __device__ __forceinline__ void quant_q8(Smem & s) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int b = warp; b < K / 32; b += NCW) {
-        const float v = s.xf[b * 32 + lane];
-        float amax = fabsf(v);
+    constexpr int NB = K / 32, PER = (NB + NCW - 1) / NCW, G = 3;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-        const float d  = __fdiv_rn(amax, 127.0f);
-        const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
-        const int q = __float2int_rn(__fmul_rn(v, id));
-        const int bl = b & 31;
-        s.xq[(b >> 5) * 1024 + (bl >> 2) * 128 + (lane >> 2) * 16 + (bl & 3) * 4 + (lane & 3)] = (signed char) q;
-        if (lane == 0) s.xd[b] = __half2float(__float2half_rn(d));
+    for (int i0 = 0; i0 < PER; i0 += G) {
+        float v[G];
+#pragma unroll
+        for (int i = 0; i < G; ++i) {
+            const int b = warp + (i0 + i) * NCW;
+            v[i] = b < NB ? s.xf[b * 32 + lane] : 0.0f;
+        }
+        q8_blocks<G>(s, warp + i0 * NCW, NB, lane, v);
     }
     cbar();
 }
@@ -484,28 +521,44 @@ __device__ __forceinline__ void gemv_q8(Smem & s, int s0, int n_rows) {
 // j of the 1024-chunk) so one 8-byte load brings 8 chain steps, and the 32 block scales behind them.
 template <int K>
 __device__ __forceinline__ void gemv_q8_f32(Smem & s, int s0, int n_rows) {
-    constexpr int SPR = K / 1024, NU = K / 256, NJ = K / 32;
+    constexpr int SPR = K / 1024, NU = K / 256;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp >= n_rows) return;
-    float xr[NJ];
-#pragma unroll
-    for (int j = 0; j < NJ; ++j) xr[j] = s.xf[32 * j + lane];
+    // like the F16 ffn_down (gemv_ring<.., XF32>): the activation comes from shared memory step by step and the
+    // weight loads are issued two 256-weight chunks ahead in program order -- with all 96 activations in registers
+    // ptxas had no room to hoist them and every chunk paid the shared-memory latency inside the FMA chain
+    const float * xr = s.xf + lane;
     for (int r = warp; r < n_rows; r += NCW) {
         float acc = 0.0f;
+        uint2 qa[2]; uint4 sa[2];
 #pragma unroll
-        for (int u = 0; u < NU; ++u) {
-            int slot = s0 + r * SPR + (u >> 2);
+        for (int a = 0; a < 2; ++a) {
+            int slot = s0 + r * SPR + (a >> 2);
             slot %= NSLOT;
             const unsigned char * rec = s.ring + (size_t) slot * SLOT_B;
-            const uint2 q8 = *reinterpret_cast<const uint2 *>(rec + (u & 3) * 256 + lane * 8);
-            const uint4 sc = *reinterpret_cast<const uint4 *>(rec + 1024 + (u & 3) * 16);
+            qa[a] = lds_v2(rec + (a & 3) * 256 + lane * 8);
+            sa[a] = lds_v4(rec + 1024 + (a & 3) * 16);
+        }
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+            const uint2 q8 = qa[u & 1];
+            const uint4 sc = sa[u & 1];
+            if (u + 2 < NU) {
+                int slot = s0 + r * SPR + ((u + 2) >> 2);
+                slot %= NSLOT;
+                const unsigned char * rec = s.ring + (size_t) slot * SLOT_B;
+                qa[u & 1] = lds_v2(rec + ((u + 2) & 3) * 256 + lane * 8);
+                sa[u & 1] = lds_v4(rec + 1024 + ((u + 2) & 3) * 16);
+            }
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
+                // the record stores q + 128 (k_q8_pack mode 1): one byte-permute drops it into the mantissa of 2^23,
+                // and (2^23 + 128 + q) - (2^23 + 128) is exactly (float) q -- no I2F (a quarter-rate instruction)
                 const unsigned word = e < 4 ? q8.x : q8.y;
-                const int qv = (int) (signed char) ((word >> (8 * (e & 3))) & 0xffu);
+                const float qf = __fsub_rn(__uint_as_float(__byte_perm(word, 0x4B000000u, 0x7650u | (unsigned) (e & 3))), 8388736.0f);
                 const unsigned sw = u4_get(sc, e >> 1);
-                const float d = __half2float(__ushort_as_half((unsigned short) ((e & 1) ? (sw >> 16) : (sw & 0xffffu))));
-                acc = __fmaf_rn(__fmul_rn((float) qv, d), xr[8 * u + e], acc);
+                const float2 d2 = __half22float2(*reinterpret_cast<const __half2 *>(&sw));
+                acc = __fmaf_rn(__fmul_rn(qf, (e & 1) ? d2.y : d2.x), xr[32 * (8 * u + e)], acc);
             }
         }
         const float res = reduce32_lanes(acc);
@@ -548,17 +601,20 @@ __device__ __forceinline__ void rmsnorm_to_xh(Smem & s, const Gam & gm, float ep
     const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
     const float ya = __fmul_rn(__fmul_rn(a, scale), gm.g[0]);
     const float yb = __fmul_rn(__fmul_rn(b, scale), gm.g[1]);
-    if (Q8) { s.xf[t] = ya; s.xf[t + NCT] = yb; } else { xh_put(s, t, ya); xh_put(s, t + NCT, yb); }
-    if (y_out)  { y_out[t] = ya;  y_out[t + NCT] = yb; }
-    if (y_out2) { y_out2[t] = ya; y_out2[t + NCT] = yb; }
-    if (has3) {
-        const float yc = __fmul_rn(__fmul_rn(c, scale), gm.g[2]);
-        if (Q8) s.xf[t + 2 * NCT] = yc; else xh_put(s, t + 2 * NCT, yc);
-        if (y_out)  y_out[t + 2 * NCT] = yc;
-        if (y_out2) y_out2[t + 2 * NCT] = yc;
+    const float yc = has3 ? __fmul_rn(__fmul_rn(c, scale), gm.g[2]) : 0.0f;
+    if (Q8) {
+        // NCT is a multiple of 32: the lanes of warp w hold Q8_0 blocks w, w + NCW, w + 2 NCW of y in registers,
+        // so the activation quantisation needs no trip through shared memory and no extra barrier
+        static_assert(NCT % 32 == 0 && 3 * NCT >= H, "block ownership of the fused quantisation");
+        const float v[3] = {ya, yb, yc};
+        q8_blocks<3>(s, warp, H / 32, lane, v);
+    } else {
+        xh_put(s, t, ya); xh_put(s, t + NCT, yb);
+        if (has3) xh_put(s, t + 2 * NCT, yc);
     }
+    if (y_out)  { y_out[t] = ya;  y_out[t + NCT] = yb; if (has3) y_out[t + 2 * NCT] = yc; }
+    if (y_out2) { y_out2[t] = ya; y_out2[t + NCT] = yb; if (has3) y_out2[t + 2 * NCT] = yc; }
     cbar();
-    if (Q8) quant_q8<H>(s);
 }
 
 // per-head RMSNorm(128)*gamma then NEOX RoPE (FMA-contracted like the reference build), one warp;
@@ -661,6 +717,41 @@ __device__ __forceinline__ float softmax_row32(float score, float M, int lane, i
     return __fmul_rn(e, inv);
 }
 
+// soft-max of a row longer than 32 entries by the whole CTA: s.sc[0..n_kv) scores -> s.ph[0..n_kv) probabilities
+// rounded to F16 (ggml_vec_soft_max_f32: 8 lanes at a time, libm tail; vec.cpp:548-617).  One cbar() inside; the
+// caller adds the one that publishes s.ph.
+template <class SM>
+__device__ __forceinline__ void softmax_long(SM & s, float M, int n_kv, int n8, int n8v) {
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    double ds = 0.0;
+    for (int ch = t; ch < n8v; ch += NCT) {
+        float e[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int tt = ch * 8 + j;
+            e[j] = tt < n_kv ? v_expf(__fsub_rn(s.sc[tt], M)) : 0.0f;     // masked: exp(-inf) = +0
+        }
+        ds += (double) __fadd_rn(__fadd_rn(__fadd_rn(e[4], e[0]), __fadd_rn(e[6], e[2])),
+                                 __fadd_rn(__fadd_rn(e[5], e[1]), __fadd_rn(e[7], e[3])));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (ch * 8 + j < n_kv) s.sc[ch * 8 + j] = e[j];
+    }
+    if (t < 8 && n8 * 8 + t < n_kv) {                        // scalar tail: libm expf
+        const int tt = n8 * 8 + t;
+        const float e = tail_expf(__fsub_rn(s.sc[tt], M));
+        ds += (double) e;
+        s.sc[tt] = e;
+    }
+    ds = warp_sum_d(ds);
+    if (lane == 0) s.dred[warp] = ds;
+    cbar();
+    double S = 0.0;
+#pragma unroll
+    for (int i = 0; i < NCW; ++i) S += s.dred[i];
+    const float inv = (float) (1.0 / S);
+    for (int tt = t; tt < n_kv; tt += NCT) s.ph[tt] = __float2half_rn(__fmul_rn(s.sc[tt], inv));
+}
+
 // address of history row r (0..KV_CH) of a K/V slice that starts at ring slot s0
 template <class SM>
 __device__ __forceinline__ const unsigned char * kv_row(const SM & s, int s0, int r) {
@@ -753,6 +844,7 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
                 s.vnew_f[d] = v[i]; s.vnew_h[d] = hv;
                 if (writer) {
                     W.vcache[kv_head_base + (size_t) pos * HD + d] = hv;
+                    if (W.vslice) W.vslice[(((size_t) (l * NKV + g) * WIDE_G + (d >> 4)) * W.n_ctx + pos) * VS_D + (d & 15)] = hv;
                     if (W.vf32 && pos < 2) W.vf32[((size_t) (l * 2 + pos) * NKV + g) * HD + d] = v[i];
                 }
             }
@@ -927,33 +1019,7 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
             if (lane < n_kv) s.ph[lane] = __float2half_rn(pv);
         }
     } else {
-        double ds = 0.0;
-        for (int ch = t; ch < n8v; ch += NCT) {
-            float e[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int tt = ch * 8 + j;
-                e[j] = tt < n_kv ? v_expf(__fsub_rn(s.sc[tt], M)) : 0.0f;     // masked: exp(-inf) = +0
-            }
-            ds += (double) __fadd_rn(__fadd_rn(__fadd_rn(e[4], e[0]), __fadd_rn(e[6], e[2])),
-                                     __fadd_rn(__fadd_rn(e[5], e[1]), __fadd_rn(e[7], e[3])));
-#pragma unroll
-            for (int j = 0; j < 8; ++j) if (ch * 8 + j < n_kv) s.sc[ch * 8 + j] = e[j];
-        }
-        if (t < 8 && n8 * 8 + t < n_kv) {                        // scalar tail: libm expf
-            const int tt = n8 * 8 + t;
-            const float e = tail_expf(__fsub_rn(s.sc[tt], M));
-            ds += (double) e;
-            s.sc[tt] = e;
-        }
-        ds = warp_sum_d(ds);
-        if (lane == 0) s.dred[warp] = ds;
-        cbar();
-        double S = 0.0;
-#pragma unroll
-        for (int i = 0; i < NCW; ++i) S += s.dred[i];
-        const float inv = (float) (1.0 / S);
-        for (int tt = t; tt < n_kv; tt += NCT) s.ph[tt] = __float2half_rn(__fmul_rn(s.sc[tt], inv));
+        softmax_long(s, M, n_kv, n8, n8v);
     }
     cbar();
     PROF(54);
@@ -1047,6 +1113,242 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     PROF(56);
     if (nck > 0) { cbar(); ring_release(s, rg, (rows_last + 7) >> 3); }
     if (writer && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }   // publish the appended K/V rows (see above)
+}
+
+// --------------------------------------------------------------------------- wide attention (long rows)
+// One CTA per head streams the whole K and V history of the head through ONE SM (2 x n_kv x 256 bytes per layer:
+// 1 MB at 2 000 positions) while 132 CTAs wait for its output.  Rows longer than DevModel::wide_min are dealt to
+// WIDE_G = 8 CTAs per head instead (CTA b: head b % 16, member b / 16; member 0 is the classic attention CTA):
+//   * scores are independent per position: member j scores its share of the K rows and publishes them as packets
+//     (x_sc, one more all-to-all inside the group), every member then holds the full row and evaluates the same
+//     soft-max (same code, same order: bit-identical in all members and with the one-CTA path);
+//   * P.V keeps the oracle's chain order per output DIM (32 accumulator lanes t % 32 over all positions, fixed fold,
+//     double-precision leftovers), so it is dealt by dims: member j owns dims 16j..16j+15 and reads the 32-byte
+//     pieces of all V rows -- contiguous in the second V layout StackW::vslice that the cache writer keeps.
+// Per member and layer that is n_kv x (256/8 + 32) bytes through the ring instead of n_kv x 512.
+__device__ __forceinline__ bool wide_pass(const DevModel & m, const StackW & W, int f32attn, int width, int pos) {
+    return W.vslice != nullptr && m.wide_min > 0 && !f32attn && width == 0 && pos + 1 > m.wide_min &&
+           (int) gridDim.x >= NH * WIDE_G;
+}
+// K rows of member j: the history rows 0..pos-1 dealt in 8-row ring slots
+__device__ __forceinline__ void wide_k_range(int pos, int j, int & r0, int & r1) {
+    const int S = (pos + 7) >> 3;
+    r0 = min(pos, ((S * j) / WIDE_G) * 8);
+    r1 = min(pos, ((S * (j + 1)) / WIDE_G) * 8);
+}
+// address of byte `off` of a slice that starts at ring slot s0
+template <class SM>
+__device__ __forceinline__ const unsigned char * slice_byte(const SM & s, int s0, int off) {
+    int slot = s0 + (off >> 11);
+    if (slot >= SM::NSLOTS) slot -= SM::NSLOTS;
+    return s.ring + (size_t) slot * SLOT_B + (off & (SLOT_B - 1));
+}
+
+template <class SM>
+__device__ __forceinline__ void attention_wide(const DevModel & m, const StackW & W, int l, int pos,
+                                            const AttnRegs & ar, unsigned ep_in, unsigned ep_out, SM & s, Ring & rg, Watch & wd_) {
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int h = (int) blockIdx.x % NH, j = (int) blockIdx.x / NH;
+    const int g = h >> 1;
+    const bool leader = j == 0, writer = leader && (h & 1) == 0;
+    const int n_kv = pos + 1;
+    const float kq_scale = 1.0f / sqrtf((float) HD);
+    const size_t kv_head_base = ((size_t) (l * NKV + g) * W.n_ctx) * HD;
+    Pkt * att = m.x_att + h * HD;
+    Pkt * scp = m.x_sc + (size_t) h * ATT_MAX_KV;
+    const int np = n_kv & ~31;                               // positions in the 32-lane part of the P.V dot
+    int kr0, kr1;
+    wide_k_range(pos, j, kr0, kr1);
+    const int nck = (kr1 - kr0 + KV_CH - 1) / KV_CH;         // K slices of this member
+    const int nvs = (pos + VS_CH - 1) / VS_CH;               // V slices (all positions, this member's dims)
+
+    PROF(50);
+    const int s0_first = nck > 0 ? ring_acquire(m, s, rg, wd_) : 0;
+    // ---- prologue: q (every member), k (leader), v (every member: the new token is a step of the P.V chains)
+    if (warp < 3 && (warp != 1 || leader)) {
+        const Pkt * src = m.x_qkv + (warp == 0 ? h * HD : warp == 1 ? NH * HD + g * HD : (NH + NKV) * HD + g * HD);
+        float v[4];
+        pk_poll_n<4>(m, src + lane, 32, 4, ep_in, v, wd_);
+        if (warp == 0) {
+            head_norm_rope(v, ar.gn, ar.rp, m.eps);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) s.qr[lane + 32 * i] = r16(v[i]);
+        } else if (warp == 1) {
+            head_norm_rope(v, ar.gn, ar.rp, m.eps);
+            __half hv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { hv[i] = __float2half_rn(v[i]); s.knew_h[lane + 32 * i] = hv[i]; }
+            if (writer) {
+                uint2 pk;
+                pk.x = (unsigned) __half_as_ushort(hv[0]) | ((unsigned) __half_as_ushort(hv[1]) << 16);
+                pk.y = (unsigned) __half_as_ushort(hv[2]) | ((unsigned) __half_as_ushort(hv[3]) << 16);
+                *reinterpret_cast<uint2 *>(W.kcache + kv_head_base + (size_t) pos * HD + lane * 4) = pk;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int d = lane + 32 * i;
+                const __half hv = __float2half_rn(v[i]);
+                s.vnew_h[d] = hv;
+                if (writer) {
+                    W.vcache[kv_head_base + (size_t) pos * HD + d] = hv;
+                    W.vslice[(((size_t) (l * NKV + g) * WIDE_G + (d >> 4)) * W.n_ctx + pos) * VS_D + (d & 15)] = hv;
+                }
+            }
+        }
+    }
+    PROF(51);
+    cbar();
+    PROF(52);
+
+    // ---- scores of this member's K rows -> packets (K rows are chain-major: one 8-byte load per lane and row)
+    {
+        float q[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) q[i] = s.qr[lane + 32 * i];
+        if (leader && warp == NCW - 1) {                     // the new token's own score (+ the pad of an odd row)
+            float a = __fmaf_rn(__half2float(s.knew_h[lane]), q[0], 0.0f);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 32]), q[1], a);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 64]), q[2], a);
+            a = __fmaf_rn(__half2float(s.knew_h[lane + 96]), q[3], a);
+            const float sv = __fmul_rn(reduce32_lanes(a), kq_scale);
+            if (lane == 0) pk_store(scp + pos, sv, ep_in);
+            if (lane == 1 && (n_kv & 1)) pk_store(scp + n_kv, 0.0f, ep_in);
+        }
+        for (int c = 0; c < nck; ++c) {
+            const int s0 = c == 0 ? s0_first : ring_acquire(m, s, rg, wd_);
+            PROF(59);
+            const int rows = min(KV_CH, kr1 - kr0 - c * KV_CH);
+            for (int r0 = warp * 4; r0 < rows; r0 += NCW * 4) {
+                float a[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int r = min(r0 + i, rows - 1);
+                    const uint2 kk = *reinterpret_cast<const uint2 *>(kv_row(s, s0, r) + lane * 8);
+                    const float2 f01 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.x));
+                    const float2 f23 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.y));
+                    a[i] = __fmaf_rn(f01.x, q[0], 0.0f);
+                    a[i] = __fmaf_rn(f01.y, q[1], a[i]); a[i] = __fmaf_rn(f23.x, q[2], a[i]); a[i] = __fmaf_rn(f23.y, q[3], a[i]);
+                }
+                int idx;
+                const float sv = __fmul_rn(reduce32_transposed<4>(a, lane, idx), kq_scale);
+                if ((lane & 7) == 0 && r0 + idx < rows) pk_store(scp + kr0 + c * KV_CH + r0 + idx, sv, ep_in);
+            }
+            PROF(72);
+            cbar();
+            ring_release(s, rg, (rows + 7) >> 3);
+            PROF(73);
+        }
+    }
+    // ---- the whole row from all members
+    float mx = -CUDART_INF_F;
+    {
+        const int n_pairs = (n_kv + 1) >> 1;
+        for (int base = 0; base < n_pairs; base += 4 * NCT) {
+            float2 f[4];
+            const int rem = n_pairs - base - t;
+            const int mine = rem > 0 ? min(4, (rem - 1) / NCT + 1) : 0;
+            pk_poll2_n<4>(m, scp + 2 * (base + t), NCT, mine, ep_in, f, wd_);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (i < mine) {
+                    const int tt = 2 * (base + t + i * NCT);
+                    s.sc[tt] = f[i].x; mx = fmaxf(mx, f[i].x);
+                    if (tt + 1 < n_kv) { s.sc[tt + 1] = f[i].y; mx = fmaxf(mx, f[i].y); }
+                }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if (lane == 0) s.fred[warp] = mx;
+    }
+    cbar();
+    PROF(53);
+    float M = s.fred[0];
+#pragma unroll
+    for (int i = 1; i < NCW; ++i) M = fmaxf(M, s.fred[i]);
+    softmax_long(s, M, n_kv, n_kv >> 3, n_kv >> 3);
+    cbar();
+    PROF(54);
+
+    // ---- P.V for dims 16j..16j+15: warp c (0, 1) owns dims 16j + 8c .. + 7, its lane a is accumulator lane a
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.0f;
+    int s0_last = 0, rows_last = 0;
+    const int n_chain = min(np, pos);                        // history positions of the 32-lane part
+    for (int cs = 0; cs < nvs; ++cs) {
+        const int s0 = ring_acquire(m, s, rg, wd_);
+        const int rows = min(VS_CH, pos - cs * VS_CH);
+        if (warp < 2) {
+#pragma unroll
+            for (int gq = 0; gq < VS_CH / 32; ++gq) {
+                const int r = gq * 32 + lane;
+                const int tt = cs * VS_CH + r;
+                if (tt < n_chain) {
+                    const uint4 vv = *reinterpret_cast<const uint4 *>(slice_byte(s, s0, r * (VS_D * 2) + warp * 16));
+                    const unsigned pu = (unsigned) __half_as_ushort(s.ph[tt]);
+                    const unsigned p2 = pu | (pu << 16);
+                    acc[0] = fhfma_lo(vv.x, p2, acc[0]); acc[1] = fhfma_hi(vv.x, p2, acc[1]);
+                    acc[2] = fhfma_lo(vv.y, p2, acc[2]); acc[3] = fhfma_hi(vv.y, p2, acc[3]);
+                    acc[4] = fhfma_lo(vv.z, p2, acc[4]); acc[5] = fhfma_hi(vv.z, p2, acc[5]);
+                    acc[6] = fhfma_lo(vv.w, p2, acc[6]); acc[7] = fhfma_hi(vv.w, p2, acc[7]);
+                }
+            }
+        }
+        if (cs + 1 < nvs) { cbar(); ring_release(s, rg, (rows * (VS_D * 2) + SLOT_B - 1) / SLOT_B); }
+        else { s0_last = s0; rows_last = rows; }             // the last slice also holds the leftover rows
+    }
+    PROF(55);
+    if (np > 0) {
+        if (warp < 2) {
+            if (pos < np && lane == (pos & 31)) {            // the new token is the last step of its chain
+                const uint4 vv = *reinterpret_cast<const uint4 *>(s.vnew_h + j * VS_D + warp * 8);
+                const unsigned pu = (unsigned) __half_as_ushort(s.ph[pos]);
+                const unsigned p2 = pu | (pu << 16);
+                acc[0] = fhfma_lo(vv.x, p2, acc[0]); acc[1] = fhfma_hi(vv.x, p2, acc[1]);
+                acc[2] = fhfma_lo(vv.y, p2, acc[2]); acc[3] = fhfma_hi(vv.y, p2, acc[3]);
+                acc[4] = fhfma_lo(vv.z, p2, acc[4]); acc[5] = fhfma_hi(vv.z, p2, acc[5]);
+                acc[6] = fhfma_lo(vv.w, p2, acc[6]); acc[7] = fhfma_hi(vv.w, p2, acc[7]);
+            }
+            // chain a of dim d -> s.sc[a * 16 + d] (the score buffer is free again)
+            *reinterpret_cast<float4 *>(s.sc + lane * VS_D + warp * 8)     = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            *reinterpret_cast<float4 *>(s.sc + lane * VS_D + warp * 8 + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+        }
+        cbar();
+    }
+    if (t < VS_D) {
+        double sumf = 0.0;
+        if (np > 0) {
+            float lq[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                lq[i] = __fadd_rn(__fadd_rn(s.sc[i * VS_D + t], s.sc[(16 + i) * VS_D + t]), __fadd_rn(s.sc[(8 + i) * VS_D + t], s.sc[(24 + i) * VS_D + t]));
+            const float t0 = __fadd_rn(lq[0], lq[4]), t1 = __fadd_rn(lq[1], lq[5]), t2 = __fadd_rn(lq[2], lq[6]), t3 = __fadd_rn(lq[3], lq[7]);
+            sumf = (double) __fadd_rn(__fadd_rn(t0, t1), __fadd_rn(t2, t3));
+        }
+        PROF(57);
+        // leftovers np..n_kv-1 in double, in order (vec.cpp:381-384); the history ones sit in the last V slice
+        const int row_base = (nvs - 1) * VS_CH;
+        for (int tt = np; tt < n_kv; tt += 4) {
+            double pd[4];
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) {
+                const int u = tt + jj, uc = min(u, n_kv - 1);
+                const int rr = min(max(uc - row_base, 0), rows_last - 1);
+                const __half * hist = reinterpret_cast<const __half *>(slice_byte(s, s0_last, rr * (VS_D * 2))) + t;
+                const __half * src = uc == pos ? s.vnew_h + j * VS_D + t : hist;
+                const float pr = __fmul_rn(__half2float(*src), __half2float(s.ph[uc]));
+                pd[jj] = u < n_kv ? (double) pr : 0.0;
+            }
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) sumf += pd[jj];
+        }
+        PROF(58);
+        pk_store(att + j * VS_D + t, (float) sumf, ep_out);
+    }
+    PROF(56);
+    if (nvs > 0) { cbar(); ring_release(s, rg, (rows_last * (VS_D * 2) + SLOT_B - 1) / SLOT_B); }
+    if (writer && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }   // publish the appended K/V rows
 }
 
 // --------------------------------------------------------------------------- token selection
@@ -1226,7 +1528,7 @@ __device__ __forceinline__ void prefetch_layer_params(const StackW & W, int l, P
     r.ga = load_gamma(W.attn_norm + (size_t) l * H);
     r.gf = load_gamma(W.ffn_norm + (size_t) l * H);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if ((int) blockIdx.x < NH && warp < 2) {
+    if ((int) blockIdx.x < NH * WIDE_G && warp < 2) {         // attention CTAs (+ the members of the wide path)
         const float * g = (warp == 0 ? W.q_norm : W.k_norm) + (size_t) l * HD;
 #pragma unroll
         for (int i = 0; i < 4; ++i) r.gn[i] = __ldg(g + lane + 32 * i);
@@ -1262,8 +1564,10 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
     const int nH = h1 - h0;
     const bool attn_cta = (int) blockIdx.x < NH;
 
+    const bool wide = wide_pass(m, W, p.f32attn, p.width, pos);
+    const bool wide_cta = wide && (int) blockIdx.x < NH * WIDE_G;
     AttnRegs ar;
-    if (attn_cta && t < 64) {                                // RoPE row of this position (warps 0, 1)
+    if ((attn_cta || wide_cta) && t < 64) {                                // RoPE row of this position (warps 0, 1)
         const float * rope_row = m.rope + (size_t) pos * HD;
         const int lane = t & 31;
         ar.rp[0] = __ldg(rope_row + lane);      ar.rp[1] = __ldg(rope_row + 64 + lane);
@@ -1307,7 +1611,8 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(5);
 
         // ---- phase B: per-head norm + RoPE + KV append + attention (CTA h owns head h)
-        if (attn_cta) attention_head(m, W, l, (int) blockIdx.x, pos, p.f32attn != 0, p.width, ar, e_qkv, e_att, s, rg, w);
+        if (wide_cta) attention_wide(m, W, l, pos, ar, e_qkv, e_att, s, rg, w);
+        else if (attn_cta && !wide) attention_head(m, W, l, (int) blockIdx.x, pos, p.f32attn != 0, p.width, ar, e_qkv, e_att, s, rg, w);
         PROF(6);
 
         // ---- phase C: attn_output mat-vec (input rounded to F16) + residual
@@ -1442,19 +1747,39 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
         if (passes[ip].stack == 0 && passes[ip].pos < 0) ++n_past;
         // attention CTAs: the K then V history of the head (rows 0..pos-1) follows the QKV slice, KV_CH rows per slice
         const bool fast = max(passes[ip].width, pos + 1) <= ATT_FAST_KV;        // same test as attention_head
-        const int n_kvs = (attn_cta && !passes[ip].f32attn && !fast) ? (pos + KV_CH - 1) / KV_CH : 0;
+        const bool wide = wide_pass(m, W, passes[ip].f32attn, passes[ip].width, pos);
+        const int n_kvs = (attn_cta && !passes[ip].f32attn && !fast && !wide) ? (pos + KV_CH - 1) / KV_CH : 0;
+        // wide attention: this member's share of the K rows, then its 16-dim slice of every V row
+        int wk0 = 0, wk1 = 0, n_wk = 0, n_wv = 0;
+        const int wh = (int) blockIdx.x % NH, wj = (int) blockIdx.x / NH;
+        if (wide && (int) blockIdx.x < NH * WIDE_G) {
+            wide_k_range(pos, wj, wk0, wk1);
+            n_wk = (wk1 - wk0 + KV_CH - 1) / KV_CH;
+            n_wv = (pos + VS_CH - 1) / VS_CH;
+        }
+        const int n_mid = 2 * n_kvs + n_wk + n_wv;
         for (int l = 0; l < n_layers && !aborted; ++l) {
-            for (int k = 0; k < 4 + 2 * n_kvs; ++k) {
+            for (int k = 0; k < 4 + n_mid; ++k) {
                 const void * src; int n_slots, slot_bytes = W.wtype == Q3T_TYPE_Q8_0 ? SLOT_Q8 : SLOT_B, tail = SLOT_B;
                 if (k == 0) { src = sl_a(W, l, z); n_slots = nA; }
-                else if (k <= 2 * n_kvs) {
+                else if (k <= n_wk) {
+                    const int c = k - 1;
+                    const int rows = min(KV_CH, wk1 - wk0 - c * KV_CH);
+                    src = W.kcache + ((size_t) (l * NKV + (wh >> 1)) * W.n_ctx + (size_t) (wk0 + c * KV_CH)) * HD;
+                    n_slots = (rows + 7) >> 3; slot_bytes = SLOT_B; tail = (rows - (n_slots - 1) * 8) * HD * 2;
+                } else if (k <= n_wk + n_wv) {
+                    const int cs = k - 1 - n_wk;
+                    const int bytes = min(VS_CH, pos - cs * VS_CH) * (VS_D * 2);
+                    src = W.vslice + (((size_t) (l * NKV + (wh >> 1)) * WIDE_G + wj) * W.n_ctx + (size_t) cs * VS_CH) * VS_D;
+                    n_slots = (bytes + SLOT_B - 1) / SLOT_B; slot_bytes = SLOT_B; tail = bytes - (n_slots - 1) * SLOT_B;
+                } else if (k <= 2 * n_kvs) {
                     const int c = (k - 1) % n_kvs;
                     const int rows = min(KV_CH, pos - c * KV_CH);
                     const __half * base = (k - 1 < n_kvs ? W.kcache : W.vcache)
                                         + ((size_t) (l * NKV + ((int) blockIdx.x >> 1)) * W.n_ctx + (size_t) c * KV_CH) * HD;
                     src = base; n_slots = (rows + 7) >> 3; slot_bytes = SLOT_B; tail = (rows - (n_slots - 1) * 8) * HD * 2;
                 } else {
-                    const int kk = k - 2 * n_kvs;
+                    const int kk = k - n_mid;
                     src = kk == 1 ? sl_o(W, l, z) : kk == 2 ? sl_gu(W, l, z) : sl_d(W, l, z);
                     n_slots = kk == 1 ? nO * 2 : kk == 2 ? nP * 2 : nD * 3;
                 }
