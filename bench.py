@@ -381,7 +381,7 @@ def run_ours(args, rank, world, local_rank):
 def config4_line(args, rank, world, t, d, have_voc, dist, sync_all):
     """BASELINE.json config 4 / the "batch 64" metric point: 64 utterances (8-64 byte texts, seed 4), greedy, `--frames`
     frames each + vocoder, strong scaling: utterance i -> rank i mod N, every rank pushes its share through the batched
-    engine (generate_batch: 8 sequences in lock-step per launch), then decodes each utterance.  Host buffers in and out;
+    engine (generate_batch: 16 sequences per launch, two interleaved lock-step groups of 8), then decodes each utterance.  Host buffers in and out;
     one timed step bracketed by barrier + synchronize, max over ranks.  Returned on rank 0 (None elsewhere)."""
     import importlib
     import torch
@@ -409,7 +409,8 @@ def config4_line(args, rank, world, t, d, have_voc, dist, sync_all):
     sync_all()
     w3 = time.perf_counter()
     nf = sum(len(c) for c in codes)
-    groups = (len(pairs) + 7) // 8
+    wave = max(1, min(16, int(os.environ.get("Q3T_BATCH_WAVE", "16"))))     # sequences per lm_batch_kernel launch (engine.cu)
+    groups = (len(pairs) + wave - 1) // wave
     stats = torch.tensor([w3 - w0, w1 - w0, w2 - w1, tm.prefill_ms * 1e-3, tm.frames_ms * 1e-3], dtype=torch.float64, device="cuda")
     tot = torch.tensor([float(ns), float(nf)], dtype=torch.float64, device="cuda")
     if dist:
@@ -421,21 +422,22 @@ def config4_line(args, rank, world, t, d, have_voc, dist, sync_all):
     ns_all, nf_all = float(tot[0]), float(tot[1])
     per_gpu = (n_utt + world - 1) // world
     # bytes one batched frame launch streams: the frame's weights once for all sequences + every sequence's KV history
-    frame_bytes = CODEPRED_FRAME_BYTES[args.wtype] + TALKER_STEP_BYTES[args.wtype] + 8 * KV_BYTES_PER_POS * (10 + args.frames / 2.0 + 1)
+    per_launch = min(wave, max(len(pairs), 1))
+    frame_bytes = CODEPRED_FRAME_BYTES[args.wtype] + TALKER_STEP_BYTES[args.wtype] + per_launch * KV_BYTES_PER_POS * (10 + args.frames / 2.0 + 1)
     ms_frame = frames_s * 1e3 / max(groups * args.frames, 1)
     peak, _ = measured_peaks()
-    return {"utterances": n_utt, "frames_each": args.frames, "n_gpus": world, "utterances_per_gpu": per_gpu, "sequences_per_launch": 8,
+    return {"utterances": n_utt, "frames_each": args.frames, "n_gpus": world, "utterances_per_gpu": per_gpu, "sequences_per_launch": per_launch,
             "value": ns_all / 24000.0 / step_s, "unit": UNIT, "scaling": "strong", "ms_per_step": step_s * 1e3,
             "phases_s_max_over_ranks": {"prompt_prefill": prefill_s, "frames": frames_s, "generate_wall": gen_s, "vocoder": voc_s},
             "ms_per_batched_frame": ms_frame, "codes_only_audio_s_per_s": nf_all / FRAME_RATE / gen_s,
-            "roofline": {"kernel": "lm_batch_kernel<8> (one launch = one frame of 8 sequences)", "bound": "hbm",
+            "roofline": {"kernel": f"lm_batch_kernel<8> (one launch = one frame of {per_launch} sequences: two interleaved lock-step groups of <= 8)", "bound": "hbm",
                          "algorithmic_bytes_per_launch": int(frame_bytes), "achieved": frame_bytes / (ms_frame * 1e-3) / 1e9,
                          "peak": peak, "unit": "GB/s", "frac": frame_bytes / (ms_frame * 1e-3) / 1e9 / peak,
-                         "note": "weights are read once per launch for 8 sequences, so HBM is not the binding resource here: the launch is "
-                                 "bound by the FMA pipe (8 x the batch-1 FMAs) and the L2-bandwidth-bound packet exchanges (DESIGN.md 4.1b)"},
-            "limiter": (f"{per_gpu} utterances per GPU = {(per_gpu + 7) // 8} lock-step group(s) of <= 8: frames of a group cost ~fixed latency + "
-                        f"0.145 ms per sequence, prompts/prefills ({prefill_s:.2f} s) and vocoder decodes ({voc_s:.2f} s) run one utterance at a "
-                        f"time and do not shrink below one group's share"),
+                         "note": "weights are read once per launch for all its sequences, so HBM is not the binding resource here: the launch is "
+                                 "bound by the FMA pipe (16 x the batch-1 FMAs) and by the SM's ingest of the activation packets (DESIGN.md 4.1b)"},
+            "limiter": (f"{per_gpu} utterances per GPU = {groups} launch wave(s) of <= {wave} sequences: a batched frame costs ~3.4 ms for 8 and "
+                        f"~5.8 ms for 16 sequences, prompts/prefills ({prefill_s:.2f} s) and vocoder decodes ({voc_s:.2f} s) run one utterance at a "
+                        f"time and do not shrink below one wave's share"),
             "workload": "config 4: 64 utterances (8-64 byte texts, seed 4), greedy, host buffers in/out, utterance i -> rank i mod N"}
 
 
@@ -491,7 +493,7 @@ def run_sharded_workload(args, rank, world, local_rank, t, d, have_voc, dist, sy
             "warmup": 1, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f16", "data": "synthetic (seeded random-init GGUF of the real 0.6B shapes)",
             "config": {"workload": f"config 4: {args.utterances} utterances (8-64 byte texts, seed 4), greedy, {args.frames} frames each + vocoder, "
-                                   f"utterance i -> rank i mod {world}, " + ("8 sequences in lock-step per kernel launch on each GPU (lm_batch_kernel)" if batched else "one utterance at a time per GPU (batch-1 engine)"),
+                                   f"utterance i -> rank i mod {world}, " + ("16 sequences per kernel launch on each GPU (lm_batch_kernel, two interleaved lock-step groups of 8)" if batched else "one utterance at a time per GPU (batch-1 engine)"),
                        "utterances": args.utterances, "frames": args.frames, "parallelism": f"request-parallel x{world} (no collective)",
                        "l2": "weights streamed per frame (3.3 GB) exceed the 126 MB L2; no explicit flush"},
             "e2e": {"value": audio_s / step_s, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},

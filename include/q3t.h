@@ -176,12 +176,20 @@ Q3T_API int  q3t_stream_next(q3t_ctx * ctx, int32_t max_frames, int32_t * codes_
 
 /* Batched generate (extension; SURVEY.md §8b "batched variants take n_seq + per-seq arrays"): n_seq
  * independent utterances, greedy, same semantics per utterance as q3t_generate with temperature 0
- * (src/tts_transformer.cpp:2577-2851).  Sequences advance in lock-step, up to 8 per kernel launch;
+ * (src/tts_transformer.cpp:2577-2851).  Up to 16 sequences per kernel launch (two interleaved lock-step groups of 8);
  * codes_out[i] int32[max_len*n_codebooks], n_frames_out[i] = frames of utterance i.
  * speaker_embd may be null (no speaker for any utterance) or hold per-utterance pointers (null entries allowed). */
 Q3T_API int  q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * const * text_tokens, const int32_t * n_tokens,
                                 const float * const * speaker_embd, int32_t max_len, int32_t language_id,
                                 float repetition_penalty, int32_t * const * codes_out, int32_t * n_frames_out);
+
+/* The same with the sampled selection of q3t_generate (temperature > 0: top-k threshold with ties, double-precision
+ * normalisation, src/tts_transformer.cpp:2349-2387, :2664-2722): utterance i draws from the stream seeded `seed + i`,
+ * i.e. its codes equal what q3t_generate returns for it with that seed.  temperature <= 0 = q3t_generate_batch. */
+Q3T_API int  q3t_generate_batch_sampled(q3t_ctx * ctx, int32_t n_seq, const int32_t * const * text_tokens, const int32_t * n_tokens,
+                                        const float * const * speaker_embd, int32_t max_len, int32_t language_id,
+                                        float repetition_penalty, float temperature, int32_t top_k, uint64_t seed,
+                                        int32_t * const * codes_out, int32_t * n_frames_out);
 
 /* AudioTokenizerDecoder::decode (src/audio_tokenizer_decoder.cpp:804-879):
  * codes int32[n_frames*16] frame-major -> samples f32; returns sample count
@@ -269,6 +277,10 @@ Q3T_API int  q3t_tts_generate_batch(q3t_tts * t, int32_t n, const int32_t * cons
                                     const float * const * speaker_embd, int32_t max_len,
                                     int32_t * const * codes_out, int32_t * n_frames_out,
                                     int32_t language_id, float repetition_penalty);   /* extension: batched greedy generate */
+Q3T_API int  q3t_tts_generate_batch_sampled(q3t_tts * t, int32_t n, const int32_t * const * text_tokens, const int32_t * n_tokens,
+                                            const float * const * speaker_embd, int32_t max_len,
+                                            int32_t * const * codes_out, int32_t * n_frames_out, int32_t language_id,
+                                            float repetition_penalty, float temperature, int32_t top_k);   /* extension: the same, sampled (utterance i: set_seed's seed + i) */
 Q3T_API void q3t_tts_set_seed(q3t_tts * t, uint64_t seed);   /* extension: the reference has no seed API */
 Q3T_API int  q3t_tts_get_config(q3t_tts * t, q3t_tts_config * out);
 Q3T_API const char * q3t_tts_get_error(q3t_tts * t);

@@ -1082,7 +1082,7 @@ extern "C" int q3t_speaker_encode(q3t_ctx * ctx, const float * samples, int32_t 
 }
 
 // ------------------------------------------------------------------------------ batched generate
-// n_seq independent utterances, greedy, in waves of Q3T_MAX_BATCH sequences that advance in lock-step
+// n_seq independent utterances, greedy, in waves of Q3T_MAX_BATCH sequences (two interleaved lock-step groups of <= 8)
 // through lm_batch_kernel (lm_batch.inc).  Each sequence gets its own packet block, KV caches, state,
 // repetition set, trailing rows and code buffer; the prompt and the prefill of a sequence run through
 // the batch-1 path into those buffers (once per utterance, ~4 ms), then the frames are batched.
@@ -1118,10 +1118,17 @@ static int rope_table(q3t_ctx * ctx, int n_rope, float ** out_dev) {
 extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * const * text_tokens, const int32_t * n_tokens,
                                   const float * const * speaker_embd, int32_t max_len, int32_t language_id,
                                   float repetition_penalty, int32_t * const * codes_out, int32_t * n_frames_out) {
+    return q3t_generate_batch_sampled(ctx, n_seq, text_tokens, n_tokens, speaker_embd, max_len, language_id, repetition_penalty,
+                                      0.0f, 0, 0, codes_out, n_frames_out);
+}
+
+extern "C" int q3t_generate_batch_sampled(q3t_ctx * ctx, int32_t n_seq, const int32_t * const * text_tokens, const int32_t * n_tokens,
+                                          const float * const * speaker_embd, int32_t max_len, int32_t language_id,
+                                          float repetition_penalty, float temperature, int32_t top_k, uint64_t seed,
+                                          int32_t * const * codes_out, int32_t * n_frames_out) {
     if (!ctx) return Q3T_ERR_ARG;
     if (!ctx->tts_ready) return set_err(ctx, Q3T_ERR_STATE, "Model not loaded");
     if (n_seq <= 0 || !text_tokens || !n_tokens || !codes_out || !n_frames_out) return set_err(ctx, Q3T_ERR_ARG, "null argument");
-    if (ctx->hm.talker.wtype != Q3T_TYPE_F16) return set_err(ctx, Q3T_ERR_STATE, "batched generation is wired up for F16 layer weights only");
     for (int i = 0; i < n_seq; ++i) n_frames_out[i] = 0;
     if (max_len <= 0) return Q3T_OK;
     cudaSetDevice(ctx->device);
@@ -1156,8 +1163,11 @@ extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * 
         return code;
     };
 
-    for (int w0 = 0; w0 < n_seq && !rc; w0 += Q3T_MAX_BATCH) {
-        const int nb = std::min(Q3T_MAX_BATCH, n_seq - w0);
+    // sequences per launch: up to 8 run as one lock-step group, up to 16 as two interleaved groups (Q3T_BATCH_WAVE: tuning knob)
+    int wave = Q3T_MAX_BATCH;
+    if (const char * e = getenv("Q3T_BATCH_WAVE")) wave = std::max(1, std::min(Q3T_MAX_BATCH, atoi(e)));
+    for (int w0 = 0; w0 < n_seq && !rc; w0 += wave) {
+        const int nb = std::min(wave, n_seq - w0);
         cudaEventRecord(ctx->ev[0], ctx->stream);
         auto t_w = now();
         for (int q = 0; q < nb && !rc; ++q) {
@@ -1194,7 +1204,9 @@ extern "C" int q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * 
             m.rope = rope; m.n_rope_pos = std::max(n_ctx, 16);
             GenState st = default_state(ctx);
             st.max_len = max_len; st.n_past = M; st.trailing_len = TL;
-            st.rep_penalty = repetition_penalty; st.temperature = 0.0f; st.top_k = 0; st.seed = 0;
+            // utterance i draws from its own stream: seed + i (= what q3t_generate produces for it with that seed)
+            st.rep_penalty = repetition_penalty; st.temperature = temperature > 0.0f ? temperature : 0.0f; st.top_k = top_k;
+            st.seed = seed + (uint64_t) i;
             if ((rc = reset_state(ctx, st, true))) break;
             const int saved_nctx = ctx->n_ctx;
             ctx->n_ctx = n_ctx;                                     // run_talker_rows checks the context bound

@@ -122,12 +122,14 @@ struct DevModel {
     GenState * st;
     // developer profiling (q3t_profile_arm): thread 0 of CTA prof_cta appends (clock64 << 8 | tag)
     int poll_d0, poll_d1;            // tuning: cycles before the first poll of a vector / between polls
+    int l2_pin;                      // code-predictor layers whose weight copies carry an L2 evict_last policy (0 = no cache hints)
+    int prod_pace, prod_piece;       // producer pacing: cycles between the pieces of a slice's bulk copy / ring slots per piece (0 = one copy)
     unsigned long long * prof; int prof_cap; int prof_cta; int prof_frame;
     unsigned int * prof_n;
 };
 
 constexpr int LM_THREADS = 384;       // 11 compute warps + 1 producer warp; 168 registers per thread
-constexpr int Q3T_MAX_BATCH = 8;    // sequences per batched frame launch (lm_batch.inc)
+constexpr int Q3T_MAX_BATCH = 16;   // sequences per batched frame launch: two interleaved lock-step groups of <= 8 (lm_batch.inc)
 constexpr int LM_MAXC    = 18;       // max KV chunks per kv-head in the attention phase
 constexpr int LM_MIN_GRID = 140;
 constexpr int LM_ATT_MAX_KV = 4608;  // KV positions the attention phase supports (P kept in shared memory)

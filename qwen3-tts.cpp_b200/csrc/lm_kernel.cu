@@ -74,7 +74,7 @@ struct __align__(128) Smem {
     int    prof_cnt;
     unsigned long long mbar[NMB];  // TMA completion barriers of the slices in flight
     volatile unsigned long long consumed;   // low 32: ring slots released, high 32: slices released
-    volatile unsigned tokens;               // exchanges completed by the compute warps (paces the producer's bursts)
+    volatile unsigned tokens;               // exchanges completed by the compute warps
 };
 
 // ------------------------------------------------------------------------------- phase profiler
@@ -142,14 +142,32 @@ __device__ __forceinline__ float2 pk_poll2(const DevModel & m, const Pkt * p, un
 
 // N packets per thread with every load in flight at once: a thread that polls its packets one after
 // the other pays one L2 round trip per packet even when all of them have already arrived.
-template <int N>
+// OPT: optimistic first round -- plain loads and ONE accumulated epoch test (~3 instructions per packet instead of ~10
+// for the predicated re-poll loop).  It pays where the packets have normally landed before the poll starts (the batched
+// kernel, whose groups hide each other's exchanges: 2 % per frame); in the batch-1 kernel, which arrives at every poll
+// early, the wasted round made the frame 6 % slower, so it stays off there.
+template <int N, bool OPT = false>
 __device__ __forceinline__ void pk_poll_n(const DevModel & m, const Pkt * p, int stride, int n_valid, unsigned ep,
                                           float (&v)[N], Watch & w) {
     unsigned long long u[N];
-    unsigned pending = n_valid >= N ? (1u << N) - 1u : (1u << n_valid) - 1u;
+    unsigned pending = n_valid >= N ? (N >= 32 ? 0xffffffffu : (1u << (N & 31)) - 1u) : (1u << n_valid) - 1u;
     unsigned spins = 0;
+    if (OPT && n_valid >= N) {
 #pragma unroll
-    for (int j = 0; j < N; ++j) u[j] = 0ull;
+        for (int j = 0; j < N; ++j)
+            asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(u[j]) : "l"(p + (size_t) j * stride) : "memory");
+        unsigned bad = 0u;
+#pragma unroll
+        for (int j = 0; j < N; ++j) bad |= (unsigned) (u[j] >> 32) ^ ep;
+        if (bad == 0u) pending = 0u;
+        else {
+#pragma unroll
+            for (int j = 0; j < N; ++j) if ((unsigned) (u[j] >> 32) == ep) pending &= ~(1u << j);
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < N; ++j) u[j] = 0ull;
+    }
     while (pending) {
 #pragma unroll
         for (int j = 0; j < N; ++j)
@@ -207,9 +225,15 @@ __device__ __forceinline__ void mbar_wait(unsigned long long * bar, uint32_t par
         :: "r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 // TMA bulk copy global -> shared::cta, completion signalled on an mbarrier (bytes multiple of 16)
-__device__ __forceinline__ void tma_load_1d(void * dst_smem, const void * src_gmem, uint32_t bytes, unsigned long long * bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 :: "r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+// pol: L2 cache policy of the copy (createpolicy), 0 = none
+__device__ __forceinline__ void tma_load_1d(void * dst_smem, const void * src_gmem, uint32_t bytes, unsigned long long * bar,
+                                            unsigned long long pol = 0ull) {
+    if (pol)
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                     :: "r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+    else
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     :: "r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
 __device__ __forceinline__ void cta_rows(int n_rows, int & r0, int & r1) {
@@ -267,7 +291,8 @@ __device__ __forceinline__ void ring_release(SM & s, Ring & rg, int n_slots) {
 // producer: one slice = `n_slots` ring slots filled from `src` (contiguous in HBM); <= 2 bulk copies
 template <class SM>
 __device__ __forceinline__ void produce_slice(SM & s, unsigned & p_slot, unsigned & p_idx, const void * src, int n_slots,
-                                              int slot_bytes = SLOT_B, int tail_bytes = SLOT_B) {
+                                              int slot_bytes = SLOT_B, int tail_bytes = SLOT_B, int pace = 0, int piece_slots = 4,
+                                              unsigned long long pol = 0ull) {
     if (n_slots <= 0) return;
     // wait for ring space and for the mbarrier of slice (p_idx - NMB) to be drained by the consumers
     while (true) {
@@ -285,14 +310,29 @@ __device__ __forceinline__ void produce_slice(SM & s, unsigned & p_slot, unsigne
         const uint32_t total = (uint32_t) (n_slots - 1) * SLOT_B + (uint32_t) tail_bytes;
         const uint32_t first = min(total, (uint32_t) n0 * SLOT_B);
         mbar_expect_tx(bar, total);
-        tma_load_1d(s.ring + (size_t) w0 * SLOT_B, src, first, bar);
-        if (total > first) tma_load_1d(s.ring, (const unsigned char *) src + first, total - first, bar);
+        if (pace > 0) {
+            // paced: pieces of `piece_slots` ring slots `pace` cycles apart.  A slice is requested the moment its ring space is
+            // released, i.e. exactly when the phase's packet exchange starts; as ONE bulk copy (up to 84 KB) from each of 148
+            // SMs that is an 8-12 MB burst into HBM / L2 during the latency-critical store -> poll round trip.  8 KB pieces 150
+            // cycles apart: frame 1.614 -> 1.486 ms, talker step 437 -> 406 us on one box (sweep in profiles/r02b_pacing_sweep.txt)
+            const uint32_t PIECE = (uint32_t) piece_slots * SLOT_B;
+            for (uint32_t off = 0; off < total; off += PIECE) {
+                const uint32_t n = min(PIECE, total - off);
+                const uint32_t in_first = off < first ? min(n, first - off) : 0u;
+                if (in_first) tma_load_1d(s.ring + (size_t) w0 * SLOT_B + off, (const unsigned char *) src + off, in_first, bar, pol);
+                if (n > in_first) tma_load_1d(s.ring + (off + in_first - first), (const unsigned char *) src + off + in_first, n - in_first, bar, pol);
+                if (off + PIECE < total) spin_cycles(pace);
+            }
+        } else {
+            tma_load_1d(s.ring + (size_t) w0 * SLOT_B, src, first, bar, pol);
+            if (total > first) tma_load_1d(s.ring, (const unsigned char *) src + first, total - first, bar, pol);
+        }
     } else {
         mbar_expect_tx(bar, (uint32_t) n_slots * (uint32_t) slot_bytes);
         // compact records in HBM (pitch slot_bytes) land at the start of 2 KB ring slots: one copy per slot
         for (int i = 0; i < n_slots; ++i) {
             int slot = w0 + i; if (slot >= SM::NSLOTS) slot -= SM::NSLOTS;
-            tma_load_1d(s.ring + (size_t) slot * SLOT_B, (const unsigned char *) src + (size_t) i * slot_bytes, (uint32_t) slot_bytes, bar);
+            tma_load_1d(s.ring + (size_t) slot * SLOT_B, (const unsigned char *) src + (size_t) i * slot_bytes, (uint32_t) slot_bytes, bar, pol);
         }
     }
     p_slot += (unsigned) n_slots;
@@ -760,6 +800,15 @@ __device__ __forceinline__ const unsigned char * kv_row(const SM & s, int s0, in
     return s.ring + (size_t) slot * SLOT_B + (r & 7) * (HD * 2);
 }
 
+// The K/V rows a layer appends (plain stores by warps 1 and 2 of the even head's CTA) are read by OTHER CTAs -- the odd
+// head of the pair, the members of the wide path -- from the next pass on, through L2 (ld.cg) or the TMA unit (async
+// proxy): they are published right after the attention output has left, i.e. before this CTA's next packets, which every
+// reader polls before it touches the history.  (Publishing once per pass instead was measured: no difference.)
+__device__ __forceinline__ void publish_kv(bool writer_cta) {
+    const int warp = threadIdx.x >> 5;
+    if (writer_cta && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }
+}
+
 template <class SM>
 __device__ void attention_head(const DevModel & m, const StackW & W, int l, int h, int pos, bool f32attn, int width,
                                const AttnRegs & ar, unsigned ep_in, unsigned ep_out, SM & s, Ring & rg, Watch & wd_) {
@@ -886,10 +935,7 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
 #pragma unroll
             for (int i = 0; i < 4; ++i) pk_store(att + lane + 32 * i, o[i], ep_out);
         }
-        // the K/V rows appended above are read by other CTAs one pass later: publish them before this
-        // CTA's next packets (off the critical path: after the attention output has left)
-        if (writer && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }
-        return;
+        return;                                              // (the appended K/V rows are published once per pass: publish_kv)
     }
 
     if (fast) {
@@ -945,7 +991,6 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
             pk_store(att + d, (float) sumf, ep_out);
         }
         PROF(56);
-        if (writer && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }
         return;
     }
 
@@ -1112,7 +1157,6 @@ __device__ void attention_head(const DevModel & m, const StackW & W, int l, int 
     }
     PROF(56);
     if (nck > 0) { cbar(); ring_release(s, rg, (rows_last + 7) >> 3); }
-    if (writer && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }   // publish the appended K/V rows (see above)
 }
 
 // --------------------------------------------------------------------------- wide attention (long rows)
@@ -1348,7 +1392,6 @@ __device__ __forceinline__ void attention_wide(const DevModel & m, const StackW 
     }
     PROF(56);
     if (nvs > 0) { cbar(); ring_release(s, rg, (rows_last * (VS_D * 2) + SLOT_B - 1) / SLOT_B); }
-    if (writer && (warp == 1 || warp == 2)) { asm volatile("fence.proxy.async.global;" ::: "memory"); __threadfence(); }   // publish the appended K/V rows
 }
 
 // --------------------------------------------------------------------------- token selection
@@ -1404,7 +1447,10 @@ __device__ __forceinline__ double u01(unsigned long long seed, unsigned long lon
 }
 
 // temperature -> top-k threshold (ties kept, `<` test) -> softmax (double sum) -> inverse CDF draw
-__device__ __noinline__ int select_sample(const DevModel & m, Smem & s, unsigned ep, Watch & w, int vocab, bool process, int suppress_start,
+// scratch of the sampler in either kernel's shared memory: 256 histogram bins + 2 control words
+__device__ __forceinline__ int * sample_hist(Smem & s) { return reinterpret_cast<int *>(s.vt); }
+template <class SM>
+__device__ __noinline__ int select_sample(const DevModel & m, SM & s, unsigned ep, Watch & w, int vocab, bool process, int suppress_start,
                              int eos_id, float rep_penalty, float temperature, int top_k,
                              unsigned long long seed, unsigned long long draw) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
@@ -1419,7 +1465,7 @@ __device__ __noinline__ int select_sample(const DevModel & m, Smem & s, unsigned
         const int idx = t * PER + i;
         l[i] = idx < vocab ? proc_logit(m, l[i], idx, process, suppress_start, eos_id, rep_penalty) / temperature : -CUDART_INF_F;
     }
-    int * hist = reinterpret_cast<int *>(s.vt);              // 256 bins + 2 control words
+    int * hist = sample_hist(s);
     if (top_k > 0 && top_k < vocab) {
         unsigned int prefix = 0, mask = 0;
         int k_rem = top_k;
@@ -1613,6 +1659,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         // ---- phase B: per-head norm + RoPE + KV append + attention (CTA h owns head h)
         if (wide_cta) attention_wide(m, W, l, pos, ar, e_qkv, e_att, s, rg, w);
         else if (attn_cta && !wide) attention_head(m, W, l, (int) blockIdx.x, pos, p.f32attn != 0, p.width, ar, e_qkv, e_att, s, rg, w);
+        publish_kv(attn_cta && ((int) blockIdx.x & 1) == 0);
         PROF(6);
 
         // ---- phase C: attn_output mat-vec (input rounded to F16) + residual
@@ -1674,7 +1721,6 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(16);
         ep += 5;
     }
-
     if (!head) return;
     // ---- head: final RMSNorm (= hidden_states) + vocabulary mat-vec + per-CTA arg-max candidate
     const unsigned e_head = ep + 1;
@@ -1731,6 +1777,14 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
     unsigned pspins = 0;
     int n_past = n_past0;
     const bool attn_cta = (int) blockIdx.x < NH;
+    // L2 residency (DevModel::l2_pin > 0): the first l2_pin layers of the code predictor are re-read by each of its 16 passes
+    // per frame -- their copies ask L2 to keep the lines (evict_last); everything that is read once per frame (talker layers,
+    // the other code-predictor layers, the heads) is marked evict_first so that it does not push them out
+    unsigned long long pol_first = 0ull, pol_last = 0ull;
+    if (m.l2_pin > 0) {
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_first));
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_last));
+    }
     for (int ip = 0; ip < n_passes && !aborted; ++ip) {
         int go = *s_go;
         while (go < 0 && ip > 0) {                                    // pass 0 is produced optimistically
@@ -1761,23 +1815,24 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
         for (int l = 0; l < n_layers && !aborted; ++l) {
             for (int k = 0; k < 4 + n_mid; ++k) {
                 const void * src; int n_slots, slot_bytes = W.wtype == Q3T_TYPE_Q8_0 ? SLOT_Q8 : SLOT_B, tail = SLOT_B;
+                unsigned long long pol = (passes[ip].stack == 1 && l < m.l2_pin) ? pol_last : pol_first;
                 if (k == 0) { src = sl_a(W, l, z); n_slots = nA; }
                 else if (k <= n_wk) {
                     const int c = k - 1;
                     const int rows = min(KV_CH, wk1 - wk0 - c * KV_CH);
                     src = W.kcache + ((size_t) (l * NKV + (wh >> 1)) * W.n_ctx + (size_t) (wk0 + c * KV_CH)) * HD;
-                    n_slots = (rows + 7) >> 3; slot_bytes = SLOT_B; tail = (rows - (n_slots - 1) * 8) * HD * 2;
+                    n_slots = (rows + 7) >> 3; slot_bytes = SLOT_B; tail = (rows - (n_slots - 1) * 8) * HD * 2; pol = 0ull;
                 } else if (k <= n_wk + n_wv) {
                     const int cs = k - 1 - n_wk;
                     const int bytes = min(VS_CH, pos - cs * VS_CH) * (VS_D * 2);
                     src = W.vslice + (((size_t) (l * NKV + (wh >> 1)) * WIDE_G + wj) * W.n_ctx + (size_t) cs * VS_CH) * VS_D;
-                    n_slots = (bytes + SLOT_B - 1) / SLOT_B; slot_bytes = SLOT_B; tail = bytes - (n_slots - 1) * SLOT_B;
+                    n_slots = (bytes + SLOT_B - 1) / SLOT_B; slot_bytes = SLOT_B; tail = bytes - (n_slots - 1) * SLOT_B; pol = 0ull;
                 } else if (k <= 2 * n_kvs) {
                     const int c = (k - 1) % n_kvs;
                     const int rows = min(KV_CH, pos - c * KV_CH);
                     const __half * base = (k - 1 < n_kvs ? W.kcache : W.vcache)
                                         + ((size_t) (l * NKV + ((int) blockIdx.x >> 1)) * W.n_ctx + (size_t) c * KV_CH) * HD;
-                    src = base; n_slots = (rows + 7) >> 3; slot_bytes = SLOT_B; tail = (rows - (n_slots - 1) * 8) * HD * 2;
+                    src = base; n_slots = (rows + 7) >> 3; slot_bytes = SLOT_B; tail = (rows - (n_slots - 1) * 8) * HD * 2; pol = 0ull;
                 } else {
                     const int kk = k - n_mid;
                     src = kk == 1 ? sl_o(W, l, z) : kk == 2 ? sl_gu(W, l, z) : sl_d(W, l, z);
@@ -1792,7 +1847,7 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
                     if (((++pspins) & 0xfff) == 0 && clock64() - t_start > 8000000000LL) { m.st->error = 1; aborted = true; break; }   // watchdog
                 }
                 if (aborted) break;
-                produce_slice(s, p_slot, p_idx, src, n_slots, slot_bytes, tail);
+                produce_slice(s, p_slot, p_idx, src, n_slots, slot_bytes, tail, m.prod_pace, m.prod_piece, pol);
             }
         }
         if (hd >= 0 && !aborted) {
@@ -1804,7 +1859,7 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
                 if (*s_go == 0) { aborted = true; break; }
                 if (((++pspins) & 0xfff) == 0 && clock64() - t_start > 8000000000LL) { m.st->error = 1; aborted = true; break; }
             }
-            if (!aborted) produce_slice(s, p_slot, p_idx, hw.w + (size_t) h0 * H, h1 - h0);
+            if (!aborted) produce_slice(s, p_slot, p_idx, hw.w + (size_t) h0 * H, h1 - h0, SLOT_B, SLOT_B, m.prod_pace, m.prod_piece, pol_first);
         }
     }
     if (*s_go == 0 || aborted) {
@@ -2012,6 +2067,20 @@ int lm_max_grid(q3t_ctx * ctx) {
     return ctx->sm_count;          // one persistent CTA per SM
 }
 
+// producer pacing (see produce_slice / producer_loop); environment overrides are tuning knobs
+static void lm_pacing(DevModel & m) {
+    static int pp = -1, pc = -1;
+    if (pp < 0) {
+        const char * e1 = getenv("Q3T_PROD_PACE"), * e2 = getenv("Q3T_PROD_PIECE");
+        pp = e1 ? atoi(e1) : 150; pc = e2 ? atoi(e2) : 4;
+        if (pc < 1) pc = 1;
+    }
+    m.prod_pace = pp; m.prod_piece = pc;
+    static int pin = -1;
+    if (pin < 0) { const char * e = getenv("Q3T_L2_PIN"); pin = e ? atoi(e) : 0; }
+    m.l2_pin = pin;
+}
+
 int lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int frame_mode) {
     if (ctx->grid <= 0) {
         const int g = lm_max_grid(ctx);
@@ -2022,6 +2091,7 @@ int lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int fram
     static int d0 = -1, d1 = -1;
     if (d0 < 0) { const char * e0 = getenv("Q3T_POLL_D0"), * e1 = getenv("Q3T_POLL_D1"); d0 = e0 ? atoi(e0) : 300; d1 = e1 ? atoi(e1) : 0; }
     m.poll_d0 = d0; m.poll_d1 = d1;
+    lm_pacing(m);
     void * args[] = { (void *) &m, (void *) &passes_dev, (void *) &n_passes, (void *) &frame_mode };
     // both stacks of a model share the weight type (the converter quantises them together)
     const bool q8 = m.talker.wtype == Q3T_TYPE_Q8_0;
@@ -2031,18 +2101,18 @@ int lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int fram
     return cuda_check(ctx, e, "lm_kernel launch");
 }
 
-// batched frame launch: nb sequences (views in `seqs`), instantiation = smallest NB >= nb
-template <int NB>
+// batched frame launch: nb sequences (views in `seqs`), instantiation = smallest NB >= group size, F16 or Q8_0 layer weights
+template <int NB, bool Q8>
 static cudaError_t launch_batch_t(q3t_ctx * ctx, const BatchModel & bm, const PassDesc * passes_dev, int n_passes) {
     static bool attr_set_dev[64] = {};                         // per device, see lm_max_grid
     bool & attr_set = attr_set_dev[ctx->device & 63];
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(lm_batch_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(BSmem<NB>));
+        cudaError_t e = cudaFuncSetAttribute(lm_batch_kernel<NB, Q8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(BSmem<NB>));
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
     void * args[] = { (void *) &bm, (void *) &passes_dev, (void *) &n_passes };
-    return cudaLaunchCooperativeKernel((const void *) lm_batch_kernel<NB>, dim3(ctx->grid), dim3(LM_THREADS), args,
+    return cudaLaunchCooperativeKernel((const void *) lm_batch_kernel<NB, Q8>, dim3(ctx->grid), dim3(LM_THREADS), args,
                                        sizeof(BSmem<NB>), ctx->stream);
 }
 
@@ -2053,13 +2123,20 @@ int lm_launch_batch(q3t_ctx * ctx, const DevModel * seqs, int nb, const PassDesc
         if (g < LM_MIN_GRID) return set_err(ctx, Q3T_ERR_CUDA, "device cannot co-schedule the persistent decode kernel (needs >= 140 SMs)");
         ctx->grid = g > 480 ? 480 : g;
     }
-    if (NH * nb > ctx->grid) return set_err(ctx, Q3T_ERR_ARG, "batch needs one CTA per (sequence, head) attention unit");
+    // up to 8 sequences: one lock-step group; more: two groups interleaved phase by phase (lm_batch.inc)
     BatchModel bm;
     bm.nb = nb;
+    bm.ng = nb > 8 ? 2 : 1;
+    bm.gbase[0] = 0; bm.gbase[1] = bm.ng == 2 ? (nb + 1) / 2 : nb; bm.gbase[2] = nb;
+    if (NH * bm.gbase[1] > ctx->grid) return set_err(ctx, Q3T_ERR_ARG, "batch needs one CTA per (sequence, head) attention unit of a group");
     for (int q = 0; q < Q3T_MAX_BATCH; ++q) bm.seq[q] = seqs[q < nb ? q : 0];
-    cudaError_t e = nb <= 2 ? launch_batch_t<2>(ctx, bm, passes_dev, n_passes)
-                  : nb <= 4 ? launch_batch_t<4>(ctx, bm, passes_dev, n_passes)
-                            : launch_batch_t<8>(ctx, bm, passes_dev, n_passes);
+    lm_pacing(bm.seq[0]);
+    // both stacks of a model share the weight type (the converter quantises them together); Q8_0 models run the 8-wide instantiation
+    const bool q8 = seqs[0].talker.wtype == Q3T_TYPE_Q8_0;
+    cudaError_t e = q8      ? launch_batch_t<8, true>(ctx, bm, passes_dev, n_passes)
+                  : nb <= 2 ? launch_batch_t<2, false>(ctx, bm, passes_dev, n_passes)
+                  : nb <= 4 ? launch_batch_t<4, false>(ctx, bm, passes_dev, n_passes)
+                            : launch_batch_t<8, false>(ctx, bm, passes_dev, n_passes);
     ctx->timing.kernel_launches++;
     return cuda_check(ctx, e, "lm_batch_kernel launch");
 }

@@ -45,7 +45,8 @@ bool synthesize_batch(TTSTransformer & tts, AudioTokenizerDecoder & dec, const s
     const auto t0 = clk::now();
     batch_stats st;
     std::vector<std::vector<int32_t>> codes;
-    if (!tts.generate_batch(text_tokens, n_tokens, speaker_embd, p.max_audio_tokens, codes, p.language_id, p.repetition_penalty)) {
+    if (!tts.generate_batch(text_tokens, n_tokens, speaker_embd, p.max_audio_tokens, codes, p.language_id, p.repetition_penalty,
+                            p.temperature, p.top_k)) {
         error = tts.get_error(); return false;
     }
     st.t_generate_ms = ms_since(t0);

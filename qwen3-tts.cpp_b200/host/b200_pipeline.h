@@ -3,7 +3,7 @@
 // whole utterance has been generated; these helpers keep its order of operations (generate -> decode) but
 //   * synthesize_stream: hands chunks of frames to the vocoder as they are generated and reports the time to the first
 //     audible samples (every layer of the vocoder is causal, so the streamed waveform equals the one-shot decode);
-//   * synthesize_batch: pushes N utterances through the batched engine (generate_batch: 8 sequences per launch) and
+//   * synthesize_batch: pushes N utterances through the batched engine (generate_batch: 16 sequences per launch) and
 //     decodes each one, with the per-phase wall times.
 // Extensions: no counterpart in the reference; namespace qwen3_tts::b200.
 #pragma once
@@ -44,7 +44,7 @@ Q3T_API bool synthesize_stream(TTSTransformer & tts, AudioTokenizerDecoder & dec
                                const float * speaker_embd, const synth_params & p, int32_t first_chunk_frames, int32_t chunk_frames,
                                const sample_sink & sink, stream_stats * stats, std::string & error);
 
-// N utterances, greedy (the batched engine has no sampler yet): audio[i] receives utterance i's waveform
+// N utterances (p.temperature <= 0: greedy; else sampled, utterance i from the stream seeded set_seed()'s seed + i): audio[i] receives utterance i's waveform
 Q3T_API bool synthesize_batch(TTSTransformer & tts, AudioTokenizerDecoder & dec, const std::vector<const int32_t *> & text_tokens,
                               const std::vector<int32_t> & n_tokens, const std::vector<const float *> & speaker_embd,
                               const synth_params & p, std::vector<std::vector<float>> & audio, batch_stats * stats, std::string & error);

@@ -113,13 +113,18 @@ Q3T_API int q3t_tts_generate(q3t_tts * t, const int32_t * tokens, int32_t n_toke
 Q3T_API int q3t_tts_generate_batch(q3t_tts * t, int32_t n, const int32_t * const * tokens, const int32_t * n_tokens,
                                    const float * const * spk, int32_t max_len, int32_t * const * codes_out, int32_t * n_frames_out,
                                    int32_t language_id, float rep) {
+    return q3t_tts_generate_batch_sampled(t, n, tokens, n_tokens, spk, max_len, codes_out, n_frames_out, language_id, rep, 0.0f, 0);
+}
+Q3T_API int q3t_tts_generate_batch_sampled(q3t_tts * t, int32_t n, const int32_t * const * tokens, const int32_t * n_tokens,
+                                           const float * const * spk, int32_t max_len, int32_t * const * codes_out, int32_t * n_frames_out,
+                                           int32_t language_id, float rep, float temperature, int32_t top_k) {
     if (!t || n <= 0) return 0;
     std::vector<const int32_t *> tk(tokens, tokens + n);
     std::vector<int32_t> nt(n_tokens, n_tokens + n);
     std::vector<const float *> sp;
     if (spk) sp.assign(spk, spk + n);
     std::vector<std::vector<int32_t>> o;
-    if (!t->t.generate_batch(tk, nt, sp, max_len, o, language_id, rep)) return 0;
+    if (!t->t.generate_batch(tk, nt, sp, max_len, o, language_id, rep, temperature, top_k)) return 0;
     const size_t ncb = (size_t) t->t.get_config().n_codebooks;
     for (int32_t i = 0; i < n; ++i) {
         if (codes_out && codes_out[i] && !o[i].empty()) memcpy(codes_out[i], o[i].data(), o[i].size() * sizeof(int32_t));

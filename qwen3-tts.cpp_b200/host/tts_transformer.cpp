@@ -250,7 +250,8 @@ bool TTSTransformer::generate_next(int32_t max_frames, std::vector<int32_t> & ne
 
 bool TTSTransformer::generate_batch(const std::vector<const int32_t *> & text_tokens, const std::vector<int32_t> & n_tokens,
                                     const std::vector<const float *> & speaker_embd, int32_t max_len,
-                                    std::vector<std::vector<int32_t>> & outputs, int32_t language_id, float repetition_penalty) {
+                                    std::vector<std::vector<int32_t>> & outputs, int32_t language_id, float repetition_penalty,
+                                    float temperature, int32_t top_k) {
     const auto t0 = std::chrono::high_resolution_clock::now();
     if (!loaded_) { error_msg_ = "Model not loaded"; return false; }
     const size_t n = text_tokens.size();
@@ -264,9 +265,9 @@ bool TTSTransformer::generate_batch(const std::vector<const int32_t *> & text_to
     std::vector<int32_t *> outp(n);
     std::vector<int32_t> nf(n, 0);
     for (size_t i = 0; i < n; ++i) { outputs[i].resize((size_t) max_len * config_.n_codebooks); outp[i] = outputs[i].data(); }
-    if (fail(q3t_generate_batch(engine_, (int32_t) n, text_tokens.data(), n_tokens.data(),
-                                speaker_embd.empty() ? nullptr : speaker_embd.data(), max_len, language_id,
-                                repetition_penalty, outp.data(), nf.data()))) {
+    if (fail(q3t_generate_batch_sampled(engine_, (int32_t) n, text_tokens.data(), n_tokens.data(),
+                                        speaker_embd.empty() ? nullptr : speaker_embd.data(), max_len, language_id,
+                                        repetition_penalty, temperature, top_k, seed_, outp.data(), nf.data()))) {
         outputs.assign(n, {});
         return false;
     }

@@ -107,12 +107,13 @@ public:
                             std::vector<float> & output);
 
     // ---- extensions (not in the reference) --------------------------------------------------
-    // n independent utterances, greedy, batched on the device (up to 8 sequences per kernel launch);
-    // outputs[i] receives what generate(..., temperature = 0) returns for utterance i
+    // n independent utterances batched on the device (up to 16 sequences per kernel launch); outputs[i] receives what
+    // generate(..., temperature = 0) returns for utterance i.  temperature > 0: sampled like generate(), utterance i
+    // drawing from the stream seeded set_seed()'s seed + i
     bool generate_batch(const std::vector<const int32_t *> & text_tokens, const std::vector<int32_t> & n_tokens,
                         const std::vector<const float *> & speaker_embd, int32_t max_len,
                         std::vector<std::vector<int32_t>> & outputs,
-                        int32_t language_id = 2050, float repetition_penalty = 1.05f);
+                        int32_t language_id = 2050, float repetition_penalty = 1.05f, float temperature = 0.0f, int32_t top_k = 0);
     // streaming generate: begin = prompt + prefill, next = up to max_frames more frames appended to `new_codes`;
     // the concatenation equals generate() with the same arguments
     bool generate_begin(const int32_t * text_tokens, int32_t n_tokens, const float * speaker_embd, int32_t max_len,

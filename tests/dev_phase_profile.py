@@ -30,7 +30,8 @@ print("frames_ms", t.timing().frames_ms, "ms/frame", t.timing().frames_ms / fram
 names = {1: "layer start", 2: "x polled", 3: "rmsnormA done", 4: "sliceA ready", 5: "gemvA+store", 6: "attention done",
          7: "att polled", 8: "sliceO ready", 9: "gemvC+store", 10: "x1 polled", 11: "rmsnormD done", 12: "sliceGU ready",
          13: "gemvD+store", 14: "m polled", 15: "sliceD ready", 16: "gemvE+store", 20: "head norm done", 21: "head done",
-         50: "att stage0 done", 51: "att qkv in (w0)", 52: "att prologue bar", 53: "att scores done", 54: "att P ready", 55: "att V slices done", 56: "att stored", 57: "att lo begin", 58: "att lo end", 59: "att K slice in", 40: "gemvA warp0", 41: "gemvA cbar", 42: "qkv stored", 30: "pass begin", 31: "x formed", 60: "E poll0", 67: "E acquire", 61: "E comp0", 62: "E poll1", 63: "E comp1", 64: "E poll2", 65: "E comp2", 60: "A acquired", 61: "D acquired", **{80 + k: f"x in ({k} polls)" for k in range(10)}, **{90 + k: f"x1 in ({k} polls)" for k in range(10)}, 70: "norm polled", 71: "norm scale", 72: "att K scored (w0)", 73: "att K released"}
+         **{100 + k: v + " g1" for k, v in {3: "rmsnormA done", 5: "gemvA+store", 7: "att polled", 9: "gemvC+store", 11: "rmsnormD done", 13: "gemvD+store", 15: "E done", 16: "gemvE+store"}.items()},
+         50: "att stage0 done", 51: "att qkv in (w0)", 52: "att prologue bar", 53: "att scores done", 54: "att P ready", 55: "att V slices done", 56: "att stored", 57: "att lo begin", 58: "att lo end", 59: "att K slice in", 40: "gemvA warp0", 41: "gemvA cbar", 42: "qkv stored", 30: "pass begin", 31: "x formed", 60: "E poll0", 67: "E acquire", 61: "E comp0", 62: "E poll1", 63: "E comp1", 64: "E poll2", 65: "E comp2", 60: "A acquired", 61: "D acquired", **{80 + k: f"x in ({k} polls)" for k in range(10)}, **{90 + k: f"x1 in ({k} polls)" for k in range(10)}, 70: "norm polled", 71: "norm scale", 74: "att qkv poll begin", 75: "att qkv polled", 72: "att K scored (w0)", 73: "att K released"}
 per_cta = {}
 for cta in range(148):
     clk, tag = t.profile_read(4096, cta)

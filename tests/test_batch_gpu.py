@@ -31,7 +31,8 @@ def tts(q3t):
     t.close()
 
 
-@pytest.mark.parametrize("n,frames", [(2, 24), (8, 40), (11, 24)])
+# up to 8 sequences run as one lock-step group, 9..16 as two interleaved groups (11 = 6 + 5, 16 = 8 + 8), more in waves of 16
+@pytest.mark.parametrize("n,frames", [(2, 24), (8, 40), (11, 24), (16, 40), (21, 16)])
 def test_batched_codes_equal_single_sequence_codes(tts, n, frames):
     utts = _utterances(n, seed=100 + n)
     got = tts.generate_batch(utts, frames)
@@ -43,6 +44,46 @@ def test_batched_codes_equal_single_sequence_codes(tts, n, frames):
         assert got[i].shape == want.shape, f"utterance {i}"
         neq = np.argwhere(got[i] != want)
         assert len(neq) == 0, f"utterance {i}: first mismatch at frame/codebook {neq[0]}"
+
+
+def test_batched_q8_0_codes_equal_single_sequence_codes(q3t):
+    """Q8_0 layer weights in the batched engine (int8 block dots, activations re-quantised per mat-vec exactly like the
+    batch-1 kernel): 13 utterances = two interleaved groups (7 + 6); codes equal generate() for each alone, which
+    tests/test_parity_gpu.py pins to the live reference for 320 frames."""
+    t = q3t.TTSTransformer()
+    assert t.load_model(models("full", "q8_0")[0]), t.get_error()
+    utts = _utterances(13, seed=813)
+    got = t.generate_batch(utts, 24)
+    assert got is not None, t.get_error()
+    for i, (toks, spk) in enumerate(utts):
+        want = t.generate(toks, spk, 24, temperature=0.0)
+        assert want is not None, t.get_error()
+        assert got[i].shape == want.shape, f"utterance {i}"
+        neq = np.argwhere(got[i] != want)
+        assert len(neq) == 0, f"utterance {i}: first mismatch at frame/codebook {neq[0]}"
+    t.close()
+
+
+def test_batched_sampled_codes_equal_single_sequence_sampled_codes(tts):
+    """Sampled decoding inside the batched engine (temperature 0.9, top-k 50, repetition penalty 1.05 = config 3's
+    settings): utterance i draws from the stream seeded seed + i with the same routine as the batch-1 kernel, so its
+    codes equal the engine's single-sequence run with that seed (whose sampler is pinned against the reference's
+    distribution and its teacher-forced trajectory in tests/test_sampling_gpu.py)."""
+    utts = _utterances(11, seed=311)
+    tts.set_seed(1234)
+    got = tts.generate_batch(utts, 24, temperature=0.9, top_k=50)
+    assert got is not None, tts.get_error()
+    greedy = tts.generate_batch(utts, 24)
+    n_diff = 0
+    for i, (toks, spk) in enumerate(utts):
+        tts.stage_prompt(toks, spk)
+        nf, _ = tts.run_staged(24, repetition_penalty=1.05, temperature=0.9, top_k=50, seed=1234 + i, with_vocoder=False)
+        want = tts.fetch_codes(nf)
+        assert got[i].shape == want.shape, f"utterance {i}"
+        neq = np.argwhere(got[i] != want)
+        assert len(neq) == 0, f"utterance {i}: first mismatch at frame/codebook {neq[0]}"
+        n_diff += int(not np.array_equal(got[i], greedy[i]))
+    assert n_diff >= 10                                          # it really sampled
 
 
 def test_config4_job_64_utterances_320_frames_equals_generate(tts):
@@ -61,16 +102,18 @@ def test_config4_job_64_utterances_320_frames_equals_generate(tts):
         assert len(neq) == 0, f"utterance {i}: first mismatch at frame/codebook {neq[0]}"
 
 
-def test_batched_early_stop_two_waves(q3t):
-    """EOS inside the batched engine: 11 utterances of the EOS-scaled model = one wave of 8 + one of 3
-    re-using the buffers; sequences stop at different frames (finished ones keep flowing with frozen outputs),
-    frame counts and codes equal generate() alone (itself pinned to the reference in test_parity_gpu)."""
+@pytest.mark.parametrize("n_utt", [11, 19])
+def test_batched_early_stop_two_waves(q3t, n_utt):
+    """EOS inside the batched engine: utterances of the EOS-scaled model, 11 = one launch of two interleaved
+    groups (6 + 5), 19 = a wave of 16 (8 + 8) + a wave of 3 re-using the buffers; sequences stop at different frames
+    (finished ones keep flowing with frozen outputs), frame counts and codes equal generate() alone (itself pinned to
+    the reference in test_parity_gpu)."""
     from test_parity_gpu import EOS_LIKE
     from util import HELLO_TINY
     t = q3t.TTSTransformer()
     assert t.load_model(models("tiny", "f16", eos_like=EOS_LIKE)[0]), t.get_error()
     utts = []
-    for i in range(11):
+    for i in range(n_utt):
         rng = np.random.default_rng(100 + i)
         toks = HELLO_TINY.copy(); toks[3:11] = rng.integers(32, 120, size=8)
         utts.append((toks, (rng.standard_normal(1024) * 0.05).astype(np.float32)))

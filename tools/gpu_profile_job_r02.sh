@@ -7,7 +7,8 @@ python bench.py --steps 2 --warmup 3 --wtype q8_0 --temperature 0.9 --top-k 50 -
 python bench.py --steps 1 --warmup 3 --frames 4096 --no-cpu-baseline --no-batch > gpurun_out/bench_r02_long.json 2> gpurun_out/bench_r02_long.err; echo "bench long rc=$?"
 timeout 300 python tests/dev_phase_profile.py 40 > gpurun_out/phase_r02_batch1.txt 2>&1
 Q3T_WTYPE=q8_0 timeout 300 python tests/dev_phase_profile.py 40 > gpurun_out/phase_r02_q8.txt 2>&1
-timeout 300 python tests/dev_phase_profile.py 40 8 > gpurun_out/phase_r02_batch8.txt 2>&1
+Q3T_BATCH_WAVE=8 timeout 300 python tests/dev_phase_profile.py 40 8 > gpurun_out/phase_r02_batch8.txt 2>&1
+timeout 300 python tests/dev_phase_profile.py 40 16 > gpurun_out/phase_r02_batch16.txt 2>&1
 python bench.py --steps 1 --warmup 1 --frames 24 --no-cpu-baseline > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/launches_r02.csv python bench.py --steps 1 --warmup 1 --frames 24 --no-cpu-baseline > gpurun_out/ncu1.log 2>&1
 mkdir -p /tmp/ncu
