@@ -117,12 +117,13 @@ struct DevModel {
     float * logits;                  // [3072]
     unsigned char * seen;            // [3072] repetition-penalty set
     const float * trailing;          // [trailing_len][1024]
+    const float * prefill_x;         // [<=16][1024] prompt rows of this sequence (batched prefill: XM_BUF reads row PassDesc::arg)
     const float * pad_embed;         // [1024]
     int * codes_out;                 // [max_len][16]
     GenState * st;
     // developer profiling (q3t_profile_arm): thread 0 of CTA prof_cta appends (clock64 << 8 | tag)
     int poll_d0, poll_d1;            // tuning: cycles before the first poll of a vector / between polls
-    int l2_pin;                      // code-predictor layers whose weight copies carry an L2 evict_last policy (0 = no cache hints)
+    int l2_pin;                      // code-predictor weight slices (4 per layer) whose copies carry an L2 evict_last policy (0 = no cache hints)
     int prod_pace, prod_piece;       // producer pacing: cycles between the pieces of a slice's bulk copy / ring slots per piece (0 = one copy)
     unsigned long long * prof; int prof_cap; int prof_cta; int prof_frame;
     unsigned int * prof_n;
@@ -195,6 +196,7 @@ struct q3t_ctx {
     q3t_timing timing{};
     int * h_done = nullptr;           // pinned flag pair polled by the generate loop
     void * h_states = nullptr;        // pinned GenState[Q3T_MAX_BATCH] read back by the batched generate loop
+    void * batch_cache = nullptr;     // per-sequence buffers of q3t_generate_batch, kept between calls (engine.cu BatchCache; freed by q3t_unload(1))
     unsigned long long * d_prof = nullptr; unsigned int * d_prof_n = nullptr; int prof_cap = 0;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
 };

@@ -356,6 +356,19 @@ __device__ __forceinline__ const void * sl_d(const StackW & W, int l, const Slic
     return sl_rows(W.wdown, W.wtype, (size_t) l * H + z.d0, 3);
 }
 
+// Q8_0 slices land in the ring exactly as they lie in HBM: records of 1088 B back to back from the slice's first slot --
+// ONE bulk copy per slice (so the paced producer applies; one copy per record made the producer thread the bottleneck) and
+// about half the ring footprint of one record per 2 KB slot.  A record may wrap around the end of the ring: q8_at() is the
+// address of byte `o` (a multiple of 8; 16-byte loads at multiples of 16) of record `i` of the slice that starts at slot s0.
+template <class SM>
+__device__ __forceinline__ const unsigned char * q8_at(const SM & s, int s0, int i, int o) {
+    constexpr unsigned RING = (unsigned) SM::NSLOTS * SLOT_B;
+    unsigned b = (unsigned) s0 * SLOT_B + (unsigned) i * SLOT_Q8 + (unsigned) o;
+    if (b >= RING) b -= RING;
+    return s.ring + b;
+}
+__host__ __device__ __forceinline__ int q8_slots(int n_rec) { return (n_rec * SLOT_Q8 + SLOT_B - 1) / SLOT_B; }   // ring slots of a slice
+
 // ------------------------------------------------------------------------------- ordered GEMV
 // fma.rn.f32.f16 (SASS FHFMA, sm_100+): d = f32(a) * f32(b) + c with a, b F16 and one rounding —
 // exactly ggml's F16C-convert + vfmadd lane step, in one instruction.
@@ -531,14 +544,12 @@ __device__ __forceinline__ void gemv_q8(Smem & s, int s0, int n_rows) {
         float acc = 0.0f;
 #pragma unroll
         for (int ch = 0; ch < SPR; ++ch) {
-            int slot = s0 + r * SPR + ch;
-            slot %= NSLOT;
-            const unsigned char * rec = s.ring + (size_t) slot * SLOT_B;
+            const int rec = r * SPR + ch;
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
-                const uint4  wq = *reinterpret_cast<const uint4 *>(rec + c * 128 + l * 16);
+                const uint4  wq = *reinterpret_cast<const uint4 *>(q8_at(s, s0, rec, c * 128 + l * 16));
                 const uint4  xq = *reinterpret_cast<const uint4 *>(s.xq + ch * 1024 + c * 128 + l * 16);
-                const uint2  ws = *reinterpret_cast<const uint2 *>(rec + 1024 + c * 8);
+                const uint2  ws = *reinterpret_cast<const uint2 *>(q8_at(s, s0, rec, 1024 + c * 8));
                 const float4 xs = *reinterpret_cast<const float4 *>(s.xd + ch * 32 + c * 4);
                 const float2 w01 = __half22float2(*reinterpret_cast<const __half2 *>(&ws.x));
                 const float2 w23 = __half22float2(*reinterpret_cast<const __half2 *>(&ws.y));
@@ -573,22 +584,16 @@ __device__ __forceinline__ void gemv_q8_f32(Smem & s, int s0, int n_rows) {
         uint2 qa[2]; uint4 sa[2];
 #pragma unroll
         for (int a = 0; a < 2; ++a) {
-            int slot = s0 + r * SPR + (a >> 2);
-            slot %= NSLOT;
-            const unsigned char * rec = s.ring + (size_t) slot * SLOT_B;
-            qa[a] = lds_v2(rec + (a & 3) * 256 + lane * 8);
-            sa[a] = lds_v4(rec + 1024 + (a & 3) * 16);
+            qa[a] = lds_v2(q8_at(s, s0, r * SPR + (a >> 2), (a & 3) * 256 + lane * 8));
+            sa[a] = lds_v4(q8_at(s, s0, r * SPR + (a >> 2), 1024 + (a & 3) * 16));
         }
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
             const uint2 q8 = qa[u & 1];
             const uint4 sc = sa[u & 1];
             if (u + 2 < NU) {
-                int slot = s0 + r * SPR + ((u + 2) >> 2);
-                slot %= NSLOT;
-                const unsigned char * rec = s.ring + (size_t) slot * SLOT_B;
-                qa[u & 1] = lds_v2(rec + ((u + 2) & 3) * 256 + lane * 8);
-                sa[u & 1] = lds_v4(rec + 1024 + ((u + 2) & 3) * 16);
+                qa[u & 1] = lds_v2(q8_at(s, s0, r * SPR + ((u + 2) >> 2), ((u + 2) & 3) * 256 + lane * 8));
+                sa[u & 1] = lds_v4(q8_at(s, s0, r * SPR + ((u + 2) >> 2), 1024 + ((u + 2) & 3) * 16));
             }
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
@@ -1473,12 +1478,16 @@ __device__ __noinline__ int select_sample(const DevModel & m, SM & s, unsigned e
             const int shift = 24 - 8 * pass;
             if (t < 256) hist[t] = 0;
             cbar();
+            // warp-aggregated: the keys of a logit vector share their leading digits, so most of a warp's entries fall into
+            // the same few bins -- one atomic per distinct bin and warp instead of one per entry (same-address shared-memory
+            // atomics serialise)
 #pragma unroll
             for (int i = 0; i < PER; ++i) {
-                if (t * PER + i < vocab) {
-                    const unsigned int key = f2key(l[i]);
-                    if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255], 1);
-                }
+                const unsigned int key = f2key(l[i]);
+                const bool act = t * PER + i < vocab && (key & mask) == prefix;
+                const unsigned int bin = (key >> shift) & 255u;
+                const unsigned int peers = __match_any_sync(0xffffffffu, act ? bin : 256u + (unsigned) lane);
+                if (act && lane == __ffs(peers) - 1) atomicAdd(&hist[bin], __popc(peers));
             }
             cbar();
             if (warp == 0) {
@@ -1653,7 +1662,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(41);
         if (t < nA) pk_store(m.x_qkv + z.a0 + t, s.outv[t], e_qkv);
         PROF(42);
-        ring_release(s, rg, nA);
+        ring_release(s, rg, Q8 ? q8_slots(nA) : nA);
         PROF(5);
 
         // ---- phase B: per-head norm + RoPE + KV append + attention (CTA h owns head h)
@@ -1685,7 +1694,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         if (Q8) gemv_q8<2048>(s, s0, nO); else gemv_ring<2048, 1, false>(s, s0, nO);
         cbar();
         if (t < nO) pk_store(m.x_x1 + z.o0 + t, __fadd_rn(s.outv[t], s.xres[z.o0 + t]), e_x1);
-        ring_release(s, rg, nO * 2);
+        ring_release(s, rg, Q8 ? q8_slots(nO * 2) : nO * 2);
         PROF(9);
 
         // ---- phase D: RMSNorm + gate/up mat-vec + SwiGLU
@@ -1704,7 +1713,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
             const float sl = __fdiv_rn(gt, __fadd_rn(1.0f, v_expf(__fsub_rn(0.0f, gt))));   // ggml_v_silu
             pk_store(m.x_m + z.p0 + t, __fmul_rn(sl, up), e_m);
         }
-        ring_release(s, rg, 2 * nP);
+        ring_release(s, rg, Q8 ? q8_slots(2 * nP) : 2 * nP);
         PROF(13);
 
         // ---- phase E: ffn_down on F32 activations (weights exact in F32) + residual
@@ -1717,7 +1726,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         if (Q8) gemv_q8_f32<3072>(s, s0, nD); else gemv_ring<3072, 1, true>(s, s0, nD);
         cbar();
         if (t < nD) pk_store(m.x_x + z.d0 + t, __fadd_rn(s.outv[t], s.xres[z.d0 + t]), e_x);
-        ring_release(s, rg, nD * 3);
+        ring_release(s, rg, Q8 ? q8_slots(nD * 3) : nD * 3);
         PROF(16);
         ep += 5;
     }
@@ -1765,11 +1774,17 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
     PROF(21);
 }
 
+constexpr int PD_CACHE = 20;               // passes of a program kept in shared memory (longer programs read the rest from HBM)
+__device__ __forceinline__ const PassDesc & pass_desc(const PassDesc * __restrict__ passes, const PassDesc * pds, int i) {
+    return i < PD_CACHE ? pds[i] : passes[i];
+}
+
 // ------------------------------------------------------------------------------- producer warp
 // Walks the same pass / layer / slice order as run_stack and keeps the ring full.  s_go: -1 until
 // the compute warps know how many passes of the program will run (EOS / max_len), then that count.
-__device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ passes, int n_passes,
+__device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ passes_g, const PassDesc * pds, int n_passes,
                               const Slices & z, Smem & s, volatile int * s_go, int n_past0) {
+    struct { const PassDesc * g; const PassDesc * c; __device__ const PassDesc & operator[](int i) const { return pass_desc(g, c, i); } } passes{passes_g, pds};
     unsigned p_slot = 0, p_idx = 0;
     const int nA = z.a1 - z.a0, nO = z.o1 - z.o0, nP = z.p1 - z.p0, nD = z.d1 - z.d0;
     bool aborted = false;
@@ -1777,9 +1792,10 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
     unsigned pspins = 0;
     int n_past = n_past0;
     const bool attn_cta = (int) blockIdx.x < NH;
-    // L2 residency (DevModel::l2_pin > 0): the first l2_pin layers of the code predictor are re-read by each of its 16 passes
-    // per frame -- their copies ask L2 to keep the lines (evict_last); everything that is read once per frame (talker layers,
-    // the other code-predictor layers, the heads) is marked evict_first so that it does not push them out
+    // L2 residency (DevModel::l2_pin > 0): the code predictor's weights are re-read by each of its 16 passes per frame, but a pass
+    // (161 MB F16) does not fit the 126 MB L2 next to the talker stream, so nothing survived between passes.  The copies of its
+    // first l2_pin weight slices ask L2 to keep the lines (evict_last); everything that is read once per frame (talker layers, the
+    // rest of the code predictor, the heads) is marked evict_first so that it does not push them out.
     unsigned long long pol_first = 0ull, pol_last = 0ull;
     if (m.l2_pin > 0) {
         asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_first));
@@ -1815,7 +1831,9 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
         for (int l = 0; l < n_layers && !aborted; ++l) {
             for (int k = 0; k < 4 + n_mid; ++k) {
                 const void * src; int n_slots, slot_bytes = W.wtype == Q3T_TYPE_Q8_0 ? SLOT_Q8 : SLOT_B, tail = SLOT_B;
-                unsigned long long pol = (passes[ip].stack == 1 && l < m.l2_pin) ? pol_last : pol_first;
+                // l2_pin counts weight slices of the code predictor in schedule order (4 per layer: QKV, O, gate/up, down)
+                const int wk = k == 0 ? 0 : k - n_mid;            // 0..3 for the four weight slices (<= 0 for K/V history slices)
+                unsigned long long pol = (passes[ip].stack == 1 && l * 4 + wk < m.l2_pin) ? pol_last : pol_first;
                 if (k == 0) { src = sl_a(W, l, z); n_slots = nA; }
                 else if (k <= n_wk) {
                     const int c = k - 1;
@@ -1837,6 +1855,10 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
                     const int kk = k - n_mid;
                     src = kk == 1 ? sl_o(W, l, z) : kk == 2 ? sl_gu(W, l, z) : sl_d(W, l, z);
                     n_slots = kk == 1 ? nO * 2 : kk == 2 ? nP * 2 : nD * 3;
+                }
+                if ((k == 0 || wk >= 1) && W.wtype == Q3T_TYPE_Q8_0) {   // n_slots counted records so far: contiguous 1088-byte records
+                    const int bytes = n_slots * SLOT_Q8;
+                    n_slots = q8_slots(n_slots); slot_bytes = SLOT_B; tail = bytes - (n_slots - 1) * SLOT_B;
                 }
                 // ring-space wait with an abort check (EOS decided while pass 0 is being produced)
                 while (true) {
@@ -1879,11 +1901,16 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem & s = *reinterpret_cast<Smem *>(smem_raw);
     __shared__ GenState gs;
-    __shared__ PassDesc pd;
+    __shared__ PassDesc pds[PD_CACHE];     // the program (a frame is 17 passes): a PassDesc read from global memory at every pass
+                                           // boundary cost two dependent L2 round trips on the critical path
     __shared__ int s_go_raw;
     volatile int * s_go = &s_go_raw;
     const int t = threadIdx.x;
 
+    {
+        const int n_ints = (n_passes < PD_CACHE ? n_passes : PD_CACHE) * (int) (sizeof(PassDesc) / sizeof(int));
+        if (t < n_ints) reinterpret_cast<int *>(pds)[t] = reinterpret_cast<const int *>(passes)[t];
+    }
     if (t == 0) {
         gs = *m.st;
         s_go_raw = frame_mode ? -1 : n_passes;
@@ -1903,7 +1930,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
     cta_rows(H,     z.d0, z.d1);
 
     if (t >= NCT) {                                   // ---- producer warp: one thread drives the TMA unit
-        if (t == NCT) producer_loop(m, passes, n_passes, z, s, s_go, gs.n_past);
+        if (t == NCT) producer_loop(m, passes, pds, n_passes, z, s, s_go, gs.n_past);
         return;
     }
 
@@ -1920,9 +1947,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
 
     for (int ip = 0; ip < n_passes; ++ip) {
         PROF(30);
-        if (t == 0) pd = passes[ip];
-        cbar();
-        const PassDesc p = pd;
+        const PassDesc & p = pass_desc(passes, pds, ip);
         const StackW & W = p.stack == 0 ? m.talker : m.cp;
         if (!pr_valid && p.xmode != XM_SELECT_ONLY) { prefetch_layer_params(W, 0, pr); pr_valid = true; }
 
@@ -1947,7 +1972,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
         }
         if (ip == 0 && frame_mode && t == 0) {
             // :2755-2757 no talker step after the last frame: the producer must not stream it either
-            const bool trunc = passes[n_passes - 1].xmode == XM_TALKER_NEXT && frame + 1 >= gs.max_len;
+            const bool trunc = pass_desc(passes, pds, n_passes - 1).xmode == XM_TALKER_NEXT && frame + 1 >= gs.max_len;
             *s_go = trunc ? n_passes - 1 : n_passes;
         }
         if (p.xmode == XM_TALKER_NEXT && frame_mode) {
@@ -1990,7 +2015,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
         // the next pass' first-layer parameters are fetched across the pass boundary
         const StackW * NW = nullptr;
         if (ip + 1 < n_passes) {
-            const int nx = passes[ip + 1].xmode, ns = passes[ip + 1].stack;
+            const int nx = pass_desc(passes, pds, ip + 1).xmode, ns = pass_desc(passes, pds, ip + 1).stack;
             if (nx != XM_SELECT_ONLY) NW = ns == 0 ? &m.talker : &m.cp;
         }
         if (!NW) pr_valid = false;
@@ -2072,13 +2097,15 @@ static void lm_pacing(DevModel & m) {
     static int pp = -1, pc = -1;
     if (pp < 0) {
         const char * e1 = getenv("Q3T_PROD_PACE"), * e2 = getenv("Q3T_PROD_PIECE");
-        pp = e1 ? atoi(e1) : 150; pc = e2 ? atoi(e2) : 4;
+        pp = e1 ? atoi(e1) : 100; pc = e2 ? atoi(e2) : 4;
         if (pc < 1) pc = 1;
     }
     m.prod_pace = pp; m.prod_piece = pc;
     static int pin = -1;
-    if (pin < 0) { const char * e = getenv("Q3T_L2_PIN"); pin = e ? atoi(e) : 0; }
-    m.l2_pin = pin;
+    if (pin == -1) { const char * e = getenv("Q3T_L2_PIN"); pin = e ? atoi(e) : -2; }
+    // measured plateau (profiles/r02c_l2_sweep.txt): 6-9 slices (47-71 MB) of the F16 code predictor, 16 of the Q8_0 one.
+    // (Prefetching every slice into L2 one layer ahead of its ring copy was measured too: 1.361 -> 1.439 ms per frame.)
+    m.l2_pin = pin >= 0 ? pin : (m.cp.wtype == Q3T_TYPE_Q8_0 ? 16 : 9);
 }
 
 int lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int frame_mode) {

@@ -12,13 +12,17 @@ from util import HELLO_FULL, models
 pytestmark = pytest.mark.gpu
 
 
-def _utterances(n, seed=17):
+def _utterances(n, seed=17, speakers="mixed"):
+    """speakers: "mixed" = every fifth utterance without a speaker vector (9 prompt rows instead of 10: such a wave is
+    prefilled one sequence at a time), "all" / "none" = uniform waves (prefilled in lock-step by the batched kernel)."""
     rng = np.random.default_rng(seed)
     out = []
     for i in range(n):
         body = rng.integers(32, 127, size=int(rng.integers(8, 65)), dtype=np.int32)       # 8..64 byte tokens
         toks = np.concatenate([HELLO_FULL[:3], body, HELLO_FULL[-5:]]).astype(np.int32)
-        spk = None if i % 5 == 4 else (rng.standard_normal(1024) * 0.05).astype(np.float32)
+        spk = (rng.standard_normal(1024) * 0.05).astype(np.float32)
+        if speakers == "none" or (speakers == "mixed" and i % 5 == 4):
+            spk = None
         out.append((toks, spk))
     return out
 
@@ -40,6 +44,22 @@ def test_batched_codes_equal_single_sequence_codes(tts, n, frames):
     assert len(got) == n
     for i, (toks, spk) in enumerate(utts):
         want = tts.generate(toks, spk, frames, temperature=0.0)
+        assert want is not None, tts.get_error()
+        assert got[i].shape == want.shape, f"utterance {i}"
+        neq = np.argwhere(got[i] != want)
+        assert len(neq) == 0, f"utterance {i}: first mismatch at frame/codebook {neq[0]}"
+
+
+@pytest.mark.parametrize("n,speakers", [(13, "all"), (5, "none"), (19, "all")])
+def test_batched_prefill_waves_equal_single_sequence_codes(tts, n, speakers):
+    """Waves whose sequences all have the same number of prompt rows are prefilled in lock-step by the batched kernel
+    (prompt rows as XM_BUF passes with the prefill's soft-max row width) instead of one sequence at a time on the batch-1
+    kernel: the codes still equal generate() for each utterance alone."""
+    utts = _utterances(n, seed=500 + n, speakers=speakers)
+    got = tts.generate_batch(utts, 16)
+    assert got is not None, tts.get_error()
+    for i, (toks, spk) in enumerate(utts):
+        want = tts.generate(toks, spk, 16, temperature=0.0)
         assert want is not None, tts.get_error()
         assert got[i].shape == want.shape, f"utterance {i}"
         neq = np.argwhere(got[i] != want)
