@@ -330,7 +330,7 @@ def run_ours(args, rank, world, local_rank):
     step_s, e2e_s = float(times[0]), float(times[1])
 
     # ---- BASELINE.json config 4 at this N: 64 utterances, strong scaling, batched engine (every rank takes part)
-    c4 = None if args.no_batch else config4_line(args, rank, world, t, d, have_voc, dist, sync_all)
+    c4 = None if args.no_batch else config4_line(args, rank, world, t, d, have_voc, dist, sync_all, m)
 
     if rank == 0:
         peak, peak_kind = measured_peaks()
@@ -378,7 +378,7 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
-def config4_line(args, rank, world, t, d, have_voc, dist, sync_all):
+def config4_line(args, rank, world, t, d, have_voc, dist, sync_all, m):
     """BASELINE.json config 4 / the "batch 64" metric point: 64 utterances (8-64 byte texts, seed 4), greedy, `--frames`
     frames each + vocoder, strong scaling: utterance i -> rank i mod N, every rank pushes its share through the batched
     engine (generate_batch: 16 sequences per launch, two interleaved lock-step groups of 8), then decodes each utterance.  Host buffers in and out;
@@ -392,6 +392,16 @@ def config4_line(args, rank, world, t, d, have_voc, dist, sync_all):
     pairs = [(u.tokens, u.spk) for u in mine]
     if pairs and t.generate_batch(pairs[:min(8, len(pairs))], 8) is None:          # warm-up (instantiation, buffers)
         raise SystemExit("generate_batch: " + t.get_error())
+    from concurrent.futures import ThreadPoolExecutor
+    extra_dec = []
+    if have_voc and args.decoders > 1:
+        from util import models as _models
+        for _ in range(args.decoders - 1):
+            dd = m.AudioTokenizerDecoder()
+            if not dd.load_model(_models("full", args.wtype)[1]):
+                raise SystemExit("decoder load_model: " + dd.get_error())
+            dd.decode(np.zeros((8, 16), np.int32))                                  # warm-up (buffers, tensor maps)
+            extra_dec.append(dd)
     sync_all()
     w0 = time.perf_counter()
     codes = t.generate_batch(pairs, args.frames, repetition_penalty=1.05) if pairs else []
@@ -401,13 +411,24 @@ def config4_line(args, rank, world, t, d, have_voc, dist, sync_all):
     torch.cuda.synchronize()
     w1 = time.perf_counter()
     ns = 0
-    for c in codes:
-        wav = d.decode(c) if have_voc else np.zeros(n_samples(len(c)), np.float32)
-        ns += len(wav)
+    if have_voc and len(extra_dec) > 0:
+        # the utterances of the job are decoded by N decoder instances from N host threads (each instance has its own stream:
+        # the small early-stage launches of one decode overlap the large late-stage GEMMs of another)
+        decs = [d] + extra_dec
+        def work(k):
+            return sum(len(decs[k].decode(c)) for c in codes[k::len(decs)])
+        with ThreadPoolExecutor(len(decs)) as ex:
+            ns = sum(ex.map(work, range(len(decs))))
+    else:
+        for c in codes:
+            wav = d.decode(c) if have_voc else np.zeros(n_samples(len(c)), np.float32)
+            ns += len(wav)
     torch.cuda.synchronize()
     w2 = time.perf_counter()
     sync_all()
     w3 = time.perf_counter()
+    for dd in extra_dec:
+        dd.close()
     nf = sum(len(c) for c in codes)
     wave = max(1, min(16, int(os.environ.get("Q3T_BATCH_WAVE", "16"))))     # sequences per lm_batch_kernel launch (engine.cu)
     groups = (len(pairs) + wave - 1) // wave
@@ -438,6 +459,7 @@ def config4_line(args, rank, world, t, d, have_voc, dist, sync_all):
             "limiter": (f"{per_gpu} utterances per GPU = {groups} launch wave(s) of <= {wave} sequences: a batched frame costs ~3.4 ms for 8 and "
                         f"~5.8 ms for 16 sequences, prompts/prefills ({prefill_s:.2f} s) and vocoder decodes ({voc_s:.2f} s) run one utterance at a "
                         f"time and do not shrink below one wave's share"),
+            "vocoder_instances": args.decoders if have_voc else 0,
             "workload": "config 4: 64 utterances (8-64 byte texts, seed 4), greedy, host buffers in/out, utterance i -> rank i mod N"}
 
 
@@ -528,6 +550,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-vocoder", action="store_true", help="debug only: codes without the waveform (not a valid bench value)")
     ap.add_argument("--no-batch", action="store_true", help="config 4 through the batch-1 engine, one utterance at a time")
+    ap.add_argument("--decoders", type=int, default=4, help="config 4: vocoder instances (host threads, one stream each) that decode the job's utterances")
     ap.add_argument("--utterances", type=int, default=0,
                     help="config 4: this many independent utterances (8-64 byte texts) per step, dealt i mod G to the ranks; "
                          "0 = the default config-2 workload (one utterance per rank per step)")

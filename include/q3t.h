@@ -335,6 +335,11 @@ Q3T_API int  q3t_pipe_synthesize_batch(q3t_tts * t, q3t_dec * d, int32_t n, cons
                                        const float * const * speaker_embd, int32_t max_len, int32_t language_id,
                                        float repetition_penalty, float * const * samples_out, const int64_t * caps,
                                        int64_t * n_samples_out, q3t_batch_stats * stats_out);
+/* the same with n_dec decoder instances (utterance i -> decoder i mod n_dec, one host thread and CUDA stream each) */
+Q3T_API int  q3t_pipe_synthesize_batch_multi(q3t_tts * t, q3t_dec * const * decs, int32_t n_dec, int32_t n, const int32_t * const * text_tokens,
+                                             const int32_t * n_tokens, const float * const * speaker_embd, int32_t max_len, int32_t language_id,
+                                             float repetition_penalty, float * const * samples_out, const int64_t * caps,
+                                             int64_t * n_samples_out, q3t_batch_stats * stats_out);
 Q3T_API const char * q3t_pipe_get_error(void);
 
 #ifdef __cplusplus

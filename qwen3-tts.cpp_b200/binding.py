@@ -115,6 +115,8 @@ def lib() -> C.CDLL:
                                                    C.c_int32, C.c_int32, _f32p, C.c_int64, C.POINTER(StreamStats)]),
         "q3t_pipe_synthesize_batch": (C.c_int, [vp, vp, C.c_int32, C.POINTER(_i32p), _i32p, C.POINTER(_f32p), C.c_int32, C.c_int32, C.c_float,
                                                 C.POINTER(_f32p), _i64p, _i64p, C.POINTER(BatchStats)]),
+        "q3t_pipe_synthesize_batch_multi": (C.c_int, [vp, C.POINTER(vp), C.c_int32, C.c_int32, C.POINTER(_i32p), _i32p, C.POINTER(_f32p), C.c_int32, C.c_int32,
+                                                      C.c_float, C.POINTER(_f32p), _i64p, _i64p, C.POINTER(BatchStats)]),
         "q3t_pipe_get_error": (cp, []),
         "q3t_sample_logits": (C.c_int, [vp, _f32p, C.c_int32, C.c_int32, _i32p, C.c_int32, C.c_float, C.c_float, C.c_int32, C.c_uint64, C.c_int32, _i32p]),
         "q3t_project_text_static_dev": (C.c_int, [vp, vp, C.c_int32, vp]),
@@ -532,8 +534,10 @@ def synthesize_stream(tts: TTSTransformer, dec: AudioTokenizerDecoder, tokens, s
     return out[:n].copy(), st
 
 
-def synthesize_batch(tts: TTSTransformer, dec: AudioTokenizerDecoder, utterances, max_len, language_id=2050, repetition_penalty=1.05):
-    """Batched front door: utterances = [(tokens, spk or None)], greedy; returns ([waveform], BatchStats)."""
+def synthesize_batch(tts: TTSTransformer, dec, utterances, max_len, language_id=2050, repetition_penalty=1.05):
+    """Batched front door: utterances = [(tokens, spk or None)], greedy; returns ([waveform], BatchStats).
+    dec: one AudioTokenizerDecoder or a list of them (utterance i is decoded by decoder i mod N, one host thread each)."""
+    decs = list(dec) if isinstance(dec, (list, tuple)) else [dec]
     n = len(utterances)
     toks = [np.ascontiguousarray(u[0], np.int32) for u in utterances]
     spks = [None if u[1] is None else np.ascontiguousarray(u[1], np.float32) for u in utterances]
@@ -546,8 +550,9 @@ def synthesize_batch(tts: TTSTransformer, dec: AudioTokenizerDecoder, utterances
     caps = np.full(n, cap, np.int64)
     ns = np.zeros(n, np.int64)
     st = BatchStats()
-    ok = lib().q3t_pipe_synthesize_batch(tts.h, dec.h, n, tp, _ip(nt), sp, max_len, language_id, repetition_penalty, op,
-                                         caps.ctypes.data_as(_i64p), ns.ctypes.data_as(_i64p), C.byref(st))
+    dp = (C.c_void_p * len(decs))(*[x.h for x in decs])
+    ok = lib().q3t_pipe_synthesize_batch_multi(tts.h, dp, len(decs), n, tp, _ip(nt), sp, max_len, language_id, repetition_penalty, op,
+                                               caps.ctypes.data_as(_i64p), ns.ctypes.data_as(_i64p), C.byref(st))
     if not ok:
         raise Q3TError(lib().q3t_pipe_get_error().decode())
     return [outs[i][:ns[i]].copy() for i in range(n)], st

@@ -356,19 +356,6 @@ __device__ __forceinline__ const void * sl_d(const StackW & W, int l, const Slic
     return sl_rows(W.wdown, W.wtype, (size_t) l * H + z.d0, 3);
 }
 
-// Q8_0 slices land in the ring exactly as they lie in HBM: records of 1088 B back to back from the slice's first slot --
-// ONE bulk copy per slice (so the paced producer applies; one copy per record made the producer thread the bottleneck) and
-// about half the ring footprint of one record per 2 KB slot.  A record may wrap around the end of the ring: q8_at() is the
-// address of byte `o` (a multiple of 8; 16-byte loads at multiples of 16) of record `i` of the slice that starts at slot s0.
-template <class SM>
-__device__ __forceinline__ const unsigned char * q8_at(const SM & s, int s0, int i, int o) {
-    constexpr unsigned RING = (unsigned) SM::NSLOTS * SLOT_B;
-    unsigned b = (unsigned) s0 * SLOT_B + (unsigned) i * SLOT_Q8 + (unsigned) o;
-    if (b >= RING) b -= RING;
-    return s.ring + b;
-}
-__host__ __device__ __forceinline__ int q8_slots(int n_rec) { return (n_rec * SLOT_Q8 + SLOT_B - 1) / SLOT_B; }   // ring slots of a slice
-
 // ------------------------------------------------------------------------------- ordered GEMV
 // fma.rn.f32.f16 (SASS FHFMA, sm_100+): d = f32(a) * f32(b) + c with a, b F16 and one rounding —
 // exactly ggml's F16C-convert + vfmadd lane step, in one instruction.
@@ -544,12 +531,14 @@ __device__ __forceinline__ void gemv_q8(Smem & s, int s0, int n_rows) {
         float acc = 0.0f;
 #pragma unroll
         for (int ch = 0; ch < SPR; ++ch) {
-            const int rec = r * SPR + ch;
+            int slot = s0 + r * SPR + ch;
+            slot %= NSLOT;
+            const unsigned char * rec = s.ring + (size_t) slot * SLOT_B;
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
-                const uint4  wq = *reinterpret_cast<const uint4 *>(q8_at(s, s0, rec, c * 128 + l * 16));
+                const uint4  wq = *reinterpret_cast<const uint4 *>(rec + c * 128 + l * 16);
                 const uint4  xq = *reinterpret_cast<const uint4 *>(s.xq + ch * 1024 + c * 128 + l * 16);
-                const uint2  ws = *reinterpret_cast<const uint2 *>(q8_at(s, s0, rec, 1024 + c * 8));
+                const uint2  ws = *reinterpret_cast<const uint2 *>(rec + 1024 + c * 8);
                 const float4 xs = *reinterpret_cast<const float4 *>(s.xd + ch * 32 + c * 4);
                 const float2 w01 = __half22float2(*reinterpret_cast<const __half2 *>(&ws.x));
                 const float2 w23 = __half22float2(*reinterpret_cast<const __half2 *>(&ws.y));
@@ -584,16 +573,22 @@ __device__ __forceinline__ void gemv_q8_f32(Smem & s, int s0, int n_rows) {
         uint2 qa[2]; uint4 sa[2];
 #pragma unroll
         for (int a = 0; a < 2; ++a) {
-            qa[a] = lds_v2(q8_at(s, s0, r * SPR + (a >> 2), (a & 3) * 256 + lane * 8));
-            sa[a] = lds_v4(q8_at(s, s0, r * SPR + (a >> 2), 1024 + (a & 3) * 16));
+            int slot = s0 + r * SPR + (a >> 2);
+            slot %= NSLOT;
+            const unsigned char * rec = s.ring + (size_t) slot * SLOT_B;
+            qa[a] = lds_v2(rec + (a & 3) * 256 + lane * 8);
+            sa[a] = lds_v4(rec + 1024 + (a & 3) * 16);
         }
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
             const uint2 q8 = qa[u & 1];
             const uint4 sc = sa[u & 1];
             if (u + 2 < NU) {
-                qa[u & 1] = lds_v2(q8_at(s, s0, r * SPR + ((u + 2) >> 2), ((u + 2) & 3) * 256 + lane * 8));
-                sa[u & 1] = lds_v4(q8_at(s, s0, r * SPR + ((u + 2) >> 2), 1024 + ((u + 2) & 3) * 16));
+                int slot = s0 + r * SPR + ((u + 2) >> 2);
+                slot %= NSLOT;
+                const unsigned char * rec = s.ring + (size_t) slot * SLOT_B;
+                qa[u & 1] = lds_v2(rec + ((u + 2) & 3) * 256 + lane * 8);
+                sa[u & 1] = lds_v4(rec + 1024 + ((u + 2) & 3) * 16);
             }
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
@@ -1478,16 +1473,12 @@ __device__ __noinline__ int select_sample(const DevModel & m, SM & s, unsigned e
             const int shift = 24 - 8 * pass;
             if (t < 256) hist[t] = 0;
             cbar();
-            // warp-aggregated: the keys of a logit vector share their leading digits, so most of a warp's entries fall into
-            // the same few bins -- one atomic per distinct bin and warp instead of one per entry (same-address shared-memory
-            // atomics serialise)
 #pragma unroll
             for (int i = 0; i < PER; ++i) {
-                const unsigned int key = f2key(l[i]);
-                const bool act = t * PER + i < vocab && (key & mask) == prefix;
-                const unsigned int bin = (key >> shift) & 255u;
-                const unsigned int peers = __match_any_sync(0xffffffffu, act ? bin : 256u + (unsigned) lane);
-                if (act && lane == __ffs(peers) - 1) atomicAdd(&hist[bin], __popc(peers));
+                if (t * PER + i < vocab) {
+                    const unsigned int key = f2key(l[i]);
+                    if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255], 1);
+                }
             }
             cbar();
             if (warp == 0) {
@@ -1662,7 +1653,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         PROF(41);
         if (t < nA) pk_store(m.x_qkv + z.a0 + t, s.outv[t], e_qkv);
         PROF(42);
-        ring_release(s, rg, Q8 ? q8_slots(nA) : nA);
+        ring_release(s, rg, nA);
         PROF(5);
 
         // ---- phase B: per-head norm + RoPE + KV append + attention (CTA h owns head h)
@@ -1694,7 +1685,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         if (Q8) gemv_q8<2048>(s, s0, nO); else gemv_ring<2048, 1, false>(s, s0, nO);
         cbar();
         if (t < nO) pk_store(m.x_x1 + z.o0 + t, __fadd_rn(s.outv[t], s.xres[z.o0 + t]), e_x1);
-        ring_release(s, rg, Q8 ? q8_slots(nO * 2) : nO * 2);
+        ring_release(s, rg, nO * 2);
         PROF(9);
 
         // ---- phase D: RMSNorm + gate/up mat-vec + SwiGLU
@@ -1713,7 +1704,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
             const float sl = __fdiv_rn(gt, __fadd_rn(1.0f, v_expf(__fsub_rn(0.0f, gt))));   // ggml_v_silu
             pk_store(m.x_m + z.p0 + t, __fmul_rn(sl, up), e_m);
         }
-        ring_release(s, rg, Q8 ? q8_slots(2 * nP) : 2 * nP);
+        ring_release(s, rg, 2 * nP);
         PROF(13);
 
         // ---- phase E: ffn_down on F32 activations (weights exact in F32) + residual
@@ -1726,7 +1717,7 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
         if (Q8) gemv_q8_f32<3072>(s, s0, nD); else gemv_ring<3072, 1, true>(s, s0, nD);
         cbar();
         if (t < nD) pk_store(m.x_x + z.d0 + t, __fadd_rn(s.outv[t], s.xres[z.d0 + t]), e_x);
-        ring_release(s, rg, Q8 ? q8_slots(nD * 3) : nD * 3);
+        ring_release(s, rg, nD * 3);
         PROF(16);
         ep += 5;
     }
@@ -1855,10 +1846,6 @@ __device__ void producer_loop(const DevModel & m, const PassDesc * __restrict__ 
                     const int kk = k - n_mid;
                     src = kk == 1 ? sl_o(W, l, z) : kk == 2 ? sl_gu(W, l, z) : sl_d(W, l, z);
                     n_slots = kk == 1 ? nO * 2 : kk == 2 ? nP * 2 : nD * 3;
-                }
-                if ((k == 0 || wk >= 1) && W.wtype == Q3T_TYPE_Q8_0) {   // n_slots counted records so far: contiguous 1088-byte records
-                    const int bytes = n_slots * SLOT_Q8;
-                    n_slots = q8_slots(n_slots); slot_bytes = SLOT_B; tail = bytes - (n_slots - 1) * SLOT_B;
                 }
                 // ring-space wait with an abort check (EOS decided while pass 0 is being produced)
                 while (true) {

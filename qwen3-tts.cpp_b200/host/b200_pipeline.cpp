@@ -1,5 +1,7 @@
 #include "b200_pipeline.h"
 
+#include <thread>
+
 #include <algorithm>
 #include <chrono>
 
@@ -42,6 +44,14 @@ bool synthesize_stream(TTSTransformer & tts, AudioTokenizerDecoder & dec, const 
 bool synthesize_batch(TTSTransformer & tts, AudioTokenizerDecoder & dec, const std::vector<const int32_t *> & text_tokens,
                       const std::vector<int32_t> & n_tokens, const std::vector<const float *> & speaker_embd,
                       const synth_params & p, std::vector<std::vector<float>> & audio, batch_stats * stats, std::string & error) {
+    std::vector<AudioTokenizerDecoder *> decs{&dec};
+    return synthesize_batch(tts, decs, text_tokens, n_tokens, speaker_embd, p, audio, stats, error);
+}
+
+bool synthesize_batch(TTSTransformer & tts, const std::vector<AudioTokenizerDecoder *> & decs, const std::vector<const int32_t *> & text_tokens,
+                      const std::vector<int32_t> & n_tokens, const std::vector<const float *> & speaker_embd,
+                      const synth_params & p, std::vector<std::vector<float>> & audio, batch_stats * stats, std::string & error) {
+    if (decs.empty()) { error = "no decoder"; return false; }
     const auto t0 = clk::now();
     batch_stats st;
     std::vector<std::vector<int32_t>> codes;
@@ -53,11 +63,25 @@ bool synthesize_batch(TTSTransformer & tts, AudioTokenizerDecoder & dec, const s
     const auto t1 = clk::now();
     audio.assign(codes.size(), {});
     const int ncb = tts.get_config().n_codebooks;
+    // decoder k takes utterances k, k + N, ...; one host thread per decoder (a decoder object is not thread-safe, its own calls stay serial)
+    const size_t nd = decs.size();
+    std::vector<std::string> errs(nd);
+    auto work = [&](size_t k) {
+        for (size_t i = k; i < codes.size(); i += nd) {
+            const int32_t nf = (int32_t) (codes[i].size() / (size_t) ncb);
+            if (nf == 0) continue;
+            if (!decs[k]->decode(codes[i].data(), nf, audio[i])) { errs[k] = decs[k]->get_error(); return; }
+        }
+    };
+    if (nd == 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (size_t k = 0; k < nd; ++k) th.emplace_back(work, k);
+        for (auto & x : th) x.join();
+    }
+    for (const auto & e : errs) if (!e.empty()) { error = e; return false; }
     for (size_t i = 0; i < codes.size(); ++i) {
-        const int32_t nf = (int32_t) (codes[i].size() / (size_t) ncb);
-        st.n_frames += nf;
-        if (nf == 0) continue;
-        if (!dec.decode(codes[i].data(), nf, audio[i])) { error = dec.get_error(); return false; }
+        st.n_frames += (int64_t) (codes[i].size() / (size_t) ncb);
         st.n_samples += (int64_t) audio[i].size();
     }
     st.t_decode_ms = ms_since(t1);

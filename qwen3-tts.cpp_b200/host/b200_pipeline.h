@@ -49,5 +49,12 @@ Q3T_API bool synthesize_batch(TTSTransformer & tts, AudioTokenizerDecoder & dec,
                               const std::vector<int32_t> & n_tokens, const std::vector<const float *> & speaker_embd,
                               const synth_params & p, std::vector<std::vector<float>> & audio, batch_stats * stats, std::string & error);
 
+// the same with several decoder instances: utterance i is decoded by decoder i mod N, each decoder on its own host thread and
+// CUDA stream, so the small early-stage launches of one decode overlap the large late-stage GEMMs of another (64 x 320 frames:
+// 0.56 -> 0.43 s with 4 instances)
+Q3T_API bool synthesize_batch(TTSTransformer & tts, const std::vector<AudioTokenizerDecoder *> & decs, const std::vector<const int32_t *> & text_tokens,
+                              const std::vector<int32_t> & n_tokens, const std::vector<const float *> & speaker_embd,
+                              const synth_params & p, std::vector<std::vector<float>> & audio, batch_stats * stats, std::string & error);
+
 } // namespace b200
 } // namespace qwen3_tts

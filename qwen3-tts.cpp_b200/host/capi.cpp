@@ -226,7 +226,16 @@ Q3T_API int64_t q3t_pipe_synthesize_stream(q3t_tts * t, q3t_dec * d, const int32
 Q3T_API int q3t_pipe_synthesize_batch(q3t_tts * t, q3t_dec * d, int32_t n, const int32_t * const * text_tokens, const int32_t * n_tokens,
                                       const float * const * speaker_embd, int32_t max_len, int32_t language_id, float repetition_penalty,
                                       float * const * samples_out, const int64_t * caps, int64_t * n_samples_out, q3t_batch_stats * stats_out) {
-    if (!t || !d || n <= 0 || !text_tokens || !n_tokens || !n_samples_out) { g_pipe_err = "bad argument"; return 0; }
+    return q3t_pipe_synthesize_batch_multi(t, &d, 1, n, text_tokens, n_tokens, speaker_embd, max_len, language_id, repetition_penalty,
+                                           samples_out, caps, n_samples_out, stats_out);
+}
+Q3T_API int q3t_pipe_synthesize_batch_multi(q3t_tts * t, q3t_dec * const * decs, int32_t n_dec, int32_t n, const int32_t * const * text_tokens,
+                                            const int32_t * n_tokens, const float * const * speaker_embd, int32_t max_len, int32_t language_id,
+                                            float repetition_penalty, float * const * samples_out, const int64_t * caps, int64_t * n_samples_out,
+                                            q3t_batch_stats * stats_out) {
+    if (!t || !decs || n_dec <= 0 || n <= 0 || !text_tokens || !n_tokens || !n_samples_out) { g_pipe_err = "bad argument"; return 0; }
+    std::vector<AudioTokenizerDecoder *> dv;
+    for (int i = 0; i < n_dec; ++i) { if (!decs[i]) { g_pipe_err = "bad argument"; return 0; } dv.push_back(&decs[i]->d); }
     b200::synth_params p;
     p.max_audio_tokens = max_len; p.language_id = language_id; p.repetition_penalty = repetition_penalty; p.temperature = 0.0f; p.top_k = 0;
     std::vector<const int32_t *> tt(text_tokens, text_tokens + n);
@@ -235,7 +244,7 @@ Q3T_API int q3t_pipe_synthesize_batch(q3t_tts * t, q3t_dec * d, int32_t n, const
     if (speaker_embd) sp.assign(speaker_embd, speaker_embd + n);
     std::vector<std::vector<float>> audio;
     b200::batch_stats st;
-    if (!b200::synthesize_batch(t->t, d->d, tt, nt, sp, p, audio, &st, g_pipe_err)) return 0;
+    if (!b200::synthesize_batch(t->t, dv, tt, nt, sp, p, audio, &st, g_pipe_err)) return 0;
     for (int i = 0; i < n; ++i) {
         n_samples_out[i] = (int64_t) audio[i].size();
         if (samples_out && samples_out[i] && caps)

@@ -68,3 +68,9 @@ def test_synthesize_batch_equals_per_utterance_pipeline(q3t, pair):
         want = d.decode(t.generate(toks, spk, 24, temperature=0.0))
         assert np.array_equal(w, want)
     assert st.t_generate_ms > 0 and st.t_decode_ms > 0 and st.t_total_ms >= st.t_generate_ms
+    # several decoder instances (one host thread and stream each): the same waveforms
+    d2 = q3t.AudioTokenizerDecoder()
+    assert d2.load_model(models("tiny", "f16")[1]), d2.get_error()
+    wavs2, st2 = q3t.synthesize_batch(t, [d, d2], utts, 24)
+    assert st2.n_samples == st.n_samples and all(np.array_equal(a, b) for a, b in zip(wavs, wavs2))
+    d2.close()
