@@ -638,7 +638,7 @@ int64_t vocoder_run(q3t_ctx * ctx, const int32_t * codes_dev, int T, float ** sa
     }
     Arena A{v->arena, 0, v->arena_bytes};
     int64_t & nl = ctx->timing.kernel_launches;
-    // developer aid: Q3T_VOC_DEBUG_DIR=<dir> writes stage outputs as raw files (tests/dev_voc_trace.py)
+    // developer aid: Q3T_VOC_DEBUG_DIR=<dir> writes stage outputs as raw files (tools/dev/dev_voc_trace.py)
     const char * dbg_dir = getenv("Q3T_VOC_DEBUG_DIR");
     auto dump = [&](const char * name, const void * dev, size_t bytes) {
         if (!dbg_dir) return;

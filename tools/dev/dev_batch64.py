@@ -3,7 +3,7 @@ split (Q3T_BATCH_TRACE=1) next to the CUDA-event times."""
 import os, sys, time, importlib
 os.environ.setdefault("Q3T_BATCH_TRACE", "1")
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from util import pkg, models
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 320
 m = pkg(); t = m.TTSTransformer()

@@ -1,7 +1,7 @@
 """Developer script: throughput of generate_batch (frames_ms from CUDA events) for several batch sizes."""
 import os, sys, time
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from util import pkg, models, HELLO_FULL
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 120
 sizes = [int(x) for x in sys.argv[2].split(",")] if len(sys.argv) > 2 else [1, 2, 4, 8, 16]

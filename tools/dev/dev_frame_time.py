@@ -1,7 +1,7 @@
 """Developer script: ms/frame of a short staged run (for parameter sweeps via environment variables)."""
 import os, sys
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from util import pkg, models, HELLO_FULL
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 60
 m = pkg(); t = m.TTSTransformer()

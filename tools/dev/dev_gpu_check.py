@@ -1,7 +1,7 @@
-"""Developer script (not collected by pytest): first-light comparison on a GPU box."""
+"""Developer script (lives outside tests/): first-light comparison on a GPU box."""
 import sys, time
 import numpy as np
-sys.path.insert(0, __import__('os').path.dirname(__import__('os').path.abspath(__file__)))
+sys.path.insert(0, __import__('os').path.join(__import__('os').path.dirname(__import__('os').path.abspath(__file__)), '..', '..', 'tests'))
 from util import pkg, models, HELLO_TINY, HELLO_FULL
 from oracle import reflib
 

@@ -1,7 +1,7 @@
 """Developer script: talker steps at long contexts vs the live reference (bit-exact check)."""
 import os, sys
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from util import pkg, models
 from oracle import reflib
 preset = sys.argv[1] if len(sys.argv) > 1 else "tiny"

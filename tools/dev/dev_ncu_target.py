@@ -2,7 +2,7 @@
 lm_batch_kernel) and one vocoder decode (vgemm_umma) on the full-size random-init model."""
 import os, sys
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from util import pkg, models, HELLO_FULL
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 24
 m = pkg()

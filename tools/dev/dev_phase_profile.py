@@ -1,10 +1,10 @@
-"""Developer script (not collected by pytest): per-phase clock breakdown of lm_kernel on a B200.
+"""Developer script (lives outside tests/): per-phase clock breakdown of lm_kernel on a B200.
 Arms the in-kernel profiler (every CTA records its own marks with plain stores), runs a few frames
 and prints, for the LAST frame launch, the mean cycles between consecutive marks for some CTAs and
 the min / max over CTAs of every segment (a CTA that never waits in a poll is the critical one)."""
 import os, sys, collections
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from util import pkg, models, HELLO_FULL
 
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 40

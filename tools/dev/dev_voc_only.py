@@ -1,7 +1,7 @@
 """Developer script: vocoder alone on random codes (for ncu launch lists)."""
 import os, sys, time
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from util import pkg, models
 T = int(sys.argv[1]) if len(sys.argv) > 1 else 320
 m = pkg(); d = m.AudioTokenizerDecoder(); assert d.load_model(models("full", "f16")[1]), d.get_error()

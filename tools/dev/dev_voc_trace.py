@@ -1,8 +1,8 @@
-"""Developer script (not collected by pytest): per-stage comparison of the CUDA vocoder against the
+"""Developer script (lives outside tests/): per-stage comparison of the CUDA vocoder against the
 reference's ggml graph nodes.  Reference side runs anywhere; the CUDA side needs a B200."""
 import os, sys, tempfile
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from util import pkg, models
 from oracle import reflib
 

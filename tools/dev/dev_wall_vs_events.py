@@ -1,7 +1,7 @@
 """Developer script: wall clock vs CUDA-event time of run_staged / generate (host overhead hunt)."""
 import os, sys, time, subprocess, threading
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from util import pkg, models, HELLO_FULL
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 320
 poll = len(sys.argv) > 2 and sys.argv[2] == "smi"

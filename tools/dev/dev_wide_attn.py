@@ -4,7 +4,7 @@
   time:           talker step time of the full model vs n_kv (run once with Q3T_WIDE_MIN=0 and once without)"""
 import os, sys
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from util import pkg, models
 mode = sys.argv[1] if len(sys.argv) > 1 else "check"
 m = pkg()

@@ -13,6 +13,6 @@ mkdir -p /tmp/ncu
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:lm_kernel -s 40 -c 1 -o /tmp/ncu/lm_kernel python bench.py --steps 1 --warmup 1 --frames 24 --no-cpu-baseline > gpurun_out/ncu2.log 2>&1
 ncu -i /tmp/ncu/lm_kernel.ncu-rep --page details > gpurun_out/lm_kernel_r1g_details.txt 2>&1
 ncu -i /tmp/ncu/lm_kernel.ncu-rep --page raw --csv > gpurun_out/lm_kernel_r1g_raw.csv 2>&1
-timeout 600 ncu --set full --clock-control none -k regex:vgemm_umma -s 130 -c 12 -o /tmp/ncu/vgemm python tests/dev_voc_only.py > gpurun_out/ncu3.log 2>&1
+timeout 600 ncu --set full --clock-control none -k regex:vgemm_umma -s 130 -c 12 -o /tmp/ncu/vgemm python tools/dev/dev_voc_only.py > gpurun_out/ncu3.log 2>&1
 ncu -i /tmp/ncu/vgemm.ncu-rep --page raw --csv > gpurun_out/vgemm_umma_r1g_raw.csv 2>&1
 ls -la /tmp/ncu

@@ -113,7 +113,7 @@ def main():
                 "sm__inst_executed_pipe_tensor.sum", "lts__throughput.avg.pct_of_peak_sustained_elapsed", "dram__bytes_read.sum", "dram__bytes_write.sum",
                 "sm__warps_active.avg.pct_of_peak_sustained_active"]
         with open(os.path.join(PROF, f"{tag}_vgemm_umma_ncu.txt"), "w") as f:
-            f.write("# ncu --set full --clock-control none -k regex:vgemm_umma -s 130 -c 12: python tests/dev_voc_only.py (320-frame decode, decoder-block launches)\n")
+            f.write("# ncu --set full --clock-control none -k regex:vgemm_umma -s 130 -c 12: python tools/dev/dev_voc_only.py (320-frame decode, decoder-block launches)\n")
             f.write(" | ".join(["kernel"] + keys) + "\n")
             for d in raw_rows(vg):
                 f.write(" | ".join([d.get("Kernel Name", ("", "?"))[1][:32]] + [f"{d[k][1]} {d[k][0]}" if k in d else "-" for k in keys]) + "\n")
