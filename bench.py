@@ -394,6 +394,8 @@ def config4_line(args, rank, world, t, d, have_voc, dist, sync_all, m):
         raise SystemExit("generate_batch: " + t.get_error())
     from concurrent.futures import ThreadPoolExecutor
     extra_dec = []
+    if args.decoders <= 0:
+        args.decoders = max(1, min(4, (os.cpu_count() or 8) // (2 * world)))
     if have_voc and args.decoders > 1:
         from util import models as _models
         for _ in range(args.decoders - 1):
@@ -550,7 +552,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-vocoder", action="store_true", help="debug only: codes without the waveform (not a valid bench value)")
     ap.add_argument("--no-batch", action="store_true", help="config 4 through the batch-1 engine, one utterance at a time")
-    ap.add_argument("--decoders", type=int, default=4, help="config 4: vocoder instances (host threads, one stream each) that decode the job's utterances")
+    ap.add_argument("--decoders", type=int, default=0, help="config 4: vocoder instances (host threads, one stream each) that decode the job's "
+                                                            "utterances; 0 = min(4, host cores / (2 x ranks)), so 8 ranks do not oversubscribe the host")
     ap.add_argument("--utterances", type=int, default=0,
                     help="config 4: this many independent utterances (8-64 byte texts) per step, dealt i mod G to the ranks; "
                          "0 = the default config-2 workload (one utterance per rank per step)")
