@@ -1742,24 +1742,29 @@ __device__ void run_stack(const DevModel & m, const StackW & W, const PassDesc &
     const int s0 = ring_acquire(m, s, rg, w);
     gemv_ring<1024, 2, false>(s, s0, nH);
     cbar();
-    float pv = -CUDART_INF_F;
+    // the CTA's rows (nH <= 22 on >= 140 CTAs) all sit in warp 0: its arg-max candidate (first maximum wins, as the host
+    // argmax of src/tts_transformer.cpp:2182-2192) is folded with shuffles instead of a serial scan through shared memory
+    float pv = -CUDART_INF_F; int pi = 0x7fffffff;
     if (t < nH) {
         const float raw = s.outv[t];
         m.logits[h0 + t] = raw;
         if (p.logits_dst) p.logits_dst[h0 + t] = raw;
         pk_store(m.x_logit + h0 + t, raw, e_head);
         pv = proc_logit(m, raw, h0 + t, process, gs.suppress_start, gs.eos_id, gs.rep_penalty);
+        pi = h0 + t;
     }
-    cbar();
-    if (t < nH) s.outv[t] = pv;
     ring_release(s, rg, nH);
-    cbar();
-    if (t == 0) {
-        float bv = -CUDART_INF_F; int bi = 0x7fffffff;
-        for (int i = 0; i < nH; ++i) if (s.outv[i] > bv) { bv = s.outv[i]; bi = h0 + i; }
-        if (nH > 0 && bi == 0x7fffffff) bi = h0;       // all -inf: keep first-index semantics
-        pk_store(m.x_cand + 2 * blockIdx.x, bv, e_head);
-        pk_store(m.x_cand + 2 * blockIdx.x + 1, __int_as_float(bi), e_head);
+    if (t < 32) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, pv, o);
+            const int   oi = __shfl_xor_sync(0xffffffffu, pi, o);
+            if (ov > pv || (ov == pv && oi < pi)) { pv = ov; pi = oi; }
+        }
+        if (t == 0) {
+            pk_store(m.x_cand + 2 * blockIdx.x, pv, e_head);
+            pk_store(m.x_cand + 2 * blockIdx.x + 1, __int_as_float(pi), e_head);
+        }
     }
     ep += 1;
     PROF(21);
@@ -2080,14 +2085,16 @@ int lm_max_grid(q3t_ctx * ctx) {
 }
 
 // producer pacing (see produce_slice / producer_loop); environment overrides are tuning knobs
-static void lm_pacing(DevModel & m) {
-    static int pp = -1, pc = -1;
-    if (pp < 0) {
+static void lm_pacing(DevModel & m, bool batched = false) {
+    static int pp = -2, pc = -1;
+    if (pp == -2) {
         const char * e1 = getenv("Q3T_PROD_PACE"), * e2 = getenv("Q3T_PROD_PIECE");
-        pp = e1 ? atoi(e1) : 100; pc = e2 ? atoi(e2) : 4;
+        pp = e1 ? atoi(e1) : -1; pc = e2 ? atoi(e2) : 4;
         if (pc < 1) pc = 1;
     }
-    m.prod_pace = pp; m.prod_piece = pc;
+    // the batch-1 kernel wants its refills in 8 KB pieces 100 cycles apart; the batched kernel hides its exchanges behind the
+    // other group's arithmetic and is (slightly) better off with whole-slice copies (5.84 -> 5.78 ms per 16-sequence frame)
+    m.prod_pace = pp >= 0 ? pp : (batched ? 0 : 100); m.prod_piece = pc;
     static int pin = -1;
     if (pin == -1) { const char * e = getenv("Q3T_L2_PIN"); pin = e ? atoi(e) : -2; }
     // measured plateau (profiles/r02c_l2_sweep.txt): 6-9 slices (47-71 MB) of the F16 code predictor, 16 of the Q8_0 one.
@@ -2144,7 +2151,7 @@ int lm_launch_batch(q3t_ctx * ctx, const DevModel * seqs, int nb, const PassDesc
     bm.gbase[0] = 0; bm.gbase[1] = bm.ng == 2 ? (nb + 1) / 2 : nb; bm.gbase[2] = nb;
     if (NH * bm.gbase[1] > ctx->grid) return set_err(ctx, Q3T_ERR_ARG, "batch needs one CTA per (sequence, head) attention unit of a group");
     for (int q = 0; q < Q3T_MAX_BATCH; ++q) bm.seq[q] = seqs[q < nb ? q : 0];
-    lm_pacing(bm.seq[0]);
+    lm_pacing(bm.seq[0], true);
     // both stacks of a model share the weight type (the converter quantises them together); Q8_0 models run the 8-wide instantiation
     const bool q8 = seqs[0].talker.wtype == Q3T_TYPE_Q8_0;
     cudaError_t e = q8      ? launch_batch_t<8, true>(ctx, bm, passes_dev, n_passes)
