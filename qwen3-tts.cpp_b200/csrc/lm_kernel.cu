@@ -2092,9 +2092,9 @@ static void lm_pacing(DevModel & m, bool batched = false) {
         pp = e1 ? atoi(e1) : -1; pc = e2 ? atoi(e2) : 4;
         if (pc < 1) pc = 1;
     }
-    // the batch-1 kernel wants its refills in 8 KB pieces 100 cycles apart; the batched kernel hides its exchanges behind the
+    // the batch-1 kernel wants its refills in 8 KB pieces 80 cycles apart; the batched kernel hides its exchanges behind the
     // other group's arithmetic and is (slightly) better off with whole-slice copies (5.84 -> 5.78 ms per 16-sequence frame)
-    m.prod_pace = pp >= 0 ? pp : (batched ? 0 : 100); m.prod_piece = pc;
+    m.prod_pace = pp >= 0 ? pp : (batched ? 0 : 80); m.prod_piece = pc;
     static int pin = -1;
     if (pin == -1) { const char * e = getenv("Q3T_L2_PIN"); pin = e ? atoi(e) : -2; }
     // measured plateau (profiles/r02c_l2_sweep.txt): 6-9 slices (47-71 MB) of the F16 code predictor, 16 of the Q8_0 one.
@@ -2110,7 +2110,7 @@ int lm_launch(q3t_ctx * ctx, const PassDesc * passes_dev, int n_passes, int fram
     }
     DevModel m = ctx->hm;
     static int d0 = -1, d1 = -1;
-    if (d0 < 0) { const char * e0 = getenv("Q3T_POLL_D0"), * e1 = getenv("Q3T_POLL_D1"); d0 = e0 ? atoi(e0) : 300; d1 = e1 ? atoi(e1) : 0; }
+    if (d0 < 0) { const char * e0 = getenv("Q3T_POLL_D0"), * e1 = getenv("Q3T_POLL_D1"); d0 = e0 ? atoi(e0) : 150; d1 = e1 ? atoi(e1) : 0; }
     m.poll_d0 = d0; m.poll_d1 = d1;
     lm_pacing(m);
     void * args[] = { (void *) &m, (void *) &passes_dev, (void *) &n_passes, (void *) &frame_mode };
