@@ -5,16 +5,19 @@
 // (src/tts_transformer.cpp:1268-1411, 1534-1829, 2310-2575, 2664-2804).
 //
 // Design (B200-first):
-//   * ONE cooperative launch of `grid` (= #SMs) CTAs x 512 threads runs a whole *program* of
+//   * ONE cooperative launch of `grid` (= #SMs) CTAs x 384 threads runs a whole *program* of
 //     passes (a pass = one token through one layer stack + optional head): a frame is
 //     16 code-predictor passes + 1 talker pass, a prefill is M talker passes.
 //   * Batch-1 decode is a chain of ~600 dependent mat-vecs per frame, so the kernel is built around
 //     the LATENCY of that chain while HBM streams underneath it:
-//       - warp 15 of every CTA is a producer: it walks the (deterministic) schedule of weight
+//       - warp 11 of every CTA is a producer: it walks the (deterministic) schedule of weight
 //         slices of this CTA and keeps a 160 KB shared-memory ring full with TMA bulk copies
 //         (cp.async.bulk global->shared, mbarrier complete_tx), gated only by ring space — the
-//         weight stream never waits for the dependency chain;
-//       - warps 0..14 compute.  Every phase boundary is an all-to-all exchange of a small
+//         weight stream never waits for the dependency chain; a slice is issued as 8 KB pieces a
+//         few dozen cycles apart, with L2 cache policies (the code predictor's first slices
+//         evict_last, everything read once per frame evict_first): bursts of the weight stream
+//         and HBM queueing were what made the packet exchanges slow;
+//       - warps 0..10 compute.  Every phase boundary is an all-to-all exchange of a small
 //         activation vector; instead of a grid barrier (fence + atomic + poll + reload = 4 L2 round
 //         trips) activations travel as 8-byte {value, epoch} packets (one store, one polling
 //         load: the value is valid iff its epoch matches) — the NCCL "LL" idea used inside one GPU;
@@ -93,7 +96,7 @@ __device__ __forceinline__ void prof_mark(const DevModel & m, int * cnt, int tag
 #define PROF(tag) prof_mark(m, &s.prof_cnt, tag)
 
 // ------------------------------------------------------------------------------- CTA-level sync
-// barrier among the 480 compute threads only (the producer warp runs free)
+// barrier among the 352 compute threads only (the producer warp runs free)
 __device__ __forceinline__ void cbar() { asm volatile("bar.sync 1, %0;" :: "n"(NCT) : "memory"); }
 
 // ------------------------------------------------------------------------------- LL packets
