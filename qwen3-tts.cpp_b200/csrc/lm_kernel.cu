@@ -616,7 +616,7 @@ __device__ __forceinline__ void xh_put(Smem & s, int k, float v) {
 
 // ------------------------------------------------------------------------------- RMSNorm
 // y = (x * rsqrt(mean(x^2)+eps)) * gamma; sum of squares in double (oracle D.5,
-// ggml/src/ggml-cpu/ops.cpp:3666-3691).  x = s.xres; thread t owns elements t, t+480, t+960.
+// ggml/src/ggml-cpu/ops.cpp:3666-3691).  x = s.xres; thread t owns elements t, t+352, t+704.
 // Writes F16(y) into s.xh (the F16 mat-vec input) and optionally the unrounded y (hidden states).
 // gamma values come in registers (fetched a layer ahead).  Ends with a cbar().
 struct Gam { float g[3]; };
@@ -1976,7 +1976,7 @@ lm_kernel(const __grid_constant__ DevModel m, const PassDesc * __restrict__ pass
             if (frame >= gs.max_len) { done = 1; break; }
         }
 
-        // ---- form x in shared memory (elements t, t+480, t+960)
+        // ---- form x in shared memory (elements t, t+352, t+704)
         for (int k = t; k < H; k += NCT) {
             float xv = 0.f;
             switch (p.xmode) {
