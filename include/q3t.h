@@ -178,7 +178,10 @@ Q3T_API int  q3t_stream_next(q3t_ctx * ctx, int32_t max_frames, int32_t * codes_
  * independent utterances, greedy, same semantics per utterance as q3t_generate with temperature 0
  * (src/tts_transformer.cpp:2577-2851).  Up to 16 sequences per kernel launch (two interleaved lock-step groups of 8);
  * codes_out[i] int32[max_len*n_codebooks], n_frames_out[i] = frames of utterance i.
- * speaker_embd may be null (no speaker for any utterance) or hold per-utterance pointers (null entries allowed). */
+ * speaker_embd may be null (no speaker for any utterance) or hold per-utterance pointers (null entries allowed).
+ * Waves whose sequences all have the same number of prompt rows are also prefilled in lock-step.  The per-sequence device
+ * buffers of a call (KV caches, packets, code rows: ~80 MB per sequence at max_len 320, 16 sequences) stay allocated in the
+ * context for the next call and are released by q3t_unload(ctx, 1) / q3t_ctx_destroy. */
 Q3T_API int  q3t_generate_batch(q3t_ctx * ctx, int32_t n_seq, const int32_t * const * text_tokens, const int32_t * n_tokens,
                                 const float * const * speaker_embd, int32_t max_len, int32_t language_id,
                                 float repetition_penalty, int32_t * const * codes_out, int32_t * n_frames_out);
