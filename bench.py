@@ -392,7 +392,6 @@ def config4_line(args, rank, world, t, d, have_voc, dist, sync_all, m):
     pairs = [(u.tokens, u.spk) for u in mine]
     if pairs and t.generate_batch(pairs[:min(8, len(pairs))], 8) is None:          # warm-up (instantiation, buffers)
         raise SystemExit("generate_batch: " + t.get_error())
-    from concurrent.futures import ThreadPoolExecutor
     extra_dec = []
     if args.decoders <= 0:
         args.decoders = max(1, min(4, (os.cpu_count() or 8) // (2 * world)))
@@ -402,7 +401,7 @@ def config4_line(args, rank, world, t, d, have_voc, dist, sync_all, m):
             dd = m.AudioTokenizerDecoder()
             if not dd.load_model(_models("full", args.wtype)[1]):
                 raise SystemExit("decoder load_model: " + dd.get_error())
-            dd.decode(np.zeros((8, 16), np.int32))                                  # warm-up (buffers, tensor maps)
+            dd.decode(np.zeros((args.frames, 16), np.int32))                        # warm-up at the job's length (scratch sized: no cudaMalloc in the timed region)
             extra_dec.append(dd)
     sync_all()
     w0 = time.perf_counter()
@@ -416,11 +415,7 @@ def config4_line(args, rank, world, t, d, have_voc, dist, sync_all, m):
     if have_voc and len(extra_dec) > 0:
         # the utterances of the job are decoded by N decoder instances from N host threads (each instance has its own stream:
         # the small early-stage launches of one decode overlap the large late-stage GEMMs of another)
-        decs = [d] + extra_dec
-        def work(k):
-            return sum(len(decs[k].decode(c)) for c in codes[k::len(decs)])
-        with ThreadPoolExecutor(len(decs)) as ex:
-            ns = sum(ex.map(work, range(len(decs))))
+        ns = sum(len(w) for w in m.decode_batch([d] + extra_dec, codes))     # q3t_pipe_decode_batch_multi: the threads are C++ (no GIL)
     else:
         for c in codes:
             wav = d.decode(c) if have_voc else np.zeros(n_samples(len(c)), np.float32)

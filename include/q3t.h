@@ -343,6 +343,9 @@ Q3T_API int  q3t_pipe_synthesize_batch_multi(q3t_tts * t, q3t_dec * const * decs
                                              const int32_t * n_tokens, const float * const * speaker_embd, int32_t max_len, int32_t language_id,
                                              float repetition_penalty, float * const * samples_out, const int64_t * caps,
                                              int64_t * n_samples_out, q3t_batch_stats * stats_out);
+/* the decode half alone: codes[i] int32[n_frames[i]*16] -> samples_out[i] (room for caps[i] floats), utterance i on decoder i mod n_dec */
+Q3T_API int  q3t_pipe_decode_batch_multi(q3t_dec * const * decs, int32_t n_dec, int32_t n, const int32_t * const * codes, const int32_t * n_frames,
+                                         float * const * samples_out, const int64_t * caps, int64_t * n_samples_out);
 Q3T_API const char * q3t_pipe_get_error(void);
 
 #ifdef __cplusplus

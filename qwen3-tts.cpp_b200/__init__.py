@@ -11,5 +11,5 @@ without a B200 every compute call returns the engine's error.
 """
 from .binding import (  # noqa: F401
     LIB_PATH, lib, build, TTSTransformer, AudioTokenizerDecoder, GGUFLoader, Q3TError, declared_symbols,
-    synthesize_stream, synthesize_batch, StreamStats, BatchStats, AudioTokenizerEncoder,
+    synthesize_stream, synthesize_batch, decode_batch, StreamStats, BatchStats, AudioTokenizerEncoder,
 )

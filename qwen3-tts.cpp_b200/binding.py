@@ -117,6 +117,7 @@ def lib() -> C.CDLL:
                                                 C.POINTER(_f32p), _i64p, _i64p, C.POINTER(BatchStats)]),
         "q3t_pipe_synthesize_batch_multi": (C.c_int, [vp, C.POINTER(vp), C.c_int32, C.c_int32, C.POINTER(_i32p), _i32p, C.POINTER(_f32p), C.c_int32, C.c_int32,
                                                       C.c_float, C.POINTER(_f32p), _i64p, _i64p, C.POINTER(BatchStats)]),
+        "q3t_pipe_decode_batch_multi": (C.c_int, [C.POINTER(vp), C.c_int32, C.c_int32, C.POINTER(_i32p), _i32p, C.POINTER(_f32p), _i64p, _i64p]),
         "q3t_pipe_get_error": (cp, []),
         "q3t_sample_logits": (C.c_int, [vp, _f32p, C.c_int32, C.c_int32, _i32p, C.c_int32, C.c_float, C.c_float, C.c_int32, C.c_uint64, C.c_int32, _i32p]),
         "q3t_project_text_static_dev": (C.c_int, [vp, vp, C.c_int32, vp]),
@@ -532,6 +533,23 @@ def synthesize_stream(tts: TTSTransformer, dec: AudioTokenizerDecoder, tokens, s
     if n < 0:
         raise Q3TError(lib().q3t_pipe_get_error().decode())
     return out[:n].copy(), st
+
+
+def decode_batch(decs, codes_list):
+    """codes_list: list of int32 [T_i, 16] arrays; utterance i is decoded by decs[i mod N] (one host thread per decoder, in C++)."""
+    decs = list(decs) if isinstance(decs, (list, tuple)) else [decs]
+    n = len(codes_list)
+    cs = [np.ascontiguousarray(c, np.int32) for c in codes_list]
+    nf = np.array([len(c) for c in cs], np.int32)
+    outs = [np.empty(max(1920 * int(k) - 555, 1), np.float32) for k in nf]
+    caps = np.array([len(o) for o in outs], np.int64)
+    ns = np.zeros(n, np.int64)
+    cp_ = (_i32p * n)(*[_ip(c) for c in cs])
+    op = (_f32p * n)(*[_fp(o) for o in outs])
+    dp = (C.c_void_p * len(decs))(*[x.h for x in decs])
+    if not lib().q3t_pipe_decode_batch_multi(dp, len(decs), n, cp_, _ip(nf), op, caps.ctypes.data_as(_i64p), ns.ctypes.data_as(_i64p)):
+        raise Q3TError(lib().q3t_pipe_get_error().decode())
+    return [outs[i][:ns[i]] for i in range(n)]
 
 
 def synthesize_batch(tts: TTSTransformer, dec, utterances, max_len, language_id=2050, repetition_penalty=1.05):

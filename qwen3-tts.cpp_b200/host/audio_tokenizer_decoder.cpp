@@ -71,6 +71,17 @@ bool AudioTokenizerDecoder::decode(const int32_t * codes, int32_t n_frames, std:
     return true;
 }
 
+bool AudioTokenizerDecoder::decode_to(const int32_t * codes, int32_t n_frames, float * out, int64_t cap, int64_t & n_samples) {
+    n_samples = 0;
+    if (!loaded_) { error_msg_ = "Model not loaded"; return false; }
+    if (!codes || n_frames <= 0 || !out) { error_msg_ = "codes or out is null or n_frames <= 0"; return false; }
+    if (cap < q3t_vocoder_n_samples(n_frames)) { error_msg_ = "output buffer too small"; return false; }
+    const int64_t got = q3t_vocoder_decode(engine_, codes, n_frames, out, cap);
+    if (got < 0) { error_msg_ = q3t_last_error(engine_); return false; }
+    n_samples = got;
+    return true;
+}
+
 bool AudioTokenizerDecoder::decode_append(const int32_t * codes, int32_t n_new_frames, std::vector<float> & new_samples) {
     if (!loaded_) { error_msg_ = "Model not loaded"; return false; }
     if (!codes || n_new_frames <= 0) { error_msg_ = "codes is null or n_frames <= 0"; return false; }

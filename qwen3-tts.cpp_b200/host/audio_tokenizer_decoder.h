@@ -46,6 +46,8 @@ public:
     void stream_reset() { stream_codes_.clear(); stream_done_ = 0; }
     bool decode_append(const int32_t * codes, int32_t n_new_frames, std::vector<float> & new_samples);
     q3t_ctx * engine() const { return engine_; }
+    // decode() into a caller's buffer of `cap` floats (no intermediate vector); n_samples receives the count written
+    bool decode_to(const int32_t * codes, int32_t n_frames, float * out, int64_t cap, int64_t & n_samples);
 
 private:
     audio_decoder_config config_;

@@ -63,14 +63,31 @@ bool synthesize_batch(TTSTransformer & tts, const std::vector<AudioTokenizerDeco
     const auto t1 = clk::now();
     audio.assign(codes.size(), {});
     const int ncb = tts.get_config().n_codebooks;
+    std::vector<const int32_t *> cp(codes.size());
+    std::vector<int32_t> nfv(codes.size());
+    for (size_t i = 0; i < codes.size(); ++i) { cp[i] = codes[i].data(); nfv[i] = (int32_t) (codes[i].size() / (size_t) ncb); }
+    if (!decode_batch(decs, cp, nfv, audio, error)) return false;
+    for (size_t i = 0; i < codes.size(); ++i) {
+        st.n_frames += (int64_t) (codes[i].size() / (size_t) ncb);
+        st.n_samples += (int64_t) audio[i].size();
+    }
+    st.t_decode_ms = ms_since(t1);
+    st.t_total_ms = ms_since(t0);
+    if (stats) *stats = st;
+    return true;
+}
+
+bool decode_batch(const std::vector<AudioTokenizerDecoder *> & decs, const std::vector<const int32_t *> & codes,
+                  const std::vector<int32_t> & n_frames, std::vector<std::vector<float>> & audio, std::string & error) {
+    if (decs.empty() || codes.size() != n_frames.size()) { error = "bad argument"; return false; }
+    audio.assign(codes.size(), {});
     // decoder k takes utterances k, k + N, ...; one host thread per decoder (a decoder object is not thread-safe, its own calls stay serial)
     const size_t nd = decs.size();
     std::vector<std::string> errs(nd);
     auto work = [&](size_t k) {
         for (size_t i = k; i < codes.size(); i += nd) {
-            const int32_t nf = (int32_t) (codes[i].size() / (size_t) ncb);
-            if (nf == 0) continue;
-            if (!decs[k]->decode(codes[i].data(), nf, audio[i])) { errs[k] = decs[k]->get_error(); return; }
+            if (n_frames[i] <= 0) continue;
+            if (!decs[k]->decode(codes[i], n_frames[i], audio[i])) { errs[k] = decs[k]->get_error(); return; }
         }
     };
     if (nd == 1) work(0);
@@ -80,13 +97,6 @@ bool synthesize_batch(TTSTransformer & tts, const std::vector<AudioTokenizerDeco
         for (auto & x : th) x.join();
     }
     for (const auto & e : errs) if (!e.empty()) { error = e; return false; }
-    for (size_t i = 0; i < codes.size(); ++i) {
-        st.n_frames += (int64_t) (codes[i].size() / (size_t) ncb);
-        st.n_samples += (int64_t) audio[i].size();
-    }
-    st.t_decode_ms = ms_since(t1);
-    st.t_total_ms = ms_since(t0);
-    if (stats) *stats = st;
     return true;
 }
 

@@ -56,5 +56,10 @@ Q3T_API bool synthesize_batch(TTSTransformer & tts, const std::vector<AudioToken
                               const std::vector<int32_t> & n_tokens, const std::vector<const float *> & speaker_embd,
                               const synth_params & p, std::vector<std::vector<float>> & audio, batch_stats * stats, std::string & error);
 
+// the decode half alone: codes[i] (frame-major, n_frames[i] x n_codebooks) -> audio[i], utterance i on decoder i mod N (one host
+// thread per decoder)
+Q3T_API bool decode_batch(const std::vector<AudioTokenizerDecoder *> & decs, const std::vector<const int32_t *> & codes,
+                          const std::vector<int32_t> & n_frames, std::vector<std::vector<float>> & audio, std::string & error);
+
 } // namespace b200
 } // namespace qwen3_tts

@@ -8,6 +8,7 @@
 #include "tts_transformer.h"
 
 #include <cstring>
+#include <thread>
 #include <vector>
 
 using namespace qwen3_tts;
@@ -228,6 +229,31 @@ Q3T_API int q3t_pipe_synthesize_batch(q3t_tts * t, q3t_dec * d, int32_t n, const
                                       float * const * samples_out, const int64_t * caps, int64_t * n_samples_out, q3t_batch_stats * stats_out) {
     return q3t_pipe_synthesize_batch_multi(t, &d, 1, n, text_tokens, n_tokens, speaker_embd, max_len, language_id, repetition_penalty,
                                            samples_out, caps, n_samples_out, stats_out);
+}
+Q3T_API int q3t_pipe_decode_batch_multi(q3t_dec * const * decs, int32_t n_dec, int32_t n, const int32_t * const * codes, const int32_t * n_frames,
+                                        float * const * samples_out, const int64_t * caps, int64_t * n_samples_out) {
+    if (!decs || n_dec <= 0 || n <= 0 || !codes || !n_frames || !n_samples_out) { g_pipe_err = "bad argument"; return 0; }
+    std::vector<AudioTokenizerDecoder *> dv;
+    for (int i = 0; i < n_dec; ++i) { if (!decs[i]) { g_pipe_err = "bad argument"; return 0; } dv.push_back(&decs[i]->d); }
+    if (!samples_out || !caps) { g_pipe_err = "bad argument"; return 0; }
+    // straight into the caller's buffers: decoder k takes utterances k, k + n_dec, ... on its own host thread
+    std::vector<std::string> errs((size_t) n_dec);
+    auto work = [&](int k) {
+        for (int i = k; i < n; i += n_dec) {
+            n_samples_out[i] = 0;
+            if (n_frames[i] <= 0) continue;
+            if (!codes[i] || !samples_out[i]) { errs[(size_t) k] = "bad argument"; return; }
+            if (!dv[(size_t) k]->decode_to(codes[i], n_frames[i], samples_out[i], caps[i], n_samples_out[i])) { errs[(size_t) k] = dv[(size_t) k]->get_error(); return; }
+        }
+    };
+    if (n_dec == 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (int k = 0; k < n_dec; ++k) th.emplace_back(work, k);
+        for (auto & x : th) x.join();
+    }
+    for (const auto & e : errs) if (!e.empty()) { g_pipe_err = e; return 0; }
+    return 1;
 }
 Q3T_API int q3t_pipe_synthesize_batch_multi(q3t_tts * t, q3t_dec * const * decs, int32_t n_dec, int32_t n, const int32_t * const * text_tokens,
                                             const int32_t * n_tokens, const float * const * speaker_embd, int32_t max_len, int32_t language_id,

@@ -73,4 +73,6 @@ def test_synthesize_batch_equals_per_utterance_pipeline(q3t, pair):
     assert d2.load_model(models("tiny", "f16")[1]), d2.get_error()
     wavs2, st2 = q3t.synthesize_batch(t, [d, d2], utts, 24)
     assert st2.n_samples == st.n_samples and all(np.array_equal(a, b) for a, b in zip(wavs, wavs2))
+    wavs3 = q3t.decode_batch([d, d2], [t.generate(toks, spk, 24, temperature=0.0) for toks, spk in utts[:5]])
+    assert all(np.array_equal(a, b) for a, b in zip(wavs[:5], wavs3))
     d2.close()

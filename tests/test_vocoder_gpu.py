@@ -50,6 +50,18 @@ def test_causality_prefix_property(dec):
     assert snr_db(full[:n], part[:n]) > 90.0
 
 
+def test_repeated_decodes_are_bit_identical(dec):
+    """The decoder keeps its scratch between calls: alternating lengths and codes must not leak state from one decode into the next."""
+    rng = np.random.default_rng(21)
+    lens = [12, 30, 7, 19, 25, 41]
+    sets = {T: [rng.integers(0, 2048, size=(T, 16), dtype=np.int32) for _ in range(2)] for T in lens}
+    first = {T: [dec.decode(c).copy() for c in sets[T]] for T in lens}
+    for rnd in range(2):
+        for T in lens:
+            for c, w in zip(sets[T], first[T]):
+                assert np.array_equal(dec.decode(c), w), (rnd, T)
+
+
 def test_error_behaviour(q3t, dec):
     assert dec.L.q3t_dec_decode(dec.h, None, 4, None, 0) < 0
     assert dec.decode(np.zeros((0, 16), np.int32)) is None
