@@ -467,11 +467,11 @@ class AudioTokenizerDecoder:
         codes = np.ascontiguousarray(codes, np.int32)
         T = codes.shape[0]
         cap = max(int(self.L.q3t_vocoder_n_samples(T)), 0) + 16
-        out = np.zeros(cap, np.float32)
+        out = np.empty(cap, np.float32)                       # written by the D2H copy: no zero fill, no second pass
         n = self.L.q3t_dec_decode(self.h, _ip(codes), T, _fp(out), cap)
         if n < 0:
             return None
-        return out[:n].copy()
+        return out[:n]
 
     # streaming extension: the concatenation of decode_append() results equals decode() of all the frames
     def stream_reset(self):
@@ -481,11 +481,11 @@ class AudioTokenizerDecoder:
         codes = np.ascontiguousarray(codes, np.int32)
         T = codes.shape[0]
         cap = 1920 * T + 16
-        out = np.zeros(cap, np.float32)
+        out = np.empty(cap, np.float32)
         n = self.L.q3t_dec_decode_append(self.h, _ip(codes), T, _fp(out), cap)
         if n < 0:
             return None
-        return out[:n].copy()
+        return out[:n]
 
 
 class AudioTokenizerEncoder:
