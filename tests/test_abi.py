@@ -74,6 +74,11 @@ def test_fails_loudly_without_gpu(q3t, tiny_models):
     assert t.predict_codes(np.zeros(1024, np.float32), None) is None
     assert t.get_error() == "Model not loaded"
     assert t.generate_batch([(np.arange(8, dtype=np.int32), None)], 4) is None
+    # the batched decode front door: an unloaded decoder is reported, bad arguments are rejected before any decoder is touched
+    with pytest.raises(q3t.Q3TError, match="Model not loaded"):
+        q3t.decode_batch([d], [np.zeros((2, 16), np.int32)])
+    assert L.q3t_pipe_decode_batch_multi(None, 0, 0, None, None, None, None, None) == 0
+    assert L.q3t_pipe_get_error() == b"bad argument"
 
 
 def test_gguf_loader_matches_python_reader(q3t, tiny_models):
